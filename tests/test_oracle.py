@@ -1,0 +1,120 @@
+"""The CPU oracle against the reference's own outputs (tests/golden, made by oracle/make_golden.py)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from oracle import netresdeep_oracle as O
+
+
+def _load(tag):
+    return np.load(os.path.join(GOLDEN, tag + ".npz"))
+
+
+def _rel(a, b):
+    a = torch.as_tensor(a, dtype=torch.float64); b = torch.as_tensor(b, dtype=torch.float64)
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+@pytest.mark.parametrize("tag", ["step_c32_nb10_b8", "step_c64_nb3_b4"])
+def test_init_matches_reference_bitwise_checksums(tag):
+    g = _load(tag)
+    p, _ = O.init_params(int(g["C"]), int(g["NB"]), seed=0)
+    for k in O.PARAM_ORDER:
+        assert float(p[k].double().sum()) == float(g[f"w0_sum/{k}"]), k
+        assert float(p[k].double().abs().sum()) == float(g[f"w0_abs/{k}"]), k
+
+
+@pytest.mark.parametrize("tag", ["step_c32_nb10_b8", "step_c64_nb3_b4"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_step_matches_reference(tag, dtype):
+    torch.set_num_threads(1)
+    g = _load(tag)
+    C, NB = int(g["C"]), int(g["NB"])
+    p, bufs = O.init_params(C, NB, seed=0, dtype=dtype)
+    x = torch.from_numpy(g["x"]).to(dtype); y = torch.from_numpy(g["labels"])
+    losses = []
+    for s in range(int(g["steps"])):
+        p_new, logits, loss, grads = O.train_step(p, bufs, x, y, NB, float(g["lr"]))
+        if s == 0:
+            assert _rel(logits, g["logits"]) < 2e-6
+            # body grads carry ReLU-mask flip noise even fp32-vs-fp64: B is tiny here
+            for k in O.PARAM_ORDER:
+                tol = 2e-5 if k.startswith("fc") else 5e-3
+                assert _rel(grads[k], g[f"grad/{k}"]) < tol, (k, _rel(grads[k], g[f"grad/{k}"]))
+            assert _rel(bufs["running_mean"], g["running_mean"]) < 1e-5
+            assert _rel(bufs["running_var"], g["running_var"]) < 1e-5
+            assert int(bufs["num_batches_tracked"]) == int(g["num_batches_tracked"]) == NB
+        p = p_new
+        losses.append(float(loss))
+    assert abs(losses[0] - g["losses"][0]) < 1e-5 * abs(g["losses"][0])
+    np.testing.assert_allclose(losses, g["losses"], rtol=5e-2)
+
+
+def test_loss_curve_lr1e2_degenerate():
+    """lr=1e-2 curve of config 1 (B=64): spikes then collapses to ln 10."""
+    torch.set_num_threads(1)
+    g = _load("curve_c32_nb10_b64_lr1e-2")
+    gen = torch.Generator().manual_seed(1234)
+    x = torch.randn(64, 3, 32, 32, generator=gen); y = torch.randint(0, 10, (64,), generator=gen)
+    assert float(x.double().sum()) == float(g["x_sum"])
+    assert np.array_equal(y.numpy(), g["labels"])
+    p, bufs = O.init_params(32, 10, seed=0)
+    losses = []
+    for s in range(int(g["steps"])):
+        p, _, loss, _ = O.train_step(p, bufs, x, y, 10, 1e-2)
+        losses.append(float(loss))
+    assert abs(losses[0] - g["losses"][0]) < 1e-5
+    assert abs(losses[-1] - g["losses"][-1]) < 5e-2
+    assert abs(losses[-1] - np.log(10)) < 0.1
+
+
+def test_ddp_simulation_matches_real_ddp_gloo():
+    torch.set_num_threads(1)
+    g = _load("ddp_w2_c32_nb10_b8")
+    W, NB = int(g["W"]), int(g["NB"])
+    p, b0 = O.init_params(32, NB, seed=0)           # rank 0's init wins (DDP ctor broadcast)
+    bufs = [dict((k, v.clone()) for k, v in b0.items()) for _ in range(W)]
+    xs = [torch.from_numpy(g[f"r{r}/x"]) for r in range(W)]
+    ys = [torch.from_numpy(g[f"r{r}/labels"]) for r in range(W)]
+    for s in range(2):
+        p_new, logits, losses, gavg = O.ddp_train_step(p, bufs, xs, ys, NB, 1e-2)
+        for r in range(W):
+            assert _rel(logits[r], g[f"r{r}/s{s}/logits"]) < (2e-6 if s == 0 else 1e-3)
+            assert abs(float(losses[r]) - float(g[f"r{r}/s{s}/loss"])) < (1e-5 if s == 0 else 1e-2)
+            assert _rel(bufs[r]["running_mean"], g[f"r{r}/s{s}/running_mean"]) < (1e-5 if s == 0 else 1e-3)
+        if s == 0:
+            for k in O.PARAM_ORDER:
+                tol = 2e-5 if k.startswith("fc") else 5e-3
+                assert _rel(gavg[k], g[f"r0/s0/grad/{k}"]) < tol, k
+                # every rank holds the same averaged gradient
+                assert np.array_equal(g[f"r0/s0/grad/{k}"], g[f"r1/s0/grad/{k}"])
+        p = p_new
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="reference tree only exists in the build container")
+def test_oracle_vs_live_reference_fp64():
+    """fp64 oracle vs fp64 reference: no mask-flip noise, so everything agrees to ~1e-12."""
+    import sys
+    sys.path.insert(0, "/root/reference")
+    from model.resnet import NetResDeep
+    torch.manual_seed(0)
+    m = NetResDeep().double()
+    p, bufs = O.init_params(32, 10, seed=0, dtype=torch.float64)
+    gen = torch.Generator().manual_seed(7)
+    x = torch.randn(16, 3, 32, 32, generator=gen, dtype=torch.float64); y = torch.randint(0, 10, (16,), generator=gen)
+    out = m(x); loss = torch.nn.CrossEntropyLoss()(out, y); loss.backward()
+    logits, c = O.forward(p, bufs, x, 10)
+    l2, dl = O.cross_entropy(logits, y)
+    grads = O.backward(p, c, dl)
+    assert _rel(logits, out.detach()) < 1e-12
+    named = dict(m.named_parameters())
+    ref = {"conv1.weight": "conv1.weight", "conv1.bias": "conv1.bias", "rb.conv.weight": "resblocks.0.conv.weight",
+           "rb.bn.weight": "resblocks.0.batch_norm.weight", "rb.bn.bias": "resblocks.0.batch_norm.bias",
+           "fc1.weight": "fc1.weight", "fc1.bias": "fc1.bias", "fc2.weight": "fc2.weight", "fc2.bias": "fc2.bias"}
+    for k, rk in ref.items():
+        assert _rel(grads[k], named[rk].grad) < 1e-10, (k, _rel(grads[k], named[rk].grad))
+    bn = m.resblocks[0].batch_norm
+    assert _rel(bufs["running_var"], bn.running_var) < 1e-12
