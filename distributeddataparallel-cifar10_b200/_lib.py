@@ -1,0 +1,79 @@
+"""ctypes binding of libnrd.so (include/nrd.h).  No CPU fallback: a missing library is an error."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libnrd.so")
+
+NRD_F32, NRD_BF16 = 0, 1
+CONV_CUDA_CORE, CONV_TCGEN05 = 0, 1
+
+
+class NrdError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: the CUDA extension is the product and there is no CPU fallback. "
+            "Build it with `python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc).")
+    return C.CDLL(LIB_PATH)
+
+
+lib = _load()
+vp, i32, i64, u64, u32, f32, sz = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_uint32, C.c_float, C.c_size_t
+
+_PROTOS = {
+    "nrd_last_error": (C.c_char_p, []),
+    "nrd_version": (i32, []),
+    "nrd_param_offsets": (i32, [i32, C.POINTER(i64)]),
+    "nrd_workspace_bytes": (sz, [i32, i32, i32, i32]),
+    "nrd_plan_create": (i32, [C.POINTER(vp), i32, i32, i32, i32, i32, vp, sz, vp, vp, vp, vp]),
+    "nrd_plan_destroy": (i32, [vp]),
+    "nrd_plan_set_conv_impl": (i32, [vp, i32]),
+    "nrd_plan_conv_impl": (i32, [vp]),
+    "nrd_plan_tensor": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)]),
+    "nrd_pack_weights": (i32, [vp, vp]),
+    "nrd_forward": (i32, [vp, vp, vp, i32, vp]),
+    "nrd_cross_entropy": (i32, [vp, vp, i32, f32, vp, vp, vp, vp]),
+    "nrd_backward": (i32, [vp, vp, vp]),
+    "nrd_sgd_update": (i32, [vp, vp, sz, f32, f32, vp]),
+    "nrd_train_step": (i32, [vp, vp, vp, f32, vp, vp, vp]),
+    "nrd_gen_batch": (i32, [vp, vp, i32, u64, u32, u64, vp]),
+    "nrd_pack_conv_weight": (i32, [vp, i32, vp, vp, vp]),
+    "nrd_conv3x3_fwd": (i32, [vp, vp, vp, i32, i32, i32, vp, C.POINTER(i32), vp, vp]),
+    "nrd_wgrad_partial_bytes": (sz, [i32, i32]),
+    "nrd_conv3x3_wgrad": (i32, [vp, vp, vp, i32, i32, i32, vp, vp]),
+    "nrd_bn_finalize": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]),
+    "nrd_bn_relu_add": (i32, [vp, vp, vp, vp, i32, i32, i32, vp]),
+    "nrd_bn_bwd_scratch_bytes": (sz, [i32, i32]),
+    "nrd_bn_relu_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]),
+    "nrd_stem_fwd": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, vp]),
+    "nrd_stem_bwd_partial_bytes": (sz, [i32, i32]),
+    "nrd_stem_bwd": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]),
+    "nrd_maxpool_fwd": (i32, [vp, vp, vp, i32, i32, i32, vp]),
+    "nrd_maxpool_bwd": (i32, [vp, vp, vp, i32, i32, i32, vp]),
+    "nrd_launch_count": (C.c_ulonglong, []),
+    "nrd_plan_run_op": (i32, [vp, i32, i32, vp]),
+}
+for _n, (_res, _args) in _PROTOS.items():
+    _f = getattr(lib, _n)          # AttributeError here = header and library out of sync
+    _f.restype, _f.argtypes = _res, _args
+
+EXPORTS = tuple(_PROTOS)
+
+
+def last_error() -> str:
+    return lib.nrd_last_error().decode()
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        raise NrdError(f"{what or 'libnrd'} failed ({rc}): {last_error()}")
+
+
+def param_offsets(n_chans: int):
+    arr = (i64 * 10)()
+    check(lib.nrd_param_offsets(n_chans, arr), "nrd_param_offsets")
+    return list(arr)

@@ -1,0 +1,92 @@
+// Shared declarations for libnrd.so (B200 / sm_100a NetResDeep training step).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/nrd.h"
+
+typedef __nv_bfloat16 bf16;
+
+#define NRD_BN_EPS 1e-5f      // nn.BatchNorm2d default (model/resnet.py:28)
+#define NRD_BN_MOMENTUM 0.1f  // nn.BatchNorm2d default (model/resnet.py:28)
+#define NRD_HW 16             // ResBlock resolution
+#define NRD_PIX 256           // 16*16
+#define NRD_TILE_PIX 128      // one conv CTA tile: 8 rows x 16 cols of one image
+#define NRD_FC1_OUT 32
+#define NRD_NCLS 10
+#define NRD_NUM_SMS 148
+
+void nrd_set_error(const char* fmt, ...);
+
+#define NRD_CHECK_CUDA(call)                                                                   \
+  do {                                                                                         \
+    cudaError_t e__ = (call);                                                                  \
+    if (e__ != cudaSuccess) {                                                                  \
+      nrd_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));     \
+      return NRD_ECUDA;                                                                        \
+    }                                                                                          \
+  } while (0)
+
+#define NRD_REQUIRE(cond, ...)                                                                 \
+  do {                                                                                         \
+    if (!(cond)) {                                                                             \
+      nrd_set_error(__VA_ARGS__);                                                              \
+      return NRD_EINVAL;                                                                       \
+    }                                                                                          \
+  } while (0)
+
+#define NRD_TRY(call)                                                                          \
+  do {                                                                                         \
+    int r__ = (call);                                                                          \
+    if (r__ != NRD_OK) return r__;                                                             \
+  } while (0)
+
+struct nrd_plan {
+  int device, B, C, NB, dtype, conv_impl;
+  size_t esz;       // activation element size
+  size_t act_elems; // B*256*C
+  float *params, *grads, *bn_running;
+  int64_t* nbt;
+  int64_t off[10];
+  const float* images_last;  // images of the last nrd_forward (stem backward reads them)
+  // workspace carve-up
+  char* xs;            // (NB+1) saved block inputs x_k, NHWC T
+  char* ys;            // NB saved conv outputs y_k, NHWC T
+  char* dy;            // dL/dy_k scratch
+  char* dxa;           // dL/dx ping
+  char* dxb;           // dL/dx pong
+  uint8_t* idx0;       // stem pool argmax [B,16,16,C]
+  char* pooled;        // [B,8,8,C] T
+  uint8_t* idx2;       // [B,8,8,C]
+  float* h1;           // [B,32] relu(fc1)
+  float* dh1;          // [B,32]
+  float* dlogits;      // [B,10]  (train_step path)
+  float* loss_rows;    // [B]
+  float* saved_stats;  // [NB][2C] mean | invstd
+  float* scale_shift;  // [NB][2C]
+  float* stats_partial;// [B*2][2C]
+  float* bnbwd_scratch;
+  float* wgrad_partial;
+  float* stem_partial;
+  float* w_fwd;        // [9][C][C] tap-major fp32 (ci rows, co contiguous)
+  float* w_dgrad;      // [9][C][C] flipped taps, (co rows, ci contiguous)
+  float* w1p;          // fc1 weight in NHWC column order [32][64*C]
+  float* conv1_wp;     // [27][C]
+  bf16* wtc_fwd;       // tcgen05 B operand: [Cout][9*Cin] bf16, K-major
+  bf16* wtc_dgrad;     // same for dgrad (transposed + flipped)
+  // TMA descriptors for the tcgen05 path (filled by nrd_tc_plan_init)
+  CUtensorMap tm_x[32];   // per saved x_k (k <= NB), box [1,8,16,C]
+  CUtensorMap tm_dy;      // dy scratch
+  CUtensorMap tm_wf, tm_wd;
+  int tc_ready;
+};
+
+// tcgen05 path (conv_tc.cu)
+int nrd_tc_plan_init(nrd_plan* p);
+int nrd_tc_conv_fwd(nrd_plan* p, int k, cudaStream_t st);                       // y_k = conv(x_k) + stats partials
+int nrd_tc_conv_dgrad(nrd_plan* p, const void* g, void* dx_out, cudaStream_t st); // dx = dgrad(dy) + g
+int nrd_tc_conv_wgrad(nrd_plan* p, int k, int first, cudaStream_t st);          // partial (+)= wgrad(x_k, dy)
+int nrd_tc_stats_blocks(const nrd_plan* p);

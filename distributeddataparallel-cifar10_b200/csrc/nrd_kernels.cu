@@ -1,0 +1,1239 @@
+// CUDA-core kernels of the NetResDeep training step (validation-mode fp32 path and every
+// non-GEMM op of the bf16 path).  Activations are NHWC, T = float | bf16; parameters, gradients,
+// BN statistics and all accumulation are fp32 (fp64 for the final cross-CTA combines).
+// Every cross-CTA reduction is two-stage with a fixed summation order => bitwise reproducible.
+#include "nrd_common.cuh"
+#include <stdarg.h>
+
+// ------------------------------------------------------------------------------------------
+// element helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
+
+// 8 contiguous elements <-> 8 floats (16 B for bf16, 32 B for fp32); pointer must be 16-B aligned
+__device__ __forceinline__ void ld8(const float* p, float (&v)[8]) {
+  float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void ld8(const bf16* p, float (&v)[8]) {
+  uint4 r = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+}
+__device__ __forceinline__ void st8(float* p, const float (&v)[8]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void st8(bf16* p, const float (&v)[8]) {
+  uint4 r; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+  *reinterpret_cast<uint4*>(p) = r;
+}
+__device__ __forceinline__ void ld4(const float* p, float (&v)[4]) {
+  float4 a = *reinterpret_cast<const float4*>(p); v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+__device__ __forceinline__ void ld4(const bf16* p, float (&v)[4]) {
+  uint2 r = *reinterpret_cast<const uint2*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+  float2 a = __bfloat1622float2(h[0]), b = __bfloat1622float2(h[1]);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+__device__ __forceinline__ void st4(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void st4(bf16* p, const float (&v)[4]) {
+  uint2 r; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+  h[0] = __floats2bfloat162_rn(v[0], v[1]); h[1] = __floats2bfloat162_rn(v[2], v[3]);
+  *reinterpret_cast<uint2*>(p) = r;
+}
+
+// ------------------------------------------------------------------------------------------
+// weight packing (runs after every parameter change)
+// ------------------------------------------------------------------------------------------
+// w_fwd[t][ci][co]   = W[co][ci][ky][kx],            t = ky*3+kx
+// w_dgrad[t][co][ci] = W[co][ci][2-ky][2-kx]  (dgrad is a forward conv of dy with flipped taps)
+// wtc_fwd[co][t*C+ci]  (bf16, K-major B operand), wtc_dgrad[ci][t*C+co] (bf16, flipped taps)
+// w1p[j][hw*C+c]     = fc1.weight[j][c*64+hw]        (flatten order c,h,w -> NHWC order)
+// conv1_wp[k][co]    = conv1.weight[co][k],          k = ci*9+ky*3+kx
+__global__ void k_pack_weights(const float* __restrict__ rb_w, const float* __restrict__ fc1_w,
+                               const float* __restrict__ conv1_w, int C, float* __restrict__ w_fwd,
+                               float* __restrict__ w_dgrad, bf16* __restrict__ wtc_fwd,
+                               bf16* __restrict__ wtc_dgrad, float* __restrict__ w1p,
+                               float* __restrict__ conv1_wp) {
+  const int n_rb = C * C * 9, n_fc1 = NRD_FC1_OUT * 64 * C, n_c1 = C * 27;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_rb + n_fc1 + n_c1; i += gridDim.x * blockDim.x) {
+    if (i < n_rb) {
+      int co = i / (C * 9), r = i % (C * 9), ci = r / 9, t = r % 9;
+      float w = rb_w[i];
+      if (w_fwd) w_fwd[(t * C + ci) * C + co] = w;
+      if (w_dgrad) w_dgrad[((8 - t) * C + co) * C + ci] = w;
+      if (wtc_fwd) wtc_fwd[(size_t)co * 9 * C + t * C + ci] = __float2bfloat16_rn(w);
+      if (wtc_dgrad) wtc_dgrad[(size_t)ci * 9 * C + (8 - t) * C + co] = __float2bfloat16_rn(w);
+    } else if (i < n_rb + n_fc1) {
+      int q = i - n_rb;
+      int j = q / (64 * C), r = q % (64 * C), c = r / 64, hw = r % 64;
+      if (w1p) w1p[(size_t)j * 64 * C + hw * C + c] = fc1_w[q];
+    } else {
+      int q = i - n_rb - n_fc1;
+      int co = q / 27, k = q % 27;
+      if (conv1_wp) conv1_wp[k * C + co] = conv1_w[q];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// stem: x0 = maxpool2(relu(conv1(x) + b))            (model/resnet.py:16)
+// grid (4 bands, B); block 64*(C/8) threads: thread = (pooled pixel of the band, 8-channel group)
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void k_stem_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27][C]*/,
+                           const float* __restrict__ bias, T* __restrict__ x0, uint8_t* __restrict__ idx0, int C) {
+  extern __shared__ float sm[];
+  float* tile = sm;                 // [3][10][35], padded to 1056 floats so wsm stays 16-B aligned
+  float* wsm = sm + 1056;           // [27][C]
+  float* bsm = wsm + 27 * C;        // [C]
+  const int band = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, nt = blockDim.x;
+  const float* im = img + (size_t)b * 3 * 1024;
+  for (int i = tid; i < 3 * 10 * 34; i += nt) {
+    int ci = i / 340, r = (i % 340) / 34, c = i % 34;
+    int gr = band * 8 - 1 + r, gc = c - 1;
+    float v = 0.f;
+    if (gr >= 0 && gr < 32 && gc >= 0 && gc < 32) v = im[ci * 1024 + gr * 32 + gc];
+    tile[(ci * 10 + r) * 35 + c] = v;
+  }
+  for (int i = tid; i < 27 * C; i += nt) wsm[i] = wp[i];
+  for (int i = tid; i < C; i += nt) bsm[i] = bias[i];
+  __syncthreads();
+  const int ncg = C / 8, cg = tid % ncg, px = tid / ncg, ppy = px / 16, ppx = px % 16;
+  float acc[4][8];
+#pragma unroll
+  for (int p = 0; p < 4; ++p)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[p][j] = 0.f;
+#pragma unroll
+  for (int ci = 0; ci < 3; ++ci) {
+    float patch[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) patch[r][c] = tile[(ci * 10 + 2 * ppy + r) * 35 + 2 * ppx + c];
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const float* w = wsm + (ci * 9 + ky * 3 + kx) * C + cg * 8;
+        float4 w0 = *reinterpret_cast<const float4*>(w), w1 = *reinterpret_cast<const float4*>(w + 4);
+        float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          float v = patch[(p >> 1) + ky][(p & 1) + kx];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[p][j] = fmaf(v, wv[j], acc[p][j]);
+        }
+      }
+  }
+  float out[8]; uint8_t id[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float bj = bsm[cg * 8 + j];
+    float m = acc[0][j] + bj; int mi = 0;
+#pragma unroll
+    for (int p = 1; p < 4; ++p) { float v = acc[p][j] + bj; if (v > m) { m = v; mi = p; } }  // first max wins
+    out[j] = fmaxf(m, 0.f); id[j] = (uint8_t)mi;
+  }
+  size_t o = (((size_t)b * 16 + band * 4 + ppy) * 16 + ppx) * C + cg * 8;
+  st8(x0 + o, out);
+  uint2 pk; uint8_t* pb = reinterpret_cast<uint8_t*>(&pk);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) pb[j] = id[j];
+  *reinterpret_cast<uint2*>(idx0 + o) = pk;
+}
+
+// stem backward: dconv1.weight / dconv1.bias only (the input needs no grad).  One CTA loops over
+// images; thread = (co, pixel-group); per-CTA partial [28][C] (27 taps + bias), reduced afterwards.
+template <typename T>
+__global__ void k_stem_bwd(const float* __restrict__ img, const T* __restrict__ g0, const T* __restrict__ x0,
+                           const uint8_t* __restrict__ idx0, float* __restrict__ partial, int B, int C) {
+  extern __shared__ float sm[];
+  float* tile = sm;                       // [3][34][35] zero-padded image
+  float* red = sm + 3 * 34 * 35;          // [ngroups][28][C]
+  const int tid = threadIdx.x, nt = blockDim.x, co = tid % C, grp = tid / C, ngrp = nt / C;
+  float acc[28];
+#pragma unroll
+  for (int k = 0; k < 28; ++k) acc[k] = 0.f;
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    __syncthreads();
+    const float* im = img + (size_t)b * 3072;
+    for (int i = tid; i < 3 * 34 * 34; i += nt) {
+      int ci = i / 1156, r = (i % 1156) / 34, c = i % 34;
+      float v = 0.f;
+      if (r >= 1 && r <= 32 && c >= 1 && c <= 32) v = im[ci * 1024 + (r - 1) * 32 + (c - 1)];
+      tile[(ci * 34 + r) * 35 + c] = v;
+    }
+    __syncthreads();
+    for (int px = grp; px < 256; px += ngrp) {
+      size_t o = ((size_t)b * 256 + px) * C + co;
+      float xv = to_f(x0[o]);
+      float g = (xv > 0.f) ? to_f(g0[o]) : 0.f;    // relu'(0) = 0; pool routes to the first max
+      int id = idx0[o];
+      int h = 2 * (px / 16) + (id >> 1), w = 2 * (px % 16) + (id & 1);   // conv-output position
+      acc[27] += g;
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx)
+            acc[ci * 9 + ky * 3 + kx] = fmaf(g, tile[(ci * 34 + h + ky) * 35 + w + kx], acc[ci * 9 + ky * 3 + kx]);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 28; ++k) red[(grp * 28 + k) * C + co] = acc[k];
+  __syncthreads();
+  for (int i = tid; i < 28 * C; i += nt) {
+    float s = 0.f;
+    for (int g = 0; g < ngrp; ++g) s += red[g * 28 * C + i];
+    partial[(size_t)blockIdx.x * 28 * C + i] = s;
+  }
+}
+
+__global__ void k_stem_bwd_reduce(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dw,
+                                  float* __restrict__ db) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 28 * C) return;
+  double s = 0.0;
+  for (int b = 0; b < nblk; ++b) s += (double)partial[(size_t)b * 28 * C + i];
+  int k = i / C, co = i % C;
+  if (k < 27) dw[co * 27 + k] = (float)s; else db[co] = (float)s;
+}
+
+// ------------------------------------------------------------------------------------------
+// conv3x3 pad 1, C -> C, NHWC, direct on CUDA cores.  CTA = 8x16 pixel tile of one image.
+// w: [9][Cin][Cout] fp32.  Optional: per-CTA BN partial sums of the fp32 results; residual add.
+// ------------------------------------------------------------------------------------------
+template <typename T, int C>
+__global__ void __launch_bounds__(256) k_conv3x3(const T* __restrict__ x, const float* __restrict__ w,
+                                                 T* __restrict__ y, float* __restrict__ stats_partial,
+                                                 const T* __restrict__ residual) {
+  constexpr int CP = C + 1;            // padded channel stride (bank-conflict free)
+  constexpr int NCOG = C / 4;          // threads along output channels (4 each)
+  constexpr int NPG = 256 / NCOG;      // pixel groups
+  constexpr int PPT = 128 / NPG;       // pixels per thread (consecutive in a row)
+  constexpr int GPR = 16 / PPT;        // groups per row
+  extern __shared__ float sm[];
+  float* xs = sm;                      // [10][18][CP]
+  float* ws = sm + 10 * 18 * CP;       // [9][C][C]
+  const int tid = threadIdx.x, blk = blockIdx.x, b = blk >> 1, r0 = (blk & 1) * 8;
+  const T* xb = x + (size_t)b * NRD_PIX * C;
+  for (int i = tid; i < 10 * 18 * (C / 4); i += 256) {
+    int c4 = i % (C / 4), pc = (i / (C / 4)) % 18, pr = i / (C / 4) / 18;
+    int gr = r0 - 1 + pr, gc = pc - 1;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (gr >= 0 && gr < 16 && gc >= 0 && gc < 16) ld4(xb + ((size_t)gr * 16 + gc) * C + c4 * 4, v);
+    float* d = xs + (pr * 18 + pc) * CP + c4 * 4;
+    d[0] = v[0]; d[1] = v[1]; d[2] = v[2]; d[3] = v[3];
+  }
+  for (int i = tid; i < 9 * C * C / 4; i += 256)
+    reinterpret_cast<float4*>(ws)[i] = reinterpret_cast<const float4*>(w)[i];
+  __syncthreads();
+  const int cog = tid % NCOG, pg = tid / NCOG, row = pg / GPR, col0 = (pg % GPR) * PPT;
+  float acc[PPT][4];
+#pragma unroll
+  for (int j = 0; j < PPT; ++j) { acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f; }
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+    const float* xr = xs + ((row + ky) * 18 + col0) * CP;
+#pragma unroll 4
+    for (int ci = 0; ci < C; ++ci) {
+      float in[PPT + 2];
+#pragma unroll
+      for (int j = 0; j < PPT + 2; ++j) in[j] = xr[j * CP + ci];
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        float4 wv = *reinterpret_cast<const float4*>(ws + ((ky * 3 + kx) * C + ci) * C + cog * 4);
+#pragma unroll
+        for (int j = 0; j < PPT; ++j) {
+          acc[j][0] = fmaf(in[j + kx], wv.x, acc[j][0]); acc[j][1] = fmaf(in[j + kx], wv.y, acc[j][1]);
+          acc[j][2] = fmaf(in[j + kx], wv.z, acc[j][2]); acc[j][3] = fmaf(in[j + kx], wv.w, acc[j][3]);
+        }
+      }
+    }
+  }
+  // epilogue
+  float s[4] = {0.f, 0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int j = 0; j < PPT; ++j) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { s[e] += acc[j][e]; q[e] = fmaf(acc[j][e], acc[j][e], q[e]); }
+    size_t o = ((size_t)b * NRD_PIX + (r0 + row) * 16 + col0 + j) * C + cog * 4;
+    float v[4] = {acc[j][0], acc[j][1], acc[j][2], acc[j][3]};
+    if (residual) { float rr[4]; ld4(residual + o, rr); v[0] += rr[0]; v[1] += rr[1]; v[2] += rr[2]; v[3] += rr[3]; }
+    st4(y + o, v);
+  }
+  if (stats_partial) {
+    __syncthreads();                   // everyone is done with xs; reuse it as [NPG][2][C]
+    float* red = sm;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { red[(pg * 2 + 0) * C + cog * 4 + e] = s[e]; red[(pg * 2 + 1) * C + cog * 4 + e] = q[e]; }
+    __syncthreads();
+    if (tid < 2 * C) {
+      float t = 0.f;
+      for (int g = 0; g < NPG; ++g) t += red[g * 2 * C + tid];
+      stats_partial[(size_t)blk * 2 * C + tid] = t;
+    }
+  }
+}
+
+// wgrad: partial[blk][ky*3+kx][co][ci] (+)= sum over the CTA's tiles of dy[p][co] * x[p+tap][ci].
+// grid (nblk, 3): blockIdx.y = ky.  thread = (ci, group of CO_PT output channels).
+template <typename T, int C>
+__global__ void __launch_bounds__(256) k_wgrad(const T* __restrict__ x, const T* __restrict__ dy,
+                                               float* __restrict__ partial, int ntiles, int first) {
+  constexpr int CP = C + 1;
+  constexpr int NCOG = 256 / C;
+  constexpr int CO_PT = C / NCOG;
+  extern __shared__ float sm[];
+  float* xs = sm;                 // [3 rows... we keep 10][18][CP]
+  float* ds = sm + 10 * 18 * CP;  // [128][C]
+  const int tid = threadIdx.x, ky = blockIdx.y, ci = tid % C, cog = tid / C;
+  float acc[3][CO_PT];
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+#pragma unroll
+    for (int e = 0; e < CO_PT; ++e) acc[k][e] = 0.f;
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int b = t >> 1, r0 = (t & 1) * 8;
+    const T* xb = x + (size_t)b * NRD_PIX * C;
+    __syncthreads();
+    for (int i = tid; i < 10 * 18 * (C / 4); i += 256) {
+      int c4 = i % (C / 4), pc = (i / (C / 4)) % 18, pr = i / (C / 4) / 18;
+      int gr = r0 - 1 + pr, gc = pc - 1;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (gr >= 0 && gr < 16 && gc >= 0 && gc < 16) ld4(xb + ((size_t)gr * 16 + gc) * C + c4 * 4, v);
+      float* d = xs + (pr * 18 + pc) * CP + c4 * 4;
+      d[0] = v[0]; d[1] = v[1]; d[2] = v[2]; d[3] = v[3];
+    }
+    const T* db = dy + ((size_t)b * NRD_PIX + r0 * 16) * C;
+    for (int i = tid; i < 128 * C / 4; i += 256) {
+      float v[4]; ld4(db + (size_t)i * 4, v);
+      *reinterpret_cast<float4*>(ds + i * 4) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    __syncthreads();
+    for (int p = 0; p < 128; ++p) {
+      const int r = p >> 4, c = p & 15;
+      const float* xr = xs + ((r + ky) * 18 + c) * CP + ci;
+      float x0 = xr[0], x1 = xr[CP], x2 = xr[2 * CP];
+      const float* dp = ds + p * C + cog * CO_PT;
+#pragma unroll
+      for (int e4 = 0; e4 < CO_PT / 4; ++e4) {
+        float4 d4 = *reinterpret_cast<const float4*>(dp + e4 * 4);
+        float dv[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          acc[0][e4 * 4 + e] = fmaf(x0, dv[e], acc[0][e4 * 4 + e]);
+          acc[1][e4 * 4 + e] = fmaf(x1, dv[e], acc[1][e4 * 4 + e]);
+          acc[2][e4 * 4 + e] = fmaf(x2, dv[e], acc[2][e4 * 4 + e]);
+        }
+      }
+    }
+  }
+  float* out = partial + (size_t)blockIdx.x * 9 * C * C;
+#pragma unroll
+  for (int kx = 0; kx < 3; ++kx)
+#pragma unroll
+    for (int e = 0; e < CO_PT; ++e) {
+      size_t o = ((size_t)(ky * 3 + kx) * C + cog * CO_PT + e) * C + ci;
+      out[o] = first ? acc[kx][e] : out[o] + acc[kx][e];
+    }
+}
+
+// dW[co][ci][t] (OIHW) = sum_blk partial[blk][t][co][ci]
+__global__ void k_wgrad_reduce(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dw) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 9 * C * C) return;
+  double s = 0.0;
+  for (int b = 0; b < nblk; ++b) s += (double)partial[(size_t)b * 9 * C * C + i];
+  int t = i / (C * C), co = (i / C) % C, ci = i % C;
+  dw[((size_t)co * C + ci) * 9 + t] = (float)s;
+}
+
+// ------------------------------------------------------------------------------------------
+// BatchNorm2d (training) forward pieces                                 (model/resnet.py:35-37)
+// ------------------------------------------------------------------------------------------
+// finalize: partial [blocks][2C] -> mean, invstd (saved), scale/shift, running-stat EMA, nbt += 1
+__global__ void k_bn_finalize(const float* __restrict__ partial, int blocks, int count, int C,
+                              const float* __restrict__ gamma, const float* __restrict__ beta,
+                              float* __restrict__ saved, float* __restrict__ scale_shift,
+                              float* __restrict__ running, int64_t* __restrict__ nbt) {
+  __shared__ double red[256];
+  const int tid = threadIdx.x, ncol = 2 * C, col = tid % ncol, slice = tid / ncol, nslice = 256 / ncol;
+  double s = 0.0;
+  for (int i = slice; i < blocks; i += nslice) s += (double)partial[(size_t)i * ncol + col];
+  red[tid] = s;
+  __syncthreads();
+  if (tid < C) {
+    double S = 0.0, Q = 0.0;
+    for (int k = 0; k < nslice; ++k) { S += red[k * ncol + tid]; Q += red[k * ncol + C + tid]; }
+    double mean = S / count, var = Q / count - mean * mean;
+    if (var < 0.0) var = 0.0;
+    float invstd = (float)(1.0 / sqrt(var + (double)NRD_BN_EPS));
+    float sc = gamma[tid] * invstd;
+    saved[tid] = (float)mean; saved[C + tid] = invstd;
+    scale_shift[tid] = sc; scale_shift[C + tid] = beta[tid] - (float)mean * sc;
+    if (running) {
+      double unbiased = var * ((double)count / (double)(count - 1));
+      running[tid] = (1.f - NRD_BN_MOMENTUM) * running[tid] + NRD_BN_MOMENTUM * (float)mean;
+      running[C + tid] = (1.f - NRD_BN_MOMENTUM) * running[C + tid] + NRD_BN_MOMENTUM * (float)unbiased;
+    }
+  }
+  if (tid == 0 && nbt) *nbt += 1;
+}
+
+// eval mode: scale/shift from the running statistics
+__global__ void k_bn_eval_coeffs(const float* __restrict__ running, const float* __restrict__ gamma,
+                                 const float* __restrict__ beta, int C, float* __restrict__ scale_shift) {
+  int c = threadIdx.x;
+  if (c < C) {
+    float invstd = (float)(1.0 / sqrt((double)running[C + c] + (double)NRD_BN_EPS));
+    float sc = gamma[c] * invstd;
+    scale_shift[c] = sc; scale_shift[C + c] = beta[c] - running[c] * sc;
+  }
+}
+
+// out = relu(y*scale + shift) + x
+template <typename T>
+__global__ void k_bn_relu_add(const T* __restrict__ y, const T* __restrict__ x, const float* __restrict__ scale_shift,
+                              T* __restrict__ out, size_t n8, int C) {
+  __shared__ float ss[128];
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) ss[i] = scale_shift[i];
+  __syncthreads();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    int c0 = (int)((i * 8) % C);
+    float yv[8], xv[8], o[8];
+    ld8(y + i * 8, yv); ld8(x + i * 8, xv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = fmaxf(fmaf(yv[j], ss[c0 + j], ss[C + c0 + j]), 0.f) + xv[j];
+    st8(out + i * 8, o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// BN + ReLU backward.  g = dL/d(out) (the residual branch passes g through unchanged).
+//   z = y*scale+shift, dz = g*[z>0], xhat = (y-mean)*invstd
+//   dbeta = sum dz, dgamma = sum dz*xhat, dy = gamma*invstd*(dz - dbeta/n - xhat*dgamma/n)
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) k_bn_bwd_reduce(const T* __restrict__ g, const T* __restrict__ y,
+                                                       const float* __restrict__ scale_shift,
+                                                       const float* __restrict__ saved, float* __restrict__ partial,
+                                                       int C) {
+  __shared__ float red[4096];  // [rows][2][C], rows = 256/(C/8) => rows*2*C = 4096 floats
+  const int tid = threadIdx.x, ncg = C / 8, cg = tid % ncg, pr = tid / ncg, nrow = 256 / ncg;
+  float sc[8], sh[8], mu[8], is[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale_shift[cg * 8 + j]; sh[j] = scale_shift[C + cg * 8 + j];
+    mu[j] = saved[cg * 8 + j]; is[j] = saved[C + cg * 8 + j];
+  }
+  float s1[8], s2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+  const size_t base = (size_t)blockIdx.x * NRD_PIX * C;   // one image per CTA
+  for (int px = pr; px < NRD_PIX; px += nrow) {
+    float gv[8], yv[8];
+    ld8(g + base + (size_t)px * C + cg * 8, gv); ld8(y + base + (size_t)px * C + cg * 8, yv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float z = fmaf(yv[j], sc[j], sh[j]);
+      float dz = z > 0.f ? gv[j] : 0.f;
+      s1[j] += dz; s2[j] = fmaf(dz, (yv[j] - mu[j]) * is[j], s2[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { red[(pr * 2 + 0) * C + cg * 8 + j] = s1[j]; red[(pr * 2 + 1) * C + cg * 8 + j] = s2[j]; }
+  __syncthreads();
+  if (tid < 2 * C) {
+    float t = 0.f;
+    for (int r = 0; r < nrow; ++r) t += red[r * 2 * C + tid];
+    partial[(size_t)blockIdx.x * 2 * C + tid] = t;
+  }
+}
+
+// partial [blocks][2C] -> dbeta/dgamma (set or accumulate) + coefficients coef[3][C] = {gamma*invstd, dbeta/n, dgamma/n}
+__global__ void k_bn_bwd_finalize(const float* __restrict__ partial, int blocks, int count, int C,
+                                  const float* __restrict__ gamma, const float* __restrict__ saved,
+                                  float* __restrict__ dgamma, float* __restrict__ dbeta, int accumulate,
+                                  float* __restrict__ coef) {
+  __shared__ double red[256];
+  const int tid = threadIdx.x, ncol = 2 * C, col = tid % ncol, slice = tid / ncol, nslice = 256 / ncol;
+  double s = 0.0;
+  for (int i = slice; i < blocks; i += nslice) s += (double)partial[(size_t)i * ncol + col];
+  red[tid] = s;
+  __syncthreads();
+  if (tid < C) {
+    double db = 0.0, dg = 0.0;
+    for (int k = 0; k < nslice; ++k) { db += red[k * ncol + tid]; dg += red[k * ncol + C + tid]; }
+    if (accumulate) { dbeta[tid] += (float)db; dgamma[tid] += (float)dg; }
+    else { dbeta[tid] = (float)db; dgamma[tid] = (float)dg; }
+    coef[tid] = gamma[tid] * saved[C + tid];
+    coef[C + tid] = (float)(db / count);
+    coef[2 * C + tid] = (float)(dg / count);
+  }
+}
+
+template <typename T>
+__global__ void k_bn_bwd_apply(const T* __restrict__ g, const T* __restrict__ y, const float* __restrict__ scale_shift,
+                               const float* __restrict__ saved, const float* __restrict__ coef, T* __restrict__ dy,
+                               size_t n8, int C) {
+  __shared__ float p[7 * 64];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    p[i] = scale_shift[i]; p[C + i] = scale_shift[C + i]; p[2 * C + i] = saved[i]; p[3 * C + i] = saved[C + i];
+    p[4 * C + i] = coef[i]; p[5 * C + i] = coef[C + i]; p[6 * C + i] = coef[2 * C + i];
+  }
+  __syncthreads();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    int c0 = (int)((i * 8) % C);
+    float gv[8], yv[8], o[8];
+    ld8(g + i * 8, gv); ld8(y + i * 8, yv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      int c = c0 + j;
+      float z = fmaf(yv[j], p[c], p[C + c]);
+      float dz = z > 0.f ? gv[j] : 0.f;
+      float xh = (yv[j] - p[2 * C + c]) * p[3 * C + c];
+      o[j] = p[4 * C + c] * (dz - p[5 * C + c] - xh * p[6 * C + c]);
+    }
+    st8(dy + i * 8, o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// 2x2/2 max pool at 16x16 -> 8x8 (model/resnet.py:18); gradient goes to the FIRST max
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void k_maxpool_fwd(const T* __restrict__ x, T* __restrict__ p, uint8_t* __restrict__ idx, int B, int C) {
+  const int ncg = C / 8;
+  size_t n = (size_t)B * 64 * ncg;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    int cg = (int)(i % ncg); size_t pp = i / ncg; int pw = (int)(pp % 8), ph = (int)((pp / 8) % 8); size_t b = pp / 64;
+    float m[8]; int mi[8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float v[8];
+      ld8(x + ((b * 16 + 2 * ph + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + cg * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) if (q == 0 || v[j] > m[j]) { m[j] = v[j]; mi[j] = q; }
+    }
+    st8(p + pp * C + cg * 8, m);
+    uint2 pk; uint8_t* pb = reinterpret_cast<uint8_t*>(&pk);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) pb[j] = (uint8_t)mi[j];
+    *reinterpret_cast<uint2*>(idx + pp * C + cg * 8) = pk;
+  }
+}
+
+template <typename T>
+__global__ void k_maxpool_bwd(const T* __restrict__ gp, const uint8_t* __restrict__ idx, T* __restrict__ gx, int B, int C) {
+  const int ncg = C / 8;
+  size_t n = (size_t)B * 64 * ncg;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    int cg = (int)(i % ncg); size_t pp = i / ncg; int pw = (int)(pp % 8), ph = (int)((pp / 8) % 8); size_t b = pp / 64;
+    float g[8]; ld8(gp + pp * C + cg * 8, g);
+    uint2 pk = *reinterpret_cast<const uint2*>(idx + pp * C + cg * 8);
+    const uint8_t* pb = reinterpret_cast<const uint8_t*>(&pk);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = (pb[j] == q) ? g[j] : 0.f;
+      st8(gx + ((b * 16 + 2 * ph + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + cg * 8, v);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// head: fc1 + relu, fc2, softmax cross-entropy                     (model/resnet.py:19-21, main.py:28)
+// ------------------------------------------------------------------------------------------
+// h1[b][j] = relu(sum_i p[b][i] * w1p[j][i] + b1[j]); CTA = 8 batch rows, warp = 4 outputs
+template <typename T>
+__global__ void __launch_bounds__(256) k_fc1_fwd(const T* __restrict__ p, const float* __restrict__ w1p,
+                                                 const float* __restrict__ b1, float* __restrict__ h1, int B, int K) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, b0 = blockIdx.x * 8, j0 = warp * 4;
+  float acc[8][4];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f;
+  for (int i = lane * 4; i < K; i += 128) {
+    float w[4][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ld4(w1p + (size_t)(j0 + j) * K + i, w[j]);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      if (b0 + r < B) {
+        float pv[4]; ld4(p + (size_t)(b0 + r) * K + i, pv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          acc[r][j] += pv[0] * w[j][0] + pv[1] * w[j][1] + pv[2] * w[j][2] + pv[3] * w[j][3];
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 8; ++r)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float v = acc[r][j];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && b0 + r < B) h1[(size_t)(b0 + r) * NRD_FC1_OUT + j0 + j] = fmaxf(v + b1[j0 + j], 0.f);
+    }
+}
+
+__global__ void k_fc2_fwd(const float* __restrict__ h1, const float* __restrict__ w2, const float* __restrict__ b2,
+                          float* __restrict__ logits, int B) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * NRD_NCLS) return;
+  int b = i / NRD_NCLS, c = i % NRD_NCLS;
+  float s = b2[c];
+#pragma unroll
+  for (int j = 0; j < NRD_FC1_OUT; ++j) s = fmaf(h1[b * NRD_FC1_OUT + j], w2[c * NRD_FC1_OUT + j], s);
+  logits[i] = s;
+}
+
+// per-row loss and dlogits = (softmax - onehot) * grad_scale / B
+__global__ void k_ce_rows(const float* __restrict__ logits, const int64_t* __restrict__ labels, int B, float gscale,
+                          float* __restrict__ loss_rows, float* __restrict__ dlogits) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float v[NRD_NCLS], m = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < NRD_NCLS; ++c) { v[c] = logits[b * NRD_NCLS + c]; m = fmaxf(m, v[c]); }
+  float s = 0.f;
+#pragma unroll
+  for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
+  int lab = (int)labels[b];
+  float inv = 1.f / s, sc = gscale / (float)B;
+  loss_rows[b] = logf(s) + m - logits[b * NRD_NCLS + lab];
+  if (dlogits) {
+#pragma unroll
+    for (int c = 0; c < NRD_NCLS; ++c) dlogits[b * NRD_NCLS + c] = (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc;
+  }
+}
+
+__global__ void k_loss_mean(const float* __restrict__ loss_rows, int B, float* __restrict__ loss) {
+  __shared__ double red[256];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < B; i += 256) s += (double)loss_rows[i];
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) *loss = (float)(red[0] / B);
+}
+
+// dh1[b][j] = sum_c dlogits[b][c] * w2[c][j] * [h1>0]
+__global__ void k_fc2_bwd(const float* __restrict__ dlogits, const float* __restrict__ w2, const float* __restrict__ h1,
+                          float* __restrict__ dh1, int B) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * NRD_FC1_OUT) return;
+  int b = i / NRD_FC1_OUT, j = i % NRD_FC1_OUT;
+  float s = 0.f;
+#pragma unroll
+  for (int c = 0; c < NRD_NCLS; ++c) s = fmaf(dlogits[b * NRD_NCLS + c], w2[c * NRD_FC1_OUT + j], s);
+  dh1[i] = h1[i] > 0.f ? s : 0.f;
+}
+
+// dW2[c][j], db2[c], dbfc1[j]: one CTA of 384 threads, each output summed over the batch in order
+__global__ void k_head_wgrad(const float* __restrict__ dlogits, const float* __restrict__ h1,
+                             const float* __restrict__ dh1, int B, float* __restrict__ dw2,
+                             float* __restrict__ db2, float* __restrict__ dbfc1) {
+  int t = threadIdx.x;
+  float s = 0.f;
+  if (t < 320) {
+    int c = t / 32, j = t % 32;
+    for (int b = 0; b < B; ++b) s = fmaf(dlogits[b * NRD_NCLS + c], h1[b * NRD_FC1_OUT + j], s);
+    dw2[t] = s;
+  } else if (t < 330) {
+    int c = t - 320;
+    for (int b = 0; b < B; ++b) s += dlogits[b * NRD_NCLS + c];
+    db2[c] = s;
+  } else if (t < 362) {
+    int j = t - 330;
+    for (int b = 0; b < B; ++b) s += dh1[b * NRD_FC1_OUT + j];
+    dbfc1[j] = s;
+  }
+}
+
+// dWfc1[j][c*64+hw] = sum_b dh1[b][j] * p[b][hw*C+c].  CTA = 64 consecutive NHWC columns x 32 rows.
+template <typename T>
+__global__ void __launch_bounds__(256) k_fc1_wgrad(const T* __restrict__ p, const float* __restrict__ dh1,
+                                                   float* __restrict__ dw1, int B, int C) {
+  __shared__ float ds[256 * NRD_FC1_OUT];
+  const int tid = threadIdx.x, il = tid % 64, jg = tid / 64, K = 64 * C, i = blockIdx.x * 64 + il;
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  for (int bb = 0; bb < B; bb += 256) {
+    int nb = min(256, B - bb);
+    __syncthreads();
+    for (int q = tid; q < nb * NRD_FC1_OUT; q += 256) ds[q] = dh1[(size_t)bb * NRD_FC1_OUT + q];
+    __syncthreads();
+    for (int b = 0; b < nb; ++b) {
+      float pv = to_f(p[(size_t)(bb + b) * K + i]);
+      const float4* d4 = reinterpret_cast<const float4*>(ds + b * NRD_FC1_OUT + jg * 8);
+      float4 a = d4[0], c4 = d4[1];
+      acc[0] = fmaf(pv, a.x, acc[0]); acc[1] = fmaf(pv, a.y, acc[1]); acc[2] = fmaf(pv, a.z, acc[2]); acc[3] = fmaf(pv, a.w, acc[3]);
+      acc[4] = fmaf(pv, c4.x, acc[4]); acc[5] = fmaf(pv, c4.y, acc[5]); acc[6] = fmaf(pv, c4.z, acc[6]); acc[7] = fmaf(pv, c4.w, acc[7]);
+    }
+  }
+  int hw = i / C, c = i % C;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) dw1[(size_t)(jg * 8 + e) * K + c * 64 + hw] = acc[e];
+}
+
+// d(pooled)[b][hw][c] = sum_j dh1[b][j] * w1p[j][hw*C+c], scattered through pool-2's argmax into gx [B,16,16,C]
+template <typename T>
+__global__ void __launch_bounds__(256) k_fc1_dgrad_unpool(const float* __restrict__ dh1, const float* __restrict__ w1p,
+                                                          const uint8_t* __restrict__ idx2, T* __restrict__ gx,
+                                                          int B, int C) {
+  __shared__ float d[NRD_FC1_OUT];
+  const int K = 64 * C, per_b = K / 256, b = blockIdx.x / per_b, i = (blockIdx.x % per_b) * 256 + threadIdx.x;
+  if (threadIdx.x < NRD_FC1_OUT) d[threadIdx.x] = dh1[(size_t)b * NRD_FC1_OUT + threadIdx.x];
+  __syncthreads();
+  float s = 0.f;
+#pragma unroll 8
+  for (int j = 0; j < NRD_FC1_OUT; ++j) s = fmaf(d[j], w1p[(size_t)j * K + i], s);
+  int hw = i / C, c = i % C, ph = hw / 8, pw = hw % 8, id = idx2[(size_t)b * K + i];
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+    gx[(((size_t)b * 16 + 2 * ph + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + c] = from_f<T>(q == id ? s : 0.f);
+}
+
+// ------------------------------------------------------------------------------------------
+// fused DDP mean + SGD step: p <- p - lr * inv_world * g                      (main.py:27,39,63)
+// ------------------------------------------------------------------------------------------
+__global__ void k_sgd(float* __restrict__ p, const float* __restrict__ g, size_t n, float step_scale) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    p[i] = fmaf(-step_scale, g[i], p[i]);
+}
+
+// ------------------------------------------------------------------------------------------
+// synthetic CIFAR-shaped batch: Philox-4x32-10, counter = (element/4, rank, step lo, step hi)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                              uint32_t k1, uint32_t (&out)[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+__global__ void k_gen_batch(float* __restrict__ img, int64_t* __restrict__ labels, int B, uint64_t seed, uint32_t rank,
+                            uint64_t step) {
+  const size_t n4 = (size_t)B * 3072 / 4;
+  const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4 + (size_t)B; i += (size_t)gridDim.x * blockDim.x) {
+    uint32_t r[4];
+    if (i < n4) {
+      philox4x32_10((uint32_t)i, rank, (uint32_t)step, (uint32_t)(step >> 32), k0, k1, r);
+      // Box-Muller on two pairs of 32-bit uniforms; u in (0,1]
+      float u0 = ((float)(r[0] >> 8) + 1.0f) * (1.0f / 16777216.0f), u1 = (float)(r[1] >> 8) * (1.0f / 16777216.0f);
+      float u2 = ((float)(r[2] >> 8) + 1.0f) * (1.0f / 16777216.0f), u3 = (float)(r[3] >> 8) * (1.0f / 16777216.0f);
+      float ra = sqrtf(-2.0f * logf(u0)), rb = sqrtf(-2.0f * logf(u2));
+      float s0, c0, s1, c1;
+      sincospif(2.0f * u1, &s0, &c0); sincospif(2.0f * u3, &s1, &c1);
+      reinterpret_cast<float4*>(img)[i] = make_float4(ra * c0, ra * s0, rb * c1, rb * s1);
+    } else {
+      size_t b = i - n4;
+      philox4x32_10((uint32_t)b, rank | 0x80000000u, (uint32_t)step, (uint32_t)(step >> 32), k0, k1, r);
+      labels[b] = (int64_t)(r[0] % 10u);
+    }
+  }
+}
+
+// ==========================================================================================
+// host side
+// ==========================================================================================
+static thread_local char g_err[512] = "";
+void nrd_set_error(const char* fmt, ...) {
+  va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+}
+extern "C" const char* nrd_last_error(void) { return g_err; }
+extern "C" int nrd_version(void) { return 100; }
+
+#include <atomic>
+static std::atomic<unsigned long long> g_launches{0};
+void nrd_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+extern "C" unsigned long long nrd_launch_count(void) { return g_launches.load(); }
+#define LAUNCH_CHECK() do { nrd_count_launch(); NRD_CHECK_CUDA(cudaGetLastError()); } while (0)
+
+static inline int grid_for(size_t n, int block, int cap = NRD_NUM_SMS * 8) {
+  size_t g = (n + block - 1) / block;
+  if (g > (size_t)cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+static bool valid_C(int C) { return C == 32 || C == 64; }
+static bool valid_dt(int dt) { return dt == NRD_F32 || dt == NRD_BF16; }
+
+extern "C" int nrd_param_offsets(int C, int64_t off[10]) {
+  NRD_REQUIRE(valid_C(C), "nrd_param_offsets: C must be 32 or 64 (got %d)", C);
+  int64_t sizes[9] = {(int64_t)C * 27, C, (int64_t)C * C * 9, C, C, (int64_t)NRD_FC1_OUT * 64 * C, NRD_FC1_OUT,
+                      NRD_NCLS * NRD_FC1_OUT, NRD_NCLS};
+  off[0] = 0;
+  for (int i = 0; i < 9; ++i) off[i + 1] = off[i] + sizes[i];
+  return NRD_OK;
+}
+
+// ---- per-op launchers -------------------------------------------------------------------
+static int wgrad_blocks(int B) { int t = B * 2; return t < NRD_NUM_SMS ? t : NRD_NUM_SMS; }
+static int stem_bwd_blocks(int B) { return B < NRD_NUM_SMS ? B : NRD_NUM_SMS; }
+
+// opt-in dynamic shared memory is a per-device function attribute: set it once per (kernel, device),
+// outside any stream capture (the first, eager call does it)
+template <typename F>
+static int set_smem_once(F* fn, size_t smem, bool (&done)[64]) {
+  int dev = 0;
+  NRD_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 64 && done[dev]) return NRD_OK;
+  NRD_CHECK_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (dev < 64) done[dev] = true;
+  return NRD_OK;
+}
+
+template <typename T>
+static int launch_conv(const void* x, const float* w, void* y, int B, int C, float* stats, const void* res, cudaStream_t st) {
+  if (C == 32) {
+    size_t smem = (10 * 18 * 33 + 9 * 32 * 32) * sizeof(float);
+    static bool done[64]; NRD_TRY(set_smem_once(k_conv3x3<T, 32>, smem, done));
+    k_conv3x3<T, 32><<<B * 2, 256, smem, st>>>((const T*)x, w, (T*)y, stats, (const T*)res);
+  } else {
+    size_t smem = (10 * 18 * 65 + 9 * 64 * 64) * sizeof(float);
+    static bool done[64]; NRD_TRY(set_smem_once(k_conv3x3<T, 64>, smem, done));
+    k_conv3x3<T, 64><<<B * 2, 256, smem, st>>>((const T*)x, w, (T*)y, stats, (const T*)res);
+  }
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+static int conv_fwd_any(const void* x, const float* w, void* y, int B, int C, int dt, float* stats, const void* res, cudaStream_t st) {
+  return dt == NRD_F32 ? launch_conv<float>(x, w, y, B, C, stats, res, st) : launch_conv<bf16>(x, w, y, B, C, stats, res, st);
+}
+
+template <typename T>
+static int launch_wgrad(const void* x, const void* dy, float* partial, int B, int C, int first, cudaStream_t st) {
+  dim3 grid(wgrad_blocks(B), 3);
+  if (C == 32) {
+    size_t smem = (10 * 18 * 33 + 128 * 32) * sizeof(float);
+    static bool done[64]; NRD_TRY(set_smem_once(k_wgrad<T, 32>, smem, done));
+    k_wgrad<T, 32><<<grid, 256, smem, st>>>((const T*)x, (const T*)dy, partial, B * 2, first);
+  } else {
+    size_t smem = (10 * 18 * 65 + 128 * 64) * sizeof(float);
+    static bool done[64]; NRD_TRY(set_smem_once(k_wgrad<T, 64>, smem, done));
+    k_wgrad<T, 64><<<grid, 256, smem, st>>>((const T*)x, (const T*)dy, partial, B * 2, first);
+  }
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+static int wgrad_any(const void* x, const void* dy, float* partial, int B, int C, int dt, int first, cudaStream_t st) {
+  return dt == NRD_F32 ? launch_wgrad<float>(x, dy, partial, B, C, first, st) : launch_wgrad<bf16>(x, dy, partial, B, C, first, st);
+}
+static int wgrad_reduce(const float* partial, int B, int C, float* dw, cudaStream_t st) {
+  k_wgrad_reduce<<<(9 * C * C + 255) / 256, 256, 0, st>>>(partial, wgrad_blocks(B), C, dw);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+static int bn_relu_add_any(const void* y, const void* x, const float* ss, void* out, int B, int C, int dt, cudaStream_t st) {
+  size_t n8 = (size_t)B * NRD_PIX * C / 8;
+  int g = grid_for(n8, 256);
+  if (dt == NRD_F32) k_bn_relu_add<float><<<g, 256, 0, st>>>((const float*)y, (const float*)x, ss, (float*)out, n8, C);
+  else k_bn_relu_add<bf16><<<g, 256, 0, st>>>((const bf16*)y, (const bf16*)x, ss, (bf16*)out, n8, C);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+// scratch layout: [B][2C] partials | coef [3C]
+static int bn_relu_bwd_any(const void* g, const void* y, const float* ss, const float* saved, const float* gamma, void* dy,
+                           float* dgamma, float* dbeta, int accumulate, int B, int C, int dt, float* scratch, cudaStream_t st) {
+  float* partial = scratch; float* coef = scratch + (size_t)B * 2 * C;
+  if (dt == NRD_F32) k_bn_bwd_reduce<float><<<B, 256, 0, st>>>((const float*)g, (const float*)y, ss, saved, partial, C);
+  else k_bn_bwd_reduce<bf16><<<B, 256, 0, st>>>((const bf16*)g, (const bf16*)y, ss, saved, partial, C);
+  LAUNCH_CHECK();
+  k_bn_bwd_finalize<<<1, 256, 0, st>>>(partial, B, B * NRD_PIX, C, gamma, saved, dgamma, dbeta, accumulate, coef);
+  LAUNCH_CHECK();
+  size_t n8 = (size_t)B * NRD_PIX * C / 8;
+  int gr = grid_for(n8, 256);
+  if (dt == NRD_F32) k_bn_bwd_apply<float><<<gr, 256, 0, st>>>((const float*)g, (const float*)y, ss, saved, coef, (float*)dy, n8, C);
+  else k_bn_bwd_apply<bf16><<<gr, 256, 0, st>>>((const bf16*)g, (const bf16*)y, ss, saved, coef, (bf16*)dy, n8, C);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+static int stem_fwd_any(const float* img, const float* wp, const float* bias, void* x0, uint8_t* idx0, int B, int C, int dt, cudaStream_t st) {
+  dim3 grid(4, B); int threads = 64 * (C / 8);
+  size_t smem = (1056 + 27 * C + C) * sizeof(float);
+  if (dt == NRD_F32) k_stem_fwd<float><<<grid, threads, smem, st>>>(img, wp, bias, (float*)x0, idx0, C);
+  else k_stem_fwd<bf16><<<grid, threads, smem, st>>>(img, wp, bias, (bf16*)x0, idx0, C);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+static int stem_bwd_any(const float* img, const void* g0, const void* x0, const uint8_t* idx0, float* dw, float* db, int B, int C,
+                        int dt, float* partial, cudaStream_t st) {
+  int nblk = stem_bwd_blocks(B);
+  size_t smem = (3 * 34 * 35 + (256 / C) * 28 * C) * sizeof(float);
+  if (dt == NRD_F32) k_stem_bwd<float><<<nblk, 256, smem, st>>>(img, (const float*)g0, (const float*)x0, idx0, partial, B, C);
+  else k_stem_bwd<bf16><<<nblk, 256, smem, st>>>(img, (const bf16*)g0, (const bf16*)x0, idx0, partial, B, C);
+  LAUNCH_CHECK();
+  k_stem_bwd_reduce<<<(28 * C + 255) / 256, 256, 0, st>>>(partial, nblk, C, dw, db);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+// ---- per-op C entries -------------------------------------------------------------------
+extern "C" int nrd_pack_conv_weight(const float* w, int C, float* w_fwd, float* w_dgrad, void* stream) {
+  NRD_REQUIRE(valid_C(C) && w, "nrd_pack_conv_weight: bad arguments");
+  k_pack_weights<<<grid_for((size_t)C * C * 9, 256), 256, 0, (cudaStream_t)stream>>>(w, nullptr, nullptr, C, w_fwd, w_dgrad,
+                                                                                     nullptr, nullptr, nullptr, nullptr);
+  // the kernel's index space also covers fc1/conv1; with null outputs those iterations are no-ops
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_conv3x3_fwd(const void* x, const float* w_packed, void* y, int B, int C, int dtype, float* stats_partial,
+                               int* stats_blocks, const void* residual, void* stream) {
+  NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && x && w_packed && y, "nrd_conv3x3_fwd: bad arguments (B=%d C=%d dtype=%d)", B, C, dtype);
+  if (stats_blocks) *stats_blocks = B * 2;
+  return conv_fwd_any(x, w_packed, y, B, C, dtype, stats_partial, residual, (cudaStream_t)stream);
+}
+
+extern "C" size_t nrd_wgrad_partial_bytes(int B, int C) { return (size_t)wgrad_blocks(B) * 9 * C * C * sizeof(float); }
+
+extern "C" int nrd_conv3x3_wgrad(const void* x, const void* dy, float* dw, int B, int C, int dtype, float* partial, void* stream) {
+  NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && x && dy && dw && partial, "nrd_conv3x3_wgrad: bad arguments");
+  NRD_TRY(wgrad_any(x, dy, partial, B, C, dtype, 1, (cudaStream_t)stream));
+  return wgrad_reduce(partial, B, C, dw, (cudaStream_t)stream);
+}
+
+extern "C" int nrd_bn_finalize(const float* partial, int blocks, int count, int C, const float* gamma, const float* beta,
+                               float* saved, float* scale_shift, float* bn_running, int64_t* nbt, void* stream) {
+  NRD_REQUIRE(valid_C(C) && blocks > 0 && count > 1 && partial && gamma && beta && saved && scale_shift, "nrd_bn_finalize: bad arguments");
+  k_bn_finalize<<<1, 256, 0, (cudaStream_t)stream>>>(partial, blocks, count, C, gamma, beta, saved, scale_shift, bn_running, nbt);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_bn_relu_add(const void* y, const void* x, const float* scale_shift, void* out, int B, int C, int dtype, void* stream) {
+  NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && y && x && out && scale_shift, "nrd_bn_relu_add: bad arguments");
+  return bn_relu_add_any(y, x, scale_shift, out, B, C, dtype, (cudaStream_t)stream);
+}
+
+extern "C" size_t nrd_bn_bwd_scratch_bytes(int B, int C) { return ((size_t)B * 2 * C + 3 * C) * sizeof(float); }
+
+extern "C" int nrd_bn_relu_bwd(const void* g, const void* y, const float* scale_shift, const float* saved, const float* gamma, void* dy,
+                               float* dgamma_dbeta, int accumulate, int B, int C, int dtype, float* scratch, void* stream) {
+  NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && g && y && dy && scratch && dgamma_dbeta, "nrd_bn_relu_bwd: bad arguments");
+  return bn_relu_bwd_any(g, y, scale_shift, saved, gamma, dy, dgamma_dbeta, dgamma_dbeta + C, accumulate, B, C, dtype, scratch,
+                         (cudaStream_t)stream);
+}
+
+extern "C" int nrd_stem_fwd(const float* images, const float* conv1_w, const float* conv1_b, void* x0, uint8_t* idx0, int B, int C,
+                            int dtype, void* stream) {
+  NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && images && conv1_w && conv1_b && x0 && idx0, "nrd_stem_fwd: bad arguments");
+  // conv1_w here is the PACKED [27][C] copy (see nrd_plan / k_pack_weights)
+  return stem_fwd_any(images, conv1_w, conv1_b, x0, idx0, B, C, dtype, (cudaStream_t)stream);
+}
+extern "C" size_t nrd_stem_bwd_partial_bytes(int B, int C) { return (size_t)stem_bwd_blocks(B) * 28 * C * sizeof(float); }
+extern "C" int nrd_stem_bwd(const float* images, const void* g0, const void* x0, const uint8_t* idx0, float* dw, float* db, int B, int C,
+                            int dtype, float* partial, void* stream) {
+  NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && images && g0 && x0 && idx0 && dw && db && partial, "nrd_stem_bwd: bad arguments");
+  return stem_bwd_any(images, g0, x0, idx0, dw, db, B, C, dtype, partial, (cudaStream_t)stream);
+}
+
+extern "C" int nrd_maxpool_fwd(const void* x, void* pooled, uint8_t* idx, int B, int C, int dtype, void* stream) {
+  NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && x && pooled && idx, "nrd_maxpool_fwd: bad arguments");
+  size_t n = (size_t)B * 64 * (C / 8);
+  if (dtype == NRD_F32) k_maxpool_fwd<float><<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>((const float*)x, (float*)pooled, idx, B, C);
+  else k_maxpool_fwd<bf16><<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)pooled, idx, B, C);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+extern "C" int nrd_maxpool_bwd(const void* gp, const uint8_t* idx, void* gx, int B, int C, int dtype, void* stream) {
+  NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && gp && gx && idx, "nrd_maxpool_bwd: bad arguments");
+  size_t n = (size_t)B * 64 * (C / 8);
+  if (dtype == NRD_F32) k_maxpool_bwd<float><<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>((const float*)gp, idx, (float*)gx, B, C);
+  else k_maxpool_bwd<bf16><<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)gp, idx, (bf16*)gx, B, C);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_cross_entropy(const float* logits, const int64_t* labels, int B, float grad_scale, float* loss_out, float* dlogits,
+                                 float* row_scratch, void* stream) {
+  NRD_REQUIRE(B > 0 && logits && labels && row_scratch, "nrd_cross_entropy: bad arguments");
+  k_ce_rows<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(logits, labels, B, grad_scale, row_scratch, dlogits);
+  LAUNCH_CHECK();
+  if (loss_out) { k_loss_mean<<<1, 256, 0, (cudaStream_t)stream>>>(row_scratch, B, loss_out); LAUNCH_CHECK(); }
+  return NRD_OK;
+}
+
+extern "C" int nrd_sgd_update(float* params, const float* grads, size_t n, float lr, float inv_world, void* stream) {
+  NRD_REQUIRE(params && grads, "nrd_sgd_update: null pointer");
+  if (n == 0) return NRD_OK;
+  k_sgd<<<grid_for(n, 256, NRD_NUM_SMS * 2), 256, 0, (cudaStream_t)stream>>>(params, grads, n, lr * inv_world);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_gen_batch(float* images, int64_t* labels, int B, uint64_t seed, uint32_t rank, uint64_t step, void* stream) {
+  NRD_REQUIRE(B > 0 && images && labels, "nrd_gen_batch: bad arguments");
+  size_t n = (size_t)B * 768 + B;
+  k_gen_batch<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(images, labels, B, seed, rank, step);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+// ---- plan ---------------------------------------------------------------------------------
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+struct Carver {
+  char* base; size_t off;
+  template <typename U> U* take(size_t bytes) { U* p = base ? reinterpret_cast<U*>(base + off) : nullptr; off += align256(bytes); return p; }
+};
+
+static void carve(nrd_plan* p, char* base, size_t* total) {
+  const int B = p->B, C = p->C, NB = p->NB;
+  const size_t act = p->act_elems * p->esz;
+  Carver cv{base, 0};
+  p->xs = cv.take<char>(act * (NB + 1));
+  p->ys = cv.take<char>(act * NB);
+  p->dy = cv.take<char>(act);
+  p->dxa = cv.take<char>(act);
+  p->dxb = cv.take<char>(act);
+  p->idx0 = cv.take<uint8_t>(p->act_elems);
+  p->pooled = cv.take<char>(act / 4);
+  p->idx2 = cv.take<uint8_t>(p->act_elems / 4);
+  p->h1 = cv.take<float>((size_t)B * NRD_FC1_OUT * 4);
+  p->dh1 = cv.take<float>((size_t)B * NRD_FC1_OUT * 4);
+  p->dlogits = cv.take<float>((size_t)B * NRD_NCLS * 4);
+  p->loss_rows = cv.take<float>((size_t)B * 4);
+  p->saved_stats = cv.take<float>((size_t)NB * 2 * C * 4);
+  p->scale_shift = cv.take<float>((size_t)NB * 2 * C * 4);
+  p->stats_partial = cv.take<float>((size_t)(B * 2 > 1024 ? B * 2 : 1024) * 2 * C * 4);
+  p->bnbwd_scratch = cv.take<float>(nrd_bn_bwd_scratch_bytes(B, C));
+  p->wgrad_partial = cv.take<float>(nrd_wgrad_partial_bytes(B, C));
+  p->stem_partial = cv.take<float>(nrd_stem_bwd_partial_bytes(B, C));
+  p->w_fwd = cv.take<float>((size_t)9 * C * C * 4);
+  p->w_dgrad = cv.take<float>((size_t)9 * C * C * 4);
+  p->w1p = cv.take<float>((size_t)NRD_FC1_OUT * 64 * C * 4);
+  p->conv1_wp = cv.take<float>((size_t)27 * C * 4);
+  p->wtc_fwd = cv.take<bf16>((size_t)9 * C * C * 2);
+  p->wtc_dgrad = cv.take<bf16>((size_t)9 * C * C * 2);
+  *total = cv.off;
+}
+
+static int fill_shape(nrd_plan* p, int B, int C, int NB, int dtype) {
+  NRD_REQUIRE(valid_C(C), "C (n_chans1) must be 32 or 64, got %d", C);
+  NRD_REQUIRE(valid_dt(dtype), "dtype must be NRD_F32 or NRD_BF16, got %d", dtype);
+  NRD_REQUIRE(B >= 1 && B <= 8192, "per-rank batch must be in [1, 8192], got %d", B);
+  NRD_REQUIRE(NB >= 1 && NB <= 31, "n_blocks must be in [1, 31], got %d", NB);
+  p->B = B; p->C = C; p->NB = NB; p->dtype = dtype;
+  p->esz = dtype == NRD_F32 ? 4 : 2;
+  p->act_elems = (size_t)B * NRD_PIX * C;
+  return nrd_param_offsets(C, p->off);
+}
+
+extern "C" size_t nrd_workspace_bytes(int B, int C, int NB, int dtype) {
+  nrd_plan tmp; memset(&tmp, 0, sizeof(tmp));
+  if (fill_shape(&tmp, B, C, NB, dtype) != NRD_OK) return 0;
+  size_t total = 0; carve(&tmp, nullptr, &total);
+  return total;
+}
+
+extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB, int dtype, void* workspace, size_t workspace_bytes,
+                               float* params, float* grads, float* bn_running, int64_t* nbt) {
+  NRD_REQUIRE(out && workspace && params && grads && bn_running && nbt, "nrd_plan_create: null pointer");
+  NRD_REQUIRE(((uintptr_t)workspace & 255) == 0, "nrd_plan_create: workspace must be 256-byte aligned");
+  nrd_plan* p = new nrd_plan; memset(p, 0, sizeof(*p));
+  int r = fill_shape(p, B, C, NB, dtype);
+  if (r != NRD_OK) { delete p; return r; }
+  size_t total = 0; carve(p, (char*)workspace, &total);
+  if (total > workspace_bytes) { delete p; nrd_set_error("workspace too small: need %zu bytes, got %zu", total, workspace_bytes); return NRD_EINVAL; }
+  p->device = device; p->params = params; p->grads = grads; p->bn_running = bn_running; p->nbt = nbt;
+  p->conv_impl = NRD_CONV_CUDA_CORE;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
+  if (dtype == NRD_BF16) {
+    r = nrd_tc_plan_init(p);
+    if (r != NRD_OK) { delete p; return r; }   // no silent fallback: the bf16 product path IS the tcgen05 path
+    if (p->tc_ready) p->conv_impl = NRD_CONV_TCGEN05;
+  }
+  *out = p;
+  return NRD_OK;
+}
+
+extern "C" int nrd_plan_destroy(nrd_plan* p) { delete p; return NRD_OK; }
+
+extern "C" int nrd_plan_set_conv_impl(nrd_plan* p, int impl) {
+  NRD_REQUIRE(p, "null plan");
+  NRD_REQUIRE(impl == NRD_CONV_CUDA_CORE || (impl == NRD_CONV_TCGEN05 && p->dtype == NRD_BF16 && p->tc_ready),
+              "conv impl %d not available for this plan (dtype=%d)", impl, p->dtype);
+  p->conv_impl = impl;
+  return NRD_OK;
+}
+
+extern "C" int nrd_plan_conv_impl(const nrd_plan* p) { return p ? p->conv_impl : NRD_EINVAL; }
+
+extern "C" int nrd_plan_tensor(nrd_plan* p, int what, int k, void** ptr, size_t* bytes) {
+  NRD_REQUIRE(p && ptr && bytes, "null pointer");
+  const size_t act = p->act_elems * p->esz;
+  switch (what) {
+    case 0: NRD_REQUIRE(k >= 0 && k <= p->NB, "k out of range"); *ptr = p->xs + act * k; *bytes = act; break;
+    case 1: NRD_REQUIRE(k >= 0 && k < p->NB, "k out of range"); *ptr = p->ys + act * k; *bytes = act; break;
+    case 2: *ptr = p->dy; *bytes = act; break;
+    case 3: *ptr = p->pooled; *bytes = act / 4; break;
+    case 4: NRD_REQUIRE(k >= 0 && k < p->NB, "k out of range"); *ptr = p->saved_stats + (size_t)k * 2 * p->C; *bytes = 2 * p->C * 4; break;
+    case 5: *ptr = p->dxa; *bytes = act; break;
+    default: nrd_set_error("nrd_plan_tensor: unknown selector %d", what); return NRD_EINVAL;
+  }
+  return NRD_OK;
+}
+
+#define PRM(i) (p->params + p->off[i])
+#define GRD(i) (p->grads + p->off[i])
+enum { P_C1W = 0, P_C1B, P_RBW, P_BNG, P_BNB, P_FC1W, P_FC1B, P_FC2W, P_FC2B };
+
+extern "C" int nrd_pack_weights(nrd_plan* p, void* stream) {
+  NRD_REQUIRE(p, "null plan");
+  NRD_CHECK_CUDA(cudaSetDevice(p->device));
+  const int C = p->C;
+  size_t n = (size_t)C * C * 9 + (size_t)NRD_FC1_OUT * 64 * C + C * 27;
+  k_pack_weights<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(PRM(P_RBW), PRM(P_FC1W), PRM(P_C1W), C, p->w_fwd, p->w_dgrad,
+                                                                     p->wtc_fwd, p->wtc_dgrad, p->w1p, p->conv1_wp);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int training, void* stream) {
+  NRD_REQUIRE(p && images && logits, "nrd_forward: null pointer");
+  NRD_CHECK_CUDA(cudaSetDevice(p->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int B = p->B, C = p->C, NB = p->NB, dt = p->dtype;
+  const size_t act = p->act_elems * p->esz;
+  p->images_last = images;
+  NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st));
+  if (!training) { k_bn_eval_coeffs<<<1, 64, 0, st>>>(p->bn_running, PRM(P_BNG), PRM(P_BNB), C, p->scale_shift); LAUNCH_CHECK(); }
+  for (int k = 0; k < NB; ++k) {
+    char* xk = p->xs + act * k; char* yk = p->ys + act * k; char* xn = p->xs + act * (k + 1);
+    float* ss = training ? p->scale_shift + (size_t)k * 2 * C : p->scale_shift;
+    int blocks = B * 2;
+    if (p->conv_impl == NRD_CONV_TCGEN05) { NRD_TRY(nrd_tc_conv_fwd(p, k, st)); blocks = nrd_tc_stats_blocks(p); }
+    else NRD_TRY(conv_fwd_any(xk, p->w_fwd, yk, B, C, dt, training ? p->stats_partial : nullptr, nullptr, st));
+    if (training) {
+      k_bn_finalize<<<1, 256, 0, st>>>(p->stats_partial, blocks, B * NRD_PIX, C, PRM(P_BNG), PRM(P_BNB),
+                                       p->saved_stats + (size_t)k * 2 * C, ss, p->bn_running, p->nbt);
+      LAUNCH_CHECK();
+    }
+    NRD_TRY(bn_relu_add_any(yk, xk, ss, xn, B, C, dt, st));
+  }
+  NRD_TRY(nrd_maxpool_fwd(p->xs + act * NB, p->pooled, p->idx2, B, C, dt, stream));
+  const int K = 64 * C;
+  if (dt == NRD_F32) k_fc1_fwd<float><<<(B + 7) / 8, 256, 0, st>>>((const float*)p->pooled, p->w1p, PRM(P_FC1B), p->h1, B, K);
+  else k_fc1_fwd<bf16><<<(B + 7) / 8, 256, 0, st>>>((const bf16*)p->pooled, p->w1p, PRM(P_FC1B), p->h1, B, K);
+  LAUNCH_CHECK();
+  k_fc2_fwd<<<(B * NRD_NCLS + 255) / 256, 256, 0, st>>>(p->h1, PRM(P_FC2W), PRM(P_FC2B), logits, B);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
+  NRD_REQUIRE(p && dlogits, "nrd_backward: null pointer");
+  NRD_CHECK_CUDA(cudaSetDevice(p->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int B = p->B, C = p->C, NB = p->NB, dt = p->dtype;
+  const size_t act = p->act_elems * p->esz;
+  // head
+  k_fc2_bwd<<<(B * NRD_FC1_OUT + 255) / 256, 256, 0, st>>>(dlogits, PRM(P_FC2W), p->h1, p->dh1, B);
+  LAUNCH_CHECK();
+  k_head_wgrad<<<1, 384, 0, st>>>(dlogits, p->h1, p->dh1, B, GRD(P_FC2W), GRD(P_FC2B), GRD(P_FC1B));
+  LAUNCH_CHECK();
+  if (dt == NRD_F32) k_fc1_wgrad<float><<<C, 256, 0, st>>>((const float*)p->pooled, p->dh1, GRD(P_FC1W), B, C);
+  else k_fc1_wgrad<bf16><<<C, 256, 0, st>>>((const bf16*)p->pooled, p->dh1, GRD(P_FC1W), B, C);
+  LAUNCH_CHECK();
+  char* g = p->dxa; char* gn = p->dxb;
+  const int K = 64 * C;
+  if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<B * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (float*)g, B, C);
+  else k_fc1_dgrad_unpool<bf16><<<B * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (bf16*)g, B, C);
+  LAUNCH_CHECK();
+  // residual blocks, last to first; the shared block's grads accumulate over the NB applications
+  for (int k = NB - 1; k >= 0; --k) {
+    const int first = (k == NB - 1);
+    char* xk = p->xs + act * k; char* yk = p->ys + act * k;
+    NRD_TRY(bn_relu_bwd_any(g, yk, p->scale_shift + (size_t)k * 2 * C, p->saved_stats + (size_t)k * 2 * C, PRM(P_BNG), p->dy,
+                            GRD(P_BNG), GRD(P_BNB), !first, B, C, dt, p->bnbwd_scratch, st));
+    if (p->conv_impl == NRD_CONV_TCGEN05) {
+      NRD_TRY(nrd_tc_conv_wgrad(p, k, first, st));
+      NRD_TRY(nrd_tc_conv_dgrad(p, g, gn, st));
+    } else {
+      NRD_TRY(wgrad_any(xk, p->dy, p->wgrad_partial, B, C, dt, first, st));
+      NRD_TRY(conv_fwd_any(p->dy, p->w_dgrad, gn, B, C, dt, nullptr, g, st));
+    }
+    char* t = g; g = gn; gn = t;
+  }
+  NRD_TRY(wgrad_reduce(p->wgrad_partial, B, C, GRD(P_RBW), st));
+  NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st));
+  return NRD_OK;
+}
+
+extern "C" int nrd_train_step(nrd_plan* p, const float* images, const int64_t* labels, float lr, float* logits, float* loss_out,
+                              void* stream) {
+  NRD_REQUIRE(p && images && labels && logits && loss_out, "nrd_train_step: null pointer");
+  NRD_TRY(nrd_forward(p, images, logits, 1, stream));
+  NRD_TRY(nrd_cross_entropy(logits, labels, p->B, 1.0f, loss_out, p->dlogits, p->loss_rows, stream));
+  NRD_TRY(nrd_backward(p, p->dlogits, stream));
+  NRD_TRY(nrd_sgd_update(p->params, p->grads, (size_t)p->off[9], lr, 1.0f, stream));
+  return nrd_pack_weights(p, stream);
+}
+
+// Run ONE internal op of the step on the plan's buffers (bench.py times each kernel class with CUDA
+// events on the launching stream; ncu captures use the same entry).  Inputs are whatever the last
+// nrd_forward / nrd_backward left in the workspace.
+extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
+  NRD_REQUIRE(p && k >= 0 && k < p->NB, "nrd_plan_run_op: bad arguments");
+  NRD_CHECK_CUDA(cudaSetDevice(p->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int B = p->B, C = p->C, dt = p->dtype;
+  const size_t act = p->act_elems * p->esz;
+  char* xk = p->xs + act * k; char* yk = p->ys + act * k;
+  float* ss = p->scale_shift + (size_t)k * 2 * C; float* sv = p->saved_stats + (size_t)k * 2 * C;
+  switch (op) {
+    case NRD_OP_CONV_FWD:
+      if (p->conv_impl == NRD_CONV_TCGEN05) return nrd_tc_conv_fwd(p, k, st);
+      return conv_fwd_any(xk, p->w_fwd, yk, B, C, dt, p->stats_partial, nullptr, st);
+    case NRD_OP_BN_APPLY: return bn_relu_add_any(yk, xk, ss, p->dxb, B, C, dt, st);
+    case NRD_OP_BN_BWD: {
+      // dgamma/dbeta go to a sink (h1 is dead after backward and holds >= 2C floats) so profiling leaves the grads alone
+      return bn_relu_bwd_any(p->dxa, yk, ss, sv, PRM(P_BNG), p->dy, p->h1, p->h1 + C, 0, B, C, dt, p->bnbwd_scratch, st);
+    }
+    case NRD_OP_WGRAD:
+      if (p->conv_impl == NRD_CONV_TCGEN05) return nrd_tc_conv_wgrad(p, k, 1, st);
+      return wgrad_any(xk, p->dy, p->wgrad_partial, B, C, dt, 1, st);
+    case NRD_OP_DGRAD:
+      if (p->conv_impl == NRD_CONV_TCGEN05) return nrd_tc_conv_dgrad(p, p->dxa, p->dxb, st);
+      return conv_fwd_any(p->dy, p->w_dgrad, p->dxb, B, C, dt, nullptr, p->dxa, st);
+    case NRD_OP_STEM_FWD:
+      NRD_REQUIRE(p->images_last, "run a forward first");
+      return stem_fwd_any(p->images_last, p->conv1_wp, PRM(P_C1B), p->dxb, p->idx0, B, C, dt, st);
+    case NRD_OP_STEM_BWD:
+      NRD_REQUIRE(p->images_last, "run a forward first");
+      return stem_bwd_any(p->images_last, p->dxa, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st);
+    default: nrd_set_error("nrd_plan_run_op: unknown op %d", op); return NRD_EINVAL;
+  }
+}

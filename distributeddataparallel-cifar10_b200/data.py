@@ -1,0 +1,64 @@
+"""On-device synthetic CIFAR-10-shaped loader (replaces torchvision CIFAR10 + DataLoader of
+main.py:53-61 for benchmarking: there is no dataset on the box).  Iterating yields
+`(imgs fp32 [B,3,32,32], labels int64 [B])` already on the device, so `.to(rank)` is free."""
+import numpy as np
+import torch
+
+from ._lib import lib, check
+from .engine import _stream_ptr
+
+
+class SyntheticCifar10Loader:
+    def __init__(self, batch_size=32, steps_per_epoch=196, device="cuda", seed=1234, rank=0):
+        self.batch_size, self.steps, self.seed, self.rank = batch_size, steps_per_epoch, seed, rank
+        self.device = torch.device(device)
+        self._step = 0
+
+    def __len__(self):
+        return self.steps
+
+    def batch(self, step: int):
+        imgs = torch.empty(self.batch_size, 3, 32, 32, dtype=torch.float32, device=self.device)
+        labels = torch.empty(self.batch_size, dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib.nrd_gen_batch(imgs.data_ptr(), labels.data_ptr(), self.batch_size, self.seed, self.rank, step, _stream_ptr()),
+                  "nrd_gen_batch")
+        return imgs, labels
+
+    def __iter__(self):
+        for _ in range(self.steps):
+            yield self.batch(self._step)
+            self._step += 1
+
+
+# ---- host restatement of the generator (tests compare the device batch with it) -------------
+def _philox4x32_10(c0, c1, c2, c3, k0, k1):
+    M0, M1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57)
+    c0, c1, c2, c3 = (np.asarray(v, dtype=np.uint64) for v in (c0, c1, c2, c3))
+    k0, k1 = np.uint64(k0), np.uint64(k1)
+    mask = np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        p0, p1 = M0 * c0, M1 * c2
+        hi0, lo0, hi1, lo1 = p0 >> np.uint64(32), p0 & mask, p1 >> np.uint64(32), p1 & mask
+        c0, c1, c2, c3 = (hi1 ^ c1 ^ k0) & mask, lo1, (hi0 ^ c3 ^ k1) & mask, lo0
+        k0, k1 = (k0 + np.uint64(0x9E3779B9)) & mask, (k1 + np.uint64(0xBB67AE85)) & mask
+    return c0, c1, c2, c3
+
+
+def host_batch(batch_size, seed=1234, rank=0, step=0):
+    """numpy restatement of k_gen_batch: same counters, same Box-Muller."""
+    n4 = batch_size * 768
+    k0, k1 = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
+    i = np.arange(n4, dtype=np.uint64)
+    z = np.zeros_like(i)
+    r = _philox4x32_10(i, z + np.uint64(rank), z + np.uint64(step & 0xFFFFFFFF), z + np.uint64(step >> 32), k0, k1)
+    u = [(x >> np.uint64(8)).astype(np.float32) for x in r]
+    u0, u1 = (u[0] + np.float32(1)) * np.float32(1 / 16777216), u[1] * np.float32(1 / 16777216)
+    u2, u3 = (u[2] + np.float32(1)) * np.float32(1 / 16777216), u[3] * np.float32(1 / 16777216)
+    ra, rb = np.sqrt(np.float32(-2) * np.log(u0)), np.sqrt(np.float32(-2) * np.log(u2))
+    a0, a1 = np.float32(2 * np.pi) * u1, np.float32(2 * np.pi) * u3
+    img = np.stack([ra * np.cos(a0), ra * np.sin(a0), rb * np.cos(a1), rb * np.sin(a1)], axis=1).astype(np.float32)
+    b = np.arange(batch_size, dtype=np.uint64)
+    zb = np.zeros_like(b)
+    rl = _philox4x32_10(b, zb + np.uint64(rank | 0x80000000), zb + np.uint64(step & 0xFFFFFFFF), zb + np.uint64(step >> 32), k0, k1)
+    return img.reshape(batch_size, 3, 32, 32), (rl[0] % np.uint64(10)).astype(np.int64)

@@ -1,0 +1,90 @@
+"""Whole-step CUDA graph: forward, loss, backward, gradient exchange, fused mean+SGD and weight
+re-pack replayed as ONE graph launch (the ~70 us roofline step cannot afford ~60 separate
+launches from Python).  This is main.py:34-39 for one rank."""
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from ._lib import lib, check
+from .engine import _stream_ptr
+
+
+class TrainStep:
+    """step = TrainStep(model_or_ddp, batch_size, lr); loss = step(imgs, labels)
+
+    `imgs`/`labels` may be device tensors (copied device-to-device into the graph's static inputs)
+    or pinned host tensors (async H2D on the same stream).  Returns the device loss tensor of the
+    step (read it with .item() only when you need the number, main.py:41)."""
+
+    def __init__(self, model, batch_size: int, lr: float = 1e-2, use_graph: bool = True):
+        from .parallel import DistributedDataParallel
+        self.ddp = model if isinstance(model, DistributedDataParallel) else None
+        self.module = model.module if self.ddp is not None else model
+        self.eng = self.module.engine
+        self.B, self.lr = batch_size, lr
+        dev = next(self.module.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("TrainStep needs the model on a CUDA device")
+        self.device = dev
+        self.world = self.ddp.world_size if self.ddp is not None else 1
+        self.imgs = torch.zeros(batch_size, 3, 32, 32, dtype=torch.float32, device=dev)
+        self.labels = torch.zeros(batch_size, dtype=torch.int64, device=dev)
+        self.logits = torch.empty(batch_size, 10, dtype=torch.float32, device=dev)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.plan = self.eng.plan(batch_size, dev)
+        self.eng.ensure_packed(self.plan)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.kernel_launches = None
+        if use_graph:
+            self._capture()
+
+    # the step body, launched on the current stream
+    def _body(self):
+        eng, pl, st = self.eng, self.plan, _stream_ptr()
+        if self.world > 1:
+            self.ddp._sync_buffers()                                   # C2
+        check(lib.nrd_forward(pl.handle, self.imgs.data_ptr(), self.logits.data_ptr(), 1, st), "nrd_forward")
+        check(lib.nrd_cross_entropy(self.logits.data_ptr(), self.labels.data_ptr(), self.B, 1.0, self.loss.data_ptr(),
+                                    pl.dlogits.data_ptr(), pl.loss_rows.data_ptr(), st), "nrd_cross_entropy")
+        check(lib.nrd_backward(pl.handle, pl.dlogits.data_ptr(), st), "nrd_backward")
+        if self.world > 1:
+            body, head = eng.bucket_slices()
+            for lo, hi in (head, body):
+                dist.all_reduce(eng.flat_grads[lo:hi], op=dist.ReduceOp.SUM, group=self.ddp.process_group)   # C3
+        # fused mean + SGD (K16), then re-derive the packed weight copies
+        check(lib.nrd_sgd_update(eng.flat_params.data_ptr(), eng.flat_grads.data_ptr(), eng.offsets[9], self.lr,
+                                 1.0 / self.world, st), "nrd_sgd_update")
+        check(lib.nrd_pack_weights(pl.handle, st), "nrd_pack_weights")
+
+    def _capture(self):
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        # snapshot state: warm-up steps on a side stream must not change the model
+        keep = (self.eng.flat_params.clone(), self.eng.bn_running.clone(), self.eng.nbt.clone())
+        with torch.cuda.stream(s):
+            for _ in range(2):
+                self._body()
+        torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, stream=s):
+            self._body()
+        self.eng.flat_params.copy_(keep[0]); self.eng.bn_running.copy_(keep[1]); self.eng.nbt.copy_(keep[2])
+        check(lib.nrd_pack_weights(self.plan.handle, _stream_ptr()), "nrd_pack_weights")
+        torch.cuda.synchronize(self.device)
+
+    def __call__(self, imgs: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        self.imgs.copy_(imgs, non_blocking=True)
+        self.labels.copy_(labels, non_blocking=True)
+        return self.run()
+
+    def run(self) -> torch.Tensor:
+        """Replay on the static inputs already in `self.imgs` / `self.labels`."""
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._body()
+        self.eng.weights_epoch += 1
+        self.plan.packed_version = self.eng._weights_version()
+        return self.loss

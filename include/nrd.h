@@ -1,0 +1,162 @@
+/* nrd.h -- C ABI of libnrd.so, the B200 (sm_100a) NetResDeep data-parallel training step.
+ *
+ * The reference (BaamPark/DistributedDataParallel-Cifar10) has no FFI: its hot path is a
+ * chain of PyTorch calls.  This header is the boundary a maintainer would bind instead
+ * (ctypes stub in INTEGRATION.md); each entry names the reference call site it replaces
+ * (file:line relative to the reference tree).
+ *
+ * Conventions
+ *  - every entry returns 0 on success or a negative NRD_E* code; the message is in
+ *    nrd_last_error() (thread-local);
+ *  - all pointers are DEVICE pointers unless said otherwise; the library never allocates
+ *    or frees caller tensors -- scratch comes from a caller-provided workspace whose size
+ *    nrd_workspace_bytes() reports;
+ *  - every launch goes to the `stream` argument (a cudaStream_t passed as void*), is
+ *    asynchronous to the host and capturable in a CUDA graph; entries may be called from
+ *    any host thread (autograd runs backward on its own thread) -- they cudaSetDevice()
+ *    to the plan's device first;
+ *  - activations are NHWC (pixels x channels); `dtype` is the activation storage type and
+ *    the tensor-core operand type (NRD_F32: validation mode, fp32 everywhere, CUDA cores;
+ *    NRD_BF16: bf16 storage + tcgen05 tensor cores, fp32 accumulate).  Parameters,
+ *    gradients, BN statistics and the loss are always fp32 in PyTorch's own layouts
+ *    (conv OIHW, fc1 columns in (c,h,w) order) so they alias the nn.Module's tensors.
+ */
+#ifndef NRD_H_
+#define NRD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NRD_F32 0
+#define NRD_BF16 1
+
+#define NRD_OK 0
+#define NRD_EINVAL (-1)   /* bad argument (shape, dtype, null pointer, workspace too small) */
+#define NRD_ECUDA (-2)    /* a CUDA runtime/driver call failed */
+#define NRD_EUNSUPPORTED (-3)
+
+/* conv implementation selector for NRD_BF16 plans (nrd_plan_set_conv_impl) */
+#define NRD_CONV_CUDA_CORE 0  /* direct conv on CUDA cores (also the only NRD_F32 path) */
+#define NRD_CONV_TCGEN05 1    /* implicit GEMM on tcgen05 tensor cores, TMA-staged NHWC tiles */
+
+typedef struct nrd_plan nrd_plan; /* opaque: shapes + carved workspace + TMA descriptors */
+
+const char* nrd_last_error(void);
+int nrd_version(void);
+
+/* ---- flat parameter vector --------------------------------------------------------------
+ * The 9 unique parameter tensors of NetResDeep (model/resnet.py:9-13,27-28) live in ONE flat
+ * fp32 vector (gradients in a second one of the same shape) so that the bucketed allreduce
+ * and the fused update need no gather.  Order: conv1.weight, conv1.bias, resblock conv.weight,
+ * bn.weight, bn.bias  [= bucket "body"]  then fc1.weight, fc1.bias, fc2.weight, fc2.bias
+ * [= bucket "head"].  offsets[i] is the first float of tensor i, offsets[9] the total. */
+int nrd_param_offsets(int C, int64_t offsets[10]);
+
+/* ---- plan -------------------------------------------------------------------------------- */
+size_t nrd_workspace_bytes(int B, int C, int NB, int dtype);
+/* params/grads: flat fp32 vectors (above).  bn_running: [2*C] fp32 = running_mean|running_var,
+ * nbt: int64 scalar (BatchNorm2d buffers, model/resnet.py:28).  workspace must be 256-B aligned. */
+int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB, int dtype,
+                    void* workspace, size_t workspace_bytes,
+                    float* params, float* grads, float* bn_running, int64_t* nbt);
+int nrd_plan_destroy(nrd_plan* plan);
+int nrd_plan_set_conv_impl(nrd_plan* plan, int impl);
+int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
+/* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
+ * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch */
+int nrd_plan_tensor(nrd_plan* plan, int what, int k, void** ptr, size_t* bytes);
+
+/* Re-derive the packed weight copies (tap-major / transposed / bf16 / NHWC-ordered fc1) from the
+ * fp32 master parameters.  Must run after anything that changed the parameters
+ * (optimizer.step() main.py:39, load_state_dict, the DDP ctor broadcast main.py:63). */
+int nrd_pack_weights(nrd_plan* plan, void* stream);
+
+/* ---- whole-model entries ------------------------------------------------------------------
+ * nrd_forward  = NetResDeep.forward (model/resnet.py:15-22) in training mode: batch-stat BN,
+ *   running-stat EMA applied NB times, nbt += NB; keeps x_k, y_k, pool indices for backward.
+ *   images: fp32 NCHW [B,3,32,32] (what main.py:33 moves to the device); logits: fp32 [B,10].
+ *   training=0 gives eval-mode BN (running statistics, no side effects).
+ * nrd_cross_entropy = nn.CrossEntropyLoss() forward AND its gradient (main.py:28,35,38):
+ *   loss = mean_b(-log softmax(logits)[label]); dlogits = (softmax - onehot)/B * grad_scale.
+ * nrd_backward = loss.backward() below the logits (main.py:38): overwrites the flat grads.
+ * nrd_sgd_update = the DDP mean (main.py:63; c10d reducer divides by world size) fused with
+ *   optimizer.step() of optim.SGD(lr) (main.py:27,39): p <- p - lr * inv_world * g, n floats.
+ * nrd_train_step = main.py:34-39 for one rank without the allreduce: forward, loss, backward,
+ *   update (inv_world = 1) and weight re-pack; loss_out: fp32 scalar on the device. */
+int nrd_forward(nrd_plan* plan, const float* images, float* logits, int training, void* stream);
+int nrd_cross_entropy(const float* logits, const int64_t* labels, int B, float grad_scale,
+                      float* loss_out, float* dlogits, float* row_scratch /* [B] */, void* stream);
+int nrd_backward(nrd_plan* plan, const float* dlogits, void* stream);
+int nrd_sgd_update(float* params, const float* grads, size_t n, float lr, float inv_world, void* stream);
+int nrd_train_step(nrd_plan* plan, const float* images, const int64_t* labels, float lr,
+                   float* logits, float* loss_out, void* stream);
+
+/* ---- synthetic CIFAR-shaped batch (replaces the DataLoader of main.py:53-61) ---------------
+ * images[b,c,h,w] ~ N(0,1) fp32 NCHW, labels ~ U{0..9} int64; counter-based (Philox-4x32-10
+ * keyed by seed, counter = (element, rank, step)), reproducible on the CPU. */
+int nrd_gen_batch(float* images, int64_t* labels, int B, uint64_t seed, uint32_t rank, uint64_t step,
+                  void* stream);
+
+/* ---- per-op entries (unit parity tests; the Python autograd Functions of single ops) ------
+ * T = plan dtype is replaced by an explicit `dtype`; tensors NHWC.  H = W = 16 for the block
+ * convolution (the only resolution the ResBlock runs at, model/resnet.py:16-17). */
+/* conv3x3 pad 1, no bias (ResBlock.conv, model/resnet.py:34).  w_packed: fp32 [9][Cin=C][Cout=C]
+ * (tap-major, from nrd_pack_conv_weight).  stats_partial (optional): [blocks][2][C] per-CTA sum
+ * and sum of squares of the fp32 outputs; *stats_blocks receives the CTA count (host pointer). */
+int nrd_pack_conv_weight(const float* w_oihw, int C, float* w_fwd /*[9][C][C]*/, float* w_dgrad /*[9][C][C]*/, void* stream);
+int nrd_conv3x3_fwd(const void* x, const float* w_packed, void* y, int B, int C, int dtype,
+                    float* stats_partial, int* stats_blocks, const void* residual, void* stream);
+/* wgrad: dW[co][ci][ky][kx] (OIHW fp32, OVERWRITTEN) = sum_p dy[p][co] * x[p+tap][ci].
+ * partial: scratch of nrd_wgrad_partial_bytes(B, C). */
+size_t nrd_wgrad_partial_bytes(int B, int C);
+int nrd_conv3x3_wgrad(const void* x, const void* dy, float* dw_oihw, int B, int C, int dtype,
+                      float* partial, void* stream);
+/* BatchNorm2d training forward pieces (model/resnet.py:35-37): finalize turns the per-CTA
+ * partials into mean/invstd (saved: [2C]) and scale/shift ([2C]), and applies the running-stat
+ * EMA (momentum 0.1, unbiased variance) when bn_running != NULL; apply computes
+ * out = relu(y*scale+shift) + x. */
+int nrd_bn_finalize(const float* stats_partial, int blocks, int count, int C, const float* gamma,
+                    const float* beta, float* saved_mean_invstd, float* scale_shift,
+                    float* bn_running, int64_t* nbt, void* stream);
+int nrd_bn_relu_add(const void* y, const void* x, const float* scale_shift, void* out, int B, int C,
+                    int dtype, void* stream);
+/* BatchNorm2d + ReLU + residual backward (native_batch_norm_backward + threshold_backward):
+ * given g = dL/d(out), y, scale_shift and saved stats: dgamma/dbeta (ACCUMULATED into
+ * dgamma_dbeta [2C] when accumulate != 0) and dy.  scratch: [blocks][2][C] + [2C] floats. */
+size_t nrd_bn_bwd_scratch_bytes(int B, int C);
+int nrd_bn_relu_bwd(const void* g, const void* y, const float* scale_shift, const float* saved_mean_invstd,
+                    const float* gamma, void* dy, float* dgamma_dbeta, int accumulate, int B, int C,
+                    int dtype, float* scratch, void* stream);
+/* stem: max_pool2d(relu(conv1(x)),2) (model/resnet.py:16).  x0: NHWC [B,16,16,C], idx0: u8. */
+int nrd_stem_fwd(const float* images, const float* conv1_w, const float* conv1_b, void* x0, uint8_t* idx0,
+                 int B, int C, int dtype, void* stream);
+size_t nrd_stem_bwd_partial_bytes(int B, int C);
+int nrd_stem_bwd(const float* images, const void* g0, const void* x0, const uint8_t* idx0, float* dconv1_w,
+                 float* dconv1_b, int B, int C, int dtype, float* partial, void* stream);
+/* max_pool2d(out,2) at 16x16 -> 8x8 (model/resnet.py:18) and its gradient scatter */
+int nrd_maxpool_fwd(const void* x, void* pooled, uint8_t* idx, int B, int C, int dtype, void* stream);
+int nrd_maxpool_bwd(const void* gpooled, const uint8_t* idx, void* gx, int B, int C, int dtype, void* stream);
+
+/* ---- measurement hooks (bench.py / ncu; no reference counterpart: the reference has no profiler) ---
+ * nrd_launch_count: kernels launched by this library in this process so far (graph replays do not
+ * pass through the library and are counted by the caller as captured launches x replays).
+ * nrd_plan_run_op: launch ONE kernel class of the step on the plan's buffers, for CUDA-event timing
+ * on the launching stream.  Needs a preceding nrd_forward + nrd_backward on the plan. */
+#define NRD_OP_CONV_FWD 0  /* y_k = conv3x3(x_k) + BN partial sums      (model/resnet.py:34) */
+#define NRD_OP_BN_APPLY 1  /* relu(bn(y_k)) + x_k                        (model/resnet.py:35-37) */
+#define NRD_OP_BN_BWD 2    /* BN+ReLU backward: reduce, finalize, apply  (loss.backward, main.py:38) */
+#define NRD_OP_WGRAD 3     /* conv weight gradient partials */
+#define NRD_OP_DGRAD 4     /* conv input gradient + residual */
+#define NRD_OP_STEM_FWD 5  /* conv1 + relu + pool                        (model/resnet.py:16) */
+#define NRD_OP_STEM_BWD 6
+unsigned long long nrd_launch_count(void);
+int nrd_plan_run_op(nrd_plan* plan, int op, int k, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NRD_H_ */
