@@ -1101,6 +1101,9 @@ extern "C" int nrd_plan_tensor(nrd_plan* p, int what, int k, void** ptr, size_t*
     case 3: *ptr = p->pooled; *bytes = act / 4; break;
     case 4: NRD_REQUIRE(k >= 0 && k < p->NB, "k out of range"); *ptr = p->saved_stats + (size_t)k * 2 * p->C; *bytes = 2 * p->C * 4; break;
     case 5: *ptr = p->dxa; *bytes = act; break;
+    case 6: *ptr = p->dxb; *bytes = act; break;
+    case 7: *ptr = p->wgrad_partial; *bytes = nrd_wgrad_partial_bytes(p->B, p->C); break;
+    case 8: *ptr = p->stats_partial; *bytes = (size_t)(p->B * 2 > 1024 ? p->B * 2 : 1024) * 2 * p->C * 4; break;
     default: nrd_set_error("nrd_plan_tensor: unknown selector %d", what); return NRD_EINVAL;
   }
   return NRD_OK;

@@ -67,7 +67,8 @@ int nrd_plan_destroy(nrd_plan* plan);
 int nrd_plan_set_conv_impl(nrd_plan* plan, int impl);
 int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
 /* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
- * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch */
+ * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch (ping),
+ * 6 = dx scratch (pong), 7 = wgrad per-CTA partials [ctas][9][C][C], 8 = BN-stat per-CTA partials [ctas][2][C] */
 int nrd_plan_tensor(nrd_plan* plan, int what, int k, void** ptr, size_t* bytes);
 
 /* Re-derive the packed weight copies (tap-major / transposed / bf16 / NHWC-ordered fc1) from the

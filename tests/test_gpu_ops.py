@@ -11,6 +11,7 @@ import torch
 import torch.nn.functional as F
 
 from util import *  # noqa: F401,F403
+from ddp_cifar10_b200 import _lib
 
 pytestmark = pytest.mark.gpu
 TOL = {"fp32": 1e-5, "bf16": 1e-2}
@@ -24,7 +25,9 @@ def _rnd(x, dt):
 def _pack_conv(w):
     Cc = w.shape[0]
     wf = torch.empty(9 * Cc * Cc, device=DEV); wd = torch.empty_like(wf)
-    check(lib.nrd_pack_conv_weight(dev_f32(w).data_ptr(), Cc, wf.data_ptr(), wd.data_ptr(), st()))
+    w_d = dev_f32(w)
+    check(lib.nrd_pack_conv_weight(w_d.data_ptr(), Cc, wf.data_ptr(), wd.data_ptr(), st()))
+    torch.cuda.synchronize()
     return wf, wd
 
 
@@ -70,7 +73,8 @@ def test_bn_forward_and_backward(dt, B, Cc):
     part = torch.stack([y.double().sum(dim=(0, 2, 3)), (y.double() ** 2).sum(dim=(0, 2, 3))]).float().reshape(1, -1).to(DEV).contiguous()
     saved = torch.empty(2 * Cc, device=DEV); ss = torch.empty(2 * Cc, device=DEV)
     run = torch.cat([rm0, rv0]).to(DEV); nbt = torch.tensor(7, dtype=torch.int64, device=DEV)
-    check(lib.nrd_bn_finalize(part.data_ptr(), 1, n, Cc, dev_f32(gamma).data_ptr(), dev_f32(beta).data_ptr(), saved.data_ptr(), ss.data_ptr(),
+    gam_d, bet_d = dev_f32(gamma), dev_f32(beta)          # keep the device copies alive across the calls
+    check(lib.nrd_bn_finalize(part.data_ptr(), 1, n, Cc, gam_d.data_ptr(), bet_d.data_ptr(), saved.data_ptr(), ss.data_ptr(),
                               run.data_ptr(), nbt.data_ptr(), st()))
     yd, xd = nhwc(y, dt), nhwc(x, dt); out = torch.empty_like(yd)
     check(lib.nrd_bn_relu_add(yd.data_ptr(), xd.data_ptr(), ss.data_ptr(), out.data_ptr(), B, Cc, CODE[dt], st()))
@@ -88,7 +92,7 @@ def test_bn_forward_and_backward(dt, B, Cc):
     gd = nhwc(gout, dt); dy = torch.empty_like(gd)
     dgb = torch.full((2 * Cc,), 3.0, device=DEV)
     scratch = torch.empty(lib.nrd_bn_bwd_scratch_bytes(B, Cc) // 4, device=DEV)
-    check(lib.nrd_bn_relu_bwd(gd.data_ptr(), yd.data_ptr(), ss.data_ptr(), saved.data_ptr(), dev_f32(gamma).data_ptr(), dy.data_ptr(),
+    check(lib.nrd_bn_relu_bwd(gd.data_ptr(), yd.data_ptr(), ss.data_ptr(), saved.data_ptr(), gam_d.data_ptr(), dy.data_ptr(),
                               dgb.data_ptr(), 1, B, Cc, CODE[dt], scratch.data_ptr(), st()))
     assert relmax(nchw(dy), yr.grad) < (TOL[dt] if dt == "bf16" else 5e-5)
     assert relmax(dgb[:Cc] - 3.0, gr.grad) < 1e-4 and relmax(dgb[Cc:] - 3.0, br.grad) < 1e-4
@@ -102,8 +106,8 @@ def test_stem_fwd_bwd(dt, B, Cc):
     w = (torch.rand(Cc, 3, 3, 3, generator=g) - 0.5) * 0.38; b = (torch.rand(Cc, generator=g) - 0.5) * 0.38
     wp = w.reshape(Cc, 27).t().contiguous()
     x0 = torch.empty(B, 16, 16, Cc, dtype=TDT[dt], device=DEV); idx = torch.empty(B, 16, 16, Cc, dtype=torch.uint8, device=DEV)
-    xd = dev_f32(x)
-    check(lib.nrd_stem_fwd(xd.data_ptr(), dev_f32(wp).data_ptr(), dev_f32(b).data_ptr(), x0.data_ptr(), idx.data_ptr(), B, Cc, CODE[dt], st()))
+    xd, wp_d, b_d = dev_f32(x), dev_f32(wp), dev_f32(b)
+    check(lib.nrd_stem_fwd(xd.data_ptr(), wp_d.data_ptr(), b_d.data_ptr(), x0.data_ptr(), idx.data_ptr(), B, Cc, CODE[dt], st()))
     wr = w.double().requires_grad_(True); br = b.double().requires_grad_(True)
     ref = F.max_pool2d(torch.relu(F.conv2d(x.double(), wr, br, padding=1)), 2)
     assert relmax(nchw(x0), ref.detach()) < (1e-5 if dt == "fp32" else 1e-2)
@@ -132,7 +136,8 @@ def test_maxpool_first_max_ties(dt):
     gp = _rnd(torch.randn(B, Cc, 8, 8, generator=g), dt)
     ref.backward(gp.double())
     gx = torch.empty_like(xd)
-    check(lib.nrd_maxpool_bwd(nhwc(gp, dt).data_ptr(), idx.data_ptr(), gx.data_ptr(), B, Cc, CODE[dt], st()))
+    gp_d = nhwc(gp, dt)
+    check(lib.nrd_maxpool_bwd(gp_d.data_ptr(), idx.data_ptr(), gx.data_ptr(), B, Cc, CODE[dt], st()))
     assert torch.equal(nchw(gx).double(), xr.grad)          # gradient lands on the FIRST max of each window
 
 

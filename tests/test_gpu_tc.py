@@ -1,0 +1,62 @@
+"""tcgen05 tensor-core convolutions (fwd / dgrad / wgrad) against (a) our CUDA-core kernels on the
+same bf16 operands and (b) torch fp32 conv on the same bf16-rounded operands.  Tolerance: fp32 side
+outputs (BN partial sums, weight-grad partials) <= 1e-3 relative (north_star; measured ~1e-6: only the
+accumulation order differs); bf16 outputs within one bf16 rounding step (2^-8) of the fp32 result."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from util import *  # noqa: F401,F403
+from ddp_cifar10_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+OP_CONV_FWD, OP_WGRAD, OP_DGRAD = 0, 3, 4
+
+
+def _put(pl, what, k, t):
+    pl.tensor_view(what, k).view(torch.bfloat16).copy_(t.to(DEV, torch.bfloat16).flatten())
+
+
+@pytest.mark.parametrize("B,Cc", [(3, 32), (80, 32), (256, 32), (2, 64), (75, 64)])
+def test_tc_conv_fwd_dgrad_wgrad(B, Cc):
+    g = torch.Generator().manual_seed(B + Cc)
+    m = nrd.NetResDeep(Cc, 2, dtype="bf16").to(DEV)
+    eng = m.engine
+    pl = eng.plan(B, torch.device(DEV))
+    eng.ensure_packed(pl)
+    x = torch.randn(B, 16, 16, Cc, generator=g).bfloat16()
+    dy = torch.randn(B, 16, 16, Cc, generator=g).bfloat16()
+    res = torch.randn(B, 16, 16, Cc, generator=g).bfloat16()
+    _put(pl, 0, 0, x); _put(pl, 2, 0, dy); _put(pl, 5, 0, res)
+    w = m.resblocks[0].conv.weight.detach().bfloat16().float().cpu()      # operands as the tensor cores see them
+    got = {}
+    for name, impl in (("cc", _lib.CONV_CUDA_CORE), ("tc", _lib.CONV_TCGEN05)):
+        eng.set_conv_impl(impl)
+        assert lib.nrd_plan_conv_impl(pl.handle) == impl
+        for what in (1, 6, 7, 8):
+            pl.tensor_view(what, 0).zero_()
+        for op in (OP_CONV_FWD, OP_DGRAD, OP_WGRAD):
+            check(lib.nrd_plan_run_op(pl.handle, op, 0, st()), f"run_op {op}")
+        torch.cuda.synchronize()
+        nblk = min(2 * B, 148)
+        got[name] = dict(
+            y=pl.tensor_view(1, 0).view(torch.bfloat16).float().view(B, 16, 16, Cc).cpu(),
+            dx=pl.tensor_view(6, 0).view(torch.bfloat16).float().view(B, 16, 16, Cc).cpu(),
+            dw=pl.tensor_view(7, 0).view(torch.float32).view(nblk, 9, Cc, Cc).double().sum(0).cpu(),
+            stats=pl.tensor_view(8, 0).view(torch.float32)[: (2 * B if name == "cc" else nblk) * 2 * Cc].view(-1, 2, Cc).double().sum(0).cpu())
+    xn, dyn, rn = (t.float().permute(0, 3, 1, 2) for t in (x, dy, res))
+    if name:   # the CUDA-core path uses fp32 weights, the tensor cores bf16-rounded ones: compare each with its own oracle
+        ref_y = F.conv2d(xn.double(), w.double(), padding=1)
+        ref_dx = torch.nn.grad.conv2d_input(xn.shape, w.double(), dyn.double(), padding=1) + rn.double()
+        ref_dw = torch.nn.grad.conv2d_weight(xn.double(), w.shape, dyn.double(), padding=1)     # [co][ci][ky][kx]
+    tc = got["tc"]
+    assert relmax(tc["y"].permute(0, 3, 1, 2), ref_y) < 2 ** -8 * 1.01
+    assert relmax(tc["dx"].permute(0, 3, 1, 2), ref_dx) < 2 ** -8 * 1.01
+    assert relmax(tc["stats"][0], ref_y.sum(dim=(0, 2, 3))) < 1e-3 and relmax(tc["stats"][1], (ref_y ** 2).sum(dim=(0, 2, 3))) < 1e-4
+    # partial layout [tap][co][ci] -> OIHW
+    dw = tc["dw"].view(3, 3, Cc, Cc).permute(2, 3, 0, 1)
+    assert relmax(dw, ref_dw) < 1e-4, relmax(dw, ref_dw)
+    # and against our own CUDA-core kernels (fp32 weights there: bf16 weight rounding is the only extra difference)
+    cc = got["cc"]
+    assert rell2(tc["y"], cc["y"]) < 5e-3 and rell2(tc["dx"], cc["dx"]) < 5e-3
+    assert relmax(tc["dw"], cc["dw"]) < 1e-4
