@@ -37,6 +37,7 @@ _PROTOS = {
     "nrd_pack_weights": (i32, [vp, vp]),
     "nrd_forward": (i32, [vp, vp, vp, i32, vp]),
     "nrd_cross_entropy": (i32, [vp, vp, i32, f32, vp, vp, vp, vp]),
+    "nrd_cross_entropy_static": (i32, [vp, vp, i32, f32, vp, vp, vp]),
     "nrd_backward": (i32, [vp, vp, vp]),
     "nrd_sgd_update": (i32, [vp, vp, sz, f32, f32, vp]),
     "nrd_train_step": (i32, [vp, vp, vp, f32, vp, vp, vp]),

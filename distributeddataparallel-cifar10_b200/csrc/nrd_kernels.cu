@@ -771,6 +771,7 @@ extern "C" const char* nrd_last_error(void) { return g_err; }
 extern "C" int nrd_version(void) { return 100; }
 
 #include <atomic>
+#include <mutex>
 static std::atomic<unsigned long long> g_launches{0};
 void nrd_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 extern "C" unsigned long long nrd_launch_count(void) { return g_launches.load(); }
@@ -981,6 +982,46 @@ extern "C" int nrd_cross_entropy(const float* logits, const int64_t* labels, int
   k_ce_rows<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(logits, labels, B, grad_scale, row_scratch, dlogits);
   LAUNCH_CHECK();
   if (loss_out) { k_loss_mean<<<1, 256, 0, (cudaStream_t)stream>>>(row_scratch, B, loss_out); LAUNCH_CHECK(); }
+  return NRD_OK;
+}
+
+// ---- allocation-free cross-entropy ---------------------------------------------------------
+// Some callers cannot hand us scratch memory because they cannot allocate any: code that runs after
+// the application has given the whole device to another allocator or a fixed arena, plug-in hooks
+// that only receive input/output pointers, and callers already inside a region where cudaMalloc is
+// illegal.  For them the per-row loss scratch of nrd_cross_entropy lives in this file-scope device
+// array instead (32 KiB, resident on every GPU that loads the library until the process exits).
+#define NRD_CE_STATIC_MAX_ROWS 8192
+static __device__ __align__(256) float g_ce_static_rows[NRD_CE_STATIC_MAX_ROWS];
+static float* g_ce_static_ptr[64];       // device address of the array, looked up once per device
+static std::mutex g_ce_static_mu;
+
+extern "C" int nrd_cross_entropy_static(const float* logits, const int64_t* labels, int B, float grad_scale, float* loss_out,
+                                        float* dlogits, void* stream) {
+  NRD_REQUIRE(B > 0 && logits && labels && loss_out, "nrd_cross_entropy_static: bad arguments");
+  NRD_REQUIRE(B <= NRD_CE_STATIC_MAX_ROWS,
+              "nrd_cross_entropy_static: B=%d is beyond the built-in scratch (%d rows); call nrd_cross_entropy with your own row_scratch",
+              B, NRD_CE_STATIC_MAX_ROWS);
+  int dev = -1;
+  NRD_CHECK_CUDA(cudaGetDevice(&dev));
+  NRD_REQUIRE(dev >= 0 && dev < 64, "nrd_cross_entropy_static: device index %d not supported", dev);
+  float* rows = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_ce_static_mu);
+    if (!g_ce_static_ptr[dev]) {
+      // In host code the array's name is only a handle; the address a kernel can use comes from the runtime,
+      // per device, with that device current.  This is the one-time set-up of the first call on a device.
+      void* p = nullptr;
+      NRD_CHECK_CUDA(cudaGetSymbolAddress(&p, g_ce_static_rows));
+      g_ce_static_ptr[dev] = static_cast<float*>(p);
+    }
+    rows = g_ce_static_ptr[dev];
+  }
+  // rows [0,B) are fully overwritten before they are read, so nothing has to start at zero
+  k_ce_rows<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(logits, labels, B, grad_scale, rows, dlogits);
+  LAUNCH_CHECK();
+  k_loss_mean<<<1, 256, 0, (cudaStream_t)stream>>>(rows, B, loss_out);
+  LAUNCH_CHECK();
   return NRD_OK;
 }
 

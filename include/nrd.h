@@ -91,6 +91,17 @@ int nrd_pack_weights(nrd_plan* plan, void* stream);
 int nrd_forward(nrd_plan* plan, const float* images, float* logits, int training, void* stream);
 int nrd_cross_entropy(const float* logits, const int64_t* labels, int B, float grad_scale,
                       float* loss_out, float* dlogits, float* row_scratch /* [B] */, void* stream);
+/* nrd_cross_entropy_static: the same computation for callers that cannot allocate device memory and
+ * therefore cannot supply row_scratch (the device was handed to another allocator or a fixed arena,
+ * a hook that only gets input/output pointers, a context where cudaMalloc is not allowed).  It has no
+ * counterpart in the reference.  The per-row scratch is a 32 KiB array built into the library (held on
+ * every GPU that loads it until the process exits), so B must be <= 8192 or the call fails with
+ * NRD_EINVAL; nothing is allocated or freed.  The first call on each device looks up the array's
+ * device address (one-time set-up): make that first call before starting any stream capture.  All
+ * calls on a device share the one array: calls that may overlap on the GPU (different streams) race,
+ * so keep them on one stream or order them with events.  No state carries from call to call. */
+int nrd_cross_entropy_static(const float* logits, const int64_t* labels, int B, float grad_scale,
+                             float* loss_out, float* dlogits, void* stream);
 int nrd_backward(nrd_plan* plan, const float* dlogits, void* stream);
 int nrd_sgd_update(float* params, const float* grads, size_t n, float lr, float inv_world, void* stream);
 int nrd_train_step(nrd_plan* plan, const float* images, const int64_t* labels, float lr,
