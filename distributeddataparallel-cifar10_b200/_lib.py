@@ -6,7 +6,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libnrd.so")
 
 NRD_F32, NRD_BF16 = 0, 1
-CONV_CUDA_CORE, CONV_TCGEN05 = 0, 1
+CONV_CUDA_CORE, CONV_TCGEN05, CONV_TCGEN05_UNFUSED = 0, 1, 2
 
 
 class NrdError(RuntimeError):

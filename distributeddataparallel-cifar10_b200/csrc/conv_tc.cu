@@ -5,10 +5,13 @@
 //                        tap-flipped / transposed bf16 weight copy, residual add in the epilogue)
 //   k_tc_wgrad<C>        dW[tap][ci][co] (+)= sum_p x[p+tap][ci] * dy[p][co]        (per-CTA partial, fixed-order reduce later)
 //
-// Data movement: one CTA tile = 8 rows x 16 cols of one image = 128 pixels = the UMMA M (fwd) or K (wgrad) extent.
-// TMA loads the NHWC bf16 tile of each of the 9 taps as a 4-D box {C,16,8,1} at coordinates shifted by the tap;
-// out-of-bounds rows/cols are zero-filled by the TMA unit, which IS the conv padding.  The inner extent is C*2 bytes
-// (64 B for C=32 -> SWIZZLE_64B, 128 B for C=64 -> SWIZZLE_128B), the layout the UMMA smem descriptors name.
+// Data movement (v2): TMA issue rate, not bytes, bounded v1 (one box per tap = 9 x 128 rows of 64 B per 128 pixels,
+// ~4 cycles/row; profiles/r01_launches_bench_nograph_v1.md).  Now a work item is ROWS image rows (a whole 16x16 image
+// for C=32, half for C=64) and TMA loads it THREE times, once per horizontal tap kx, as a 4-D box {C,16,ROWS+2,1} at
+// w-coordinate kx-1 and h-coordinate r0-1: out-of-bounds rows/cols are zero-filled by the TMA unit, which IS the conv
+// padding.  The vertical taps ky are then just +ky*16 pixel rows = +ky*1024 B (C=32) on the UMMA descriptor start
+// address, which keeps every operand start aligned to the swizzle atom.  Inner extent = C*2 bytes (64 B -> SWIZZLE_64B,
+// 128 B -> SWIZZLE_128B), the layout the UMMA smem descriptors name.
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM alloc + MMA issuer (one lane), warps 2..5 = epilogue
 // (TMEM -> registers -> bf16 -> global), double-buffered TMEM accumulators so the epilogue of tile i overlaps the MMAs
 // of tile i+1.  Every mbarrier wait has a clock64() timeout that traps instead of hanging the GPU.
@@ -124,9 +127,32 @@ template <int C> struct Cfg {
   static constexpr int WTAP_BYTES = C * ROW_BYTES;              // one tap of the weights: [C rows][C k]
   static constexpr uint32_t LAYOUT = (C == 32) ? 4u : 2u;       // SWIZZLE_64B : SWIZZLE_128B
   static constexpr int SBO = 8 * ROW_BYTES;                     // 8-row core-matrix group stride
-  static constexpr int NST = (C == 32) ? 8 : 6;                 // activation stages (conv kernel)
   static constexpr int KSTEPS = C / 16;                         // UMMA K=16 steps per tap
+  static constexpr int ROWS = (C == 32) ? 16 : 8;               // image rows per work item
+  static constexpr int MT = ROWS / 8;                           // 128-pixel M tiles per work item
+  static constexpr int ITEMS_PER_IMG = 16 / ROWS;
+  static constexpr int IMGROW_BYTES = 16 * ROW_BYTES;           // one image row (16 pixels)
+  static constexpr int BUF_BYTES = (ROWS + 2) * IMGROW_BYTES;   // one kx-shifted, row-haloed copy of the item
+  static constexpr int NST = 2;                                 // work-item stages
 };
+
+// self-resetting grid-wide barrier (all CTAs co-resident: cooperative launch).  bar[0] = arrival count, bar[1] = generation.
+__device__ __forceinline__ void grid_barrier(unsigned int* bar, unsigned int nblocks) {
+  volatile unsigned int* vgen = bar + 1;
+  const unsigned int gen = *vgen;
+  __threadfence();
+  if (atomicAdd(bar, 1u) == nblocks - 1) {
+    bar[0] = 0;
+    __threadfence();
+    atomicAdd(bar + 1, 1u);
+  } else {
+    long long t0 = clock64();
+    while (*vgen == gen) {
+      if (clock64() - t0 > 4000000000LL) __trap();
+    }
+  }
+  __threadfence();
+}
 
 // recursive-halving warp transpose-reduce: on return lane l holds sum over the 32 lanes of v[l]
 __device__ __forceinline__ float warp_col_sum(float (&v)[32], int lane) {
@@ -144,37 +170,56 @@ __device__ __forceinline__ float warp_col_sum(float (&v)[32], int lane) {
 }
 
 // ============================================================================================
-// conv fwd / dgrad
+// conv fwd / dgrad / fused fwd block
+//   MODE 0: y = conv(x), per-CTA BN partial sums                       (two-kernel forward, any batch)
+//   MODE 1: dx = conv(dy, flipped W) + g                               (dgrad)
+//   MODE 2: whole ResBlock forward: accumulators of ALL the CTA's tiles stay in TMEM; pass 1 takes the BN partial sums,
+//           a grid barrier makes every CTA's partials visible, each CTA combines them in the same fixed order,
+//           pass 2 re-reads TMEM and writes y (bf16) and x_next = relu(bn(y)) + x.   (cooperative launch)
 // ============================================================================================
+struct BlockFwdArgs {
+  const float* gamma; const float* beta;     // [C]
+  float* saved;                              // [2C] mean | invstd of this application (for backward)
+  float* scale_shift;                        // [2C]
+  float* running;                            // [2C] running_mean | running_var (EMA, CTA 0)
+  long long* nbt;                            // num_batches_tracked
+  const bf16* x;                             // block input (residual)
+  bf16* xnext;                               // block output
+  unsigned int* gbar;                        // grid barrier words
+  int count;                                 // B*256
+};
+
 template <int C, int MODE>
 __global__ void __launch_bounds__(192, 1)
 k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, bf16* __restrict__ out,
-          const bf16* __restrict__ residual, float* __restrict__ stats_partial, int ntiles) {
+          const bf16* __restrict__ residual, float* __restrict__ stats_partial, int nitems, BlockFwdArgs fa) {
   using K = Cfg<C>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
-  const uint32_t a_smem = base;                                   // NST stages
-  const uint32_t w_smem = a_smem + K::NST * K::TILE_BYTES;       // 9 taps
+  constexpr int STAGE_BYTES = 3 * K::BUF_BYTES;
+  constexpr int NACC = (MODE == 2) ? (512 / C) : 2;               // accumulator slots of C columns
+  const uint32_t a_smem = base;                                   // NST stages x 3 kx-buffers
+  const uint32_t w_smem = a_smem + K::NST * STAGE_BYTES;         // 9 taps
   const uint32_t bar0 = w_smem + 9 * K::WTAP_BYTES;              // barriers (8 B each)
   auto full = [&](int s) { return bar0 + 8u * s; };
   auto empty = [&](int s) { return bar0 + 8u * (K::NST + s); };
   const uint32_t wfull = bar0 + 8u * (2 * K::NST);
   auto tfull = [&](int s) { return bar0 + 8u * (2 * K::NST + 1 + s); };
-  auto tempty = [&](int s) { return bar0 + 8u * (2 * K::NST + 3 + s); };
-  const uint32_t tmem_slot = bar0 + 8u * (2 * K::NST + 5);
-  const uint32_t red_off = 9 * K::WTAP_BYTES + K::NST * K::TILE_BYTES + 8 * (2 * K::NST + 6);
-  float* red = reinterpret_cast<float*>(gen_base + red_off);      // [4][2][C]
+  auto tempty = [&](int s) { return bar0 + 8u * (2 * K::NST + 1 + NACC + s); };
+  const uint32_t tmem_slot = bar0 + 8u * (2 * K::NST + 1 + 2 * NACC);
+  constexpr int BAR_BYTES = 8 * (2 * K::NST + 2 + 2 * NACC);
+  float* red = reinterpret_cast<float*>(gen_base + K::NST * STAGE_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES);   // [4][2][C] (+ [2C] scale/shift)
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  constexpr uint32_t TMEM_COLS = (2 * C <= 64) ? 64 : 128;
+  constexpr uint32_t TMEM_COLS = (MODE == 2) ? 512 : ((2 * C <= 64) ? 64 : 128);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW);
     for (int s = 0; s < K::NST; ++s) { mbar_init(full(s), 1); mbar_init(empty(s), 1); }
     mbar_init(wfull, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull(s), 1); mbar_init(tempty(s), 4); }
+    for (int s = 0; s < NACC; ++s) { mbar_init(tfull(s), 1); mbar_init(tempty(s), 4); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -185,18 +230,17 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 
   if (warp == 0) {
     if (lane == 0) {
-      // ===== TMA producer =====
+      // ===== TMA producer: 3 loads (kx = 0,1,2) per work item =====
       mbar_expect_tx(wfull, 9 * K::WTAP_BYTES);
       for (int t = 0; t < 9; ++t) tma_load_2d(w_smem + t * K::WTAP_BYTES, &tmW, wfull, t * C, 0);
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int b = tile >> 1, r0 = (tile & 1) * 8;
-        for (int t = 0; t < 9; ++t) {
-          mbar_wait(empty(stage), phase ^ 1);
-          mbar_expect_tx(full(stage), K::TILE_BYTES);
-          tma_load_4d(a_smem + stage * K::TILE_BYTES, &tmA, full(stage), 0, t % 3 - 1, r0 + t / 3 - 1, b);
-          if (++stage == K::NST) { stage = 0; phase ^= 1; }
-        }
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        const int b = item / K::ITEMS_PER_IMG, r0 = (item % K::ITEMS_PER_IMG) * K::ROWS;
+        mbar_wait(empty(stage), phase ^ 1);
+        mbar_expect_tx(full(stage), STAGE_BYTES);
+        for (int kx = 0; kx < 3; ++kx)
+          tma_load_4d(a_smem + stage * STAGE_BYTES + kx * K::BUF_BYTES, &tmA, full(stage), 0, kx - 1, r0 - 1, b);
+        if (++stage == K::NST) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -204,24 +248,27 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       // ===== MMA issuer =====
       constexpr uint32_t idesc = make_idesc(128, C, 0, 0);
       mbar_wait(wfull, 0);
-      int stage = 0; uint32_t phase = 0; int it = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(tempty(as), aphase ^ 1);
+      int stage = 0; uint32_t phase = 0; int tile = 0;
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        mbar_wait(full(stage), phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * C;
-        for (int t = 0; t < 9; ++t) {
-          mbar_wait(full(stage), phase);
-          tc_fence_after();
-          const uint64_t ad = make_sdesc(a_smem + stage * K::TILE_BYTES, 16, K::SBO, K::LAYOUT);
-          const uint64_t bd = make_sdesc(w_smem + t * K::WTAP_BYTES, 16, K::SBO, K::LAYOUT);
+        for (int m = 0; m < K::MT; ++m, ++tile) {
+          const int as = (MODE == 2) ? tile : (tile & 1);
+          if (MODE != 2) { mbar_wait(tempty(as), ((tile >> 1) & 1) ^ 1); tc_fence_after(); }
+          const uint32_t d_tmem = tmem_base + as * C;
 #pragma unroll
-          for (int k = 0; k < K::KSTEPS; ++k)   // +32 B along K inside the swizzled row = +2 in the (addr>>4) field
-            umma_bf16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (t | k) != 0);
-          umma_commit(empty(stage));
-          if (t == 8) umma_commit(tfull(as));
-          if (++stage == K::NST) { stage = 0; phase ^= 1; }
+          for (int t = 0; t < 9; ++t) {
+            const uint32_t a_addr = a_smem + stage * STAGE_BYTES + (t % 3) * K::BUF_BYTES + (m * 8 + t / 3) * K::IMGROW_BYTES;
+            const uint64_t ad = make_sdesc(a_addr, 16, K::SBO, K::LAYOUT);
+            const uint64_t bd = make_sdesc(w_smem + t * K::WTAP_BYTES, 16, K::SBO, K::LAYOUT);
+#pragma unroll
+            for (int k = 0; k < K::KSTEPS; ++k)   // +32 B along K inside the swizzled row = +2 in the (addr>>4) field
+              umma_bf16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (t | k) != 0);
+          }
+          umma_commit(tfull(as));
         }
+        umma_commit(empty(stage));
+        if (++stage == K::NST) { stage = 0; phase ^= 1; }
       }
     }
   } else {
@@ -230,50 +277,53 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     float ssum[C / 32], qsum[C / 32];
 #pragma unroll
     for (int h = 0; h < C / 32; ++h) ssum[h] = qsum[h] = 0.f;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-      const int b = tile >> 1, r0 = (tile & 1) * 8;
-      mbar_wait(tfull(as), aphase);
-      tc_fence_after();
-      const size_t gp = (size_t)b * NRD_PIX + r0 * 16 + q * 32 + lane;   // this thread's pixel
-      bf16* orow = out + gp * C;
+    int tile = 0;
+    for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+      const int b = item / K::ITEMS_PER_IMG, r0 = (item % K::ITEMS_PER_IMG) * K::ROWS;
+      for (int m = 0; m < K::MT; ++m, ++tile) {
+        const int as = (MODE == 2) ? tile : (tile & 1);
+        mbar_wait(tfull(as), (MODE == 2) ? 0u : (uint32_t)((tile >> 1) & 1));
+        tc_fence_after();
+        const size_t gp = (size_t)b * NRD_PIX + (r0 + m * 8) * 16 + q * 32 + lane;   // this thread's pixel
 #pragma unroll
-      for (int h = 0; h < C / 32; ++h) {
-        float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * C + h * 32, v);
-        if (h == C / 32 - 1) {               // accumulator is in registers: hand the TMEM stage back
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(tempty(as));
-        }
-        if (MODE == 1) {
-          const uint4* rrow = reinterpret_cast<const uint4*>(residual + gp * C + h * 32);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 rv = rrow[j];
-            const __nv_bfloat162* rh = reinterpret_cast<const __nv_bfloat162*>(&rv);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) { float2 f = __bfloat1622float2(rh[e]); v[j * 8 + 2 * e] += f.x; v[j * 8 + 2 * e + 1] += f.y; }
+        for (int h = 0; h < C / 32; ++h) {
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * C + h * 32, v);
+          if (MODE != 2 && h == C / 32 - 1) {      // accumulator is in registers: hand the TMEM slot back
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty(as));
           }
-        }
+          if (MODE == 1) {
+            const uint4* rrow = reinterpret_cast<const uint4*>(residual + gp * C + h * 32);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint4 pk; __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+            for (int j = 0; j < 4; ++j) {
+              uint4 rv = rrow[j];
+              const __nv_bfloat162* rh = reinterpret_cast<const __nv_bfloat162*>(&rv);
 #pragma unroll
-          for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[j * 8 + 2 * e], v[j * 8 + 2 * e + 1]);
-          reinterpret_cast<uint4*>(orow + h * 32)[j] = pk;
-        }
-        if (MODE == 0) {
-          float sq[32];
+              for (int e = 0; e < 4; ++e) { float2 f = __bfloat1622float2(rh[e]); v[j * 8 + 2 * e] += f.x; v[j * 8 + 2 * e + 1] += f.y; }
+            }
+          }
+          if (MODE != 2) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
-          ssum[h] += warp_col_sum(v, lane);
-          qsum[h] += warp_col_sum(sq, lane);
+            for (int j = 0; j < 4; ++j) {
+              uint4 pk; __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[j * 8 + 2 * e], v[j * 8 + 2 * e + 1]);
+              reinterpret_cast<uint4*>(out + gp * C + h * 32)[j] = pk;
+            }
+          }
+          if (MODE != 1) {
+            float sq[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
+            ssum[h] += warp_col_sum(v, lane);
+            qsum[h] += warp_col_sum(sq, lane);
+          }
         }
       }
     }
-    if (MODE == 0) {
+    if (MODE != 1) {
 #pragma unroll
       for (int h = 0; h < C / 32; ++h) { red[(q * 2 + 0) * C + h * 32 + lane] = ssum[h]; red[(q * 2 + 1) * C + h * 32 + lane] = qsum[h]; }
       asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -284,6 +334,82 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         stats_partial[(size_t)blockIdx.x * 2 * C + t] = s;
       }
     }
+    if (MODE == 2) {
+      // ---- every CTA's partials -> global; grid barrier; identical fixed-order combine in every CTA ----
+      const int t = threadIdx.x - 64;                 // 0..127
+      float* ss_sm = red + 8 * C;                     // [2C] scale | shift
+      double* dred = reinterpret_cast<double*>(red + 10 * C);   // [RP][2C], RP*2C = 512
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // partial row written
+      if (t == 0) grid_barrier(fa.gbar, gridDim.x);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      {
+        // partial matrix [gridDim.x][2C] fp32: every thread owns one float4 column chunk and every RP-th row, all loads
+        // independent (one L2 round trip), fp64 accumulation, then a fixed-order combine over the RP row classes
+        constexpr int NC4 = 2 * C / 4, RP = 128 / NC4;
+        const int c4 = t % NC4, r = t / NC4;
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 8
+        for (int row = r; row < (int)gridDim.x; row += RP) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(stats_partial + (size_t)row * 2 * C) + c4);
+          a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+        }
+        double* d = dred + (size_t)r * 2 * C + c4 * 4;
+        d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (t < C) {
+        constexpr int RP = 128 / (2 * C / 4);
+        double S = 0.0, Q = 0.0;
+#pragma unroll
+        for (int k = 0; k < RP; ++k) { S += dred[k * 2 * C + t]; Q += dred[k * 2 * C + C + t]; }
+        const double mean = S / fa.count;
+        double var = Q / fa.count - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float invstd = (float)(1.0 / sqrt(var + (double)NRD_BN_EPS));
+        const float sc = fa.gamma[t] * invstd, sh = fa.beta[t] - (float)mean * sc;
+        ss_sm[t] = sc; ss_sm[C + t] = sh;
+        if (blockIdx.x == 0) {
+          fa.saved[t] = (float)mean; fa.saved[C + t] = invstd;
+          fa.scale_shift[t] = sc; fa.scale_shift[C + t] = sh;
+          const double unbiased = var * ((double)fa.count / (double)(fa.count - 1));
+          fa.running[t] = (1.f - NRD_BN_MOMENTUM) * fa.running[t] + NRD_BN_MOMENTUM * (float)mean;
+          fa.running[C + t] = (1.f - NRD_BN_MOMENTUM) * fa.running[C + t] + NRD_BN_MOMENTUM * (float)unbiased;
+          if (t == 0) *fa.nbt += 1;
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      // ---- pass 2: y (bf16) and x_next = relu(y_bf16*scale + shift) + x ----
+      tile = 0;
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        const int b = item / K::ITEMS_PER_IMG, r0 = (item % K::ITEMS_PER_IMG) * K::ROWS;
+        for (int m = 0; m < K::MT; ++m, ++tile) {
+          const size_t gp = (size_t)b * NRD_PIX + (r0 + m * 8) * 16 + q * 32 + lane;
+#pragma unroll
+          for (int h = 0; h < C / 32; ++h) {
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * C + h * 32, v);
+            const uint4* xrow = reinterpret_cast<const uint4*>(fa.x + gp * C + h * 32);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 yk, xk = xrow[j], ok;
+              __nv_bfloat162* yh = reinterpret_cast<__nv_bfloat162*>(&yk);
+              const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xk);
+              __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const int c = h * 32 + j * 8 + 2 * e;
+                yh[e] = __floats2bfloat162_rn(v[j * 8 + 2 * e], v[j * 8 + 2 * e + 1]);
+                const float2 yr = __bfloat1622float2(yh[e]), xr = __bfloat1622float2(xh[e]);   // BN sees the STORED y (as backward will)
+                oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, ss_sm[c], ss_sm[C + c]), 0.f) + xr.x,
+                                              fmaxf(fmaf(yr.y, ss_sm[c + 1], ss_sm[C + c + 1]), 0.f) + xr.y);
+              }
+              reinterpret_cast<uint4*>(out + gp * C + h * 32)[j] = yk;
+              reinterpret_cast<uint4*>(fa.xnext + gp * C + h * 32)[j] = ok;
+            }
+          }
+        }
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -291,29 +417,29 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 }
 
 // ============================================================================================
-// wgrad: both operands MN-major (channels contiguous, pixels = K).  A = up to 128/C taps of x stacked along M
-// (the tap tiles are consecutive in shared memory: LBO = TILE_BYTES jumps from one tap to the next), B = dy tile.
+// wgrad: both operands MN-major (channels contiguous, pixels = K).  Per work item: the 3 kx-shifted row-haloed copies of x
+// and the dy rows.  One MMA stacks 128/C vertical taps along M: tap ky+1 is one image row further = LBO.
 // ============================================================================================
 template <int C> struct WCfg {
   static constexpr int TAPS_PER_MMA = 128 / C;                         // 4 (C=32) or 2 (C=64)
-  static constexpr int GROUPS = (9 + TAPS_PER_MMA - 1) / TAPS_PER_MMA; // 3 or 5 accumulators of C columns
-  static constexpr int SLOTS = GROUPS * TAPS_PER_MMA;                  // tile slots the A descriptors may touch (12 / 10)
-  static constexpr int DY_SLOT = 9;                                    // dy sits right after the 9 taps (and doubles as junk rows)
-  static constexpr int SS_TILES = SLOTS > 10 ? SLOTS : 10;             // slots 10.. (C=32 only) are zero-filled junk
-  static constexpr int NSS = (C == 32) ? 2 : 1;                        // super-stages that fit in 227 KB
+  static constexpr int GPK = (3 + TAPS_PER_MMA - 1) / TAPS_PER_MMA;    // accumulator groups per kx: 1 or 2
+  static constexpr int GROUPS = 3 * GPK;                               // 3 or 6 accumulators of C columns
   static constexpr uint32_t TMEM_COLS = (GROUPS * C <= 128) ? 128 : 512;
+  static constexpr int DY_BYTES = Cfg<C>::ROWS * Cfg<C>::IMGROW_BYTES;
+  static constexpr int STAGE_BYTES = 3 * Cfg<C>::BUF_BYTES + DY_BYTES;
+  static constexpr int NSS = 2;
+  static constexpr int SLACK = 3 * Cfg<C>::IMGROW_BYTES;               // junk taps (ky >= 3) read up to 2 rows past the last stage
 };
 
 template <int C>
 __global__ void __launch_bounds__(192, 1)
 k_tc_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ partial,
-           int ntiles, int first) {
+           int nitems, int first) {
   using K = Cfg<C>; using W = WCfg<C>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
-  constexpr int SS_BYTES = W::SS_TILES * K::TILE_BYTES;
-  const uint32_t bar0 = base + W::NSS * SS_BYTES;
+  const uint32_t bar0 = base + W::NSS * W::STAGE_BYTES + W::SLACK;
   auto full = [&](int s) { return bar0 + 8u * s; };
   auto empty = [&](int s) { return bar0 + 8u * (W::NSS + s); };
   const uint32_t tfull = bar0 + 8u * (2 * W::NSS);
@@ -321,15 +447,6 @@ k_tc_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // junk tile slots (10..SS_TILES-1) are read by the last MMA group (their accumulator rows are discarded): zero them once
-  if constexpr (W::SS_TILES > 10) {
-    constexpr int per = (W::SS_TILES - 10) * K::TILE_BYTES / 16;
-    for (int i = threadIdx.x; i < W::NSS * per; i += blockDim.x) {
-      const int ss = i / per, o = i % per;
-      reinterpret_cast<uint4*>(gen_base + ss * SS_BYTES + 10 * K::TILE_BYTES)[o] = make_uint4(0, 0, 0, 0);
-    }
-    fence_proxy_async();
-  }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmDY);
     for (int s = 0; s < W::NSS; ++s) { mbar_init(full(s), 1); mbar_init(empty(s), 1); }
@@ -345,13 +462,13 @@ k_tc_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
   if (warp == 0) {
     if (lane == 0) {
       int ss = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int b = tile >> 1, r0 = (tile & 1) * 8;
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        const int b = item / K::ITEMS_PER_IMG, r0 = (item % K::ITEMS_PER_IMG) * K::ROWS;
         mbar_wait(empty(ss), phase ^ 1);
-        mbar_expect_tx(full(ss), 10 * K::TILE_BYTES);
-        const uint32_t sbase = base + ss * SS_BYTES;
-        for (int t = 0; t < 9; ++t) tma_load_4d(sbase + t * K::TILE_BYTES, &tmX, full(ss), 0, t % 3 - 1, r0 + t / 3 - 1, b);
-        tma_load_4d(sbase + W::DY_SLOT * K::TILE_BYTES, &tmDY, full(ss), 0, 0, r0, b);
+        mbar_expect_tx(full(ss), W::STAGE_BYTES);
+        const uint32_t sbase = base + ss * W::STAGE_BYTES;
+        for (int kx = 0; kx < 3; ++kx) tma_load_4d(sbase + kx * K::BUF_BYTES, &tmX, full(ss), 0, kx - 1, r0 - 1, b);
+        tma_load_4d(sbase + 3 * K::BUF_BYTES, &tmDY, full(ss), 0, 0, r0, b);
         if (++ss == W::NSS) { ss = 0; phase ^= 1; }
       }
     }
@@ -359,18 +476,20 @@ k_tc_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(128, C, 1, 1);
       int ss = 0; uint32_t phase = 0; bool any = false;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
         mbar_wait(full(ss), phase);
         tc_fence_after();
-        const uint32_t sbase = base + ss * SS_BYTES;
+        const uint32_t sbase = base + ss * W::STAGE_BYTES;
+        for (int y = 0; y < K::ROWS; ++y) {            // K step = one image row = 16 pixels
+          const uint64_t bd = make_sdesc(sbase + 3 * K::BUF_BYTES + y * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
 #pragma unroll
-        for (int g = 0; g < W::GROUPS; ++g) {
+          for (int kx = 0; kx < 3; ++kx)
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {          // 16 pixels (two 8-row swizzle atoms) per MMA
-            const uint64_t ad = make_sdesc(sbase + g * W::TAPS_PER_MMA * K::TILE_BYTES + k * 16 * K::ROW_BYTES, K::TILE_BYTES, K::SBO, K::LAYOUT);
-            const uint64_t bd = make_sdesc(sbase + W::DY_SLOT * K::TILE_BYTES + k * 16 * K::ROW_BYTES, K::TILE_BYTES, K::SBO, K::LAYOUT);
-            umma_bf16(tmem_base + g * C, ad, bd, idesc, (any || k > 0) ? 1u : 0u);
-          }
+            for (int j = 0; j < W::GPK; ++j) {
+              // rows of this accumulator: (tap ky = j*TAPS_PER_MMA + m/C, ci = m%C); tap ky reads image row y+ky of the haloed copy
+              const uint64_t ad = make_sdesc(sbase + kx * K::BUF_BYTES + (y + j * W::TAPS_PER_MMA) * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
+              umma_bf16(tmem_base + (kx * W::GPK + j) * C, ad, bd, idesc, (any || y > 0) ? 1u : 0u);
+            }
         }
         any = true;
         umma_commit(empty(ss));
@@ -385,21 +504,23 @@ k_tc_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
     float* outp = partial + (size_t)blockIdx.x * 9 * C * C;
     const int m = q * 32 + lane;                       // accumulator row = (tap within group)*C + ci
 #pragma unroll
-    for (int g = 0; g < W::GROUPS; ++g) {
-      const int tap = g * W::TAPS_PER_MMA + m / C, ci = m % C;
+    for (int kx = 0; kx < 3; ++kx)
 #pragma unroll
-      for (int h = 0; h < C / 32; ++h) {
-        float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + g * C + h * 32, v);
-        if (tap < 9) {
+      for (int j = 0; j < W::GPK; ++j) {
+        const int ky = j * W::TAPS_PER_MMA + m / C, ci = m % C, tap = ky * 3 + kx;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const size_t o = ((size_t)tap * C + h * 32 + j) * C + ci;      // [tap][co][ci]
-            outp[o] = first ? v[j] : outp[o] + v[j];
+        for (int h = 0; h < C / 32; ++h) {
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (kx * W::GPK + j) * C + h * 32, v);
+          if (ky < 3) {
+#pragma unroll
+            for (int jj = 0; jj < 32; ++jj) {
+              const size_t o = ((size_t)tap * C + h * 32 + jj) * C + ci;      // [tap][co][ci]
+              outp[o] = first ? v[jj] : outp[o] + v[jj];
+            }
           }
         }
       }
-    }
   }
   tc_fence_before();
   __syncthreads();
@@ -420,12 +541,13 @@ static PFN_encodeTiled get_encode() {
   return fn;
 }
 
-static int make_act_map(CUtensorMap* tm, void* ptr, int B, int C) {
+// activation map: dims {C, W=16, H=16, N=B}; box {C, 16, box_rows, 1}
+static int make_act_map(CUtensorMap* tm, void* ptr, int B, int C, int box_rows) {
   PFN_encodeTiled enc = get_encode();
   NRD_REQUIRE(enc, "cuTensorMapEncodeTiled is not available from this driver");
   cuuint64_t dims[4] = {(cuuint64_t)C, 16, 16, (cuuint64_t)B};
   cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)16 * C * 2, (cuuint64_t)256 * C * 2};
-  cuuint32_t box[4] = {(cuuint32_t)C, 16, 8, 1};
+  cuuint32_t box[4] = {(cuuint32_t)C, 16, (cuuint32_t)box_rows, 1};
   cuuint32_t es[4] = {1, 1, 1, 1};
   CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, ptr, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    C == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -447,14 +569,17 @@ static int make_w_map(CUtensorMap* tm, void* ptr, int C) {
   return NRD_OK;
 }
 
-template <int C> constexpr size_t conv_smem() {
-  return 1024 + Cfg<C>::NST * Cfg<C>::TILE_BYTES + 9 * Cfg<C>::WTAP_BYTES + 8 * (2 * Cfg<C>::NST + 6) + 4 * 2 * C * sizeof(float) + 64;
+template <int C, int MODE> constexpr size_t conv_smem() {
+  constexpr int NACC = (MODE == 2) ? (512 / C) : 2;
+  return 1024 + Cfg<C>::NST * 3 * Cfg<C>::BUF_BYTES + 9 * Cfg<C>::WTAP_BYTES + 8 * (2 * Cfg<C>::NST + 2 + 2 * NACC) +
+         (10 * C) * sizeof(float) + 512 * sizeof(double) + 64;
 }
 template <int C> constexpr size_t wgrad_smem() {
-  return 1024 + WCfg<C>::NSS * WCfg<C>::SS_TILES * Cfg<C>::TILE_BYTES + 8 * (2 * WCfg<C>::NSS + 2) + 64;
+  return 1024 + WCfg<C>::NSS * WCfg<C>::STAGE_BYTES + WCfg<C>::SLACK + 8 * (2 * WCfg<C>::NSS + 2) + 64;
 }
 
-static int conv_grid(const nrd_plan* p) { int t = p->B * 2; return t < NRD_NUM_SMS ? t : NRD_NUM_SMS; }
+static int items(const nrd_plan* p) { return p->B * (p->C == 32 ? 1 : 2); }
+static int conv_grid(const nrd_plan* p) { int t = items(p); return t < NRD_NUM_SMS ? t : NRD_NUM_SMS; }
 
 template <typename F> static int set_attr(F* fn, size_t smem) {
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -473,40 +598,72 @@ int nrd_tc_plan_init(nrd_plan* p) {
   NRD_CHECK_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, p->device));
   NRD_REQUIRE(major == 10, "the bf16 path needs an sm_100a (B200) device: tcgen05/TMEM kernels, no fallback (found sm_%d*)", major * 10);
   const size_t act = p->act_elems * p->esz;
-  for (int k = 0; k <= p->NB; ++k) NRD_TRY(make_act_map(&p->tm_x[k], p->xs + act * k, p->B, p->C));
-  NRD_TRY(make_act_map(&p->tm_dy, p->dy, p->B, p->C));
+  const int rows = (p->C == 32 ? 16 : 8);
+  for (int k = 0; k <= p->NB; ++k) NRD_TRY(make_act_map(&p->tm_x[k], p->xs + act * k, p->B, p->C, rows + 2));
+  NRD_TRY(make_act_map(&p->tm_dy, p->dy, p->B, p->C, rows + 2));      // dgrad: haloed
+  NRD_TRY(make_act_map(&p->tm_dy0, p->dy, p->B, p->C, rows));         // wgrad: the rows themselves
   NRD_TRY(make_w_map(&p->tm_wf, p->wtc_fwd, p->C));
   NRD_TRY(make_w_map(&p->tm_wd, p->wtc_dgrad, p->C));
   if (p->C == 32) {
-    NRD_TRY(set_attr(k_tc_conv<32, 0>, conv_smem<32>())); NRD_TRY(set_attr(k_tc_conv<32, 1>, conv_smem<32>()));
-    NRD_TRY(set_attr(k_tc_wgrad<32>, wgrad_smem<32>()));
+    NRD_TRY(set_attr(k_tc_conv<32, 0>, conv_smem<32, 0>())); NRD_TRY(set_attr(k_tc_conv<32, 1>, conv_smem<32, 1>()));
+    NRD_TRY(set_attr(k_tc_conv<32, 2>, conv_smem<32, 2>())); NRD_TRY(set_attr(k_tc_wgrad<32>, wgrad_smem<32>()));
   } else {
-    NRD_TRY(set_attr(k_tc_conv<64, 0>, conv_smem<64>())); NRD_TRY(set_attr(k_tc_conv<64, 1>, conv_smem<64>()));
-    NRD_TRY(set_attr(k_tc_wgrad<64>, wgrad_smem<64>()));
+    NRD_TRY(set_attr(k_tc_conv<64, 0>, conv_smem<64, 0>())); NRD_TRY(set_attr(k_tc_conv<64, 1>, conv_smem<64, 1>()));
+    NRD_TRY(set_attr(k_tc_conv<64, 2>, conv_smem<64, 2>())); NRD_TRY(set_attr(k_tc_wgrad<64>, wgrad_smem<64>()));
   }
+  // fused block forward: every CTA keeps all its accumulators in TMEM (512 columns) and all CTAs must be co-resident
+  const int grid = conv_grid(p), per_cta = (items(p) + grid - 1) / grid * (rows / 8);
+  p->tc_fused_fwd = (per_cta * p->C <= 512) ? 1 : 0;
+  NRD_CHECK_CUDA(cudaMemset(p->gbar, 0, 256));
   p->tc_ready = 1;
   return NRD_OK;
 }
 
 int nrd_tc_stats_blocks(const nrd_plan* p) { return conv_grid(p); }
+int nrd_tc_wgrad_blocks(const nrd_plan* p) { return conv_grid(p); }
 
 int nrd_tc_conv_fwd(nrd_plan* p, int k, cudaStream_t st) {
   NRD_REQUIRE(p->tc_ready, "tcgen05 path not initialised");
   const size_t act = p->act_elems * p->esz;
   bf16* y = (bf16*)(p->ys + act * k);
-  const int grid = conv_grid(p), nt = p->B * 2;
-  if (p->C == 32) k_tc_conv<32, 0><<<grid, 192, conv_smem<32>(), st>>>(p->tm_x[k], p->tm_wf, y, nullptr, p->stats_partial, nt);
-  else k_tc_conv<64, 0><<<grid, 192, conv_smem<64>(), st>>>(p->tm_x[k], p->tm_wf, y, nullptr, p->stats_partial, nt);
+  const int grid = conv_grid(p), nt = items(p);
+  BlockFwdArgs fa{};
+  if (p->C == 32) k_tc_conv<32, 0><<<grid, 192, conv_smem<32, 0>(), st>>>(p->tm_x[k], p->tm_wf, y, nullptr, p->stats_partial, nt, fa);
+  else k_tc_conv<64, 0><<<grid, 192, conv_smem<64, 0>(), st>>>(p->tm_x[k], p->tm_wf, y, nullptr, p->stats_partial, nt, fa);
   nrd_count_launch();
   NRD_CHECK_CUDA(cudaGetLastError());
   return NRD_OK;
 }
 
+// whole ResBlock forward k: y_k, x_{k+1}, saved stats, running-stat EMA in one cooperative launch
+int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st) {
+  NRD_REQUIRE(p->tc_ready && p->tc_fused_fwd, "fused block forward not available for this plan");
+  const size_t act = p->act_elems * p->esz;
+  const int C = p->C;
+  bf16* y = (bf16*)(p->ys + act * k);
+  const bf16* res = nullptr;
+  int nt = items(p);
+  BlockFwdArgs fa;
+  fa.gamma = p->params + p->off[3]; fa.beta = p->params + p->off[4];
+  fa.saved = p->saved_stats + (size_t)k * 2 * C; fa.scale_shift = p->scale_shift + (size_t)k * 2 * C;
+  fa.running = p->bn_running; fa.nbt = (long long*)p->nbt;
+  fa.x = (const bf16*)(p->xs + act * k); fa.xnext = (bf16*)(p->xs + act * (k + 1));
+  fa.gbar = p->gbar; fa.count = p->B * NRD_PIX;
+  float* sp = p->stats_partial;
+  void* args[] = {(void*)&p->tm_x[k], (void*)&p->tm_wf, (void*)&y, (void*)&res, (void*)&sp, (void*)&nt, (void*)&fa};
+  const dim3 grid(conv_grid(p)), block(192);
+  if (C == 32) NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_conv<32, 2>, grid, block, args, conv_smem<32, 2>(), st));
+  else NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_conv<64, 2>, grid, block, args, conv_smem<64, 2>(), st));
+  nrd_count_launch();
+  return NRD_OK;
+}
+
 int nrd_tc_conv_dgrad(nrd_plan* p, const void* g, void* dx_out, cudaStream_t st) {
   NRD_REQUIRE(p->tc_ready, "tcgen05 path not initialised");
-  const int grid = conv_grid(p), nt = p->B * 2;
-  if (p->C == 32) k_tc_conv<32, 1><<<grid, 192, conv_smem<32>(), st>>>(p->tm_dy, p->tm_wd, (bf16*)dx_out, (const bf16*)g, nullptr, nt);
-  else k_tc_conv<64, 1><<<grid, 192, conv_smem<64>(), st>>>(p->tm_dy, p->tm_wd, (bf16*)dx_out, (const bf16*)g, nullptr, nt);
+  const int grid = conv_grid(p), nt = items(p);
+  BlockFwdArgs fa{};
+  if (p->C == 32) k_tc_conv<32, 1><<<grid, 192, conv_smem<32, 1>(), st>>>(p->tm_dy, p->tm_wd, (bf16*)dx_out, (const bf16*)g, nullptr, nt, fa);
+  else k_tc_conv<64, 1><<<grid, 192, conv_smem<64, 1>(), st>>>(p->tm_dy, p->tm_wd, (bf16*)dx_out, (const bf16*)g, nullptr, nt, fa);
   nrd_count_launch();
   NRD_CHECK_CUDA(cudaGetLastError());
   return NRD_OK;
@@ -514,9 +671,9 @@ int nrd_tc_conv_dgrad(nrd_plan* p, const void* g, void* dx_out, cudaStream_t st)
 
 int nrd_tc_conv_wgrad(nrd_plan* p, int k, int first, cudaStream_t st) {
   NRD_REQUIRE(p->tc_ready, "tcgen05 path not initialised");
-  const int grid = conv_grid(p), nt = p->B * 2;   // same CTA count as the CUDA-core wgrad => same partial buffer / reduce
-  if (p->C == 32) k_tc_wgrad<32><<<grid, 192, wgrad_smem<32>(), st>>>(p->tm_x[k], p->tm_dy, p->wgrad_partial, nt, first);
-  else k_tc_wgrad<64><<<grid, 192, wgrad_smem<64>(), st>>>(p->tm_x[k], p->tm_dy, p->wgrad_partial, nt, first);
+  const int grid = conv_grid(p), nt = items(p);
+  if (p->C == 32) k_tc_wgrad<32><<<grid, 192, wgrad_smem<32>(), st>>>(p->tm_x[k], p->tm_dy0, p->wgrad_partial, nt, first);
+  else k_tc_wgrad<64><<<grid, 192, wgrad_smem<64>(), st>>>(p->tm_x[k], p->tm_dy0, p->wgrad_partial, nt, first);
   nrd_count_launch();
   NRD_CHECK_CUDA(cudaGetLastError());
   return NRD_OK;

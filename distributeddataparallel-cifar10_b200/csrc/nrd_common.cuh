@@ -79,9 +79,12 @@ struct nrd_plan {
   bf16* wtc_dgrad;     // same for dgrad (transposed + flipped)
   // TMA descriptors for the tcgen05 path (filled by nrd_tc_plan_init)
   CUtensorMap tm_x[32];   // per saved x_k (k <= NB), box [1,8,16,C]
-  CUtensorMap tm_dy;      // dy scratch
+  CUtensorMap tm_dy;      // dy scratch, row-haloed box (dgrad)
+  CUtensorMap tm_dy0;     // dy scratch, plain rows (wgrad)
   CUtensorMap tm_wf, tm_wd;
   int tc_ready;
+  int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
+  unsigned int* gbar;     // grid-barrier words
 };
 
 // tcgen05 path (conv_tc.cu)
@@ -90,3 +93,5 @@ int nrd_tc_conv_fwd(nrd_plan* p, int k, cudaStream_t st);                       
 int nrd_tc_conv_dgrad(nrd_plan* p, const void* g, void* dx_out, cudaStream_t st); // dx = dgrad(dy) + g
 int nrd_tc_conv_wgrad(nrd_plan* p, int k, int first, cudaStream_t st);          // partial (+)= wgrad(x_k, dy)
 int nrd_tc_stats_blocks(const nrd_plan* p);
+int nrd_tc_wgrad_blocks(const nrd_plan* p);
+int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st);                      // y_k, x_{k+1}, BN stats + EMA, one launch

@@ -847,8 +847,8 @@ static int launch_wgrad(const void* x, const void* dy, float* partial, int B, in
 static int wgrad_any(const void* x, const void* dy, float* partial, int B, int C, int dt, int first, cudaStream_t st) {
   return dt == NRD_F32 ? launch_wgrad<float>(x, dy, partial, B, C, first, st) : launch_wgrad<bf16>(x, dy, partial, B, C, first, st);
 }
-static int wgrad_reduce(const float* partial, int B, int C, float* dw, cudaStream_t st) {
-  k_wgrad_reduce<<<(9 * C * C + 255) / 256, 256, 0, st>>>(partial, wgrad_blocks(B), C, dw);
+static int wgrad_reduce(const float* partial, int nblk, int C, float* dw, cudaStream_t st) {
+  k_wgrad_reduce<<<(9 * C * C + 255) / 256, 256, 0, st>>>(partial, nblk, C, dw);
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -921,7 +921,7 @@ extern "C" size_t nrd_wgrad_partial_bytes(int B, int C) { return (size_t)wgrad_b
 extern "C" int nrd_conv3x3_wgrad(const void* x, const void* dy, float* dw, int B, int C, int dtype, float* partial, void* stream) {
   NRD_REQUIRE(valid_C(C) && valid_dt(dtype) && B > 0 && x && dy && dw && partial, "nrd_conv3x3_wgrad: bad arguments");
   NRD_TRY(wgrad_any(x, dy, partial, B, C, dtype, 1, (cudaStream_t)stream));
-  return wgrad_reduce(partial, B, C, dw, (cudaStream_t)stream);
+  return wgrad_reduce(partial, wgrad_blocks(B), C, dw, (cudaStream_t)stream);
 }
 
 extern "C" int nrd_bn_finalize(const float* partial, int blocks, int count, int C, const float* gamma, const float* beta,
@@ -1077,6 +1077,7 @@ static void carve(nrd_plan* p, char* base, size_t* total) {
   p->conv1_wp = cv.take<float>((size_t)27 * C * 4);
   p->wtc_fwd = cv.take<bf16>((size_t)9 * C * C * 2);
   p->wtc_dgrad = cv.take<bf16>((size_t)9 * C * C * 2);
+  p->gbar = cv.take<unsigned int>(256);
   *total = cv.off;
 }
 
@@ -1124,7 +1125,7 @@ extern "C" int nrd_plan_destroy(nrd_plan* p) { delete p; return NRD_OK; }
 
 extern "C" int nrd_plan_set_conv_impl(nrd_plan* p, int impl) {
   NRD_REQUIRE(p, "null plan");
-  NRD_REQUIRE(impl == NRD_CONV_CUDA_CORE || (impl == NRD_CONV_TCGEN05 && p->dtype == NRD_BF16 && p->tc_ready),
+  NRD_REQUIRE(impl == NRD_CONV_CUDA_CORE || ((impl == NRD_CONV_TCGEN05 || impl == NRD_CONV_TCGEN05_UNFUSED) && p->dtype == NRD_BF16 && p->tc_ready),
               "conv impl %d not available for this plan (dtype=%d)", impl, p->dtype);
   p->conv_impl = impl;
   return NRD_OK;
@@ -1177,8 +1178,12 @@ extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int 
   for (int k = 0; k < NB; ++k) {
     char* xk = p->xs + act * k; char* yk = p->ys + act * k; char* xn = p->xs + act * (k + 1);
     float* ss = training ? p->scale_shift + (size_t)k * 2 * C : p->scale_shift;
+    if (training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_fused_fwd) {   // conv + BN stats + grid barrier + apply: one launch
+      NRD_TRY(nrd_tc_block_fwd(p, k, st));
+      continue;
+    }
     int blocks = B * 2;
-    if (p->conv_impl == NRD_CONV_TCGEN05) { NRD_TRY(nrd_tc_conv_fwd(p, k, st)); blocks = nrd_tc_stats_blocks(p); }
+    if (p->conv_impl != NRD_CONV_CUDA_CORE) { NRD_TRY(nrd_tc_conv_fwd(p, k, st)); blocks = nrd_tc_stats_blocks(p); }
     else NRD_TRY(conv_fwd_any(xk, p->w_fwd, yk, B, C, dt, training ? p->stats_partial : nullptr, nullptr, st));
     if (training) {
       k_bn_finalize<<<1, 256, 0, st>>>(p->stats_partial, blocks, B * NRD_PIX, C, PRM(P_BNG), PRM(P_BNB),
@@ -1222,7 +1227,7 @@ extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
     char* xk = p->xs + act * k; char* yk = p->ys + act * k;
     NRD_TRY(bn_relu_bwd_any(g, yk, p->scale_shift + (size_t)k * 2 * C, p->saved_stats + (size_t)k * 2 * C, PRM(P_BNG), p->dy,
                             GRD(P_BNG), GRD(P_BNB), !first, B, C, dt, p->bnbwd_scratch, st));
-    if (p->conv_impl == NRD_CONV_TCGEN05) {
+    if (p->conv_impl != NRD_CONV_CUDA_CORE) {
       NRD_TRY(nrd_tc_conv_wgrad(p, k, first, st));
       NRD_TRY(nrd_tc_conv_dgrad(p, g, gn, st));
     } else {
@@ -1231,7 +1236,7 @@ extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
     }
     char* t = g; g = gn; gn = t;
   }
-  NRD_TRY(wgrad_reduce(p->wgrad_partial, B, C, GRD(P_RBW), st));
+  NRD_TRY(wgrad_reduce(p->wgrad_partial, p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B), C, GRD(P_RBW), st));
   NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st));
   return NRD_OK;
 }
@@ -1259,7 +1264,7 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
   float* ss = p->scale_shift + (size_t)k * 2 * C; float* sv = p->saved_stats + (size_t)k * 2 * C;
   switch (op) {
     case NRD_OP_CONV_FWD:
-      if (p->conv_impl == NRD_CONV_TCGEN05) return nrd_tc_conv_fwd(p, k, st);
+      if (p->conv_impl != NRD_CONV_CUDA_CORE) return nrd_tc_conv_fwd(p, k, st);
       return conv_fwd_any(xk, p->w_fwd, yk, B, C, dt, p->stats_partial, nullptr, st);
     case NRD_OP_BN_APPLY: return bn_relu_add_any(yk, xk, ss, p->dxb, B, C, dt, st);
     case NRD_OP_BN_BWD: {
@@ -1267,10 +1272,10 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       return bn_relu_bwd_any(p->dxa, yk, ss, sv, PRM(P_BNG), p->dy, p->h1, p->h1 + C, 0, B, C, dt, p->bnbwd_scratch, st);
     }
     case NRD_OP_WGRAD:
-      if (p->conv_impl == NRD_CONV_TCGEN05) return nrd_tc_conv_wgrad(p, k, 1, st);
+      if (p->conv_impl != NRD_CONV_CUDA_CORE) return nrd_tc_conv_wgrad(p, k, 1, st);
       return wgrad_any(xk, p->dy, p->wgrad_partial, B, C, dt, 1, st);
     case NRD_OP_DGRAD:
-      if (p->conv_impl == NRD_CONV_TCGEN05) return nrd_tc_conv_dgrad(p, p->dxa, p->dxb, st);
+      if (p->conv_impl != NRD_CONV_CUDA_CORE) return nrd_tc_conv_dgrad(p, p->dxa, p->dxb, st);
       return conv_fwd_any(p->dy, p->w_dgrad, p->dxb, B, C, dt, nullptr, p->dxa, st);
     case NRD_OP_STEM_FWD:
       NRD_REQUIRE(p->images_last, "run a forward first");
@@ -1278,6 +1283,9 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
     case NRD_OP_STEM_BWD:
       NRD_REQUIRE(p->images_last, "run a forward first");
       return stem_bwd_any(p->images_last, p->dxa, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st);
+    case NRD_OP_BLOCK_FWD:
+      NRD_REQUIRE(p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_fused_fwd, "fused block forward not available for this plan");
+      return nrd_tc_block_fwd(p, k, st);
     default: nrd_set_error("nrd_plan_run_op: unknown op %d", op); return NRD_EINVAL;
   }
 }

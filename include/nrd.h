@@ -41,7 +41,9 @@ extern "C" {
 
 /* conv implementation selector for NRD_BF16 plans (nrd_plan_set_conv_impl) */
 #define NRD_CONV_CUDA_CORE 0  /* direct conv on CUDA cores (also the only NRD_F32 path) */
-#define NRD_CONV_TCGEN05 1    /* implicit GEMM on tcgen05 tensor cores, TMA-staged NHWC tiles */
+#define NRD_CONV_TCGEN05 1    /* implicit GEMM on tcgen05 tensor cores, TMA-staged NHWC tiles; ResBlock forward fused
+                                 (conv + BN statistics + grid barrier + BN apply + ReLU + residual) when it fits TMEM */
+#define NRD_CONV_TCGEN05_UNFUSED 2 /* same tensor-core kernels, BN as separate kernels (any batch size; cross-check) */
 
 typedef struct nrd_plan nrd_plan; /* opaque: shapes + carved workspace + TMA descriptors */
 
@@ -165,6 +167,8 @@ int nrd_maxpool_bwd(const void* gpooled, const uint8_t* idx, void* gx, int B, in
 #define NRD_OP_DGRAD 4     /* conv input gradient + residual */
 #define NRD_OP_STEM_FWD 5  /* conv1 + relu + pool                        (model/resnet.py:16) */
 #define NRD_OP_STEM_BWD 6
+#define NRD_OP_BLOCK_FWD 7 /* whole ResBlock forward k in one cooperative launch (tcgen05 plans): conv + BN + ReLU + add;
+                              NOTE: applies the running-stat EMA and nbt += 1 like a real forward */
 unsigned long long nrd_launch_count(void);
 int nrd_plan_run_op(nrd_plan* plan, int op, int k, void* stream);
 

@@ -38,12 +38,11 @@ def test_tc_conv_fwd_dgrad_wgrad(B, Cc):
         for op in (OP_CONV_FWD, OP_DGRAD, OP_WGRAD):
             check(lib.nrd_plan_run_op(pl.handle, op, 0, st()), f"run_op {op}")
         torch.cuda.synchronize()
-        nblk = min(2 * B, 148)
         got[name] = dict(
             y=pl.tensor_view(1, 0).view(torch.bfloat16).float().view(B, 16, 16, Cc).cpu(),
             dx=pl.tensor_view(6, 0).view(torch.bfloat16).float().view(B, 16, 16, Cc).cpu(),
-            dw=pl.tensor_view(7, 0).view(torch.float32).view(nblk, 9, Cc, Cc).double().sum(0).cpu(),
-            stats=pl.tensor_view(8, 0).view(torch.float32)[: (2 * B if name == "cc" else nblk) * 2 * Cc].view(-1, 2, Cc).double().sum(0).cpu())
+            dw=pl.tensor_view(7, 0).view(torch.float32).view(-1, 9, Cc, Cc).double().sum(0).cpu(),        # unused CTA slots were zeroed
+            stats=pl.tensor_view(8, 0).view(torch.float32).view(-1, 2, Cc).double().sum(0).cpu())
     xn, dyn, rn = (t.float().permute(0, 3, 1, 2) for t in (x, dy, res))
     if name:   # the CUDA-core path uses fp32 weights, the tensor cores bf16-rounded ones: compare each with its own oracle
         ref_y = F.conv2d(xn.double(), w.double(), padding=1)
@@ -60,3 +59,27 @@ def test_tc_conv_fwd_dgrad_wgrad(B, Cc):
     cc = got["cc"]
     assert rell2(tc["y"], cc["y"]) < 5e-3 and rell2(tc["dx"], cc["dx"]) < 5e-3
     assert relmax(tc["dw"], cc["dw"]) < 1e-4
+
+
+@pytest.mark.parametrize("B,Cc,NB", [(5, 32, 3), (256, 32, 2), (300, 32, 2), (3, 64, 2), (150, 64, 2)])
+def test_fused_block_forward_bitwise_equals_unfused(B, Cc, NB):
+    """conv + BN statistics + grid barrier + BN/ReLU/residual in ONE cooperative kernel (accumulators parked in TMEM)
+    must give bit-identical activations, saved statistics, running statistics and gradients to the same tensor-core
+    convolution followed by the separate finalize / apply kernels."""
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for impl in (_lib.CONV_TCGEN05_UNFUSED, _lib.CONV_TCGEN05):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(Cc, NB, dtype="bf16").to(DEV)
+        m.engine.set_conv_impl(impl)
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        pl = m.engine._last_plan
+        bn = m.resblocks[0].batch_norm
+        res.append((out.detach().clone(), m.engine.flat_grads.clone(), bn.running_mean.clone(), bn.running_var.clone(),
+                    int(bn.num_batches_tracked), pl.tensor_view(0, NB).clone(), pl.tensor_view(1, NB - 1).clone(),
+                    pl.tensor_view(4, NB - 1).clone()))
+    a, b = res
+    assert a[4] == b[4] == NB
+    for i in (0, 1, 2, 3, 5, 6, 7):
+        assert torch.equal(a[i], b[i]), i
