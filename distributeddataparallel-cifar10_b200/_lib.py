@@ -33,6 +33,7 @@ _PROTOS = {
     "nrd_plan_destroy": (i32, [vp]),
     "nrd_plan_set_conv_impl": (i32, [vp, i32]),
     "nrd_plan_conv_impl": (i32, [vp]),
+    "nrd_plan_set_option": (i32, [vp, i32, i32]),
     "nrd_plan_tensor": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)]),
     "nrd_pack_weights": (i32, [vp, vp]),
     "nrd_forward": (i32, [vp, vp, vp, i32, vp]),

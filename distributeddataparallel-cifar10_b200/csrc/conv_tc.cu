@@ -136,24 +136,6 @@ template <int C> struct Cfg {
   static constexpr int NST = 2;                                 // work-item stages
 };
 
-// self-resetting grid-wide barrier (all CTAs co-resident: cooperative launch).  bar[0] = arrival count, bar[1] = generation.
-__device__ __forceinline__ void grid_barrier(unsigned int* bar, unsigned int nblocks) {
-  volatile unsigned int* vgen = bar + 1;
-  const unsigned int gen = *vgen;
-  __threadfence();
-  if (atomicAdd(bar, 1u) == nblocks - 1) {
-    bar[0] = 0;
-    __threadfence();
-    atomicAdd(bar + 1, 1u);
-  } else {
-    long long t0 = clock64();
-    while (*vgen == gen) {
-      if (clock64() - t0 > 4000000000LL) __trap();
-    }
-  }
-  __threadfence();
-}
-
 // recursive-halving warp transpose-reduce: on return lane l holds sum over the 32 lanes of v[l]
 __device__ __forceinline__ float warp_col_sum(float (&v)[32], int lane) {
 #pragma unroll
@@ -340,7 +322,7 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       float* ss_sm = red + 8 * C;                     // [2C] scale | shift
       double* dred = reinterpret_cast<double*>(red + 10 * C);   // [RP][2C], RP*2C = 512
       asm volatile("bar.sync 1, 128;" ::: "memory");  // partial row written
-      if (t == 0) grid_barrier(fa.gbar, gridDim.x);
+      if (t == 0) nrd_grid_barrier(fa.gbar, gridDim.x);
       asm volatile("bar.sync 1, 128;" ::: "memory");
       {
         // partial matrix [gridDim.x][2C] fp32: every thread owns one float4 column chunk and every RP-th row, all loads
@@ -513,11 +495,16 @@ k_tc_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
           float v[32];
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (kx * W::GPK + j) * C + h * 32, v);
           if (ky < 3) {
+            float* dst = outp + ((size_t)tap * C + h * 32) * C + ci;          // [tap][co][ci], co stride = C floats
+            if (!first) {     // all 32 loads first: a load/store chain through possibly-aliasing pointers would serialise
+              float old[32];
 #pragma unroll
-            for (int jj = 0; jj < 32; ++jj) {
-              const size_t o = ((size_t)tap * C + h * 32 + jj) * C + ci;      // [tap][co][ci]
-              outp[o] = first ? v[jj] : outp[o] + v[jj];
+              for (int jj = 0; jj < 32; ++jj) old[jj] = __ldcg(dst + (size_t)jj * C);
+#pragma unroll
+              for (int jj = 0; jj < 32; ++jj) v[jj] += old[jj];
             }
+#pragma unroll
+            for (int jj = 0; jj < 32; ++jj) dst[(size_t)jj * C] = v[jj];
           }
         }
       }
@@ -614,7 +601,6 @@ int nrd_tc_plan_init(nrd_plan* p) {
   // fused block forward: every CTA keeps all its accumulators in TMEM (512 columns) and all CTAs must be co-resident
   const int grid = conv_grid(p), per_cta = (items(p) + grid - 1) / grid * (rows / 8);
   p->tc_fused_fwd = (per_cta * p->C <= 512) ? 1 : 0;
-  NRD_CHECK_CUDA(cudaMemset(p->gbar, 0, 256));
   p->tc_ready = 1;
   return NRD_OK;
 }

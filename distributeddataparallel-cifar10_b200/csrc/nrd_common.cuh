@@ -63,6 +63,7 @@ struct nrd_plan {
   uint8_t* idx2;       // [B,8,8,C]
   float* h1;           // [B,32] relu(fc1)
   float* dh1;          // [B,32]
+  float* fc1_part;     // [K/128][B][32] split-K partial products of fc1
   float* dlogits;      // [B,10]  (train_step path)
   float* loss_rows;    // [B]
   float* saved_stats;  // [NB][2C] mean | invstd
@@ -73,7 +74,7 @@ struct nrd_plan {
   float* stem_partial;
   float* w_fwd;        // [9][C][C] tap-major fp32 (ci rows, co contiguous)
   float* w_dgrad;      // [9][C][C] flipped taps, (co rows, ci contiguous)
-  float* w1p;          // fc1 weight in NHWC column order [32][64*C]
+  float* w1p;          // fc1 weight, k-major transpose in NHWC column order: w1t[64*C][32]
   float* conv1_wp;     // [27][C]
   bf16* wtc_fwd;       // tcgen05 B operand: [Cout][9*Cin] bf16, K-major
   bf16* wtc_dgrad;     // same for dgrad (transposed + flipped)
@@ -83,9 +84,29 @@ struct nrd_plan {
   CUtensorMap tm_dy0;     // dy scratch, plain rows (wgrad)
   CUtensorMap tm_wf, tm_wd;
   int tc_ready;
+  int fuse_bn_bwd;        // BN+ReLU backward as one cooperative kernel when it fits shared memory
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
   unsigned int* gbar;     // grid-barrier words
 };
+
+// self-resetting grid-wide barrier (all CTAs co-resident: cooperative launch).  bar[0] = arrival count, bar[1] = generation.
+// Call from ONE thread per CTA, bracketed by CTA-level barriers.  A spin that lasts ~2 s traps instead of hanging the GPU.
+static __device__ __forceinline__ void nrd_grid_barrier(unsigned int* bar, unsigned int nblocks) {
+  volatile unsigned int* vgen = bar + 1;
+  const unsigned int gen = *vgen;
+  __threadfence();
+  if (atomicAdd(bar, 1u) == nblocks - 1) {
+    bar[0] = 0;
+    __threadfence();
+    atomicAdd(bar + 1, 1u);
+  } else {
+    long long t0 = clock64();
+    while (*vgen == gen) {
+      if (clock64() - t0 > 4000000000LL) __trap();
+    }
+  }
+  __threadfence();
+}
 
 // tcgen05 path (conv_tc.cu)
 int nrd_tc_plan_init(nrd_plan* p);

@@ -59,7 +59,7 @@ __device__ __forceinline__ void st4(bf16* p, const float (&v)[4]) {
 // w_fwd[t][ci][co]   = W[co][ci][ky][kx],            t = ky*3+kx
 // w_dgrad[t][co][ci] = W[co][ci][2-ky][2-kx]  (dgrad is a forward conv of dy with flipped taps)
 // wtc_fwd[co][t*C+ci]  (bf16, K-major B operand), wtc_dgrad[ci][t*C+co] (bf16, flipped taps)
-// w1p[j][hw*C+c]     = fc1.weight[j][c*64+hw]        (flatten order c,h,w -> NHWC order)
+// w1p[hw*C+c][j]     = fc1.weight[j][c*64+hw]        (k-major transpose; flatten order c,h,w -> NHWC order)
 // conv1_wp[k][co]    = conv1.weight[co][k],          k = ci*9+ky*3+kx
 __global__ void k_pack_weights(const float* __restrict__ rb_w, const float* __restrict__ fc1_w,
                                const float* __restrict__ conv1_w, int C, float* __restrict__ w_fwd,
@@ -78,7 +78,7 @@ __global__ void k_pack_weights(const float* __restrict__ rb_w, const float* __re
     } else if (i < n_rb + n_fc1) {
       int q = i - n_rb;
       int j = q / (64 * C), r = q % (64 * C), c = r / 64, hw = r % 64;
-      if (w1p) w1p[(size_t)j * 64 * C + hw * C + c] = fc1_w[q];
+      if (w1p) w1p[((size_t)hw * C + c) * NRD_FC1_OUT + j] = fc1_w[q];   // w1t[k][j], k = NHWC column
     } else {
       int q = i - n_rb - n_fc1;
       int co = q / 27, k = q % 27;
@@ -155,14 +155,18 @@ __global__ void k_stem_fwd(const float* __restrict__ img, const float* __restric
   *reinterpret_cast<uint2*>(idx0 + o) = pk;
 }
 
-// stem backward: dconv1.weight / dconv1.bias only (the input needs no grad).  One CTA loops over
-// images; thread = (co, pixel-group); per-CTA partial [28][C] (27 taps + bias), reduced afterwards.
+// stem backward: dconv1.weight / dconv1.bias only (the input needs no grad).  One CTA loops over images; per image the
+// masked pooled gradient (relu'(0)=0, pool routes to the first max) and the arg-max indices are staged in shared memory
+// with coalesced loads, then thread = (co, pixel-group) accumulates its 27 taps + bias from shared memory only.
+// Per-CTA partial [28][C], reduced afterwards in fixed order.
 template <typename T>
-__global__ void k_stem_bwd(const float* __restrict__ img, const T* __restrict__ g0, const T* __restrict__ x0,
+__global__ void __launch_bounds__(256) k_stem_bwd(const float* __restrict__ img, const T* __restrict__ g0, const T* __restrict__ x0,
                            const uint8_t* __restrict__ idx0, float* __restrict__ partial, int B, int C) {
   extern __shared__ float sm[];
   float* tile = sm;                       // [3][34][35] zero-padded image
-  float* red = sm + 3 * 34 * 35;          // [ngroups][28][C]
+  float* gm = sm + 3 * 34 * 35 + 2;       // [256][C] masked gradient (16-B aligned: 3570+2 floats)
+  uint8_t* im_idx = reinterpret_cast<uint8_t*>(gm + 256 * C);   // [256][C]
+  float* red = gm;                        // reused at the end: [ngroups][28][C]  (ngroups*28 <= 256)
   const int tid = threadIdx.x, nt = blockDim.x, co = tid % C, grp = tid / C, ngrp = nt / C;
   float acc[28];
 #pragma unroll
@@ -176,13 +180,19 @@ __global__ void k_stem_bwd(const float* __restrict__ img, const T* __restrict__ 
       if (r >= 1 && r <= 32 && c >= 1 && c <= 32) v = im[ci * 1024 + (r - 1) * 32 + (c - 1)];
       tile[(ci * 34 + r) * 35 + c] = v;
     }
+    const size_t base = (size_t)b * 256 * C;
+    for (int i = tid; i < 256 * C / 8; i += nt) {
+      float gv[8], xv[8];
+      ld8(g0 + base + (size_t)i * 8, gv); ld8(x0 + base + (size_t)i * 8, xv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) gm[i * 8 + j] = xv[j] > 0.f ? gv[j] : 0.f;
+      *reinterpret_cast<uint2*>(im_idx + (size_t)i * 8) = *reinterpret_cast<const uint2*>(idx0 + base + (size_t)i * 8);
+    }
     __syncthreads();
     for (int px = grp; px < 256; px += ngrp) {
-      size_t o = ((size_t)b * 256 + px) * C + co;
-      float xv = to_f(x0[o]);
-      float g = (xv > 0.f) ? to_f(g0[o]) : 0.f;    // relu'(0) = 0; pool routes to the first max
-      int id = idx0[o];
-      int h = 2 * (px / 16) + (id >> 1), w = 2 * (px % 16) + (id & 1);   // conv-output position
+      const float g = gm[px * C + co];
+      const int id = im_idx[px * C + co];
+      const int h = 2 * (px / 16) + (id >> 1), w = 2 * (px % 16) + (id & 1);   // conv-output position
       acc[27] += g;
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci)
@@ -204,14 +214,23 @@ __global__ void k_stem_bwd(const float* __restrict__ img, const T* __restrict__ 
   }
 }
 
-__global__ void k_stem_bwd_reduce(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dw,
+// CTA = 32 outputs x 8 row classes, fixed-order combine
+__global__ void __launch_bounds__(256) k_stem_bwd_reduce(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dw,
                                   float* __restrict__ db) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 28 * C) return;
+  __shared__ double red[8][33];
+  const int o = threadIdx.x & 31, r = threadIdx.x >> 5, i = blockIdx.x * 32 + o, n = 28 * C;
   double s = 0.0;
-  for (int b = 0; b < nblk; ++b) s += (double)partial[(size_t)b * 28 * C + i];
-  int k = i / C, co = i % C;
-  if (k < 27) dw[co * 27 + k] = (float)s; else db[co] = (float)s;
+#pragma unroll 8
+  for (int b = r; b < nblk; b += 8) s += (double)__ldcg(partial + (size_t)b * n + i);
+  red[r][o] = s;
+  __syncthreads();
+  if (r == 0) {
+    double tot = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) tot += red[k][o];
+    int k = i / C, co = i % C;
+    if (k < 27) dw[co * 27 + k] = (float)tot; else db[co] = (float)tot;
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -354,33 +373,61 @@ __global__ void __launch_bounds__(256) k_wgrad(const T* __restrict__ x, const T*
     }
 }
 
-// dW[co][ci][t] (OIHW) = sum_blk partial[blk][t][co][ci]
-__global__ void k_wgrad_reduce(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dw) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 9 * C * C) return;
+// dW[co][ci][t] (OIHW) = sum_blk partial[blk][t][co][ci].  CTA = 32 outputs x 8 row classes, fixed-order combine.
+__global__ void __launch_bounds__(256) k_wgrad_reduce(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dw) {
+  __shared__ double red[8][33];
+  const int o = threadIdx.x & 31, r = threadIdx.x >> 5, i = blockIdx.x * 32 + o, n = 9 * C * C;
   double s = 0.0;
-  for (int b = 0; b < nblk; ++b) s += (double)partial[(size_t)b * 9 * C * C + i];
-  int t = i / (C * C), co = (i / C) % C, ci = i % C;
-  dw[((size_t)co * C + ci) * 9 + t] = (float)s;
+#pragma unroll 8
+  for (int b = r; b < nblk; b += 8) s += (double)__ldcg(partial + (size_t)b * n + i);
+  red[r][o] = s;
+  __syncthreads();
+  if (r == 0) {
+    double tot = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) tot += red[k][o];
+    int t = i / (C * C), co = (i / C) % C, ci = i % C;
+    dw[((size_t)co * C + ci) * 9 + t] = (float)tot;
+  }
 }
 
 // ------------------------------------------------------------------------------------------
 // BatchNorm2d (training) forward pieces                                 (model/resnet.py:35-37)
 // ------------------------------------------------------------------------------------------
+// Column sums of a per-CTA partial matrix [rows][2C] (fp32) in fp64, fixed order, by one CTA of 256 threads: every
+// thread owns one float4 column chunk and every RP-th row (all loads independent: one L2 round trip), then the RP row
+// classes are combined in order.  On return dsum[0..2C) (shared) holds the sums.
+template <int NT>
+__device__ __forceinline__ void combine_partials(const float* __restrict__ partial, int rows, int C, double* dsum /*[NT*4]*/) {
+  const int t = threadIdx.x, NC4 = 2 * C / 4, RP = NT / NC4, c4 = t % NC4, r = t / NC4;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 8
+  for (int row = r; row < rows; row += RP) {
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)row * 2 * C) + c4);
+    a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+  }
+  double* d = dsum + (size_t)r * 2 * C + c4 * 4;
+  d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
+  __syncthreads();
+  double tot = 0.0;
+  if (t < 2 * C) {
+    for (int k = 0; k < RP; ++k) tot += dsum[(size_t)k * 2 * C + t];
+  }
+  __syncthreads();
+  if (t < 2 * C) dsum[t] = tot;
+  __syncthreads();
+}
+
 // finalize: partial [blocks][2C] -> mean, invstd (saved), scale/shift, running-stat EMA, nbt += 1
-__global__ void k_bn_finalize(const float* __restrict__ partial, int blocks, int count, int C,
+__global__ void __launch_bounds__(256) k_bn_finalize(const float* __restrict__ partial, int blocks, int count, int C,
                               const float* __restrict__ gamma, const float* __restrict__ beta,
                               float* __restrict__ saved, float* __restrict__ scale_shift,
                               float* __restrict__ running, int64_t* __restrict__ nbt) {
-  __shared__ double red[256];
-  const int tid = threadIdx.x, ncol = 2 * C, col = tid % ncol, slice = tid / ncol, nslice = 256 / ncol;
-  double s = 0.0;
-  for (int i = slice; i < blocks; i += nslice) s += (double)partial[(size_t)i * ncol + col];
-  red[tid] = s;
-  __syncthreads();
+  __shared__ double dsum[1024];
+  combine_partials<256>(partial, blocks, C, dsum);
+  const int tid = threadIdx.x;
   if (tid < C) {
-    double S = 0.0, Q = 0.0;
-    for (int k = 0; k < nslice; ++k) { S += red[k * ncol + tid]; Q += red[k * ncol + C + tid]; }
+    const double S = dsum[tid], Q = dsum[C + tid];
     double mean = S / count, var = Q / count - mean * mean;
     if (var < 0.0) var = 0.0;
     float invstd = (float)(1.0 / sqrt(var + (double)NRD_BN_EPS));
@@ -467,19 +514,15 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(const T* __restrict__ g, 
 }
 
 // partial [blocks][2C] -> dbeta/dgamma (set or accumulate) + coefficients coef[3][C] = {gamma*invstd, dbeta/n, dgamma/n}
-__global__ void k_bn_bwd_finalize(const float* __restrict__ partial, int blocks, int count, int C,
+__global__ void __launch_bounds__(256) k_bn_bwd_finalize(const float* __restrict__ partial, int blocks, int count, int C,
                                   const float* __restrict__ gamma, const float* __restrict__ saved,
                                   float* __restrict__ dgamma, float* __restrict__ dbeta, int accumulate,
                                   float* __restrict__ coef) {
-  __shared__ double red[256];
-  const int tid = threadIdx.x, ncol = 2 * C, col = tid % ncol, slice = tid / ncol, nslice = 256 / ncol;
-  double s = 0.0;
-  for (int i = slice; i < blocks; i += nslice) s += (double)partial[(size_t)i * ncol + col];
-  red[tid] = s;
-  __syncthreads();
+  __shared__ double dsum[1024];
+  combine_partials<256>(partial, blocks, C, dsum);
+  const int tid = threadIdx.x;
   if (tid < C) {
-    double db = 0.0, dg = 0.0;
-    for (int k = 0; k < nslice; ++k) { db += red[k * ncol + tid]; dg += red[k * ncol + C + tid]; }
+    const double db = dsum[tid], dg = dsum[C + tid];
     if (accumulate) { dbeta[tid] += (float)db; dgamma[tid] += (float)dg; }
     else { dbeta[tid] = (float)db; dgamma[tid] = (float)dg; }
     coef[tid] = gamma[tid] * saved[C + tid];
@@ -511,6 +554,98 @@ __global__ void k_bn_bwd_apply(const T* __restrict__ g, const T* __restrict__ y,
       o[j] = p[4 * C + c] * (dz - p[5 * C + c] - xh * p[6 * C + c]);
     }
     st8(dy + i * 8, o);
+  }
+}
+
+// Fused BN + ReLU backward (cooperative launch, grid <= #SMs, every CTA owns <= IPC whole images which it keeps in shared
+// memory between the two phases): phase 1 stages g and y and takes the per-CTA sums, a grid barrier publishes them, every
+// CTA combines all partial rows in the same fixed order, phase 2 produces dy from shared memory.  One launch and 3T of HBM
+// traffic instead of three launches and 5T.
+template <typename T>
+__global__ void __launch_bounds__(256, 1) k_bn_bwd_fused(const T* __restrict__ g, const T* __restrict__ y,
+                                                         const float* __restrict__ scale_shift, const float* __restrict__ saved,
+                                                         const float* __restrict__ gamma, T* __restrict__ dy,
+                                                         float* __restrict__ dgamma, float* __restrict__ dbeta, int accumulate,
+                                                         float* __restrict__ partial, unsigned int* gbar, int B, int C, int ipc) {
+  extern __shared__ __align__(16) uint8_t smraw[];
+  const int img_elems = NRD_PIX * C;
+  T* gs = reinterpret_cast<T*>(smraw);
+  T* ys = gs + (size_t)ipc * img_elems;
+  double* dsum = reinterpret_cast<double*>(ys + (size_t)ipc * img_elems);   // [1024]
+  float* red = reinterpret_cast<float*>(dsum + 1024);                       // [4096]
+  float* coef = red + 4096;                                                 // [3C]
+  const int tid = threadIdx.x, ncg = C / 8, cg = tid % ncg, pr = tid / ncg, nrow = 256 / ncg;
+  float sc[8], sh[8], mu[8], is[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale_shift[cg * 8 + j]; sh[j] = scale_shift[C + cg * 8 + j];
+    mu[j] = saved[cg * 8 + j]; is[j] = saved[C + cg * 8 + j];
+  }
+  float s1[8], s2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+  const int chunks = img_elems / 8;          // 16-B (bf16) / 32-B (fp32) chunks per image; chunk % ncg == cg for this thread
+  for (int i = 0; i < ipc; ++i) {
+    const int b = blockIdx.x + i * gridDim.x;
+    if (b >= B) break;
+    const size_t base = (size_t)b * img_elems;
+#pragma unroll 4
+    for (int ch = tid; ch < chunks; ch += 256) {
+      float gv[8], yv[8];
+      ld8(g + base + (size_t)ch * 8, gv); ld8(y + base + (size_t)ch * 8, yv);
+      st8(gs + (size_t)i * img_elems + (size_t)ch * 8, gv); st8(ys + (size_t)i * img_elems + (size_t)ch * 8, yv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float z = fmaf(yv[j], sc[j], sh[j]);
+        float dz = z > 0.f ? gv[j] : 0.f;
+        s1[j] += dz; s2[j] = fmaf(dz, (yv[j] - mu[j]) * is[j], s2[j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { red[(pr * 2 + 0) * C + cg * 8 + j] = s1[j]; red[(pr * 2 + 1) * C + cg * 8 + j] = s2[j]; }
+  __syncthreads();
+  if (tid < 2 * C) {
+    float t = 0.f;
+    for (int r = 0; r < nrow; ++r) t += red[r * 2 * C + tid];
+    partial[(size_t)blockIdx.x * 2 * C + tid] = t;
+  }
+  __syncthreads();
+  if (tid == 0) nrd_grid_barrier(gbar, gridDim.x);
+  __syncthreads();
+  combine_partials<256>(partial, gridDim.x, C, dsum);
+  const int count = B * NRD_PIX;
+  if (tid < C) {
+    const double db = dsum[tid], dg = dsum[C + tid];
+    if (blockIdx.x == 0) {
+      if (accumulate) { dbeta[tid] += (float)db; dgamma[tid] += (float)dg; }
+      else { dbeta[tid] = (float)db; dgamma[tid] = (float)dg; }
+    }
+    coef[tid] = gamma[tid] * saved[C + tid];
+    coef[C + tid] = (float)(db / count);
+    coef[2 * C + tid] = (float)(dg / count);
+  }
+  __syncthreads();
+  float ca[8], cb[8], cc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { ca[j] = coef[cg * 8 + j]; cb[j] = coef[C + cg * 8 + j]; cc[j] = coef[2 * C + cg * 8 + j]; }
+  for (int i = 0; i < ipc; ++i) {
+    const int b = blockIdx.x + i * gridDim.x;
+    if (b >= B) break;
+    const size_t base = (size_t)b * img_elems;
+#pragma unroll 4
+    for (int ch = tid; ch < chunks; ch += 256) {
+      float gv[8], yv[8], o[8];
+      ld8(gs + (size_t)i * img_elems + (size_t)ch * 8, gv); ld8(ys + (size_t)i * img_elems + (size_t)ch * 8, yv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float z = fmaf(yv[j], sc[j], sh[j]);
+        float dz = z > 0.f ? gv[j] : 0.f;
+        float xh = (yv[j] - mu[j]) * is[j];
+        o[j] = ca[j] * (dz - cb[j] - xh * cc[j]);
+      }
+      st8(dy + base + (size_t)ch * 8, o);
+    }
   }
 }
 
@@ -561,48 +696,59 @@ __global__ void k_maxpool_bwd(const T* __restrict__ gp, const uint8_t* __restric
 // ------------------------------------------------------------------------------------------
 // head: fc1 + relu, fc2, softmax cross-entropy                     (model/resnet.py:19-21, main.py:28)
 // ------------------------------------------------------------------------------------------
-// h1[b][j] = relu(sum_i p[b][i] * w1p[j][i] + b1[j]); CTA = 8 batch rows, warp = 4 outputs
+// fc1 as a split-K product: CTA (bx, ks) = 32 batch rows x 32 outputs over the K slice [ks*128, ks*128+128);
+// part[ks][b][j] = sum_{k in slice} p[b][k] * w1t[k][j].  The slices are summed in order by k_fc2_fwd.
 template <typename T>
-__global__ void __launch_bounds__(256) k_fc1_fwd(const T* __restrict__ p, const float* __restrict__ w1p,
-                                                 const float* __restrict__ b1, float* __restrict__ h1, int B, int K) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, b0 = blockIdx.x * 8, j0 = warp * 4;
-  float acc[8][4];
-#pragma unroll
-  for (int r = 0; r < 8; ++r) acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f;
-  for (int i = lane * 4; i < K; i += 128) {
-    float w[4][4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) ld4(w1p + (size_t)(j0 + j) * K + i, w[j]);
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      if (b0 + r < B) {
-        float pv[4]; ld4(p + (size_t)(b0 + r) * K + i, pv);
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          acc[r][j] += pv[0] * w[j][0] + pv[1] * w[j][1] + pv[2] * w[j][2] + pv[3] * w[j][3];
-      }
-    }
+__global__ void __launch_bounds__(256) k_fc1_fwd_part(const T* __restrict__ p, const float* __restrict__ w1t,
+                                                      float* __restrict__ part, int B, int K) {
+  __shared__ __align__(16) float ws[128 * 32];
+  __shared__ float ps[32 * 129];
+  const int tid = threadIdx.x, b0 = blockIdx.x * 32, k0 = blockIdx.y * 128;
+  for (int i = tid; i < 128 * 32 / 4; i += 256)
+    reinterpret_cast<float4*>(ws)[i] = reinterpret_cast<const float4*>(w1t + (size_t)k0 * 32)[i];
+  for (int i = tid; i < 32 * 32; i += 256) {          // 32 rows x 32 four-element chunks
+    int r = i >> 5, c4 = i & 31;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (b0 + r < B) ld4(p + (size_t)(b0 + r) * K + k0 + c4 * 4, v);
+    float* d = ps + r * 129 + c4 * 4;
+    d[0] = v[0]; d[1] = v[1]; d[2] = v[2]; d[3] = v[3];
   }
-#pragma unroll
-  for (int r = 0; r < 8; ++r)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float v = acc[r][j];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0 && b0 + r < B) h1[(size_t)(b0 + r) * NRD_FC1_OUT + j0 + j] = fmaxf(v + b1[j0 + j], 0.f);
-    }
+  __syncthreads();
+  const int r = tid >> 3, jq = tid & 7;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 8
+  for (int k = 0; k < 128; ++k) {
+    const float pv = ps[r * 129 + k];
+    const float4 w = *reinterpret_cast<const float4*>(ws + k * 32 + jq * 4);
+    a0 = fmaf(pv, w.x, a0); a1 = fmaf(pv, w.y, a1); a2 = fmaf(pv, w.z, a2); a3 = fmaf(pv, w.w, a3);
+  }
+  if (b0 + r < B)
+    *reinterpret_cast<float4*>(part + ((size_t)blockIdx.y * B + b0 + r) * NRD_FC1_OUT + jq * 4) = make_float4(a0, a1, a2, a3);
 }
 
-__global__ void k_fc2_fwd(const float* __restrict__ h1, const float* __restrict__ w2, const float* __restrict__ b2,
-                          float* __restrict__ logits, int B) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B * NRD_NCLS) return;
-  int b = i / NRD_NCLS, c = i % NRD_NCLS;
-  float s = b2[c];
+// h1 = relu(sum_ks part + b1) (stored for backward), logits = h1 @ w2^T + b2.  CTA = 8 batch rows.
+__global__ void __launch_bounds__(256) k_fc2_fwd(const float* __restrict__ part, int nsplit, const float* __restrict__ b1,
+                                                 const float* __restrict__ w2, const float* __restrict__ b2,
+                                                 float* __restrict__ h1, float* __restrict__ logits, int B) {
+  __shared__ float hs[8][33];
+  const int tid = threadIdx.x, r = tid >> 5, j = tid & 31, b = blockIdx.x * 8 + r;
+  float h = 0.f;
+  if (b < B) {
+    for (int s = 0; s < nsplit; ++s) h += part[((size_t)s * B + b) * NRD_FC1_OUT + j];
+    h = fmaxf(h + b1[j], 0.f);
+    h1[(size_t)b * NRD_FC1_OUT + j] = h;
+  }
+  hs[r][j] = h;
+  __syncthreads();
+  if (tid < 8 * NRD_NCLS) {
+    const int rr = tid / NRD_NCLS, c = tid % NRD_NCLS, bb = blockIdx.x * 8 + rr;
+    if (bb < B) {
+      float sacc = b2[c];
 #pragma unroll
-  for (int j = 0; j < NRD_FC1_OUT; ++j) s = fmaf(h1[b * NRD_FC1_OUT + j], w2[c * NRD_FC1_OUT + j], s);
-  logits[i] = s;
+      for (int jj = 0; jj < NRD_FC1_OUT; ++jj) sacc = fmaf(hs[rr][jj], w2[c * NRD_FC1_OUT + jj], sacc);
+      logits[(size_t)bb * NRD_NCLS + c] = sacc;
+    }
+  }
 }
 
 // per-row loss and dlogits = (softmax - onehot) * grad_scale / B
@@ -647,70 +793,107 @@ __global__ void k_fc2_bwd(const float* __restrict__ dlogits, const float* __rest
   dh1[i] = h1[i] > 0.f ? s : 0.f;
 }
 
-// dW2[c][j], db2[c], dbfc1[j]: one CTA of 384 threads, each output summed over the batch in order
-__global__ void k_head_wgrad(const float* __restrict__ dlogits, const float* __restrict__ h1,
+// dW2[c][j], db2[c], dbfc1[j]: one CTA of 384 threads, each output summed over the batch in order; the batch is staged
+// through shared memory in chunks of 64 rows (coalesced loads, then shared-memory-only loops)
+__global__ void __launch_bounds__(384) k_head_wgrad(const float* __restrict__ dlogits, const float* __restrict__ h1,
                              const float* __restrict__ dh1, int B, float* __restrict__ dw2,
                              float* __restrict__ db2, float* __restrict__ dbfc1) {
-  int t = threadIdx.x;
+  __shared__ float dl[64 * NRD_NCLS], hh[64 * NRD_FC1_OUT], dd[64 * NRD_FC1_OUT];
+  const int t = threadIdx.x;
   float s = 0.f;
-  if (t < 320) {
-    int c = t / 32, j = t % 32;
-    for (int b = 0; b < B; ++b) s = fmaf(dlogits[b * NRD_NCLS + c], h1[b * NRD_FC1_OUT + j], s);
-    dw2[t] = s;
-  } else if (t < 330) {
-    int c = t - 320;
-    for (int b = 0; b < B; ++b) s += dlogits[b * NRD_NCLS + c];
-    db2[c] = s;
-  } else if (t < 362) {
-    int j = t - 330;
-    for (int b = 0; b < B; ++b) s += dh1[b * NRD_FC1_OUT + j];
-    dbfc1[j] = s;
+  for (int b0 = 0; b0 < B; b0 += 64) {
+    const int nb = min(64, B - b0);
+    __syncthreads();
+    for (int i = t; i < nb * NRD_NCLS; i += 384) dl[i] = dlogits[(size_t)b0 * NRD_NCLS + i];
+    for (int i = t; i < nb * NRD_FC1_OUT; i += 384) { hh[i] = h1[(size_t)b0 * NRD_FC1_OUT + i]; dd[i] = dh1[(size_t)b0 * NRD_FC1_OUT + i]; }
+    __syncthreads();
+    if (t < 320) {
+      const int c = t / 32, j = t % 32;
+      for (int b = 0; b < nb; ++b) s = fmaf(dl[b * NRD_NCLS + c], hh[b * NRD_FC1_OUT + j], s);
+    } else if (t < 330) {
+      const int c = t - 320;
+      for (int b = 0; b < nb; ++b) s += dl[b * NRD_NCLS + c];
+    } else if (t < 362) {
+      const int j = t - 330;
+      for (int b = 0; b < nb; ++b) s += dd[b * NRD_FC1_OUT + j];
+    }
   }
+  if (t < 320) dw2[t] = s;
+  else if (t < 330) db2[t - 320] = s;
+  else if (t < 362) dbfc1[t - 330] = s;
 }
 
-// dWfc1[j][c*64+hw] = sum_b dh1[b][j] * p[b][hw*C+c].  CTA = 64 consecutive NHWC columns x 32 rows.
+// dWfc1[j][c*64+hw] = sum_b dh1[b][j] * p[b][hw*C+c].  CTA = 64 consecutive NHWC columns x 32 rows; the batch is staged
+// through shared memory in chunks of 64 rows.
 template <typename T>
 __global__ void __launch_bounds__(256) k_fc1_wgrad(const T* __restrict__ p, const float* __restrict__ dh1,
                                                    float* __restrict__ dw1, int B, int C) {
-  __shared__ float ds[256 * NRD_FC1_OUT];
-  const int tid = threadIdx.x, il = tid % 64, jg = tid / 64, K = 64 * C, i = blockIdx.x * 64 + il;
+  __shared__ __align__(16) float ds[64 * NRD_FC1_OUT];
+  __shared__ float ps[64 * 64];
+  const int tid = threadIdx.x, il = tid % 64, jg = tid / 64, K = 64 * C, i0 = blockIdx.x * 64;
   float acc[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-  for (int bb = 0; bb < B; bb += 256) {
-    int nb = min(256, B - bb);
+  for (int bb = 0; bb < B; bb += 64) {
+    const int nb = min(64, B - bb);
     __syncthreads();
     for (int q = tid; q < nb * NRD_FC1_OUT; q += 256) ds[q] = dh1[(size_t)bb * NRD_FC1_OUT + q];
+    for (int q = tid; q < nb * 16; q += 256) {          // 64 rows x 16 four-element chunks
+      int r = q >> 4, c4 = q & 15;
+      float v[4]; ld4(p + (size_t)(bb + r) * K + i0 + c4 * 4, v);
+      float* d = ps + r * 64 + c4 * 4;
+      d[0] = v[0]; d[1] = v[1]; d[2] = v[2]; d[3] = v[3];
+    }
     __syncthreads();
+#pragma unroll 4
     for (int b = 0; b < nb; ++b) {
-      float pv = to_f(p[(size_t)(bb + b) * K + i]);
+      const float pv = ps[b * 64 + il];
       const float4* d4 = reinterpret_cast<const float4*>(ds + b * NRD_FC1_OUT + jg * 8);
-      float4 a = d4[0], c4 = d4[1];
+      const float4 a = d4[0], c4 = d4[1];
       acc[0] = fmaf(pv, a.x, acc[0]); acc[1] = fmaf(pv, a.y, acc[1]); acc[2] = fmaf(pv, a.z, acc[2]); acc[3] = fmaf(pv, a.w, acc[3]);
       acc[4] = fmaf(pv, c4.x, acc[4]); acc[5] = fmaf(pv, c4.y, acc[5]); acc[6] = fmaf(pv, c4.z, acc[6]); acc[7] = fmaf(pv, c4.w, acc[7]);
     }
   }
-  int hw = i / C, c = i % C;
+  const int i = i0 + il, hw = i / C, c = i % C;
 #pragma unroll
   for (int e = 0; e < 8; ++e) dw1[(size_t)(jg * 8 + e) * K + c * 64 + hw] = acc[e];
 }
 
-// d(pooled)[b][hw][c] = sum_j dh1[b][j] * w1p[j][hw*C+c], scattered through pool-2's argmax into gx [B,16,16,C]
+// d(pooled)[b][hw][c] = sum_j dh1[b][j] * w1t[hw*C+c][j], scattered through pool-2's argmax into gx [B,16,16,C].
+// CTA = 8 batch rows x 256 columns: each weight row is read once per 8 rows.
 template <typename T>
-__global__ void __launch_bounds__(256) k_fc1_dgrad_unpool(const float* __restrict__ dh1, const float* __restrict__ w1p,
+__global__ void __launch_bounds__(256) k_fc1_dgrad_unpool(const float* __restrict__ dh1, const float* __restrict__ w1t,
                                                           const uint8_t* __restrict__ idx2, T* __restrict__ gx,
                                                           int B, int C) {
-  __shared__ float d[NRD_FC1_OUT];
-  const int K = 64 * C, per_b = K / 256, b = blockIdx.x / per_b, i = (blockIdx.x % per_b) * 256 + threadIdx.x;
-  if (threadIdx.x < NRD_FC1_OUT) d[threadIdx.x] = dh1[(size_t)b * NRD_FC1_OUT + threadIdx.x];
+  __shared__ float d[8][NRD_FC1_OUT];
+  const int K = 64 * C, per_b = K / 256, b0 = (blockIdx.x / per_b) * 8, i = (blockIdx.x % per_b) * 256 + threadIdx.x;
+  {
+    const int r = threadIdx.x >> 5, j = threadIdx.x & 31;
+    d[r][j] = (b0 + r < B) ? dh1[(size_t)(b0 + r) * NRD_FC1_OUT + j] : 0.f;
+  }
   __syncthreads();
-  float s = 0.f;
-#pragma unroll 8
-  for (int j = 0; j < NRD_FC1_OUT; ++j) s = fmaf(d[j], w1p[(size_t)j * K + i], s);
-  int hw = i / C, c = i % C, ph = hw / 8, pw = hw % 8, id = idx2[(size_t)b * K + i];
+  float s[8];
 #pragma unroll
-  for (int q = 0; q < 4; ++q)
-    gx[(((size_t)b * 16 + 2 * ph + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + c] = from_f<T>(q == id ? s : 0.f);
+  for (int r = 0; r < 8; ++r) s[r] = 0.f;
+  const float4* wrow = reinterpret_cast<const float4*>(w1t + (size_t)i * NRD_FC1_OUT);
+#pragma unroll
+  for (int j4 = 0; j4 < 8; ++j4) {
+    const float4 w = wrow[j4];
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+      s[r] += d[r][j4 * 4] * w.x + d[r][j4 * 4 + 1] * w.y + d[r][j4 * 4 + 2] * w.z + d[r][j4 * 4 + 3] * w.w;
+  }
+  const int hw = i / C, c = i % C, ph = hw / 8, pw = hw % 8;
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const int b = b0 + r;
+    if (b < B) {
+      const int id = idx2[(size_t)b * K + i];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        gx[(((size_t)b * 16 + 2 * ph + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + c] = from_f<T>(q == id ? s[r] : 0.f);
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -848,7 +1031,7 @@ static int wgrad_any(const void* x, const void* dy, float* partial, int B, int C
   return dt == NRD_F32 ? launch_wgrad<float>(x, dy, partial, B, C, first, st) : launch_wgrad<bf16>(x, dy, partial, B, C, first, st);
 }
 static int wgrad_reduce(const float* partial, int nblk, int C, float* dw, cudaStream_t st) {
-  k_wgrad_reduce<<<(9 * C * C + 255) / 256, 256, 0, st>>>(partial, nblk, C, dw);
+  k_wgrad_reduce<<<9 * C * C / 32, 256, 0, st>>>(partial, nblk, C, dw);
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -862,10 +1045,34 @@ static int bn_relu_add_any(const void* y, const void* x, const float* ss, void* 
   return NRD_OK;
 }
 
-// scratch layout: [B][2C] partials | coef [3C]
+static size_t bn_bwd_fused_smem(int B, int C, int dt, int* grid_out, int* ipc_out) {
+  const int grid = B < NRD_NUM_SMS ? B : NRD_NUM_SMS, ipc = (B + grid - 1) / grid;
+  if (grid_out) *grid_out = grid;
+  if (ipc_out) *ipc_out = ipc;
+  return (size_t)ipc * 2 * NRD_PIX * C * (dt == NRD_F32 ? 4 : 2) + 1024 * sizeof(double) + (4096 + 3 * 64) * sizeof(float);
+}
+
+// scratch layout: [B][2C] partials | coef [3C].  gbar != NULL selects the one-launch cooperative kernel when it fits.
 static int bn_relu_bwd_any(const void* g, const void* y, const float* ss, const float* saved, const float* gamma, void* dy,
-                           float* dgamma, float* dbeta, int accumulate, int B, int C, int dt, float* scratch, cudaStream_t st) {
+                           float* dgamma, float* dbeta, int accumulate, int B, int C, int dt, float* scratch, cudaStream_t st,
+                           unsigned int* gbar = nullptr) {
   float* partial = scratch; float* coef = scratch + (size_t)B * 2 * C;
+  int grid = 0, ipc = 0;
+  const size_t fsmem = bn_bwd_fused_smem(B, C, dt, &grid, &ipc);
+  if (gbar && fsmem <= 200 * 1024) {
+    void* args[] = {(void*)&g, (void*)&y, (void*)&ss, (void*)&saved, (void*)&gamma, (void*)&dy, (void*)&dgamma, (void*)&dbeta,
+                    (void*)&accumulate, (void*)&partial, (void*)&gbar, (void*)&B, (void*)&C, (void*)&ipc};
+    static bool done32[64], done16[64];
+    if (dt == NRD_F32) {
+      NRD_TRY(set_smem_once(k_bn_bwd_fused<float>, 200 * 1024, done32));
+      NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_bn_bwd_fused<float>, dim3(grid), dim3(256), args, fsmem, st));
+    } else {
+      NRD_TRY(set_smem_once(k_bn_bwd_fused<bf16>, 200 * 1024, done16));
+      NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_bn_bwd_fused<bf16>, dim3(grid), dim3(256), args, fsmem, st));
+    }
+    nrd_count_launch();
+    return NRD_OK;
+  }
   if (dt == NRD_F32) k_bn_bwd_reduce<float><<<B, 256, 0, st>>>((const float*)g, (const float*)y, ss, saved, partial, C);
   else k_bn_bwd_reduce<bf16><<<B, 256, 0, st>>>((const bf16*)g, (const bf16*)y, ss, saved, partial, C);
   LAUNCH_CHECK();
@@ -890,11 +1097,16 @@ static int stem_fwd_any(const float* img, const float* wp, const float* bias, vo
 static int stem_bwd_any(const float* img, const void* g0, const void* x0, const uint8_t* idx0, float* dw, float* db, int B, int C,
                         int dt, float* partial, cudaStream_t st) {
   int nblk = stem_bwd_blocks(B);
-  size_t smem = (3 * 34 * 35 + (256 / C) * 28 * C) * sizeof(float);
+  size_t smem = (3 * 34 * 35 + 2 + 256 * C) * sizeof(float) + 256 * C;
+  {
+    static bool done32[64], done16[64];
+    if (dt == NRD_F32) NRD_TRY(set_smem_once(k_stem_bwd<float>, (3 * 34 * 35 + 2 + 256 * 64) * sizeof(float) + 256 * 64, done32));
+    else NRD_TRY(set_smem_once(k_stem_bwd<bf16>, (3 * 34 * 35 + 2 + 256 * 64) * sizeof(float) + 256 * 64, done16));
+  }
   if (dt == NRD_F32) k_stem_bwd<float><<<nblk, 256, smem, st>>>(img, (const float*)g0, (const float*)x0, idx0, partial, B, C);
   else k_stem_bwd<bf16><<<nblk, 256, smem, st>>>(img, (const bf16*)g0, (const bf16*)x0, idx0, partial, B, C);
   LAUNCH_CHECK();
-  k_stem_bwd_reduce<<<(28 * C + 255) / 256, 256, 0, st>>>(partial, nblk, C, dw, db);
+  k_stem_bwd_reduce<<<28 * C / 32, 256, 0, st>>>(partial, nblk, C, dw, db);
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1063,6 +1275,7 @@ static void carve(nrd_plan* p, char* base, size_t* total) {
   p->idx2 = cv.take<uint8_t>(p->act_elems / 4);
   p->h1 = cv.take<float>((size_t)B * NRD_FC1_OUT * 4);
   p->dh1 = cv.take<float>((size_t)B * NRD_FC1_OUT * 4);
+  p->fc1_part = cv.take<float>((size_t)(64 * C / 128) * B * NRD_FC1_OUT * 4);
   p->dlogits = cv.take<float>((size_t)B * NRD_NCLS * 4);
   p->loss_rows = cv.take<float>((size_t)B * 4);
   p->saved_stats = cv.take<float>((size_t)NB * 2 * C * 4);
@@ -1110,8 +1323,11 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   if (total > workspace_bytes) { delete p; nrd_set_error("workspace too small: need %zu bytes, got %zu", total, workspace_bytes); return NRD_EINVAL; }
   p->device = device; p->params = params; p->grads = grads; p->bn_running = bn_running; p->nbt = nbt;
   p->conv_impl = NRD_CONV_CUDA_CORE;
+  p->fuse_bn_bwd = 1;
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
+  e = cudaMemset(p->gbar, 0, 256);
+  if (e != cudaSuccess) { delete p; nrd_set_error("cudaMemset(grid barrier): %s", cudaGetErrorString(e)); return NRD_ECUDA; }
   if (dtype == NRD_BF16) {
     r = nrd_tc_plan_init(p);
     if (r != NRD_OK) { delete p; return r; }   // no silent fallback: the bf16 product path IS the tcgen05 path
@@ -1129,6 +1345,14 @@ extern "C" int nrd_plan_set_conv_impl(nrd_plan* p, int impl) {
               "conv impl %d not available for this plan (dtype=%d)", impl, p->dtype);
   p->conv_impl = impl;
   return NRD_OK;
+}
+
+extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
+  NRD_REQUIRE(p, "null plan");
+  switch (option) {
+    case NRD_OPT_FUSE_BN_BWD: p->fuse_bn_bwd = value ? 1 : 0; return NRD_OK;
+    default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
+  }
 }
 
 extern "C" int nrd_plan_conv_impl(const nrd_plan* p) { return p ? p->conv_impl : NRD_EINVAL; }
@@ -1194,10 +1418,11 @@ extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int 
   }
   NRD_TRY(nrd_maxpool_fwd(p->xs + act * NB, p->pooled, p->idx2, B, C, dt, stream));
   const int K = 64 * C;
-  if (dt == NRD_F32) k_fc1_fwd<float><<<(B + 7) / 8, 256, 0, st>>>((const float*)p->pooled, p->w1p, PRM(P_FC1B), p->h1, B, K);
-  else k_fc1_fwd<bf16><<<(B + 7) / 8, 256, 0, st>>>((const bf16*)p->pooled, p->w1p, PRM(P_FC1B), p->h1, B, K);
+  const dim3 g1((B + 31) / 32, K / 128);
+  if (dt == NRD_F32) k_fc1_fwd_part<float><<<g1, 256, 0, st>>>((const float*)p->pooled, p->w1p, p->fc1_part, B, K);
+  else k_fc1_fwd_part<bf16><<<g1, 256, 0, st>>>((const bf16*)p->pooled, p->w1p, p->fc1_part, B, K);
   LAUNCH_CHECK();
-  k_fc2_fwd<<<(B * NRD_NCLS + 255) / 256, 256, 0, st>>>(p->h1, PRM(P_FC2W), PRM(P_FC2B), logits, B);
+  k_fc2_fwd<<<(B + 7) / 8, 256, 0, st>>>(p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B);
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1218,15 +1443,16 @@ extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
   LAUNCH_CHECK();
   char* g = p->dxa; char* gn = p->dxb;
   const int K = 64 * C;
-  if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<B * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (float*)g, B, C);
-  else k_fc1_dgrad_unpool<bf16><<<B * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (bf16*)g, B, C);
+  if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (float*)g, B, C);
+  else k_fc1_dgrad_unpool<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (bf16*)g, B, C);
   LAUNCH_CHECK();
   // residual blocks, last to first; the shared block's grads accumulate over the NB applications
   for (int k = NB - 1; k >= 0; --k) {
     const int first = (k == NB - 1);
     char* xk = p->xs + act * k; char* yk = p->ys + act * k;
     NRD_TRY(bn_relu_bwd_any(g, yk, p->scale_shift + (size_t)k * 2 * C, p->saved_stats + (size_t)k * 2 * C, PRM(P_BNG), p->dy,
-                            GRD(P_BNG), GRD(P_BNB), !first, B, C, dt, p->bnbwd_scratch, st));
+                            GRD(P_BNG), GRD(P_BNB), !first, B, C, dt, p->bnbwd_scratch, st,
+                            p->fuse_bn_bwd ? p->gbar : nullptr));
     if (p->conv_impl != NRD_CONV_CUDA_CORE) {
       NRD_TRY(nrd_tc_conv_wgrad(p, k, first, st));
       NRD_TRY(nrd_tc_conv_dgrad(p, g, gn, st));
@@ -1269,7 +1495,8 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
     case NRD_OP_BN_APPLY: return bn_relu_add_any(yk, xk, ss, p->dxb, B, C, dt, st);
     case NRD_OP_BN_BWD: {
       // dgamma/dbeta go to a sink (h1 is dead after backward and holds >= 2C floats) so profiling leaves the grads alone
-      return bn_relu_bwd_any(p->dxa, yk, ss, sv, PRM(P_BNG), p->dy, p->h1, p->h1 + C, 0, B, C, dt, p->bnbwd_scratch, st);
+      return bn_relu_bwd_any(p->dxa, yk, ss, sv, PRM(P_BNG), p->dy, p->h1, p->h1 + C, 0, B, C, dt, p->bnbwd_scratch, st,
+                             p->fuse_bn_bwd ? p->gbar : nullptr);
     }
     case NRD_OP_WGRAD:
       if (p->conv_impl != NRD_CONV_CUDA_CORE) return nrd_tc_conv_wgrad(p, k, 1, st);

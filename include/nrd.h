@@ -68,6 +68,10 @@ int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB, int dtype,
 int nrd_plan_destroy(nrd_plan* plan);
 int nrd_plan_set_conv_impl(nrd_plan* plan, int impl);
 int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
+/* options: NRD_OPT_FUSE_BN_BWD (default 1): BN+ReLU backward as ONE cooperative kernel (sums, grid barrier, dy) when the
+ * CTA's images fit shared memory; 0 = the three-kernel path (any batch size; cross-check). */
+#define NRD_OPT_FUSE_BN_BWD 0
+int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
  * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch (ping),
  * 6 = dx scratch (pong), 7 = wgrad per-CTA partials [ctas][9][C][C], 8 = BN-stat per-CTA partials [ctas][2][C] */
