@@ -399,6 +399,223 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 }
 
 // ============================================================================================
+// Persistent forward over ALL residual blocks (C = 32, at most 2 images per CTA, cooperative launch).
+// The block's convolution of an image depends only on that image, so each CTA keeps its images' block input on chip for
+// the whole stack: x_0 comes in by TMA (3 kx-shifted, row-haloed copies), and for every block
+//     MMA warp     36 tcgen05.mma per image from the shared-memory copies -> 2 accumulators (TMEM) per image
+//     pass 1       BN partial sums straight from TMEM (fp32), per-CTA row -> global, ONE grid barrier, fixed-order combine
+//     pass 2       y_k (bf16) and x_{k+1} = relu(bn(y_k)) + x_k -> global (saved for backward) AND x_{k+1} written back
+//                  into the three swizzled operand copies in shared memory = the next block's A operand
+// so between blocks nothing is re-read from global memory and there is one launch instead of NB (or 3*NB).
+// 320 threads: warp 0 TMA, warp 1 MMA, warps 2..5 epilogue of image slot 0, warps 6..9 epilogue of image slot 1.
+// ============================================================================================
+struct PersistFwdArgs {
+  const float* gamma; const float* beta;
+  float* saved;            // [NB][2C]
+  float* scale_shift;      // [NB][2C]
+  float* running;          // [2C]
+  long long* nbt;
+  bf16* xs;                // x_0 .. x_NB   (x_0 is read through the tensor map)
+  bf16* ys;                // y_0 .. y_NB-1
+  float* partial;          // two buffers of [gridDim.x][2C] at +0 and +512*2C floats
+  unsigned int* gbar;
+  int B, NB;
+  size_t act_elems;        // B*256*C
+};
+
+__global__ void __launch_bounds__(320, 1)
+k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmW, PersistFwdArgs a) {
+  constexpr int C = 32;
+  using K = Cfg<C>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+  constexpr int SLOT_BYTES = 3 * K::BUF_BYTES;                    // 55,296 B: three kx-copies of one image
+  const uint32_t a_smem = base;                                   // 2 image slots
+  const uint32_t w_smem = a_smem + 2 * SLOT_BYTES;               // 9 taps
+  const uint32_t bar0 = w_smem + 9 * K::WTAP_BYTES;
+  const uint32_t wfull = bar0;
+  auto xfull = [&](int s) { return bar0 + 8u * (1 + s); };
+  auto opready = [&](int s) { return bar0 + 8u * (3 + s); };
+  auto tfull = [&](int s, int m) { return bar0 + 8u * (5 + s * 2 + m); };
+  const uint32_t tmem_slot = bar0 + 8u * 9;
+  constexpr int BAR_BYTES = 8 * 10;
+  constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
+  float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [8 warps][2][C] = 512 floats
+  float* ss_sm = red + 512;                                              // [2C]
+  double* dsum = reinterpret_cast<double*>(ss_sm + 64);                  // [1024]
+  volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int img0 = blockIdx.x, img1 = blockIdx.x + gridDim.x;
+  const int nslots = (img1 < a.B) ? 2 : 1;
+  constexpr uint32_t TMEM_COLS = 128;                              // 2 slots x 2 tiles x 32 columns
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX0); tma_prefetch_desc(&tmW);
+    mbar_init(wfull, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(xfull(s), 1); mbar_init(opready(s), 128); mbar_init(tfull(s, 0), 1); mbar_init(tfull(s, 1), 1); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_gen;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(wfull, 9 * K::WTAP_BYTES);
+      for (int t = 0; t < 9; ++t) tma_load_2d(w_smem + t * K::WTAP_BYTES, &tmW, wfull, t * C, 0);
+      for (int s = 0; s < nslots; ++s) {
+        mbar_expect_tx(xfull(s), SLOT_BYTES);
+        for (int kx = 0; kx < 3; ++kx)
+          tma_load_4d(a_smem + s * SLOT_BYTES + kx * K::BUF_BYTES, &tmX0, xfull(s), 0, kx - 1, -1, s == 0 ? img0 : img1);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(128, C, 0, 0);
+      mbar_wait(wfull, 0);
+      for (int k = 0; k < a.NB; ++k) {
+        for (int s = 0; s < nslots; ++s) {
+          if (k == 0) mbar_wait(xfull(s), 0);
+          else mbar_wait(opready(s), (uint32_t)((k - 1) & 1));
+          tc_fence_after();
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            const uint32_t d_tmem = tmem_base + (s * 2 + m) * C;
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+              const uint32_t a_addr = a_smem + s * SLOT_BYTES + (t % 3) * K::BUF_BYTES + (m * 8 + t / 3) * K::IMGROW_BYTES;
+              const uint64_t ad = make_sdesc(a_addr, 16, K::SBO, K::LAYOUT);
+              const uint64_t bd = make_sdesc(w_smem + t * K::WTAP_BYTES, 16, K::SBO, K::LAYOUT);
+#pragma unroll
+              for (int kk = 0; kk < K::KSTEPS; ++kk) umma_bf16(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (t | kk) != 0);
+            }
+            umma_commit(tfull(s, m));
+          }
+        }
+      }
+    }
+  } else {
+    // ===== epilogue: group s = image slot, q = TMEM lane quarter =====
+    const int ew = warp - 2, s = ew >> 2, q = warp & 3, et = threadIdx.x - 64;    // et: 0..255
+    const bool active = s < nslots;
+    const int img = (s == 0) ? img0 : img1;
+    uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
+    const int count = a.B * NRD_PIX;
+    for (int k = 0; k < a.NB; ++k) {
+      // ---- pass 1: per-channel sum / sum of squares of this warp's 2 x 32 pixels ----
+      float ssum = 0.f, qsum = 0.f;
+      if (active) {
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          mbar_wait(tfull(s, m), (uint32_t)(k & 1));
+          tc_fence_after();
+          float v[32], sq[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C, v);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
+          ssum += warp_col_sum(v, lane);
+          qsum += warp_col_sum(sq, lane);
+        }
+      }
+      red[(ew * 2 + 0) * C + lane] = ssum; red[(ew * 2 + 1) * C + lane] = qsum;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      float* part = a.partial + (size_t)(k & 1) * 512 * 2 * C;
+      if (et < 2 * C) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[w * 2 * C + et];      // fixed order over the 8 epilogue warps
+        part[(size_t)blockIdx.x * 2 * C + et] = t;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (et == 0) nrd_grid_barrier(a.gbar, gridDim.x);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      {
+        // [gridDim.x][2C] -> column sums in fp64, fixed order (16 float4 column chunks x 16 row classes)
+        const int c4 = et & 15, r = et >> 4;
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 10
+        for (int row = r; row < (int)gridDim.x; row += 16) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(part + (size_t)row * 2 * C) + c4);
+          a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+        }
+        double* d = dsum + (size_t)r * 2 * C + c4 * 4;
+        d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (et < C) {
+        double S = 0.0, Q = 0.0;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) { S += dsum[r * 2 * C + et]; Q += dsum[r * 2 * C + C + et]; }
+        const double mean = S / count;
+        double var = Q / count - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float invstd = (float)(1.0 / sqrt(var + (double)NRD_BN_EPS));
+        const float sc = a.gamma[et] * invstd, sh = a.beta[et] - (float)mean * sc;
+        ss_sm[et] = sc; ss_sm[C + et] = sh;
+        if (blockIdx.x == 0) {
+          a.saved[(size_t)k * 2 * C + et] = (float)mean; a.saved[(size_t)k * 2 * C + C + et] = invstd;
+          a.scale_shift[(size_t)k * 2 * C + et] = sc; a.scale_shift[(size_t)k * 2 * C + C + et] = sh;
+          const double unbiased = var * ((double)count / (double)(count - 1));
+          a.running[et] = (1.f - NRD_BN_MOMENTUM) * a.running[et] + NRD_BN_MOMENTUM * (float)mean;
+          a.running[C + et] = (1.f - NRD_BN_MOMENTUM) * a.running[C + et] + NRD_BN_MOMENTUM * (float)unbiased;
+          if (et == 0) *a.nbt += 1;
+        }
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      // ---- pass 2: y_k, x_{k+1} -> global; x_{k+1} -> the three operand copies in shared memory ----
+      if (active) {
+        if (k == 0) mbar_wait(xfull(s), 0);      // the TMA-written x_0 copy is read below (residual) by this thread itself
+        bf16* yk = a.ys + (size_t)k * a.act_elems;
+        bf16* xn = a.xs + (size_t)(k + 1) * a.act_elems;
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const int p = q * 32 + lane, i = m * 8 + (p >> 4), j = p & 15;
+          const size_t gp = ((size_t)img * NRD_PIX + i * 16 + j) * C;
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C, v);
+          const int P1 = (i + 1) * 16 + j;                   // pixel index inside a copy (row-haloed: +1 row)
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) {
+            // residual x_k from the centre copy (kx = 1); 16-B chunk ch of pixel P sits at chunk ch ^ ((P>>1)&3) (SWIZZLE_64B)
+            const uint4 xk = *reinterpret_cast<const uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4));
+            uint4 yk4, ok;
+            __nv_bfloat162* yh = reinterpret_cast<__nv_bfloat162*>(&yk4);
+            const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xk);
+            __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = ch * 8 + 2 * e;
+              yh[e] = __floats2bfloat162_rn(v[c], v[c + 1]);
+              const float2 yr = __bfloat1622float2(yh[e]), xr = __bfloat1622float2(xh[e]);   // BN sees the STORED y (as backward will)
+              oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, ss_sm[c], ss_sm[C + c]), 0.f) + xr.x,
+                                            fmaxf(fmaf(yr.y, ss_sm[c + 1], ss_sm[C + c + 1]), 0.f) + xr.y);
+            }
+            reinterpret_cast<uint4*>(yk + gp)[ch] = yk4;
+            reinterpret_cast<uint4*>(xn + gp)[ch] = ok;
+            if (k + 1 < a.NB) {
+              *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
+              if (j < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
+              if (j > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
+            }
+          }
+        }
+        // TMEM reads and shared-memory operand writes of this thread are done: release the slot to the MMA warp
+        tc_fence_before();
+        fence_proxy_async();
+        mbar_arrive(opready(s));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+}
+
+// ============================================================================================
 // wgrad: both operands MN-major (channels contiguous, pixels = K).  Per work item: the 3 kx-shifted row-haloed copies of x
 // and the dy rows.  One MMA stacks 128/C vertical taps along M: tap ky+1 is one image row further = LBO.
 // ============================================================================================
@@ -565,6 +782,10 @@ template <int C> constexpr size_t wgrad_smem() {
   return 1024 + WCfg<C>::NSS * WCfg<C>::STAGE_BYTES + WCfg<C>::SLACK + 8 * (2 * WCfg<C>::NSS + 2) + 64;
 }
 
+constexpr size_t persist_smem() {
+  return 1024 + 2 * 3 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 80 + (512 + 64) * sizeof(float) + 1024 * sizeof(double) + 64;
+}
+
 static int items(const nrd_plan* p) { return p->B * (p->C == 32 ? 1 : 2); }
 static int conv_grid(const nrd_plan* p) { int t = items(p); return t < NRD_NUM_SMS ? t : NRD_NUM_SMS; }
 
@@ -601,6 +822,8 @@ int nrd_tc_plan_init(nrd_plan* p) {
   // fused block forward: every CTA keeps all its accumulators in TMEM (512 columns) and all CTAs must be co-resident
   const int grid = conv_grid(p), per_cta = (items(p) + grid - 1) / grid * (rows / 8);
   p->tc_fused_fwd = (per_cta * p->C <= 512) ? 1 : 0;
+  p->tc_persist_fwd = (p->C == 32 && p->B <= 2 * NRD_NUM_SMS) ? 1 : 0;
+  if (p->tc_persist_fwd) NRD_TRY(set_attr(k_tc_fwd_persist, persist_smem()));
   p->tc_ready = 1;
   return NRD_OK;
 }
@@ -640,6 +863,20 @@ int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st) {
   const dim3 grid(conv_grid(p)), block(192);
   if (C == 32) NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_conv<32, 2>, grid, block, args, conv_smem<32, 2>(), st));
   else NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_conv<64, 2>, grid, block, args, conv_smem<64, 2>(), st));
+  nrd_count_launch();
+  return NRD_OK;
+}
+
+// all NB residual blocks in ONE cooperative launch (C = 32, <= 2 images per CTA)
+int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st) {
+  NRD_REQUIRE(p->tc_ready && p->tc_persist_fwd, "persistent block-stack forward not available for this plan");
+  PersistFwdArgs a;
+  a.gamma = p->params + p->off[3]; a.beta = p->params + p->off[4];
+  a.saved = p->saved_stats; a.scale_shift = p->scale_shift; a.running = p->bn_running; a.nbt = (long long*)p->nbt;
+  a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.gbar = p->gbar;
+  a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems;
+  void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&a};
+  NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist, dim3(conv_grid(p)), dim3(320), args, persist_smem(), st));
   nrd_count_launch();
   return NRD_OK;
 }

@@ -84,7 +84,9 @@ struct nrd_plan {
   CUtensorMap tm_dy0;     // dy scratch, plain rows (wgrad)
   CUtensorMap tm_wf, tm_wd;
   int tc_ready;
+  int persist_fwd;        // option: use the persistent block-stack forward when available
   int fuse_bn_bwd;        // BN+ReLU backward as one cooperative kernel when it fits shared memory
+  int tc_persist_fwd;     // all NB blocks of the forward in ONE cooperative kernel (C=32, <= 2 images per CTA)
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
   unsigned int* gbar;     // grid-barrier words
 };
@@ -115,4 +117,5 @@ int nrd_tc_conv_dgrad(nrd_plan* p, const void* g, void* dx_out, cudaStream_t st)
 int nrd_tc_conv_wgrad(nrd_plan* p, int k, int first, cudaStream_t st);          // partial (+)= wgrad(x_k, dy)
 int nrd_tc_stats_blocks(const nrd_plan* p);
 int nrd_tc_wgrad_blocks(const nrd_plan* p);
+int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st);                        // x_0 -> all y_k, x_{k+1}: one launch
 int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st);                      // y_k, x_{k+1}, BN stats + EMA, one launch

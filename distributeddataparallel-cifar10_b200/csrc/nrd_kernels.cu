@@ -1324,6 +1324,7 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->device = device; p->params = params; p->grads = grads; p->bn_running = bn_running; p->nbt = nbt;
   p->conv_impl = NRD_CONV_CUDA_CORE;
   p->fuse_bn_bwd = 1;
+  p->persist_fwd = 1;
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
   e = cudaMemset(p->gbar, 0, 256);
@@ -1351,6 +1352,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
   NRD_REQUIRE(p, "null plan");
   switch (option) {
     case NRD_OPT_FUSE_BN_BWD: p->fuse_bn_bwd = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_PERSIST_FWD: p->persist_fwd = value ? 1 : 0; return NRD_OK;
     default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
   }
 }
@@ -1399,7 +1401,9 @@ extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int 
   p->images_last = images;
   NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st));
   if (!training) { k_bn_eval_coeffs<<<1, 64, 0, st>>>(p->bn_running, PRM(P_BNG), PRM(P_BNB), C, p->scale_shift); LAUNCH_CHECK(); }
-  for (int k = 0; k < NB; ++k) {
+  const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_fwd;
+  if (persist) NRD_TRY(nrd_tc_forward_blocks(p, st));
+  for (int k = 0; k < (persist ? 0 : NB); ++k) {
     char* xk = p->xs + act * k; char* yk = p->ys + act * k; char* xn = p->xs + act * (k + 1);
     float* ss = training ? p->scale_shift + (size_t)k * 2 * C : p->scale_shift;
     if (training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_fused_fwd) {   // conv + BN stats + grid barrier + apply: one launch

@@ -73,8 +73,9 @@ def test_fused_block_forward_bitwise_equals_unfused(B, Cc, NB):
         torch.manual_seed(0)
         m = nrd.NetResDeep(Cc, NB, dtype="bf16").to(DEV)
         m.engine.set_conv_impl(impl)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 1, 0))      # per-block kernels (the persistent stack is tested below)
         out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
-        pl = m.engine._last_plan
         bn = m.resblocks[0].batch_norm
         res.append((out.detach().clone(), m.engine.flat_grads.clone(), bn.running_mean.clone(), bn.running_var.clone(),
                     int(bn.num_batches_tracked), pl.tensor_view(0, NB).clone(), pl.tensor_view(1, NB - 1).clone(),
@@ -103,3 +104,28 @@ def test_fused_bn_backward_matches_three_kernel_path(dtype, B, Cc):
     if B == 800:
         assert torch.equal(res[0], res[1])
     assert rell2(res[1], res[0]) < (1e-5 if dtype == "fp32" else 2e-3), rell2(res[1], res[0])
+
+
+@pytest.mark.parametrize("B", [1, 100, 148, 149, 256, 296])
+def test_persistent_forward_matches_per_block_kernels(B):
+    """All residual blocks in ONE persistent cooperative kernel (activations stay in shared memory / TMEM between blocks)
+    against one fused kernel per block: identical MMAs; only the grouping of the fp32 BN partial sums differs, so the
+    saved statistics agree to fp32 round-off and activations to a bf16 rounding step here and there."""
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for persist in (0, 1):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(32, 10, dtype="bf16").to(DEV)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 1, persist))
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        bn = m.resblocks[0].batch_norm
+        res.append(dict(out=out.detach().clone(), grads=m.engine.flat_grads.clone(), rm=bn.running_mean.clone(), rv=bn.running_var.clone(),
+                        nbt=int(bn.num_batches_tracked), x10=pl.tensor_view(0, 10).view(torch.bfloat16).float().clone(),
+                        y9=pl.tensor_view(1, 9).view(torch.bfloat16).float().clone(), st9=pl.tensor_view(4, 9).view(torch.float32).clone()))
+    a, b = res
+    assert a["nbt"] == b["nbt"] == 10
+    assert relmax(b["rm"], a["rm"]) < 1e-5 and relmax(b["rv"], a["rv"]) < 1e-5 and relmax(b["st9"], a["st9"]) < 1e-4
+    assert rell2(b["y9"], a["y9"]) < 2e-3 and rell2(b["x10"], a["x10"]) < 2e-3 and rell2(b["out"], a["out"]) < 2e-3
+    assert rell2(b["grads"], a["grads"]) < 2e-2
