@@ -167,7 +167,7 @@ struct BlockFwdArgs {
   long long* nbt;                            // num_batches_tracked
   const bf16* x;                             // block input (residual)
   bf16* xnext;                               // block output
-  unsigned int* gbar;                        // grid barrier words
+  unsigned long long* gbar;                  // grid barrier counter
   int count;                                 // B*256
 };
 
@@ -256,6 +256,8 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   } else {
     // ===== epilogue warps 2..5: TMEM lane quarter q = warp % 4 =====
     const int q = warp & 3;
+    unsigned long long gbar_base = 0;
+    if (MODE == 2 && threadIdx.x == 64) gbar_base = nrd_grid_barrier_base(fa.gbar, gridDim.x);   // before this CTA's own arrival
     float ssum[C / 32], qsum[C / 32];
 #pragma unroll
     for (int h = 0; h < C / 32; ++h) ssum[h] = qsum[h] = 0.f;
@@ -322,7 +324,7 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       float* ss_sm = red + 8 * C;                     // [2C] scale | shift
       double* dred = reinterpret_cast<double*>(red + 10 * C);   // [RP][2C], RP*2C = 512
       asm volatile("bar.sync 1, 128;" ::: "memory");  // partial row written
-      if (t == 0) nrd_grid_barrier(fa.gbar, gridDim.x);
+      if (t == 0) nrd_grid_barrier(fa.gbar, gbar_base + gridDim.x);
       asm volatile("bar.sync 1, 128;" ::: "memory");
       {
         // partial matrix [gridDim.x][2C] fp32: every thread owns one float4 column chunk and every RP-th row, all loads
@@ -330,10 +332,15 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         constexpr int NC4 = 2 * C / 4, RP = 128 / NC4;
         const int c4 = t % NC4, r = t / NC4;
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-#pragma unroll 8
-        for (int row = r; row < (int)gridDim.x; row += RP) {
-          const float4 v = __ldcg(reinterpret_cast<const float4*>(stats_partial + (size_t)row * 2 * C) + c4);
-          a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+        for (int row0 = r; row0 < (int)gridDim.x; row0 += 8 * RP) {       // batches of 8 independent, predicated loads
+          float4 v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int row = row0 + u * RP;
+            v[u] = (row < (int)gridDim.x) ? __ldcg(reinterpret_cast<const float4*>(stats_partial + (size_t)row * 2 * C) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
         }
         double* d = dred + (size_t)r * 2 * C + c4 * 4;
         d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
@@ -418,9 +425,10 @@ struct PersistFwdArgs {
   bf16* xs;                // x_0 .. x_NB   (x_0 is read through the tensor map)
   bf16* ys;                // y_0 .. y_NB-1
   float* partial;          // two buffers of [gridDim.x][2C] at +0 and +512*2C floats
-  unsigned int* gbar;
+  unsigned long long* gbar;
   int B, NB;
   size_t act_elems;        // B*256*C
+  long long* trace;        // optional [gridDim.x][NB][8] clock64 stamps of epilogue thread 0 (profiling aid), or NULL
 };
 
 __global__ void __launch_bounds__(320, 1)
@@ -505,7 +513,11 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     const int img = (s == 0) ? img0 : img1;
     uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
     const int count = a.B * NRD_PIX;
+    unsigned long long gbar_target = 0;
+    if (et == 0) gbar_target = nrd_grid_barrier_base(a.gbar, gridDim.x);   // before this CTA's first arrival
     for (int k = 0; k < a.NB; ++k) {
+      long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + k) * 8 : nullptr;
+      if (tr) tr[0] = clock64();
       // ---- pass 1: per-channel sum / sum of squares of this warp's 2 x 32 pixels ----
       float ssum = 0.f, qsum = 0.f;
       if (active) {
@@ -513,6 +525,8 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         for (int m = 0; m < 2; ++m) {
           mbar_wait(tfull(s, m), (uint32_t)(k & 1));
           tc_fence_after();
+          if (tr && m == 0) tr[1] = clock64();
+          if (tr && m == 1) tr[2] = clock64();
           float v[32], sq[32];
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C, v);
 #pragma unroll
@@ -531,17 +545,22 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         part[(size_t)blockIdx.x * 2 * C + et] = t;
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (et == 0) nrd_grid_barrier(a.gbar, gridDim.x);
+      if (tr) tr[3] = clock64();
+      if (et == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
+      if (tr) tr[4] = clock64();
       asm volatile("bar.sync 1, 256;" ::: "memory");
       {
         // [gridDim.x][2C] -> column sums in fp64, fixed order (16 float4 column chunks x 16 row classes)
         const int c4 = et & 15, r = et >> 4;
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-#pragma unroll 10
-        for (int row = r; row < (int)gridDim.x; row += 16) {
-          const float4 v = __ldcg(reinterpret_cast<const float4*>(part + (size_t)row * 2 * C) + c4);
-          a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+        float4 v[10];                                   // gridDim.x <= 148 => at most 10 rows per class: all loads in flight at once
+#pragma unroll
+        for (int u = 0; u < 10; ++u) {
+          const int row = r + u * 16;
+          v[u] = (row < (int)gridDim.x) ? __ldcg(reinterpret_cast<const float4*>(part + (size_t)row * 2 * C) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
+#pragma unroll
+        for (int u = 0; u < 10; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
         double* d = dsum + (size_t)r * 2 * C + c4 * 4;
         d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
       }
@@ -566,6 +585,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         }
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (tr) tr[5] = clock64();
       // ---- pass 2: y_k, x_{k+1} -> global; x_{k+1} -> the three operand copies in shared memory ----
       if (active) {
         if (k == 0) mbar_wait(xfull(s), 0);      // the TMA-written x_0 copy is read below (residual) by this thread itself
@@ -591,8 +611,8 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
               const int c = ch * 8 + 2 * e;
               yh[e] = __floats2bfloat162_rn(v[c], v[c + 1]);
               const float2 yr = __bfloat1622float2(yh[e]), xr = __bfloat1622float2(xh[e]);   // BN sees the STORED y (as backward will)
-              oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, ss_sm[c], ss_sm[C + c]), 0.f) + xr.x,
-                                            fmaxf(fmaf(yr.y, ss_sm[c + 1], ss_sm[C + c + 1]), 0.f) + xr.y);
+              const float2 sc2 = *reinterpret_cast<const float2*>(ss_sm + c), sh2 = *reinterpret_cast<const float2*>(ss_sm + C + c);
+              oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, sc2.x, sh2.x), 0.f) + xr.x, fmaxf(fmaf(yr.y, sc2.y, sh2.y), 0.f) + xr.y);
             }
             reinterpret_cast<uint4*>(yk + gp)[ch] = yk4;
             reinterpret_cast<uint4*>(xn + gp)[ch] = ok;
@@ -608,6 +628,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         fence_proxy_async();
         mbar_arrive(opready(s));
       }
+      if (tr) tr[6] = clock64();
     }
   }
   tc_fence_before();
@@ -857,7 +878,7 @@ int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st) {
   fa.saved = p->saved_stats + (size_t)k * 2 * C; fa.scale_shift = p->scale_shift + (size_t)k * 2 * C;
   fa.running = p->bn_running; fa.nbt = (long long*)p->nbt;
   fa.x = (const bf16*)(p->xs + act * k); fa.xnext = (bf16*)(p->xs + act * (k + 1));
-  fa.gbar = p->gbar; fa.count = p->B * NRD_PIX;
+  fa.gbar = p->gbar + NRD_GBAR_BLOCK_FWD; fa.count = p->B * NRD_PIX;
   float* sp = p->stats_partial;
   void* args[] = {(void*)&p->tm_x[k], (void*)&p->tm_wf, (void*)&y, (void*)&res, (void*)&sp, (void*)&nt, (void*)&fa};
   const dim3 grid(conv_grid(p)), block(192);
@@ -873,8 +894,8 @@ int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st) {
   PersistFwdArgs a;
   a.gamma = p->params + p->off[3]; a.beta = p->params + p->off[4];
   a.saved = p->saved_stats; a.scale_shift = p->scale_shift; a.running = p->bn_running; a.nbt = (long long*)p->nbt;
-  a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.gbar = p->gbar;
-  a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems;
+  a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_FWD;
+  a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace;
   void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist, dim3(conv_grid(p)), dim3(320), args, persist_smem(), st));
   nrd_count_launch();

@@ -88,27 +88,38 @@ struct nrd_plan {
   int fuse_bn_bwd;        // BN+ReLU backward as one cooperative kernel when it fits shared memory
   int tc_persist_fwd;     // all NB blocks of the forward in ONE cooperative kernel (C=32, <= 2 images per CTA)
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
-  unsigned int* gbar;     // grid-barrier words
+  unsigned long long* gbar; // grid-barrier counters (one per cooperative kernel type)
+  void* trace;            // optional device buffer for in-kernel clock64 stamps (profiling aid; NULL = off)
 };
 
-// self-resetting grid-wide barrier (all CTAs co-resident: cooperative launch).  bar[0] = arrival count, bar[1] = generation.
+// Grid-wide barrier for cooperative launches (all CTAs co-resident).  ONE 64-bit monotonic counter per kernel type and plan:
+// an arrival is a release-add of 1, waiting is an acquire-poll until the counter reaches this episode's target.  The counter
+// is never reset (a given kernel type always runs with the same grid, so it is a multiple of the grid size between launches);
+// nrd_grid_barrier_base() recovers the launch's base value even if faster CTAs have already arrived at the first barrier.
 // Call from ONE thread per CTA, bracketed by CTA-level barriers.  A spin that lasts ~2 s traps instead of hanging the GPU.
-static __device__ __forceinline__ void nrd_grid_barrier(unsigned int* bar, unsigned int nblocks) {
-  volatile unsigned int* vgen = bar + 1;
-  const unsigned int gen = *vgen;
-  __threadfence();
-  if (atomicAdd(bar, 1u) == nblocks - 1) {
-    bar[0] = 0;
-    __threadfence();
-    atomicAdd(bar + 1, 1u);
-  } else {
-    long long t0 = clock64();
-    while (*vgen == gen) {
-      if (clock64() - t0 > 4000000000LL) __trap();
+static __device__ __forceinline__ unsigned long long nrd_grid_barrier_base(const unsigned long long* ctr, unsigned int nblocks) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(ctr) : "memory");
+  return v - v % nblocks;
+}
+static __device__ __forceinline__ void nrd_grid_barrier(unsigned long long* ctr, unsigned long long target) {
+  asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(ctr) : "memory");
+  unsigned long long v;
+  long long t0 = 0;
+  int spins = 0;
+  while (true) {
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(ctr) : "memory");
+    if (v >= target) break;
+    if (++spins > 1024) {
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > 4000000000LL) __trap();
     }
   }
-  __threadfence();
 }
+#define NRD_GBAR_BLOCK_FWD 0
+#define NRD_GBAR_PERSIST_FWD 1
+#define NRD_GBAR_BN_BWD 2
+#define NRD_GBAR_PERSIST_BWD 3
 
 // tcgen05 path (conv_tc.cu)
 int nrd_tc_plan_init(nrd_plan* p);

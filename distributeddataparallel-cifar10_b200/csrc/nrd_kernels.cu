@@ -401,10 +401,15 @@ template <int NT>
 __device__ __forceinline__ void combine_partials(const float* __restrict__ partial, int rows, int C, double* dsum /*[NT*4]*/) {
   const int t = threadIdx.x, NC4 = 2 * C / 4, RP = NT / NC4, c4 = t % NC4, r = t / NC4;
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-#pragma unroll 8
-  for (int row = r; row < rows; row += RP) {
-    const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)row * 2 * C) + c4);
-    a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+  for (int row0 = r; row0 < rows; row0 += 8 * RP) {       // batches of 8 independent, predicated loads (one L2 round trip each)
+    float4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int row = row0 + u * RP;
+      v[u] = (row < rows) ? __ldcg(reinterpret_cast<const float4*>(partial + (size_t)row * 2 * C) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
   }
   double* d = dsum + (size_t)r * 2 * C + c4 * 4;
   d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
@@ -566,7 +571,7 @@ __global__ void __launch_bounds__(256, 1) k_bn_bwd_fused(const T* __restrict__ g
                                                          const float* __restrict__ scale_shift, const float* __restrict__ saved,
                                                          const float* __restrict__ gamma, T* __restrict__ dy,
                                                          float* __restrict__ dgamma, float* __restrict__ dbeta, int accumulate,
-                                                         float* __restrict__ partial, unsigned int* gbar, int B, int C, int ipc) {
+                                                         float* __restrict__ partial, unsigned long long* gbar, int B, int C, int ipc) {
   extern __shared__ __align__(16) uint8_t smraw[];
   const int img_elems = NRD_PIX * C;
   T* gs = reinterpret_cast<T*>(smraw);
@@ -581,6 +586,8 @@ __global__ void __launch_bounds__(256, 1) k_bn_bwd_fused(const T* __restrict__ g
     sc[j] = scale_shift[cg * 8 + j]; sh[j] = scale_shift[C + cg * 8 + j];
     mu[j] = saved[cg * 8 + j]; is[j] = saved[C + cg * 8 + j];
   }
+  unsigned long long gbar_target = 0;
+  if (tid == 0) gbar_target = nrd_grid_barrier_base(gbar, gridDim.x) + gridDim.x;   // read before this CTA's own arrival
   float s1[8], s2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
@@ -611,7 +618,7 @@ __global__ void __launch_bounds__(256, 1) k_bn_bwd_fused(const T* __restrict__ g
     partial[(size_t)blockIdx.x * 2 * C + tid] = t;
   }
   __syncthreads();
-  if (tid == 0) nrd_grid_barrier(gbar, gridDim.x);
+  if (tid == 0) nrd_grid_barrier(gbar, gbar_target);
   __syncthreads();
   combine_partials<256>(partial, gridDim.x, C, dsum);
   const int count = B * NRD_PIX;
@@ -1055,7 +1062,7 @@ static size_t bn_bwd_fused_smem(int B, int C, int dt, int* grid_out, int* ipc_ou
 // scratch layout: [B][2C] partials | coef [3C].  gbar != NULL selects the one-launch cooperative kernel when it fits.
 static int bn_relu_bwd_any(const void* g, const void* y, const float* ss, const float* saved, const float* gamma, void* dy,
                            float* dgamma, float* dbeta, int accumulate, int B, int C, int dt, float* scratch, cudaStream_t st,
-                           unsigned int* gbar = nullptr) {
+                           unsigned long long* gbar = nullptr) {
   float* partial = scratch; float* coef = scratch + (size_t)B * 2 * C;
   int grid = 0, ipc = 0;
   const size_t fsmem = bn_bwd_fused_smem(B, C, dt, &grid, &ipc);
@@ -1290,7 +1297,7 @@ static void carve(nrd_plan* p, char* base, size_t* total) {
   p->conv1_wp = cv.take<float>((size_t)27 * C * 4);
   p->wtc_fwd = cv.take<bf16>((size_t)9 * C * C * 2);
   p->wtc_dgrad = cv.take<bf16>((size_t)9 * C * C * 2);
-  p->gbar = cv.take<unsigned int>(256);
+  p->gbar = cv.take<unsigned long long>(256);
   *total = cv.off;
 }
 
@@ -1353,6 +1360,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
   switch (option) {
     case NRD_OPT_FUSE_BN_BWD: p->fuse_bn_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_FWD: p->persist_fwd = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_TRACE: p->trace = value ? (void*)p->dxb : nullptr; return NRD_OK;   // stamps land in the dx pong scratch
     default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
   }
 }
@@ -1456,7 +1464,7 @@ extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
     char* xk = p->xs + act * k; char* yk = p->ys + act * k;
     NRD_TRY(bn_relu_bwd_any(g, yk, p->scale_shift + (size_t)k * 2 * C, p->saved_stats + (size_t)k * 2 * C, PRM(P_BNG), p->dy,
                             GRD(P_BNG), GRD(P_BNB), !first, B, C, dt, p->bnbwd_scratch, st,
-                            p->fuse_bn_bwd ? p->gbar : nullptr));
+                            p->fuse_bn_bwd ? p->gbar + NRD_GBAR_BN_BWD : nullptr));
     if (p->conv_impl != NRD_CONV_CUDA_CORE) {
       NRD_TRY(nrd_tc_conv_wgrad(p, k, first, st));
       NRD_TRY(nrd_tc_conv_dgrad(p, g, gn, st));
@@ -1500,7 +1508,7 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
     case NRD_OP_BN_BWD: {
       // dgamma/dbeta go to a sink (h1 is dead after backward and holds >= 2C floats) so profiling leaves the grads alone
       return bn_relu_bwd_any(p->dxa, yk, ss, sv, PRM(P_BNG), p->dy, p->h1, p->h1 + C, 0, B, C, dt, p->bnbwd_scratch, st,
-                             p->fuse_bn_bwd ? p->gbar : nullptr);
+                             p->fuse_bn_bwd ? p->gbar + NRD_GBAR_BN_BWD : nullptr);
     }
     case NRD_OP_WGRAD:
       if (p->conv_impl != NRD_CONV_CUDA_CORE) return nrd_tc_conv_wgrad(p, k, 1, st);
