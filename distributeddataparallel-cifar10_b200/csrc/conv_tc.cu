@@ -60,6 +60,12 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm,
       ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -637,6 +643,323 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
 }
 
 // ============================================================================================
+// Persistent backward over ALL residual blocks (C = 32, at most 2 images per CTA, cooperative launch).
+// dL/dx of an image never leaves the SM: it lives in the epilogue threads' registers (bf16 pairs, the same rounding the
+// per-block kernels apply when they store it).  Per block k = NB-1 .. 0 and image:
+//   phase A   read y_k (global, one 64-B pixel row per thread); dz = g*[bn(y)>0]; per-channel sums of dz and dz*xhat
+//             (warp transpose-reduce) -> per-CTA row -> ONE grid barrier -> fixed-order fp64 combine -> coefficients
+//   phase B   dy = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)) written (bf16, swizzled) into three kx-shifted,
+//             row-haloed copies in shared memory = the A operand of BOTH convolution gradients
+//   MMA       dgrad: 36 tcgen05.mma (K-major dy copies x flipped weights) -> 2 accumulators per image
+//             wgrad: 48 tcgen05.mma (MN-major dy copies stacked 4 vertical taps deep x MN-major x_k tile from TMA) into 3
+//             accumulators that persist over all blocks and both images: ONE partial store per CTA per step
+//   phase C   dx_k = dgrad + g -> registers (-> global only for k = 0)
+// HBM traffic per block: y_k and x_k read once; nothing written.
+// ============================================================================================
+struct PersistBwdArgs {
+  const float* gamma;
+  const float* scale_shift;   // [NB][2C]
+  const float* saved;         // [NB][2C] mean | invstd
+  float* dgamma; float* dbeta;
+  const bf16* ys;             // y_0 .. y_NB-1
+  const bf16* g_in;           // dL/dx_NB
+  bf16* dx0_out;              // dL/dx_0
+  float* partial;             // two buffers of [gridDim.x][2C] at +0 and +512*2C floats
+  float* wpartial;            // [gridDim.x][9][C][C]
+  unsigned long long* gbar;
+  int B, NB;
+  size_t act_elems;
+};
+
+__global__ void __launch_bounds__(320, 1)
+k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_constant__ CUtensorMap tmWd, PersistBwdArgs a) {
+  constexpr int C = 32;
+  using K = Cfg<C>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+  constexpr int DY_BYTES = 3 * K::BUF_BYTES;                      // three kx-copies of dy
+  constexpr int SLOT_BYTES = DY_BYTES + K::BUF_BYTES;             // + row-haloed x_k tile
+  const uint32_t a_smem = base;
+  const uint32_t w_smem = a_smem + 2 * SLOT_BYTES;
+  const uint32_t bar0 = w_smem + 9 * K::WTAP_BYTES;
+  const uint32_t wfull = bar0;
+  auto xready = [&](int s) { return bar0 + 8u * (1 + s); };
+  auto dyready = [&](int s) { return bar0 + 8u * (3 + s); };
+  auto wfree = [&](int s) { return bar0 + 8u * (5 + s); };
+  auto dxfull = [&](int s, int m) { return bar0 + 8u * (7 + s * 2 + m); };
+  const uint32_t wdone = bar0 + 8u * 11;
+  const uint32_t tmem_slot = bar0 + 8u * 12;
+  constexpr int BAR_BYTES = 8 * 14;
+  constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
+  float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [8 warps][2][C] = 512 floats
+  float* coef = red + 512;                                               // [3C] = gamma*invstd | mean(dz) | mean(dz*xhat)
+  float* bnp2 = coef + 96;                                               // 2 x [4C] scale | shift | mean | invstd of block k (double-buffered)
+  double* dsum = reinterpret_cast<double*>(bnp2 + 256);                   // [1024]
+  volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int img0 = blockIdx.x, img1 = blockIdx.x + gridDim.x;
+  const int nslots = (img1 < a.B) ? 2 : 1;
+  constexpr uint32_t TMEM_COLS = 256;                              // dgrad 2x2x32 columns + wgrad 3x32 columns
+  constexpr uint32_t ACCW = 128;
+
+  // the halo rows / columns of the dy copies are the convolution padding: zero everything once, never write them again
+  for (int i = threadIdx.x; i < 2 * DY_BYTES / 16; i += blockDim.x) {
+    const int s = i / (DY_BYTES / 16), o = i % (DY_BYTES / 16);
+    reinterpret_cast<uint4*>(gen_base + s * SLOT_BYTES)[o] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async();
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmXall); tma_prefetch_desc(&tmWd);
+    mbar_init(wfull, 1); mbar_init(wdone, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(xready(s), 1); mbar_init(dyready(s), 128); mbar_init(wfree(s), 1);
+      mbar_init(dxfull(s, 0), 1); mbar_init(dxfull(s, 1), 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_gen;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer: flipped weights once; x_k tile per block and image slot =====
+      mbar_expect_tx(wfull, 9 * K::WTAP_BYTES);
+      for (int t = 0; t < 9; ++t) tma_load_2d(w_smem + t * K::WTAP_BYTES, &tmWd, wfull, t * C, 0);
+      for (int it = 0; it < a.NB; ++it) {
+        const int k = a.NB - 1 - it;
+        for (int s = 0; s < nslots; ++s) {
+          if (it > 0) mbar_wait(wfree(s), (uint32_t)((it - 1) & 1));      // the wgrad MMAs that read the old tile are done
+          mbar_expect_tx(xready(s), K::BUF_BYTES);
+          tma_load_5d(a_smem + s * SLOT_BYTES + DY_BYTES, &tmXall, xready(s), 0, 0, -1, s == 0 ? img0 : img1, k);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===== MMA issuer =====
+      constexpr uint32_t idesc_d = make_idesc(128, C, 0, 0);      // dgrad: both K-major
+      constexpr uint32_t idesc_w = make_idesc(128, C, 1, 1);      // wgrad: both MN-major
+      mbar_wait(wfull, 0);
+      for (int it = 0; it < a.NB; ++it) {
+        for (int s = 0; s < nslots; ++s) {
+          mbar_wait(dyready(s), (uint32_t)(it & 1));
+          tc_fence_after();
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            const uint32_t d_tmem = tmem_base + (s * 2 + m) * C;
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+              const uint32_t a_addr = a_smem + s * SLOT_BYTES + (t % 3) * K::BUF_BYTES + (m * 8 + t / 3) * K::IMGROW_BYTES;
+              const uint64_t ad = make_sdesc(a_addr, 16, K::SBO, K::LAYOUT);
+              const uint64_t bd = make_sdesc(w_smem + t * K::WTAP_BYTES, 16, K::SBO, K::LAYOUT);
+#pragma unroll
+              for (int kk = 0; kk < K::KSTEPS; ++kk) umma_bf16(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc_d, (t | kk) != 0);
+            }
+            umma_commit(dxfull(s, m));
+          }
+        }
+        for (int s = 0; s < nslots; ++s) {
+          mbar_wait(xready(s), (uint32_t)(it & 1));
+          tc_fence_after();
+          const uint32_t sb = a_smem + s * SLOT_BYTES;
+          for (int yy = 0; yy < 16; ++yy) {              // K step = image row yy = 16 pixels
+            const uint64_t bd = make_sdesc(sb + DY_BYTES + (yy + 1) * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
+#pragma unroll
+            for (int kxb = 0; kxb < 3; ++kxb) {
+              // accumulator rows (j, co): dy copy kxb, buffer rows yy + j  <=>  tap (ky, kx) = (2 - j, 2 - kxb); j = 3 is junk
+              const uint64_t ad = make_sdesc(sb + kxb * K::BUF_BYTES + yy * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
+              umma_bf16(tmem_base + ACCW + kxb * C, ad, bd, idesc_w, (it > 0 || s > 0 || yy > 0) ? 1u : 0u);
+            }
+          }
+          umma_commit(wfree(s));
+        }
+      }
+      umma_commit(wdone);
+    }
+  } else {
+    // ===== epilogue: group s = image slot, q = TMEM lane quarter; thread = pixel (m*128 + q*32 + lane) of its image =====
+    const int ew = warp - 2, s = ew >> 2, q = warp & 3, et = threadIdx.x - 64;
+    const bool active = s < nslots;
+    const int img = (s == 0) ? img0 : img1;
+    uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
+    const int count = a.B * NRD_PIX;
+    unsigned long long gbar_target = 0;
+    if (et == 0) gbar_target = nrd_grid_barrier_base(a.gbar, gridDim.x);
+    uint32_t gpk[2][16];                              // dL/d(out) of this thread's two pixels, bf16 pairs
+    size_t gp[2];
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      const int p = q * 32 + lane, i = m * 8 + (p >> 4), j = p & 15;
+      gp[m] = ((size_t)img * NRD_PIX + i * 16 + j) * C;
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) {
+        uint4 v = active ? reinterpret_cast<const uint4*>(a.g_in + gp[m])[ch] : make_uint4(0, 0, 0, 0);
+        gpk[m][ch * 4 + 0] = v.x; gpk[m][ch * 4 + 1] = v.y; gpk[m][ch * 4 + 2] = v.z; gpk[m][ch * 4 + 3] = v.w;
+      }
+    }
+    float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, et < C: running dgamma / dbeta over the blocks
+    for (int it = 0; it < a.NB; ++it) {
+      const int k = a.NB - 1 - it;
+      uint32_t ypk[2][16];
+      if (active) {
+        const bf16* yk = a.ys + (size_t)k * a.act_elems;
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) {
+            uint4 v = reinterpret_cast<const uint4*>(yk + gp[m])[ch];
+            ypk[m][ch * 4 + 0] = v.x; ypk[m][ch * 4 + 1] = v.y; ypk[m][ch * 4 + 2] = v.z; ypk[m][ch * 4 + 3] = v.w;
+          }
+      }
+      float* bnp = bnp2 + (it & 1) * 128;            // slower threads may still read the previous block's copy in phase B
+      if (et < 2 * C) { bnp[et] = a.scale_shift[(size_t)k * 2 * C + et]; bnp[2 * C + et] = a.saved[(size_t)k * 2 * C + et]; }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      // ---- phase A: sums of dz and dz*xhat ----
+      float s1 = 0.f, s2 = 0.f;
+      if (active) {
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          float t[32];
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {              // dz
+            const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ypk[m][e]));
+            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][e]));
+            const int c = 2 * e;
+            t[c] = fmaf(y2.x, bnp[c], bnp[C + c]) > 0.f ? g2.x : 0.f;
+            t[c + 1] = fmaf(y2.y, bnp[c + 1], bnp[C + c + 1]) > 0.f ? g2.y : 0.f;
+          }
+          s1 += warp_col_sum(t, lane);
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {              // dz * xhat (recomputed: keeps the live set small)
+            const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ypk[m][e]));
+            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][e]));
+            const int c = 2 * e;
+            const float d0 = fmaf(y2.x, bnp[c], bnp[C + c]) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, bnp[c + 1], bnp[C + c + 1]) > 0.f ? g2.y : 0.f;
+            t[c] = d0 * ((y2.x - bnp[2 * C + c]) * bnp[3 * C + c]);
+            t[c + 1] = d1 * ((y2.y - bnp[2 * C + c + 1]) * bnp[3 * C + c + 1]);
+          }
+          s2 += warp_col_sum(t, lane);
+        }
+      }
+      red[(ew * 2 + 0) * C + lane] = s1; red[(ew * 2 + 1) * C + lane] = s2;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      float* part = a.partial + (size_t)(it & 1) * 512 * 2 * C;
+      if (et < 2 * C) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[w * 2 * C + et];
+        part[(size_t)blockIdx.x * 2 * C + et] = t;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (et == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      {
+        const int c4 = et & 15, r = et >> 4;
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        float4 v[10];
+#pragma unroll
+        for (int u = 0; u < 10; ++u) {
+          const int row = r + u * 16;
+          v[u] = (row < (int)gridDim.x) ? __ldcg(reinterpret_cast<const float4*>(part + (size_t)row * 2 * C) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 10; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
+        double* d = dsum + (size_t)r * 2 * C + c4 * 4;
+        d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (et < C) {
+        double db = 0.0, dg = 0.0;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) { db += dsum[r * 2 * C + et]; dg += dsum[r * 2 * C + C + et]; }
+        db_acc += (float)db; dg_acc += (float)dg;       // same order as the per-block path: k = NB-1 first
+        coef[et] = a.gamma[et] * bnp[3 * C + et];
+        coef[C + et] = (float)(db / count);
+        coef[2 * C + et] = (float)(dg / count);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (active) {
+        // ---- phase B: dy -> the three operand copies (once the previous block's MMAs no longer read them) ----
+        if (it > 0) mbar_wait(wfree(s), (uint32_t)((it - 1) & 1));
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const int p = q * 32 + lane, i = m * 8 + (p >> 4), j = p & 15;
+          const int P1 = (i + 1) * 16 + j;
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) {
+            uint4 ok;
+            __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = ch * 8 + 2 * e;
+              const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ypk[m][ch * 4 + e]));
+              const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][ch * 4 + e]));
+              const float z0 = fmaf(y2.x, bnp[c], bnp[C + c]), z1 = fmaf(y2.y, bnp[c + 1], bnp[C + c + 1]);
+              const float d0 = z0 > 0.f ? g2.x : 0.f, d1 = z1 > 0.f ? g2.y : 0.f;
+              const float x0 = (y2.x - bnp[2 * C + c]) * bnp[3 * C + c], x1 = (y2.y - bnp[2 * C + c + 1]) * bnp[3 * C + c + 1];
+              oh[e] = __floats2bfloat162_rn(coef[c] * (d0 - coef[C + c] - x0 * coef[2 * C + c]),
+                                            coef[c + 1] * (d1 - coef[C + c + 1] - x1 * coef[2 * C + c + 1]));
+            }
+            *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
+            if (j < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
+            if (j > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
+          }
+        }
+        fence_proxy_async();
+        mbar_arrive(dyready(s));
+        // ---- phase C: dx_k = dgrad + g ----
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          mbar_wait(dxfull(s, m), (uint32_t)(it & 1));
+          tc_fence_after();
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C, v);
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][e]));
+            const __nv_bfloat162 o = __floats2bfloat162_rn(v[2 * e] + g2.x, v[2 * e + 1] + g2.y);
+            gpk[m][e] = *reinterpret_cast<const uint32_t*>(&o);
+          }
+          if (k == 0) {
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch)
+              reinterpret_cast<uint4*>(a.dx0_out + gp[m])[ch] = make_uint4(gpk[m][ch * 4], gpk[m][ch * 4 + 1], gpk[m][ch * 4 + 2], gpk[m][ch * 4 + 3]);
+          }
+        }
+        tc_fence_before();      // the accumulators are in registers: the next block's dgrad may overwrite them (ordered by dyready)
+      }
+    }
+    if (blockIdx.x == 0 && et < C) { a.dgamma[et] = dg_acc; a.dbeta[et] = db_acc; }
+    // ---- weight-gradient partial of this CTA: accumulator rows (j, co), columns ci ----
+    if (s == 0) {
+      mbar_wait(wdone, 0);
+      tc_fence_after();
+      float* outp = a.wpartial + (size_t)blockIdx.x * 9 * C * C;
+      const int jrow = q, co = lane;
+#pragma unroll
+      for (int kxb = 0; kxb < 3; ++kxb) {
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ACCW + kxb * C, v);
+        if (jrow < 3) {
+          const int tap = (2 - jrow) * 3 + (2 - kxb);
+          float4* dst = reinterpret_cast<float4*>(outp + ((size_t)tap * C + co) * C);      // [tap][co][ci]
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) dst[c4] = make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+}
+
+// ============================================================================================
 // wgrad: both operands MN-major (channels contiguous, pixels = K).  Per work item: the 3 kx-shifted row-haloed copies of x
 // and the dy rows.  One MMA stacks 128/C vertical taps along M: tap ky+1 is one image row further = LBO.
 // ============================================================================================
@@ -807,6 +1130,10 @@ constexpr size_t persist_smem() {
   return 1024 + 2 * 3 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 80 + (512 + 64) * sizeof(float) + 1024 * sizeof(double) + 64;
 }
 
+constexpr size_t persist_bwd_smem() {
+  return 1024 + 2 * 4 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 112 + (512 + 96 + 256) * sizeof(float) + 1024 * sizeof(double) + 64;
+}
+
 static int items(const nrd_plan* p) { return p->B * (p->C == 32 ? 1 : 2); }
 static int conv_grid(const nrd_plan* p) { int t = items(p); return t < NRD_NUM_SMS ? t : NRD_NUM_SMS; }
 
@@ -844,7 +1171,19 @@ int nrd_tc_plan_init(nrd_plan* p) {
   const int grid = conv_grid(p), per_cta = (items(p) + grid - 1) / grid * (rows / 8);
   p->tc_fused_fwd = (per_cta * p->C <= 512) ? 1 : 0;
   p->tc_persist_fwd = (p->C == 32 && p->B <= 2 * NRD_NUM_SMS) ? 1 : 0;
-  if (p->tc_persist_fwd) NRD_TRY(set_attr(k_tc_fwd_persist, persist_smem()));
+  if (p->tc_persist_fwd) {
+    NRD_TRY(set_attr(k_tc_fwd_persist, persist_smem()));
+    NRD_TRY(set_attr(k_tc_bwd_persist, persist_bwd_smem()));
+    // all saved x_k as ONE 5-D tensor {C, W, H, N, k}: the block index is just the last TMA coordinate
+    PFN_encodeTiled enc = get_encode();
+    cuuint64_t dims[5] = {32, 16, 16, (cuuint64_t)p->B, (cuuint64_t)(p->NB + 1)};
+    cuuint64_t strides[4] = {64, 1024, 16384, (cuuint64_t)p->act_elems * 2};
+    cuuint32_t box[5] = {32, 16, 18, 1, 1};
+    cuuint32_t es[5] = {1, 1, 1, 1, 1};
+    CUresult r = enc(&p->tm_xall, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, p->xs, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { nrd_set_error("cuTensorMapEncodeTiled(x stack) failed: %d", (int)r); return NRD_ECUDA; }
+  }
   p->tc_ready = 1;
   return NRD_OK;
 }
@@ -898,6 +1237,22 @@ int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st) {
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace;
   void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist, dim3(conv_grid(p)), dim3(320), args, persist_smem(), st));
+  nrd_count_launch();
+  return NRD_OK;
+}
+
+// all NB residual blocks of the backward in ONE cooperative launch: g_in = dL/dx_NB -> dx0_out = dL/dx_0, dgamma, dbeta,
+// per-CTA weight-gradient partials (reduced by k_wgrad_reduce)
+int nrd_tc_backward_blocks(nrd_plan* p, const void* g_in, void* dx0_out, cudaStream_t st) {
+  NRD_REQUIRE(p->tc_ready && p->tc_persist_fwd, "persistent block-stack backward not available for this plan");
+  PersistBwdArgs a;
+  a.gamma = p->params + p->off[3]; a.scale_shift = p->scale_shift; a.saved = p->saved_stats;
+  a.dgamma = p->grads + p->off[3]; a.dbeta = p->grads + p->off[4];
+  a.ys = (const bf16*)p->ys; a.g_in = (const bf16*)g_in; a.dx0_out = (bf16*)dx0_out;
+  a.partial = p->stats_partial; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
+  a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems;
+  void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
+  NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist, dim3(conv_grid(p)), dim3(320), args, persist_bwd_smem(), st));
   nrd_count_launch();
   return NRD_OK;
 }

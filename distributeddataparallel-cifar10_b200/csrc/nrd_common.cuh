@@ -83,8 +83,10 @@ struct nrd_plan {
   CUtensorMap tm_dy;      // dy scratch, row-haloed box (dgrad)
   CUtensorMap tm_dy0;     // dy scratch, plain rows (wgrad)
   CUtensorMap tm_wf, tm_wd;
+  CUtensorMap tm_xall;    // all x_k as one 5-D tensor (persistent backward)
   int tc_ready;
   int persist_fwd;        // option: use the persistent block-stack forward when available
+  int persist_bwd;        // option: use the persistent block-stack backward when available
   int fuse_bn_bwd;        // BN+ReLU backward as one cooperative kernel when it fits shared memory
   int tc_persist_fwd;     // all NB blocks of the forward in ONE cooperative kernel (C=32, <= 2 images per CTA)
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
@@ -129,4 +131,5 @@ int nrd_tc_conv_wgrad(nrd_plan* p, int k, int first, cudaStream_t st);          
 int nrd_tc_stats_blocks(const nrd_plan* p);
 int nrd_tc_wgrad_blocks(const nrd_plan* p);
 int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st);                        // x_0 -> all y_k, x_{k+1}: one launch
+int nrd_tc_backward_blocks(nrd_plan* p, const void* g_in, void* dx0_out, cudaStream_t st);   // all blocks' backward: one launch
 int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st);                      // y_k, x_{k+1}, BN stats + EMA, one launch

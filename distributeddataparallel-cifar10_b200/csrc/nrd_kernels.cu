@@ -1332,6 +1332,7 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->conv_impl = NRD_CONV_CUDA_CORE;
   p->fuse_bn_bwd = 1;
   p->persist_fwd = 1;
+  p->persist_bwd = 1;
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
   e = cudaMemset(p->gbar, 0, 256);
@@ -1360,6 +1361,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
   switch (option) {
     case NRD_OPT_FUSE_BN_BWD: p->fuse_bn_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_FWD: p->persist_fwd = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_PERSIST_BWD: p->persist_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_TRACE: p->trace = value ? (void*)p->dxb : nullptr; return NRD_OK;   // stamps land in the dx pong scratch
     default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
   }
@@ -1459,7 +1461,12 @@ extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
   else k_fc1_dgrad_unpool<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (bf16*)g, B, C);
   LAUNCH_CHECK();
   // residual blocks, last to first; the shared block's grads accumulate over the NB applications
-  for (int k = NB - 1; k >= 0; --k) {
+  const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd;
+  if (persist) {
+    NRD_TRY(nrd_tc_backward_blocks(p, g, gn, st));
+    char* t = g; g = gn; gn = t;
+  }
+  for (int k = NB - 1; k >= (persist ? NB : 0); --k) {
     const int first = (k == NB - 1);
     char* xk = p->xs + act * k; char* yk = p->ys + act * k;
     NRD_TRY(bn_relu_bwd_any(g, yk, p->scale_shift + (size_t)k * 2 * C, p->saved_stats + (size_t)k * 2 * C, PRM(P_BNG), p->dy,

@@ -77,6 +77,9 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
 /* NRD_OPT_TRACE (default 0): profiling aid -- the persistent kernels write clock64 stamps of their phases into the dx pong
  * scratch (nrd_plan_tensor what=6): [cta][block][8] int64.  Never enable in a real step (backward uses that scratch). */
 #define NRD_OPT_TRACE 2
+/* NRD_OPT_PERSIST_BWD (default 1): the same for the backward of the residual blocks: dL/dx stays in registers, dy in
+ * shared memory, the weight-gradient accumulators in TMEM for the whole stack; 0 = per-block kernels. */
+#define NRD_OPT_PERSIST_BWD 3
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
  * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch (ping),

@@ -74,7 +74,8 @@ def test_fused_block_forward_bitwise_equals_unfused(B, Cc, NB):
         m = nrd.NetResDeep(Cc, NB, dtype="bf16").to(DEV)
         m.engine.set_conv_impl(impl)
         pl = m.engine.plan(B, torch.device(DEV))
-        check(lib.nrd_plan_set_option(pl.handle, 1, 0))      # per-block kernels (the persistent stack is tested below)
+        check(lib.nrd_plan_set_option(pl.handle, 1, 0))      # per-block kernels (the persistent stacks are tested below)
+        check(lib.nrd_plan_set_option(pl.handle, 3, 0))
         out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
         bn = m.resblocks[0].batch_norm
         res.append((out.detach().clone(), m.engine.flat_grads.clone(), bn.running_mean.clone(), bn.running_var.clone(),
@@ -129,3 +130,24 @@ def test_persistent_forward_matches_per_block_kernels(B):
     assert relmax(b["rm"], a["rm"]) < 1e-5 and relmax(b["rv"], a["rv"]) < 1e-5 and relmax(b["st9"], a["st9"]) < 1e-4
     assert rell2(b["y9"], a["y9"]) < 2e-3 and rell2(b["x10"], a["x10"]) < 2e-3 and rell2(b["out"], a["out"]) < 2e-3
     assert rell2(b["grads"], a["grads"]) < 2e-2
+
+
+@pytest.mark.parametrize("B", [1, 100, 149, 256, 296])
+def test_persistent_backward_matches_per_block_kernels(B):
+    """All residual blocks' backward in ONE persistent cooperative kernel (dL/dx in registers, dy in shared memory, the
+    weight-gradient accumulators in TMEM across blocks) against the per-block kernels (fused BN backward + wgrad + dgrad):
+    same arithmetic per element; only the grouping of fp32 partial sums differs."""
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for persist in (0, 1):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(32, 10, dtype="bf16").to(DEV)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 3, persist))
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        res.append((out.detach().clone(), module_grads(m)))
+    assert torch.equal(res[0][0], res[1][0])
+    for k in res[0][1]:
+        a, b = res[0][1][k], res[1][1][k]
+        assert rell2(b, a) < 1e-2 and cosine(b, a) > 0.9999, (k, rell2(b, a), cosine(b, a))
