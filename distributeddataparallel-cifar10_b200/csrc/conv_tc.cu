@@ -495,9 +495,11 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         for (int s = 0; s < nslots; ++s) {
           if (k == 0) mbar_wait(xfull(s), 0);
           else mbar_wait(opready(s), (uint32_t)((k - 1) & 1));
-          tc_fence_after();
+        }
+        tc_fence_after();
 #pragma unroll
-          for (int m = 0; m < 2; ++m) {
+        for (int m = 0; m < 2; ++m) {
+          for (int s = 0; s < nslots; ++s) {      // tile-major order: both image slots' epilogue groups start pass 1 early
             const uint32_t d_tmem = tmem_base + (s * 2 + m) * C;
 #pragma unroll
             for (int t = 0; t < 9; ++t) {
@@ -535,6 +537,18 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
           if (tr && m == 1) tr[2] = clock64();
           float v[32], sq[32];
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C, v);
+          {
+            // y_k does not depend on the statistics: store it now, off the post-barrier critical path
+            const int p = q * 32 + lane, i = m * 8 + (p >> 4), j = p & 15;
+            uint4* yrow = reinterpret_cast<uint4*>(a.ys + (size_t)k * a.act_elems + ((size_t)img * NRD_PIX + i * 16 + j) * C);
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) {
+              uint4 pk; __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[ch * 8 + 2 * e], v[ch * 8 + 2 * e + 1]);
+              yrow[ch] = pk;
+            }
+          }
 #pragma unroll
           for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
           ssum += warp_col_sum(v, lane);
@@ -595,12 +609,11 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       // ---- pass 2: y_k, x_{k+1} -> global; x_{k+1} -> the three operand copies in shared memory ----
       if (active) {
         if (k == 0) mbar_wait(xfull(s), 0);      // the TMA-written x_0 copy is read below (residual) by this thread itself
-        bf16* yk = a.ys + (size_t)k * a.act_elems;
         bf16* xn = a.xs + (size_t)(k + 1) * a.act_elems;
+        uint4 xo[2][4];                          // x_{k+1} of this thread's two pixels: to shared memory first, to global after the hand-over
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
           const int p = q * 32 + lane, i = m * 8 + (p >> 4), j = p & 15;
-          const size_t gp = ((size_t)img * NRD_PIX + i * 16 + j) * C;
           float v[32];
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C, v);
           const int P1 = (i + 1) * 16 + j;                   // pixel index inside a copy (row-haloed: +1 row)
@@ -608,21 +621,18 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
           for (int ch = 0; ch < 4; ++ch) {
             // residual x_k from the centre copy (kx = 1); 16-B chunk ch of pixel P sits at chunk ch ^ ((P>>1)&3) (SWIZZLE_64B)
             const uint4 xk = *reinterpret_cast<const uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4));
-            uint4 yk4, ok;
-            __nv_bfloat162* yh = reinterpret_cast<__nv_bfloat162*>(&yk4);
             const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xk);
-            __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
+            __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&xo[m][ch]);
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const int c = ch * 8 + 2 * e;
-              yh[e] = __floats2bfloat162_rn(v[c], v[c + 1]);
-              const float2 yr = __bfloat1622float2(yh[e]), xr = __bfloat1622float2(xh[e]);   // BN sees the STORED y (as backward will)
+              const float2 yr = __bfloat1622float2(__floats2bfloat162_rn(v[c], v[c + 1]));   // BN sees the STORED y (as backward will)
+              const float2 xr = __bfloat1622float2(xh[e]);
               const float2 sc2 = *reinterpret_cast<const float2*>(ss_sm + c), sh2 = *reinterpret_cast<const float2*>(ss_sm + C + c);
               oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, sc2.x, sh2.x), 0.f) + xr.x, fmaxf(fmaf(yr.y, sc2.y, sh2.y), 0.f) + xr.y);
             }
-            reinterpret_cast<uint4*>(yk + gp)[ch] = yk4;
-            reinterpret_cast<uint4*>(xn + gp)[ch] = ok;
             if (k + 1 < a.NB) {
+              const uint4 ok = xo[m][ch];
               *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
               if (j < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
               if (j > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
@@ -633,6 +643,14 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         tc_fence_before();
         fence_proxy_async();
         mbar_arrive(opready(s));
+        // x_{k+1} -> global (saved for backward) while the next block's MMAs already run
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const int p = q * 32 + lane, i = m * 8 + (p >> 4), j = p & 15;
+          uint4* xrow = reinterpret_cast<uint4*>(xn + ((size_t)img * NRD_PIX + i * 16 + j) * C);
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) xrow[ch] = xo[m][ch];
+        }
       }
       if (tr) tr[6] = clock64();
     }
@@ -669,6 +687,7 @@ struct PersistBwdArgs {
   unsigned long long* gbar;
   int B, NB;
   size_t act_elems;
+  long long* trace;           // optional clock64 stamps (profiling aid), or NULL
 };
 
 __global__ void __launch_bounds__(320, 1)
@@ -694,8 +713,9 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
   float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [8 warps][2][C] = 512 floats
   float* coef = red + 512;                                               // [3C] = gamma*invstd | mean(dz) | mean(dz*xhat)
-  float* bnp2 = coef + 96;                                               // 2 x [4C] scale | shift | mean | invstd of block k (double-buffered)
-  double* dsum = reinterpret_cast<double*>(bnp2 + 256);                   // [1024]
+  float* bnp2 = coef + 96;                                               // 2 x 64 floats (scale/shift pairs, double-buffered) + 128 floats (dy coefficients)
+  double* dsum = reinterpret_cast<double*>(bnp2 + 256);                  // [1024]
+  uint4* ybuf = reinterpret_cast<uint4*>(dsum + 1024);                   // [2 tiles][4 chunks][256 threads]: each thread's y_k rows (cp.async)                   // [1024]
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -803,49 +823,64 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       }
     }
     float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, et < C: running dgamma / dbeta over the blocks
+    // y_k of this thread's two pixels: prefetched one block ahead with cp.async into this thread's own shared-memory slots
+    const uint32_t ybuf_s = smem_u32(ybuf);
+    auto load_y = [&](int k) {
+      const bf16* yk = a.ys + (size_t)k * a.act_elems;
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ybuf_s + (uint32_t)(((m * 4 + ch) * 256 + et) * 16)),
+                       "l"(reinterpret_cast<const uint4*>(yk + gp[m]) + ch) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    auto y_pair = [&](int m, int pe) -> float2 {      // channels 2*pe, 2*pe+1 of tile m's pixel
+      const uint32_t w = reinterpret_cast<const uint32_t*>(ybuf + ((m * 4 + (pe >> 2)) * 256 + et))[pe & 3];
+      return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
+    };
+    if (active) load_y(a.NB - 1);
     for (int it = 0; it < a.NB; ++it) {
       const int k = a.NB - 1 - it;
-      uint32_t ypk[2][16];
-      if (active) {
-        const bf16* yk = a.ys + (size_t)k * a.act_elems;
-#pragma unroll
-        for (int m = 0; m < 2; ++m)
-#pragma unroll
-          for (int ch = 0; ch < 4; ++ch) {
-            uint4 v = reinterpret_cast<const uint4*>(yk + gp[m])[ch];
-            ypk[m][ch * 4 + 0] = v.x; ypk[m][ch * 4 + 1] = v.y; ypk[m][ch * 4 + 2] = v.z; ypk[m][ch * 4 + 3] = v.w;
-          }
+      long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + it) * 8 : nullptr;
+      if (tr) tr[0] = clock64();
+      // per channel pair e (channels 2e, 2e+1): ssp[e] = {scale, shift, scale', shift'} (double-buffered: a slower thread may
+      // still be in phase B of the previous block); cfp[e] = {A1, A2, A3, -, A1', A2', A3', -} with dy = dz*A1 + y*A2 + A3
+      float4* ssp = reinterpret_cast<float4*>(bnp2 + (it & 1) * 64);
+      float4* cfp = reinterpret_cast<float4*>(bnp2 + 128);
+      if (et < C) {
+        float* d = reinterpret_cast<float*>(ssp) + (et >> 1) * 4 + (et & 1) * 2;
+        d[0] = a.scale_shift[(size_t)k * 2 * C + et]; d[1] = a.scale_shift[(size_t)k * 2 * C + C + et];
       }
-      float* bnp = bnp2 + (it & 1) * 128;            // slower threads may still read the previous block's copy in phase B
-      if (et < 2 * C) { bnp[et] = a.scale_shift[(size_t)k * 2 * C + et]; bnp[2 * C + et] = a.saved[(size_t)k * 2 * C + et]; }
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
       asm volatile("bar.sync 1, 256;" ::: "memory");
-      // ---- phase A: sums of dz and dz*xhat ----
+      // ---- phase A: per-channel sums of dz and dz*y over this warp's pixels ----
       float s1 = 0.f, s2 = 0.f;
       if (active) {
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
           float t[32];
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {              // dz
-            const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ypk[m][e]));
+          for (int e = 0; e < 16; ++e) {
+            const float2 y2 = y_pair(m, e);
             const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][e]));
-            const int c = 2 * e;
-            t[c] = fmaf(y2.x, bnp[c], bnp[C + c]) > 0.f ? g2.x : 0.f;
-            t[c + 1] = fmaf(y2.y, bnp[c + 1], bnp[C + c + 1]) > 0.f ? g2.y : 0.f;
+            const float4 ss = ssp[e];
+            t[2 * e] = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f;
+            t[2 * e + 1] = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
           }
           s1 += warp_col_sum(t, lane);
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {              // dz * xhat (recomputed: keeps the live set small)
-            const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ypk[m][e]));
+          for (int e = 0; e < 16; ++e) {              // dz * y (dz recomputed: keeps the live register set small)
+            const float2 y2 = y_pair(m, e);
             const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][e]));
-            const int c = 2 * e;
-            const float d0 = fmaf(y2.x, bnp[c], bnp[C + c]) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, bnp[c + 1], bnp[C + c + 1]) > 0.f ? g2.y : 0.f;
-            t[c] = d0 * ((y2.x - bnp[2 * C + c]) * bnp[3 * C + c]);
-            t[c + 1] = d1 * ((y2.y - bnp[2 * C + c + 1]) * bnp[3 * C + c + 1]);
+            const float4 ss = ssp[e];
+            t[2 * e] = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x * y2.x : 0.f;
+            t[2 * e + 1] = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y * y2.y : 0.f;
           }
           s2 += warp_col_sum(t, lane);
         }
       }
+      if (tr) tr[1] = clock64();
       red[(ew * 2 + 0) * C + lane] = s1; red[(ew * 2 + 1) * C + lane] = s2;
       asm volatile("bar.sync 1, 256;" ::: "memory");
       float* part = a.partial + (size_t)(it & 1) * 512 * 2 * C;
@@ -856,7 +891,9 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         part[(size_t)blockIdx.x * 2 * C + et] = t;
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (tr) tr[2] = clock64();
       if (et == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
+      if (tr) tr[3] = clock64();
       asm volatile("bar.sync 1, 256;" ::: "memory");
       {
         const int c4 = et & 15, r = et >> 4;
@@ -874,15 +911,18 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (et < C) {
-        double db = 0.0, dg = 0.0;
+        double db = 0.0, dgy = 0.0;
 #pragma unroll
-        for (int r = 0; r < 16; ++r) { db += dsum[r * 2 * C + et]; dg += dsum[r * 2 * C + C + et]; }
+        for (int r = 0; r < 16; ++r) { db += dsum[r * 2 * C + et]; dgy += dsum[r * 2 * C + C + et]; }
+        const double mean = (double)a.saved[(size_t)k * 2 * C + et], is = (double)a.saved[(size_t)k * 2 * C + C + et];
+        const double dg = is * (dgy - mean * db);       // sum dz*xhat = invstd * (sum dz*y - mean * sum dz)
         db_acc += (float)db; dg_acc += (float)dg;       // same order as the per-block path: k = NB-1 first
-        coef[et] = a.gamma[et] * bnp[3 * C + et];
-        coef[C + et] = (float)(db / count);
-        coef[2 * C + et] = (float)(dg / count);
+        const double a_ = (double)a.gamma[et] * is, b_ = db / count, c_ = dg / count;
+        float* d = reinterpret_cast<float*>(cfp) + (et >> 1) * 8 + (et & 1) * 4;
+        d[0] = (float)a_; d[1] = (float)(-a_ * c_ * is); d[2] = (float)(a_ * c_ * is * mean - a_ * b_); d[3] = 0.f;
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (tr) tr[4] = clock64();
       if (active) {
         // ---- phase B: dy -> the three operand copies (once the previous block's MMAs no longer read them) ----
         if (it > 0) mbar_wait(wfree(s), (uint32_t)((it - 1) & 1));
@@ -896,14 +936,12 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
             __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              const int c = ch * 8 + 2 * e;
-              const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ypk[m][ch * 4 + e]));
-              const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][ch * 4 + e]));
-              const float z0 = fmaf(y2.x, bnp[c], bnp[C + c]), z1 = fmaf(y2.y, bnp[c + 1], bnp[C + c + 1]);
-              const float d0 = z0 > 0.f ? g2.x : 0.f, d1 = z1 > 0.f ? g2.y : 0.f;
-              const float x0 = (y2.x - bnp[2 * C + c]) * bnp[3 * C + c], x1 = (y2.y - bnp[2 * C + c + 1]) * bnp[3 * C + c + 1];
-              oh[e] = __floats2bfloat162_rn(coef[c] * (d0 - coef[C + c] - x0 * coef[2 * C + c]),
-                                            coef[c + 1] * (d1 - coef[C + c + 1] - x1 * coef[2 * C + c + 1]));
+              const int pe = ch * 4 + e;
+              const float2 y2 = y_pair(m, pe);
+              const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][pe]));
+              const float4 ss = ssp[pe], c0 = cfp[pe * 2], c1 = cfp[pe * 2 + 1];
+              const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
+              oh[e] = __floats2bfloat162_rn(fmaf(d0, c0.x, fmaf(y2.x, c0.y, c0.z)), fmaf(d1, c1.x, fmaf(y2.y, c1.y, c1.z)));
             }
             *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
             if (j < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
@@ -912,6 +950,8 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         }
         fence_proxy_async();
         mbar_arrive(dyready(s));
+        if (tr) tr[5] = clock64();
+        if (k > 0) load_y(k - 1);          // y_k is dead: fetch the next block's rows while the dgrad MMAs run
         // ---- phase C: dx_k = dgrad + g ----
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
@@ -931,6 +971,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
               reinterpret_cast<uint4*>(a.dx0_out + gp[m])[ch] = make_uint4(gpk[m][ch * 4], gpk[m][ch * 4 + 1], gpk[m][ch * 4 + 2], gpk[m][ch * 4 + 3]);
           }
         }
+        if (tr) tr[6] = clock64();
         tc_fence_before();      // the accumulators are in registers: the next block's dgrad may overwrite them (ordered by dyready)
       }
     }
@@ -1131,7 +1172,7 @@ constexpr size_t persist_smem() {
 }
 
 constexpr size_t persist_bwd_smem() {
-  return 1024 + 2 * 4 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 112 + (512 + 96 + 256) * sizeof(float) + 1024 * sizeof(double) + 64;
+  return 1024 + 2 * 4 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 112 + (512 + 96 + 256) * sizeof(float) + 1024 * sizeof(double) + 2 * 4 * 256 * 16 + 64;
 }
 
 static int items(const nrd_plan* p) { return p->B * (p->C == 32 ? 1 : 2); }
@@ -1250,7 +1291,7 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_in, void* dx0_out, cudaStr
   a.dgamma = p->grads + p->off[3]; a.dbeta = p->grads + p->off[4];
   a.ys = (const bf16*)p->ys; a.g_in = (const bf16*)g_in; a.dx0_out = (bf16*)dx0_out;
   a.partial = p->stats_partial; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
-  a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems;
+  a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd;
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist, dim3(conv_grid(p)), dim3(320), args, persist_bwd_smem(), st));
   nrd_count_launch();

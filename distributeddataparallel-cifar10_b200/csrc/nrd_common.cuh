@@ -92,6 +92,7 @@ struct nrd_plan {
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
   unsigned long long* gbar; // grid-barrier counters (one per cooperative kernel type)
   void* trace;            // optional device buffer for in-kernel clock64 stamps (profiling aid; NULL = off)
+  void* trace_bwd;        // same for the persistent backward (lives in the pooled-gradient-free part of the dy scratch)
 };
 
 // Grid-wide barrier for cooperative launches (all CTAs co-resident).  ONE 64-bit monotonic counter per kernel type and plan:

@@ -1362,7 +1362,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_FUSE_BN_BWD: p->fuse_bn_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_FWD: p->persist_fwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_BWD: p->persist_bwd = value ? 1 : 0; return NRD_OK;
-    case NRD_OPT_TRACE: p->trace = value ? (void*)p->dxb : nullptr; return NRD_OK;   // stamps land in the dx pong scratch
+    case NRD_OPT_TRACE: p->trace = value ? (void*)p->dxb : nullptr; p->trace_bwd = value ? (void*)p->dy : nullptr; return NRD_OK;   // stamps land in the dx pong / dy scratch
     default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
   }
 }

@@ -75,7 +75,8 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
  * each image's activations in shared memory / TMEM between blocks (C = 32, B <= 296); 0 = one fused kernel per block. */
 #define NRD_OPT_PERSIST_FWD 1
 /* NRD_OPT_TRACE (default 0): profiling aid -- the persistent kernels write clock64 stamps of their phases into the dx pong
- * scratch (nrd_plan_tensor what=6): [cta][block][8] int64.  Never enable in a real step (backward uses that scratch). */
+ * scratch (forward; nrd_plan_tensor what=6) and the dy scratch (backward; what=2): [cta][block][8] int64.  Never enable in
+ * a real step when B*NB*64 bytes could overlap live data (per-block kernels use those buffers). */
 #define NRD_OPT_TRACE 2
 /* NRD_OPT_PERSIST_BWD (default 1): the same for the backward of the residual blocks: dL/dx stays in registers, dy in
  * shared memory, the weight-gradient accumulators in TMEM for the whole stack; 0 = per-block kernels. */

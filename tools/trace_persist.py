@@ -24,3 +24,15 @@ for cta in (0, 1, grid - 1):
     for k in range(10):
         t = tr[cta, k]
         print("  k=%d " % k + " ".join(f"{names[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next_start=+{int(tr[cta,k+1,0]-t[0])}" if k < 9 else ""))
+
+# ---- backward ----
+y = torch.randint(0, 10, (B,), device=dev)
+out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+torch.cuda.synchronize()
+trb = pl.tensor_view(2, 0).view(torch.int64)[: grid * 10 * 8].view(grid, 10, 8).cpu()
+namesb = ["start", "phaseA", "pre-barrier", "post-barrier", "combined", "phaseB(dy ready)", "phaseC(dx)"]
+for cta in (0, grid - 1):
+    print(f"BWD CTA {cta}:")
+    for it in range(10):
+        t = trb[cta, it]
+        print("  it=%d " % it + " ".join(f"{namesb[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next=+{int(trb[cta,it+1,0]-t[0])}" if it < 9 else ""))
