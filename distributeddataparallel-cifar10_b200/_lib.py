@@ -40,6 +40,8 @@ _PROTOS = {
     "nrd_cross_entropy": (i32, [vp, vp, i32, f32, vp, vp, vp, vp]),
     "nrd_cross_entropy_static": (i32, [vp, vp, i32, f32, vp, vp, vp]),
     "nrd_backward": (i32, [vp, vp, vp]),
+    "nrd_backward_head": (i32, [vp, vp, vp]),
+    "nrd_backward_body": (i32, [vp, vp, vp]),
     "nrd_sgd_update": (i32, [vp, vp, sz, f32, f32, vp]),
     "nrd_train_step": (i32, [vp, vp, vp, f32, vp, vp, vp]),
     "nrd_gen_batch": (i32, [vp, vp, i32, u64, u32, u64, vp]),

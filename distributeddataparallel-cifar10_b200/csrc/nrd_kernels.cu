@@ -703,22 +703,40 @@ __global__ void k_maxpool_bwd(const T* __restrict__ gp, const uint8_t* __restric
 // ------------------------------------------------------------------------------------------
 // head: fc1 + relu, fc2, softmax cross-entropy                     (model/resnet.py:19-21, main.py:28)
 // ------------------------------------------------------------------------------------------
-// fc1 as a split-K product: CTA (bx, ks) = 32 batch rows x 32 outputs over the K slice [ks*128, ks*128+128);
-// part[ks][b][j] = sum_{k in slice} p[b][k] * w1t[k][j].  The slices are summed in order by k_fc2_fwd.
+// max_pool2d(x_NB, 2) fused into fc1 as a split-K product (model/resnet.py:18-20): CTA (bx, ks) = 32 batch rows x 32 outputs
+// over the K slice [ks*128, ks*128+128) of the pooled NHWC vector.  Every pooled element belongs to exactly one CTA, which
+// computes it from its 2x2 window of x_NB (first max wins), writes it and its arg-max for backward, and uses it:
+// part[ks][b][j] = sum_{k in slice} pooled[b][k] * w1t[k][j].  The slices are summed in order by k_fc2_fwd.
 template <typename T>
-__global__ void __launch_bounds__(256) k_fc1_fwd_part(const T* __restrict__ p, const float* __restrict__ w1t,
-                                                      float* __restrict__ part, int B, int K) {
+__global__ void __launch_bounds__(256) k_pool_fc1_fwd_part(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restrict__ idx2,
+                                                           const float* __restrict__ w1t, float* __restrict__ part, int B, int C) {
   __shared__ __align__(16) float ws[128 * 32];
   __shared__ float ps[32 * 129];
-  const int tid = threadIdx.x, b0 = blockIdx.x * 32, k0 = blockIdx.y * 128;
+  const int tid = threadIdx.x, b0 = blockIdx.x * 32, k0 = blockIdx.y * 128, K = 64 * C;
   for (int i = tid; i < 128 * 32 / 4; i += 256)
     reinterpret_cast<float4*>(ws)[i] = reinterpret_cast<const float4*>(w1t + (size_t)k0 * 32)[i];
-  for (int i = tid; i < 32 * 32; i += 256) {          // 32 rows x 32 four-element chunks
-    int r = i >> 5, c4 = i & 31;
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
-    if (b0 + r < B) ld4(p + (size_t)(b0 + r) * K + k0 + c4 * 4, v);
-    float* d = ps + r * 129 + c4 * 4;
-    d[0] = v[0]; d[1] = v[1]; d[2] = v[2]; d[3] = v[3];
+  for (int i = tid; i < 32 * 16; i += 256) {          // 32 rows x 16 eight-channel chunks of the slice
+    const int r = i >> 4, c8 = i & 15, b = b0 + r;
+    const int kk = k0 + c8 * 8, hw = kk / C, c = kk % C, ph = hw >> 3, pw = hw & 7;
+    float m[8]; int mi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { m[j] = 0.f; mi[j] = 0; }
+    if (b < B) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float v[8];
+        ld8(x + (((size_t)b * 16 + 2 * ph + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + c, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (q == 0 || v[j] > m[j]) { m[j] = v[j]; mi[j] = q; }
+      }
+      st8(pooled + (size_t)b * K + kk, m);
+      uint2 pk; uint8_t* pb = reinterpret_cast<uint8_t*>(&pk);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) pb[j] = (uint8_t)mi[j];
+      *reinterpret_cast<uint2*>(idx2 + (size_t)b * K + kk) = pk;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ps[r * 129 + c8 * 8 + j] = m[j];
   }
   __syncthreads();
   const int r = tid >> 3, jq = tid & 7;
@@ -758,61 +776,61 @@ __global__ void __launch_bounds__(256) k_fc2_fwd(const float* __restrict__ part,
   }
 }
 
-// per-row loss and dlogits = (softmax - onehot) * grad_scale / B
-__global__ void k_ce_rows(const float* __restrict__ logits, const int64_t* __restrict__ labels, int B, float gscale,
-                          float* __restrict__ loss_rows, float* __restrict__ dlogits) {
-  int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
-  float v[NRD_NCLS], m = -INFINITY;
-#pragma unroll
-  for (int c = 0; c < NRD_NCLS; ++c) { v[c] = logits[b * NRD_NCLS + c]; m = fmaxf(m, v[c]); }
-  float s = 0.f;
-#pragma unroll
-  for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
-  int lab = (int)labels[b];
-  float inv = 1.f / s, sc = gscale / (float)B;
-  loss_rows[b] = logf(s) + m - logits[b * NRD_NCLS + lab];
-  if (dlogits) {
-#pragma unroll
-    for (int c = 0; c < NRD_NCLS; ++c) dlogits[b * NRD_NCLS + c] = (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc;
-  }
-}
-
-__global__ void k_loss_mean(const float* __restrict__ loss_rows, int B, float* __restrict__ loss) {
+// softmax cross-entropy, forward and gradient, one CTA: per-row loss (kept in loss_rows) and dlogits =
+// (softmax - onehot) * grad_scale / B, then the mean loss by a fixed-shape tree over the CTA (deterministic).
+__global__ void __launch_bounds__(256) k_ce(const float* __restrict__ logits, const int64_t* __restrict__ labels, int B, float gscale,
+                                            float* __restrict__ loss_rows, float* __restrict__ dlogits, float* __restrict__ loss) {
   __shared__ double red[256];
-  double s = 0.0;
-  for (int i = threadIdx.x; i < B; i += 256) s += (double)loss_rows[i];
-  red[threadIdx.x] = s;
+  double acc = 0.0;
+  for (int b = threadIdx.x; b < B; b += 256) {
+    float v[NRD_NCLS], m = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < NRD_NCLS; ++c) { v[c] = logits[b * NRD_NCLS + c]; m = fmaxf(m, v[c]); }
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
+    const int lab = (int)labels[b];
+    const float inv = 1.f / s, sc = gscale / (float)B;
+    const float l = logf(s) + m - logits[b * NRD_NCLS + lab];
+    loss_rows[b] = l;
+    acc += (double)l;
+    if (dlogits) {
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) dlogits[b * NRD_NCLS + c] = (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc;
+    }
+  }
+  red[threadIdx.x] = acc;
   __syncthreads();
   for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
-  if (threadIdx.x == 0) *loss = (float)(red[0] / B);
+  if (threadIdx.x == 0 && loss) *loss = (float)(red[0] / B);
 }
 
-// dh1[b][j] = sum_c dlogits[b][c] * w2[c][j] * [h1>0]
-__global__ void k_fc2_bwd(const float* __restrict__ dlogits, const float* __restrict__ w2, const float* __restrict__ h1,
-                          float* __restrict__ dh1, int B) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B * NRD_FC1_OUT) return;
-  int b = i / NRD_FC1_OUT, j = i % NRD_FC1_OUT;
+// dh1[b][j] = sum_c dlogits[b][c] * w2[c][j] * [h1[b][j] > 0] is 10 MACs per element: every consumer below recomputes it
+// while staging its rows instead of reading it from a kernel of its own, which also makes the three consumers independent
+// of one another (head weight gradients can run beside the body backward).
+__device__ __forceinline__ float dh1_elem(const float* __restrict__ dl_row /*[10]*/, const float* __restrict__ w2s /*[10][32]*/, int j, float h) {
   float s = 0.f;
 #pragma unroll
-  for (int c = 0; c < NRD_NCLS; ++c) s = fmaf(dlogits[b * NRD_NCLS + c], w2[c * NRD_FC1_OUT + j], s);
-  dh1[i] = h1[i] > 0.f ? s : 0.f;
+  for (int c = 0; c < NRD_NCLS; ++c) s = fmaf(dl_row[c], w2s[c * NRD_FC1_OUT + j], s);
+  return h > 0.f ? s : 0.f;
 }
 
 // dW2[c][j], db2[c], dbfc1[j]: one CTA of 384 threads, each output summed over the batch in order; the batch is staged
 // through shared memory in chunks of 64 rows (coalesced loads, then shared-memory-only loops)
 __global__ void __launch_bounds__(384) k_head_wgrad(const float* __restrict__ dlogits, const float* __restrict__ h1,
-                             const float* __restrict__ dh1, int B, float* __restrict__ dw2,
+                             const float* __restrict__ w2, int B, float* __restrict__ dw2,
                              float* __restrict__ db2, float* __restrict__ dbfc1) {
-  __shared__ float dl[64 * NRD_NCLS], hh[64 * NRD_FC1_OUT], dd[64 * NRD_FC1_OUT];
+  __shared__ float dl[64 * NRD_NCLS], hh[64 * NRD_FC1_OUT], dd[64 * NRD_FC1_OUT], w2s[NRD_NCLS * NRD_FC1_OUT];
   const int t = threadIdx.x;
+  for (int i = t; i < NRD_NCLS * NRD_FC1_OUT; i += 384) w2s[i] = w2[i];
   float s = 0.f;
   for (int b0 = 0; b0 < B; b0 += 64) {
     const int nb = min(64, B - b0);
     __syncthreads();
     for (int i = t; i < nb * NRD_NCLS; i += 384) dl[i] = dlogits[(size_t)b0 * NRD_NCLS + i];
-    for (int i = t; i < nb * NRD_FC1_OUT; i += 384) { hh[i] = h1[(size_t)b0 * NRD_FC1_OUT + i]; dd[i] = dh1[(size_t)b0 * NRD_FC1_OUT + i]; }
+    for (int i = t; i < nb * NRD_FC1_OUT; i += 384) hh[i] = h1[(size_t)b0 * NRD_FC1_OUT + i];
+    __syncthreads();
+    for (int i = t; i < nb * NRD_FC1_OUT; i += 384) dd[i] = dh1_elem(dl + (i >> 5) * NRD_NCLS, w2s, i & 31, hh[i]);
     __syncthreads();
     if (t < 320) {
       const int c = t / 32, j = t % 32;
@@ -833,24 +851,29 @@ __global__ void __launch_bounds__(384) k_head_wgrad(const float* __restrict__ dl
 // dWfc1[j][c*64+hw] = sum_b dh1[b][j] * p[b][hw*C+c].  CTA = 64 consecutive NHWC columns x 32 rows; the batch is staged
 // through shared memory in chunks of 64 rows.
 template <typename T>
-__global__ void __launch_bounds__(256) k_fc1_wgrad(const T* __restrict__ p, const float* __restrict__ dh1,
-                                                   float* __restrict__ dw1, int B, int C) {
+__global__ void __launch_bounds__(256) k_fc1_wgrad(const T* __restrict__ p, const float* __restrict__ dlogits, const float* __restrict__ h1,
+                                                   const float* __restrict__ w2, float* __restrict__ dw1, int B, int C) {
   __shared__ __align__(16) float ds[64 * NRD_FC1_OUT];
   __shared__ float ps[64 * 64];
+  __shared__ float dl[64 * NRD_NCLS], w2s[NRD_NCLS * NRD_FC1_OUT];
   const int tid = threadIdx.x, il = tid % 64, jg = tid / 64, K = 64 * C, i0 = blockIdx.x * 64;
+  for (int i = tid; i < NRD_NCLS * NRD_FC1_OUT; i += 256) w2s[i] = w2[i];
   float acc[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
   for (int bb = 0; bb < B; bb += 64) {
     const int nb = min(64, B - bb);
     __syncthreads();
-    for (int q = tid; q < nb * NRD_FC1_OUT; q += 256) ds[q] = dh1[(size_t)bb * NRD_FC1_OUT + q];
+    for (int q = tid; q < nb * NRD_NCLS; q += 256) dl[q] = dlogits[(size_t)bb * NRD_NCLS + q];
     for (int q = tid; q < nb * 16; q += 256) {          // 64 rows x 16 four-element chunks
       int r = q >> 4, c4 = q & 15;
       float v[4]; ld4(p + (size_t)(bb + r) * K + i0 + c4 * 4, v);
       float* d = ps + r * 64 + c4 * 4;
       d[0] = v[0]; d[1] = v[1]; d[2] = v[2]; d[3] = v[3];
     }
+    __syncthreads();
+    for (int q = tid; q < nb * NRD_FC1_OUT; q += 256)
+      ds[q] = dh1_elem(dl + (q >> 5) * NRD_NCLS, w2s, q & 31, h1[(size_t)bb * NRD_FC1_OUT + q]);
     __syncthreads();
 #pragma unroll 4
     for (int b = 0; b < nb; ++b) {
@@ -869,14 +892,22 @@ __global__ void __launch_bounds__(256) k_fc1_wgrad(const T* __restrict__ p, cons
 // d(pooled)[b][hw][c] = sum_j dh1[b][j] * w1t[hw*C+c][j], scattered through pool-2's argmax into gx [B,16,16,C].
 // CTA = 8 batch rows x 256 columns: each weight row is read once per 8 rows.
 template <typename T>
-__global__ void __launch_bounds__(256) k_fc1_dgrad_unpool(const float* __restrict__ dh1, const float* __restrict__ w1t,
+__global__ void __launch_bounds__(256) k_fc1_dgrad_unpool(const float* __restrict__ dlogits, const float* __restrict__ h1,
+                                                          const float* __restrict__ w2, const float* __restrict__ w1t,
                                                           const uint8_t* __restrict__ idx2, T* __restrict__ gx,
                                                           int B, int C) {
   __shared__ float d[8][NRD_FC1_OUT];
+  __shared__ float dl[8 * NRD_NCLS], w2s[NRD_NCLS * NRD_FC1_OUT];
   const int K = 64 * C, per_b = K / 256, b0 = (blockIdx.x / per_b) * 8, i = (blockIdx.x % per_b) * 256 + threadIdx.x;
+  for (int q = threadIdx.x; q < NRD_NCLS * NRD_FC1_OUT; q += 256) w2s[q] = w2[q];
+  if (threadIdx.x < 8 * NRD_NCLS) {
+    const int r = threadIdx.x / NRD_NCLS;
+    dl[threadIdx.x] = (b0 + r < B) ? dlogits[(size_t)b0 * NRD_NCLS + threadIdx.x] : 0.f;
+  }
+  __syncthreads();
   {
     const int r = threadIdx.x >> 5, j = threadIdx.x & 31;
-    d[r][j] = (b0 + r < B) ? dh1[(size_t)(b0 + r) * NRD_FC1_OUT + j] : 0.f;
+    d[r][j] = (b0 + r < B) ? dh1_elem(dl + r * NRD_NCLS, w2s, j, h1[(size_t)(b0 + r) * NRD_FC1_OUT + j]) : 0.f;
   }
   __syncthreads();
   float s[8];
@@ -1198,9 +1229,8 @@ extern "C" int nrd_maxpool_bwd(const void* gp, const uint8_t* idx, void* gx, int
 extern "C" int nrd_cross_entropy(const float* logits, const int64_t* labels, int B, float grad_scale, float* loss_out, float* dlogits,
                                  float* row_scratch, void* stream) {
   NRD_REQUIRE(B > 0 && logits && labels && row_scratch, "nrd_cross_entropy: bad arguments");
-  k_ce_rows<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(logits, labels, B, grad_scale, row_scratch, dlogits);
+  k_ce<<<1, 256, 0, (cudaStream_t)stream>>>(logits, labels, B, grad_scale, row_scratch, dlogits, loss_out);
   LAUNCH_CHECK();
-  if (loss_out) { k_loss_mean<<<1, 256, 0, (cudaStream_t)stream>>>(row_scratch, B, loss_out); LAUNCH_CHECK(); }
   return NRD_OK;
 }
 
@@ -1237,9 +1267,7 @@ extern "C" int nrd_cross_entropy_static(const float* logits, const int64_t* labe
     rows = g_ce_static_ptr[dev];
   }
   // rows [0,B) are fully overwritten before they are read, so nothing has to start at zero
-  k_ce_rows<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(logits, labels, B, grad_scale, rows, dlogits);
-  LAUNCH_CHECK();
-  k_loss_mean<<<1, 256, 0, (cudaStream_t)stream>>>(rows, B, loss_out);
+  k_ce<<<1, 256, 0, (cudaStream_t)stream>>>(logits, labels, B, grad_scale, rows, dlogits, loss_out);
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1430,35 +1458,46 @@ extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int 
     }
     NRD_TRY(bn_relu_add_any(yk, xk, ss, xn, B, C, dt, st));
   }
-  NRD_TRY(nrd_maxpool_fwd(p->xs + act * NB, p->pooled, p->idx2, B, C, dt, stream));
   const int K = 64 * C;
   const dim3 g1((B + 31) / 32, K / 128);
-  if (dt == NRD_F32) k_fc1_fwd_part<float><<<g1, 256, 0, st>>>((const float*)p->pooled, p->w1p, p->fc1_part, B, K);
-  else k_fc1_fwd_part<bf16><<<g1, 256, 0, st>>>((const bf16*)p->pooled, p->w1p, p->fc1_part, B, K);
+  if (dt == NRD_F32) k_pool_fc1_fwd_part<float><<<g1, 256, 0, st>>>((const float*)(p->xs + act * NB), (float*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C);
+  else k_pool_fc1_fwd_part<bf16><<<g1, 256, 0, st>>>((const bf16*)(p->xs + act * NB), (bf16*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C);
   LAUNCH_CHECK();
   k_fc2_fwd<<<(B + 7) / 8, 256, 0, st>>>(p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B);
   LAUNCH_CHECK();
   return NRD_OK;
 }
 
+// head weight gradients (fc1.weight/bias, fc2.weight/bias): independent of the body backward given dlogits
+extern "C" int nrd_backward_head(nrd_plan* p, const float* dlogits, void* stream) {
+  NRD_REQUIRE(p && dlogits, "nrd_backward_head: null pointer");
+  NRD_CHECK_CUDA(cudaSetDevice(p->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int B = p->B, C = p->C, dt = p->dtype;
+  k_head_wgrad<<<1, 384, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), B, GRD(P_FC2W), GRD(P_FC2B), GRD(P_FC1B));
+  LAUNCH_CHECK();
+  if (dt == NRD_F32) k_fc1_wgrad<float><<<C, 256, 0, st>>>((const float*)p->pooled, dlogits, p->h1, PRM(P_FC2W), GRD(P_FC1W), B, C);
+  else k_fc1_wgrad<bf16><<<C, 256, 0, st>>>((const bf16*)p->pooled, dlogits, p->h1, PRM(P_FC2W), GRD(P_FC1W), B, C);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
 extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
-  NRD_REQUIRE(p && dlogits, "nrd_backward: null pointer");
+  NRD_TRY(nrd_backward_head(p, dlogits, stream));
+  return nrd_backward_body(p, dlogits, stream);
+}
+
+// everything below the head: d(pooled) -> residual blocks -> stem; fills the body gradients (conv1, block conv, gamma, beta)
+extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream) {
+  NRD_REQUIRE(p && dlogits, "nrd_backward_body: null pointer");
   NRD_CHECK_CUDA(cudaSetDevice(p->device));
   cudaStream_t st = (cudaStream_t)stream;
   const int B = p->B, C = p->C, NB = p->NB, dt = p->dtype;
   const size_t act = p->act_elems * p->esz;
-  // head
-  k_fc2_bwd<<<(B * NRD_FC1_OUT + 255) / 256, 256, 0, st>>>(dlogits, PRM(P_FC2W), p->h1, p->dh1, B);
-  LAUNCH_CHECK();
-  k_head_wgrad<<<1, 384, 0, st>>>(dlogits, p->h1, p->dh1, B, GRD(P_FC2W), GRD(P_FC2B), GRD(P_FC1B));
-  LAUNCH_CHECK();
-  if (dt == NRD_F32) k_fc1_wgrad<float><<<C, 256, 0, st>>>((const float*)p->pooled, p->dh1, GRD(P_FC1W), B, C);
-  else k_fc1_wgrad<bf16><<<C, 256, 0, st>>>((const bf16*)p->pooled, p->dh1, GRD(P_FC1W), B, C);
-  LAUNCH_CHECK();
   char* g = p->dxa; char* gn = p->dxb;
   const int K = 64 * C;
-  if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (float*)g, B, C);
-  else k_fc1_dgrad_unpool<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(p->dh1, p->w1p, p->idx2, (bf16*)g, B, C);
+  if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (float*)g, B, C);
+  else k_fc1_dgrad_unpool<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (bf16*)g, B, C);
   LAUNCH_CHECK();
   // residual blocks, last to first; the shared block's grads accumulate over the NB applications
   const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd;

@@ -173,9 +173,33 @@ class Engine:
         self._last_plan = pl
         return logits
 
-    def backward(self, pl: _Plan, dlogits: torch.Tensor):
+    def backward(self, pl: _Plan, dlogits: torch.Tensor, after_head=None, after_body=None):
+        """loss.backward() below the logits.  The head weight gradients (fc1/fc2: 86.6 % of the gradient bytes) run on a
+        side stream beside the body backward; `after_head` / `after_body` are called with that half's stream current right
+        after its kernels are enqueued (the DDP wrapper launches each bucket's all-reduce there).  Both halves are joined
+        on the caller's stream before returning."""
         dlogits = dlogits.contiguous().float()
-        check(lib.nrd_backward(pl.handle, dlogits.data_ptr(), _stream_ptr()), "nrd_backward")
+        main = torch.cuda.current_stream()
+        side = self._side_stream()
+        fork = torch.cuda.Event(); join = torch.cuda.Event()
+        fork.record(main)
+        side.wait_event(fork)
+        with torch.cuda.stream(side):
+            check(lib.nrd_backward_head(pl.handle, dlogits.data_ptr(), side.cuda_stream), "nrd_backward_head")
+            if after_head is not None:
+                after_head()
+            join.record(side)
+        check(lib.nrd_backward_body(pl.handle, dlogits.data_ptr(), main.cuda_stream), "nrd_backward_body")
+        if after_body is not None:
+            after_body()
+        main.wait_event(join)
+        if not torch.cuda.is_current_stream_capturing():
+            dlogits.record_stream(side)
+
+    def _side_stream(self):
+        if getattr(self, "_side", None) is None or self._side.device != self.device:
+            self._side = torch.cuda.Stream(device=self.device)
+        return self._side
 
     def sgd_update(self, lr: float, inv_world: float = 1.0, lo: int = 0, hi: Optional[int] = None):
         hi = self.offsets[9] if hi is None else hi

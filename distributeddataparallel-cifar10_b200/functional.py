@@ -27,10 +27,8 @@ class _NetResDeepFn(torch.autograd.Function):
         views = eng.grad_views()
         # accumulate semantics if the caller did not zero_grad (the reference always does, main.py:37)
         keep = [None if p.grad is None else p.grad.detach().clone() for p in params]
-        eng.backward(pl, dlogits)
-        hook = getattr(ctx.module, "_nrd_post_backward", None)
-        if hook is not None:
-            hook()                      # DDP wrapper: bucketed allreduce of the flat gradient vector
+        hooks = getattr(ctx.module, "_nrd_bucket_hooks", None)      # DDP wrapper: (head, body) bucket all-reduces
+        eng.backward(pl, dlogits, *(hooks or (None, None)))
         for p, v, k in zip(params, views, keep):
             if k is not None:
                 v.add_(k)

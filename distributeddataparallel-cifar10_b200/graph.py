@@ -47,11 +47,10 @@ class TrainStep:
         check(lib.nrd_forward(pl.handle, self.imgs.data_ptr(), self.logits.data_ptr(), 1, st), "nrd_forward")
         check(lib.nrd_cross_entropy(self.logits.data_ptr(), self.labels.data_ptr(), self.B, 1.0, self.loss.data_ptr(),
                                     pl.dlogits.data_ptr(), pl.loss_rows.data_ptr(), st), "nrd_cross_entropy")
-        check(lib.nrd_backward(pl.handle, pl.dlogits.data_ptr(), st), "nrd_backward")
-        if self.world > 1:
-            body, head = eng.bucket_slices()
-            for lo, hi in (head, body):
-                dist.all_reduce(eng.flat_grads[lo:hi], op=dist.ReduceOp.SUM, group=self.ddp.process_group)   # C3
+        # backward: head weight grads (+ their bucket's all-reduce) on a side stream beside the body backward (C3)
+        sum_head = (lambda: self.ddp._allreduce_bucket(1, average=False)) if self.world > 1 else None
+        sum_body = (lambda: self.ddp._allreduce_bucket(0, average=False)) if self.world > 1 else None
+        eng.backward(pl, pl.dlogits, sum_head, sum_body)
         # fused mean + SGD (K16), then re-derive the packed weight copies
         check(lib.nrd_sgd_update(eng.flat_params.data_ptr(), eng.flat_grads.data_ptr(), eng.offsets[9], self.lr,
                                  1.0 / self.world, st), "nrd_sgd_update")

@@ -24,14 +24,12 @@ class DistributedDataParallel(torch.nn.Module):
         self.process_group = process_group
         self.world_size = dist.get_world_size(process_group)
         self.broadcast_buffers = broadcast_buffers
-        self._comm_stream = None
         eng = module.engine
         dev = next(module.parameters()).device
         if dev.type == "cuda":
             eng.adopt(dev)
-            self._comm_stream = torch.cuda.Stream(device=dev)
             self._sync_module_states()
-        object.__setattr__(module, "_nrd_post_backward", self._allreduce_grads)
+        object.__setattr__(module, "_nrd_bucket_hooks", (lambda: self._allreduce_bucket(1), lambda: self._allreduce_bucket(0)))
 
     # C1 ------------------------------------------------------------------------------------
     def _sync_module_states(self):
@@ -54,23 +52,22 @@ class DistributedDataParallel(torch.nn.Module):
         return self.module(*inputs, **kwargs)
 
     # C3 ------------------------------------------------------------------------------------
-    def _allreduce_grads(self):
-        eng = self.module.engine
+    def _allreduce_bucket(self, which: int, average: bool = True):
+        """Mean all-reduce of one bucket of the flat gradient vector (0 = body, 1 = head) on the CURRENT stream: the engine
+        calls this right after the kernels that produce the bucket, on the stream they run on, so the head bucket's
+        exchange overlaps the whole body backward (the reference's single bucket fires only after the last gradient)."""
         if self.world_size == 1:
             return
-        body, head = eng.bucket_slices()
-        cur = torch.cuda.current_stream()
-        self._comm_stream.wait_stream(cur)
-        nccl = dist.get_backend(self.process_group) == "nccl"
-        with torch.cuda.stream(self._comm_stream):
-            for lo, hi in (head, body):
-                bucket = eng.flat_grads[lo:hi]
-                if nccl:
-                    dist.all_reduce(bucket, op=dist.ReduceOp.AVG, group=self.process_group)
-                else:
-                    dist.all_reduce(bucket, op=dist.ReduceOp.SUM, group=self.process_group)
-                    bucket.div_(self.world_size)
-        cur.wait_stream(self._comm_stream)
+        eng = self.module.engine
+        lo, hi = eng.bucket_slices()[which]
+        bucket = eng.flat_grads[lo:hi]
+        if not average:
+            dist.all_reduce(bucket, op=dist.ReduceOp.SUM, group=self.process_group)
+        elif dist.get_backend(self.process_group) == "nccl":
+            dist.all_reduce(bucket, op=dist.ReduceOp.AVG, group=self.process_group)
+        else:
+            dist.all_reduce(bucket, op=dist.ReduceOp.SUM, group=self.process_group)
+            bucket.div_(self.world_size)
 
 
 def flat_allreduce_mean_cpu(flat: torch.Tensor, n_body: int, group=None):

@@ -119,6 +119,11 @@ int nrd_cross_entropy(const float* logits, const int64_t* labels, int B, float g
 int nrd_cross_entropy_static(const float* logits, const int64_t* labels, int B, float grad_scale,
                              float* loss_out, float* dlogits, void* stream);
 int nrd_backward(nrd_plan* plan, const float* dlogits, void* stream);
+/* The two independent halves of nrd_backward, so a caller can run them on different streams and start the all-reduce of
+ * the head bucket (86.6 % of the gradient bytes) while the body backward is still running:
+ * _head fills fc1/fc2 weight+bias gradients, _body everything else (d(pooled) -> residual blocks -> stem). */
+int nrd_backward_head(nrd_plan* plan, const float* dlogits, void* stream);
+int nrd_backward_body(nrd_plan* plan, const float* dlogits, void* stream);
 int nrd_sgd_update(float* params, const float* grads, size_t n, float lr, float inv_world, void* stream);
 int nrd_train_step(nrd_plan* plan, const float* images, const int64_t* labels, float lr,
                    float* logits, float* loss_out, void* stream);
