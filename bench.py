@@ -262,8 +262,14 @@ def main():
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
     if world > 1:
+        # release the captured graph (it holds NCCL kernels) before the communicator goes away; then leave without the
+        # communicator teardown, which can block behind captured collectives
+        step.graph = None
+        del step
+        torch.cuda.synchronize(dev)
         dist.barrier()
-        dist.destroy_process_group()
+        sys.stdout.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
