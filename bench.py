@@ -220,8 +220,15 @@ def main():
     if rank == 0:
         s_act = 2 if args.dtype == "bf16" else 4
         T = B * 256 * C * s_act
-        ops = {"conv_fwd": (0, NB, 2 * T), "bn_apply": (1, NB, 3 * T), "bn_bwd": (2, NB, 5 * T), "wgrad": (3, NB, 2 * T),
-               "dgrad": (4, NB, 3 * T), "stem_fwd": (5, 1, B * 3072 * 4 + T + T // s_act), "stem_bwd": (6, 1, B * 3072 * 4 + 2 * T + T // s_act)}
+        persist = lib.nrd_plan_run_op(step.plan.handle, 8, 0, torch.cuda.current_stream().cuda_stream) == 0
+        torch.cuda.synchronize(dev)
+        # algorithmic HBM bytes per launch = SURVEY 8(d) per-image figures x the images (and blocks) one launch covers
+        if persist:
+            ops = {"stem_fwd": (5, 1, B * 3072 * 4 + T + T // s_act), "fwd_blocks(persistent)": (8, 1, NB * 4 * T),
+                   "bwd_blocks(persistent)": (9, 1, NB * 6 * T), "stem_bwd": (6, 1, B * 3072 * 4 + 2 * T + T // s_act)}
+        else:
+            ops = {"conv_fwd": (0, NB, 2 * T), "bn_apply": (1, NB, 3 * T), "bn_bwd": (2, NB, 5 * T), "wgrad": (3, NB, 2 * T),
+                   "dgrad": (4, NB, 3 * T), "stem_fwd": (5, 1, B * 3072 * 4 + T + T // s_act), "stem_bwd": (6, 1, B * 3072 * 4 + 2 * T + T // s_act)}
         stream = torch.cuda.current_stream().cuda_stream
         breakdown = {}
         for name, (op, count, nbytes) in ops.items():

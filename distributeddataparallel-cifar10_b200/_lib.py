@@ -43,6 +43,7 @@ _PROTOS = {
     "nrd_backward_head": (i32, [vp, vp, vp]),
     "nrd_backward_body": (i32, [vp, vp, vp]),
     "nrd_sgd_update": (i32, [vp, vp, sz, f32, f32, vp]),
+    "nrd_sgd_update_pack": (i32, [vp, f32, f32, vp]),
     "nrd_train_step": (i32, [vp, vp, vp, f32, vp, vp, vp]),
     "nrd_gen_batch": (i32, [vp, vp, i32, u64, u32, u64, vp]),
     "nrd_pack_conv_weight": (i32, [vp, i32, vp, vp, vp]),

@@ -64,6 +64,7 @@ struct nrd_plan {
   float* h1;           // [B,32] relu(fc1)
   float* dh1;          // [B,32]
   float* fc1_part;     // [K/128][B][32] split-K partial products of fc1
+  float* fc1w_partial; // [splits][32][64*C] batch-split partials of the fc1 weight gradient
   float* dlogits;      // [B,10]  (train_step path)
   float* loss_rows;    // [B]
   float* saved_stats;  // [NB][2C] mean | invstd

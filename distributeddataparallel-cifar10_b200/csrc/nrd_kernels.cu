@@ -214,6 +214,28 @@ __global__ void __launch_bounds__(256) k_stem_bwd(const float* __restrict__ img,
   }
 }
 
+// conv-weight and stem partials in ONE launch: CTAs [0, 9C*C/32) reduce the conv partials, the rest the stem partials
+__global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ wpartial, int wblk, const float* __restrict__ spartial, int sblk,
+                                                     int C, float* __restrict__ dw, float* __restrict__ dw1, float* __restrict__ db1) {
+  __shared__ double red[8][33];
+  const int o = threadIdx.x & 31, r = threadIdx.x >> 5, nconv = 9 * C * C / 32;
+  const bool conv = (int)blockIdx.x < nconv;
+  const int i = (conv ? blockIdx.x : blockIdx.x - nconv) * 32 + o, n = conv ? 9 * C * C : 28 * C, nblk = conv ? wblk : sblk;
+  const float* part = conv ? wpartial : spartial;
+  double s = 0.0;
+#pragma unroll 8
+  for (int b = r; b < nblk; b += 8) s += (double)__ldcg(part + (size_t)b * n + i);
+  red[r][o] = s;
+  __syncthreads();
+  if (r == 0) {
+    double tot = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) tot += red[k][o];
+    if (conv) { const int t = i / (C * C), co = (i / C) % C, ci = i % C; dw[((size_t)co * C + ci) * 9 + t] = (float)tot; }
+    else { const int k = i / C, co = i % C; if (k < 27) dw1[co * 27 + k] = (float)tot; else db1[co] = (float)tot; }
+  }
+}
+
 // CTA = 32 outputs x 8 row classes, fixed-order combine
 __global__ void __launch_bounds__(256) k_stem_bwd_reduce(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dw,
                                   float* __restrict__ db) {
@@ -815,44 +837,44 @@ __device__ __forceinline__ float dh1_elem(const float* __restrict__ dl_row /*[10
   return h > 0.f ? s : 0.f;
 }
 
-// dW2[c][j], db2[c], dbfc1[j]: one CTA of 384 threads, each output summed over the batch in order; the batch is staged
-// through shared memory in chunks of 64 rows (coalesced loads, then shared-memory-only loops)
-__global__ void __launch_bounds__(384) k_head_wgrad(const float* __restrict__ dlogits, const float* __restrict__ h1,
+// dW2[c][j], db2[c], dbfc1[j].  grid = 12 CTAs of 256 threads: CTA c < 10 -> dW2[c][:], CTA 10 -> db2, CTA 11 -> dbfc1; thread =
+// (output, one of 8 batch-row classes); every class sums its rows in order and the 8 classes are combined in order.
+__global__ void __launch_bounds__(256) k_head_wgrad(const float* __restrict__ dlogits, const float* __restrict__ h1,
                              const float* __restrict__ w2, int B, float* __restrict__ dw2,
                              float* __restrict__ db2, float* __restrict__ dbfc1) {
-  __shared__ float dl[64 * NRD_NCLS], hh[64 * NRD_FC1_OUT], dd[64 * NRD_FC1_OUT], w2s[NRD_NCLS * NRD_FC1_OUT];
-  const int t = threadIdx.x;
-  for (int i = t; i < NRD_NCLS * NRD_FC1_OUT; i += 384) w2s[i] = w2[i];
+  __shared__ float red[8][33];
+  __shared__ float w2s[NRD_NCLS * NRD_FC1_OUT];
+  const int t = threadIdx.x, o = t & 31, rg = t >> 5, role = blockIdx.x;
+  if (role == 11) { for (int i = t; i < NRD_NCLS * NRD_FC1_OUT; i += 256) w2s[i] = w2[i]; __syncthreads(); }
   float s = 0.f;
-  for (int b0 = 0; b0 < B; b0 += 64) {
-    const int nb = min(64, B - b0);
-    __syncthreads();
-    for (int i = t; i < nb * NRD_NCLS; i += 384) dl[i] = dlogits[(size_t)b0 * NRD_NCLS + i];
-    for (int i = t; i < nb * NRD_FC1_OUT; i += 384) hh[i] = h1[(size_t)b0 * NRD_FC1_OUT + i];
-    __syncthreads();
-    for (int i = t; i < nb * NRD_FC1_OUT; i += 384) dd[i] = dh1_elem(dl + (i >> 5) * NRD_NCLS, w2s, i & 31, hh[i]);
-    __syncthreads();
-    if (t < 320) {
-      const int c = t / 32, j = t % 32;
-      for (int b = 0; b < nb; ++b) s = fmaf(dl[b * NRD_NCLS + c], hh[b * NRD_FC1_OUT + j], s);
-    } else if (t < 330) {
-      const int c = t - 320;
-      for (int b = 0; b < nb; ++b) s += dl[b * NRD_NCLS + c];
-    } else if (t < 362) {
-      const int j = t - 330;
-      for (int b = 0; b < nb; ++b) s += dd[b * NRD_FC1_OUT + j];
-    }
+  if (role < 10) {
+#pragma unroll 4
+    for (int b = rg; b < B; b += 8) s = fmaf(dlogits[(size_t)b * NRD_NCLS + role], h1[(size_t)b * NRD_FC1_OUT + o], s);
+  } else if (role == 10) {
+    if (o < NRD_NCLS)
+#pragma unroll 4
+      for (int b = rg; b < B; b += 8) s += dlogits[(size_t)b * NRD_NCLS + o];
+  } else {
+#pragma unroll 2
+    for (int b = rg; b < B; b += 8) s += dh1_elem(dlogits + (size_t)b * NRD_NCLS, w2s, o, h1[(size_t)b * NRD_FC1_OUT + o]);
   }
-  if (t < 320) dw2[t] = s;
-  else if (t < 330) db2[t - 320] = s;
-  else if (t < 362) dbfc1[t - 330] = s;
+  red[rg][o] = s;
+  __syncthreads();
+  if (rg == 0) {
+    float tot = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) tot += red[k][o];
+    if (role < 10) dw2[role * NRD_FC1_OUT + o] = tot;
+    else if (role == 10) { if (o < NRD_NCLS) db2[o] = tot; }
+    else dbfc1[o] = tot;
+  }
 }
 
-// dWfc1[j][c*64+hw] = sum_b dh1[b][j] * p[b][hw*C+c].  CTA = 64 consecutive NHWC columns x 32 rows; the batch is staged
-// through shared memory in chunks of 64 rows.
+// dWfc1[j][c*64+hw] = sum_b dh1[b][j] * p[b][hw*C+c].  CTA (x, y) = 64 consecutive NHWC columns x 32 rows over the batch rows
+// b == y*64 .. (64-row chunks strided by gridDim.y); partial[y][j][k] summed in order by k_fc1_wgrad_reduce.
 template <typename T>
 __global__ void __launch_bounds__(256) k_fc1_wgrad(const T* __restrict__ p, const float* __restrict__ dlogits, const float* __restrict__ h1,
-                                                   const float* __restrict__ w2, float* __restrict__ dw1, int B, int C) {
+                                                   const float* __restrict__ w2, float* __restrict__ partial, int B, int C) {
   __shared__ __align__(16) float ds[64 * NRD_FC1_OUT];
   __shared__ float ps[64 * 64];
   __shared__ float dl[64 * NRD_NCLS], w2s[NRD_NCLS * NRD_FC1_OUT];
@@ -861,7 +883,7 @@ __global__ void __launch_bounds__(256) k_fc1_wgrad(const T* __restrict__ p, cons
   float acc[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-  for (int bb = 0; bb < B; bb += 64) {
+  for (int bb = blockIdx.y * 64; bb < B; bb += gridDim.y * 64) {
     const int nb = min(64, B - bb);
     __syncthreads();
     for (int q = tid; q < nb * NRD_NCLS; q += 256) dl[q] = dlogits[(size_t)bb * NRD_NCLS + q];
@@ -884,9 +906,19 @@ __global__ void __launch_bounds__(256) k_fc1_wgrad(const T* __restrict__ p, cons
       acc[4] = fmaf(pv, c4.x, acc[4]); acc[5] = fmaf(pv, c4.y, acc[5]); acc[6] = fmaf(pv, c4.z, acc[6]); acc[7] = fmaf(pv, c4.w, acc[7]);
     }
   }
-  const int i = i0 + il, hw = i / C, c = i % C;
+  float* out = partial + (size_t)blockIdx.y * NRD_FC1_OUT * K;
 #pragma unroll
-  for (int e = 0; e < 8; ++e) dw1[(size_t)(jg * 8 + e) * K + c * 64 + hw] = acc[e];
+  for (int e = 0; e < 8; ++e) out[(size_t)(jg * 8 + e) * K + i0 + il] = acc[e];     // [split][j][NHWC column]: coalesced
+}
+
+// dWfc1[j][c*64+hw] = sum_split partial[split][j][hw*C+c]
+__global__ void k_fc1_wgrad_reduce(const float* __restrict__ partial, int nsplit, int C, float* __restrict__ dw1) {
+  const int K = 64 * C, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= NRD_FC1_OUT * K) return;
+  float s = 0.f;
+  for (int q = 0; q < nsplit; ++q) s += partial[(size_t)q * NRD_FC1_OUT * K + i];
+  const int j = i / K, k = i % K, hw = k / C, c = k % C;
+  dw1[(size_t)j * K + c * 64 + hw] = s;
 }
 
 // d(pooled)[b][hw][c] = sum_j dh1[b][j] * w1t[hw*C+c][j], scattered through pool-2's argmax into gx [B,16,16,C].
@@ -940,6 +972,33 @@ __global__ void __launch_bounds__(256) k_fc1_dgrad_unpool(const float* __restric
 __global__ void k_sgd(float* __restrict__ p, const float* __restrict__ g, size_t n, float step_scale) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     p[i] = fmaf(-step_scale, g[i], p[i]);
+}
+
+// p <- p - step_scale * g over the whole flat vector AND the packed copies of the three tensors that have them, one launch
+// (off[] = flat offsets of the 9 tensors; index order as k_pack_weights)
+__global__ void k_sgd_pack(float* __restrict__ p, const float* __restrict__ g, float step_scale, int C, const long long* __restrict__ offp,
+                           long long o_c1w, long long o_rbw, long long o_fc1w, long long n,
+                           float* __restrict__ w_fwd, float* __restrict__ w_dgrad, bf16* __restrict__ wtc_fwd, bf16* __restrict__ wtc_dgrad,
+                           float* __restrict__ w1p, float* __restrict__ conv1_wp) {
+  (void)offp;
+  const long long n_rb = (long long)C * C * 9, n_fc1 = (long long)NRD_FC1_OUT * 64 * C, n_c1 = (long long)C * 27;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float w = fmaf(-step_scale, g[i], p[i]);
+    p[i] = w;
+    if (i >= o_rbw && i < o_rbw + n_rb) {
+      const int q = (int)(i - o_rbw), co = q / (C * 9), r = q % (C * 9), ci = r / 9, t = r % 9;
+      w_fwd[(t * C + ci) * C + co] = w;
+      w_dgrad[((8 - t) * C + co) * C + ci] = w;
+      wtc_fwd[(size_t)co * 9 * C + t * C + ci] = __float2bfloat16_rn(w);
+      wtc_dgrad[(size_t)ci * 9 * C + (8 - t) * C + co] = __float2bfloat16_rn(w);
+    } else if (i >= o_fc1w && i < o_fc1w + n_fc1) {
+      const int q = (int)(i - o_fc1w), j = q / (64 * C), r = q % (64 * C), c = r / 64, hw = r % 64;
+      w1p[((size_t)hw * C + c) * NRD_FC1_OUT + j] = w;
+    } else if (i >= o_c1w && i < o_c1w + n_c1) {
+      const int q = (int)(i - o_c1w), co = q / 27, k = q % 27;
+      conv1_wp[k * C + co] = w;
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1017,6 +1076,7 @@ extern "C" int nrd_param_offsets(int C, int64_t off[10]) {
 }
 
 // ---- per-op launchers -------------------------------------------------------------------
+static int fc1_wgrad_splits(int B) { int n = (B + 63) / 64; return n < 8 ? n : 8; }
 static int wgrad_blocks(int B) { int t = B * 2; return t < NRD_NUM_SMS ? t : NRD_NUM_SMS; }
 static int stem_bwd_blocks(int B) { return B < NRD_NUM_SMS ? B : NRD_NUM_SMS; }
 
@@ -1133,7 +1193,7 @@ static int stem_fwd_any(const float* img, const float* wp, const float* bias, vo
   return NRD_OK;
 }
 static int stem_bwd_any(const float* img, const void* g0, const void* x0, const uint8_t* idx0, float* dw, float* db, int B, int C,
-                        int dt, float* partial, cudaStream_t st) {
+                        int dt, float* partial, cudaStream_t st, bool do_reduce = true) {
   int nblk = stem_bwd_blocks(B);
   size_t smem = (3 * 34 * 35 + 2 + 256 * C) * sizeof(float) + 256 * C;
   {
@@ -1144,8 +1204,10 @@ static int stem_bwd_any(const float* img, const void* g0, const void* x0, const 
   if (dt == NRD_F32) k_stem_bwd<float><<<nblk, 256, smem, st>>>(img, (const float*)g0, (const float*)x0, idx0, partial, B, C);
   else k_stem_bwd<bf16><<<nblk, 256, smem, st>>>(img, (const bf16*)g0, (const bf16*)x0, idx0, partial, B, C);
   LAUNCH_CHECK();
-  k_stem_bwd_reduce<<<28 * C / 32, 256, 0, st>>>(partial, nblk, C, dw, db);
-  LAUNCH_CHECK();
+  if (do_reduce) {
+    k_stem_bwd_reduce<<<28 * C / 32, 256, 0, st>>>(partial, nblk, C, dw, db);
+    LAUNCH_CHECK();
+  }
   return NRD_OK;
 }
 
@@ -1311,6 +1373,7 @@ static void carve(nrd_plan* p, char* base, size_t* total) {
   p->h1 = cv.take<float>((size_t)B * NRD_FC1_OUT * 4);
   p->dh1 = cv.take<float>((size_t)B * NRD_FC1_OUT * 4);
   p->fc1_part = cv.take<float>((size_t)(64 * C / 128) * B * NRD_FC1_OUT * 4);
+  p->fc1w_partial = cv.take<float>((size_t)fc1_wgrad_splits(B) * NRD_FC1_OUT * 64 * C * 4);
   p->dlogits = cv.take<float>((size_t)B * NRD_NCLS * 4);
   p->loss_rows = cv.take<float>((size_t)B * 4);
   p->saved_stats = cv.take<float>((size_t)NB * 2 * C * 4);
@@ -1430,6 +1493,18 @@ extern "C" int nrd_pack_weights(nrd_plan* p, void* stream) {
   return NRD_OK;
 }
 
+// optimizer.step() (+ DDP mean) and the weight re-pack in ONE launch over the flat vector
+extern "C" int nrd_sgd_update_pack(nrd_plan* p, float lr, float inv_world, void* stream) {
+  NRD_REQUIRE(p, "null plan");
+  NRD_CHECK_CUDA(cudaSetDevice(p->device));
+  const long long n = p->off[9];
+  k_sgd_pack<<<grid_for((size_t)n, 256, NRD_NUM_SMS * 2), 256, 0, (cudaStream_t)stream>>>(
+      p->params, p->grads, lr * inv_world, p->C, nullptr, p->off[P_C1W], p->off[P_RBW], p->off[P_FC1W], n, p->w_fwd, p->w_dgrad,
+      p->wtc_fwd, p->wtc_dgrad, p->w1p, p->conv1_wp);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
 extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int training, void* stream) {
   NRD_REQUIRE(p && images && logits, "nrd_forward: null pointer");
   NRD_CHECK_CUDA(cudaSetDevice(p->device));
@@ -1474,10 +1549,13 @@ extern "C" int nrd_backward_head(nrd_plan* p, const float* dlogits, void* stream
   NRD_CHECK_CUDA(cudaSetDevice(p->device));
   cudaStream_t st = (cudaStream_t)stream;
   const int B = p->B, C = p->C, dt = p->dtype;
-  k_head_wgrad<<<1, 384, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), B, GRD(P_FC2W), GRD(P_FC2B), GRD(P_FC1B));
+  k_head_wgrad<<<12, 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), B, GRD(P_FC2W), GRD(P_FC2B), GRD(P_FC1B));
   LAUNCH_CHECK();
-  if (dt == NRD_F32) k_fc1_wgrad<float><<<C, 256, 0, st>>>((const float*)p->pooled, dlogits, p->h1, PRM(P_FC2W), GRD(P_FC1W), B, C);
-  else k_fc1_wgrad<bf16><<<C, 256, 0, st>>>((const bf16*)p->pooled, dlogits, p->h1, PRM(P_FC2W), GRD(P_FC1W), B, C);
+  const int nsplit = fc1_wgrad_splits(B);
+  if (dt == NRD_F32) k_fc1_wgrad<float><<<dim3(C, nsplit), 256, 0, st>>>((const float*)p->pooled, dlogits, p->h1, PRM(P_FC2W), p->fc1w_partial, B, C);
+  else k_fc1_wgrad<bf16><<<dim3(C, nsplit), 256, 0, st>>>((const bf16*)p->pooled, dlogits, p->h1, PRM(P_FC2W), p->fc1w_partial, B, C);
+  LAUNCH_CHECK();
+  k_fc1_wgrad_reduce<<<(NRD_FC1_OUT * 64 * C + 255) / 256, 256, 0, st>>>(p->fc1w_partial, nsplit, C, GRD(P_FC1W));
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1520,8 +1598,10 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
     }
     char* t = g; g = gn; gn = t;
   }
-  NRD_TRY(wgrad_reduce(p->wgrad_partial, p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B), C, GRD(P_RBW), st));
-  NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st));
+  NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
+  k_body_reduce<<<9 * C * C / 32 + 28 * C / 32, 256, 0, st>>>(p->wgrad_partial, p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B),
+                                                           p->stem_partial, stem_bwd_blocks(B), C, GRD(P_RBW), GRD(P_C1W), GRD(P_C1B));
+  LAUNCH_CHECK();
   return NRD_OK;
 }
 
@@ -1531,8 +1611,7 @@ extern "C" int nrd_train_step(nrd_plan* p, const float* images, const int64_t* l
   NRD_TRY(nrd_forward(p, images, logits, 1, stream));
   NRD_TRY(nrd_cross_entropy(logits, labels, p->B, 1.0f, loss_out, p->dlogits, p->loss_rows, stream));
   NRD_TRY(nrd_backward(p, p->dlogits, stream));
-  NRD_TRY(nrd_sgd_update(p->params, p->grads, (size_t)p->off[9], lr, 1.0f, stream));
-  return nrd_pack_weights(p, stream);
+  return nrd_sgd_update_pack(p, lr, 1.0f, stream);
 }
 
 // Run ONE internal op of the step on the plan's buffers (bench.py times each kernel class with CUDA
@@ -1568,6 +1647,12 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
     case NRD_OP_STEM_BWD:
       NRD_REQUIRE(p->images_last, "run a forward first");
       return stem_bwd_any(p->images_last, p->dxa, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st);
+    case NRD_OP_FWD_BLOCKS:
+      NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent forward not available for this plan");
+      return nrd_tc_forward_blocks(p, st);
+    case NRD_OP_BWD_BLOCKS:
+      NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent backward not available for this plan");
+      return nrd_tc_backward_blocks(p, p->dxa, p->dxb, st);
     case NRD_OP_BLOCK_FWD:
       NRD_REQUIRE(p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_fused_fwd, "fused block forward not available for this plan");
       return nrd_tc_block_fwd(p, k, st);

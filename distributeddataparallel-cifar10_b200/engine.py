@@ -202,6 +202,12 @@ class Engine:
         return self._side
 
     def sgd_update(self, lr: float, inv_world: float = 1.0, lo: int = 0, hi: Optional[int] = None):
+        if lo == 0 and hi is None and self._last_plan is not None:
+            # whole vector: update and weight re-pack in one launch
+            check(lib.nrd_sgd_update_pack(self._last_plan.handle, lr, inv_world, _stream_ptr()), "nrd_sgd_update_pack")
+            self.weights_epoch += 1
+            self._last_plan.packed_version = self._weights_version()
+            return
         hi = self.offsets[9] if hi is None else hi
         check(lib.nrd_sgd_update(self.flat_params.data_ptr() + 4 * lo, self.flat_grads.data_ptr() + 4 * lo, hi - lo,
                                  lr, inv_world, _stream_ptr()), "nrd_sgd_update")

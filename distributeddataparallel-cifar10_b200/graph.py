@@ -52,9 +52,7 @@ class TrainStep:
         sum_body = (lambda: self.ddp._allreduce_bucket(0, average=False)) if self.world > 1 else None
         eng.backward(pl, pl.dlogits, sum_head, sum_body)
         # fused mean + SGD (K16), then re-derive the packed weight copies
-        check(lib.nrd_sgd_update(eng.flat_params.data_ptr(), eng.flat_grads.data_ptr(), eng.offsets[9], self.lr,
-                                 1.0 / self.world, st), "nrd_sgd_update")
-        check(lib.nrd_pack_weights(pl.handle, st), "nrd_pack_weights")
+        check(lib.nrd_sgd_update_pack(pl.handle, self.lr, 1.0 / self.world, st), "nrd_sgd_update_pack")
 
     def _capture(self):
         s = torch.cuda.Stream(device=self.device)

@@ -125,6 +125,8 @@ int nrd_backward(nrd_plan* plan, const float* dlogits, void* stream);
 int nrd_backward_head(nrd_plan* plan, const float* dlogits, void* stream);
 int nrd_backward_body(nrd_plan* plan, const float* dlogits, void* stream);
 int nrd_sgd_update(float* params, const float* grads, size_t n, float lr, float inv_world, void* stream);
+/* nrd_sgd_update_pack = nrd_sgd_update over the plan's whole flat vector + nrd_pack_weights, one launch. */
+int nrd_sgd_update_pack(nrd_plan* plan, float lr, float inv_world, void* stream);
 int nrd_train_step(nrd_plan* plan, const float* images, const int64_t* labels, float lr,
                    float* logits, float* loss_out, void* stream);
 
@@ -188,6 +190,8 @@ int nrd_maxpool_bwd(const void* gpooled, const uint8_t* idx, void* gx, int B, in
 #define NRD_OP_STEM_BWD 6
 #define NRD_OP_BLOCK_FWD 7 /* whole ResBlock forward k in one cooperative launch (tcgen05 plans): conv + BN + ReLU + add;
                               NOTE: applies the running-stat EMA and nbt += 1 like a real forward */
+#define NRD_OP_FWD_BLOCKS 8 /* all residual blocks' forward in the persistent kernel (same side effects as a real forward) */
+#define NRD_OP_BWD_BLOCKS 9 /* all residual blocks' backward in the persistent kernel (overwrites the block gradients) */
 unsigned long long nrd_launch_count(void);
 int nrd_plan_run_op(nrd_plan* plan, int op, int k, void* stream);
 
