@@ -86,6 +86,8 @@ struct nrd_plan {
   CUtensorMap tm_wf, tm_wd;
   CUtensorMap tm_xall;    // all x_k as one 5-D tensor (persistent backward)
   int tc_ready;
+  int tc_stem;            // tensor-core stem kernels available (bf16, C = 32)
+  int use_tc_stem;        // option
   int persist_fwd;        // option: use the persistent block-stack forward when available
   int persist_bwd;        // option: use the persistent block-stack backward when available
   int fuse_bn_bwd;        // BN+ReLU backward as one cooperative kernel when it fits shared memory
@@ -130,6 +132,9 @@ int nrd_tc_plan_init(nrd_plan* p);
 int nrd_tc_conv_fwd(nrd_plan* p, int k, cudaStream_t st);                       // y_k = conv(x_k) + stats partials
 int nrd_tc_conv_dgrad(nrd_plan* p, const void* g, void* dx_out, cudaStream_t st); // dx = dgrad(dy) + g
 int nrd_tc_conv_wgrad(nrd_plan* p, int k, int first, cudaStream_t st);          // partial (+)= wgrad(x_k, dy)
+int nrd_tc_stem_init(nrd_plan* p);
+int nrd_tc_stem_fwd(nrd_plan* p, const float* images, cudaStream_t st);
+int nrd_tc_stem_bwd(nrd_plan* p, const float* images, const void* g0, cudaStream_t st);   // per-CTA partials only
 int nrd_tc_stats_blocks(const nrd_plan* p);
 int nrd_tc_wgrad_blocks(const nrd_plan* p);
 int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st);                        // x_0 -> all y_k, x_{k+1}: one launch

@@ -1424,6 +1424,7 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->fuse_bn_bwd = 1;
   p->persist_fwd = 1;
   p->persist_bwd = 1;
+  p->use_tc_stem = 1;
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
   e = cudaMemset(p->gbar, 0, 256);
@@ -1432,6 +1433,8 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
     r = nrd_tc_plan_init(p);
     if (r != NRD_OK) { delete p; return r; }   // no silent fallback: the bf16 product path IS the tcgen05 path
     if (p->tc_ready) p->conv_impl = NRD_CONV_TCGEN05;
+    r = nrd_tc_stem_init(p);
+    if (r != NRD_OK) { delete p; return r; }
   }
   *out = p;
   return NRD_OK;
@@ -1453,6 +1456,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_FUSE_BN_BWD: p->fuse_bn_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_FWD: p->persist_fwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_BWD: p->persist_bwd = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_TC_STEM: p->use_tc_stem = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_TRACE: p->trace = value ? (void*)p->dxb : nullptr; p->trace_bwd = value ? (void*)p->dy : nullptr; return NRD_OK;   // stamps land in the dx pong / dy scratch
     default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
   }
@@ -1472,6 +1476,7 @@ extern "C" int nrd_plan_tensor(nrd_plan* p, int what, int k, void** ptr, size_t*
     case 5: *ptr = p->dxa; *bytes = act; break;
     case 6: *ptr = p->dxb; *bytes = act; break;
     case 7: *ptr = p->wgrad_partial; *bytes = nrd_wgrad_partial_bytes(p->B, p->C); break;
+    case 9: *ptr = p->stem_partial; *bytes = nrd_stem_bwd_partial_bytes(p->B, p->C); break;
     case 8: *ptr = p->stats_partial; *bytes = (size_t)(p->B * 2 > 1024 ? p->B * 2 : 1024) * 2 * p->C * 4; break;
     default: nrd_set_error("nrd_plan_tensor: unknown selector %d", what); return NRD_EINVAL;
   }
@@ -1512,7 +1517,8 @@ extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int 
   const int B = p->B, C = p->C, NB = p->NB, dt = p->dtype;
   const size_t act = p->act_elems * p->esz;
   p->images_last = images;
-  NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st));
+  if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_fwd(p, images, st));
+  else NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st));
   if (!training) { k_bn_eval_coeffs<<<1, 64, 0, st>>>(p->bn_running, PRM(P_BNG), PRM(P_BNB), C, p->scale_shift); LAUNCH_CHECK(); }
   const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_fwd;
   if (persist) NRD_TRY(nrd_tc_forward_blocks(p, st));
@@ -1598,7 +1604,8 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
     }
     char* t = g; g = gn; gn = t;
   }
-  NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
+  if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_bwd(p, p->images_last, g, st));
+  else NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
   k_body_reduce<<<9 * C * C / 32 + 28 * C / 32, 256, 0, st>>>(p->wgrad_partial, p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B),
                                                            p->stem_partial, stem_bwd_blocks(B), C, GRD(P_RBW), GRD(P_C1W), GRD(P_C1B));
   LAUNCH_CHECK();
@@ -1643,9 +1650,11 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       return conv_fwd_any(p->dy, p->w_dgrad, p->dxb, B, C, dt, nullptr, p->dxa, st);
     case NRD_OP_STEM_FWD:
       NRD_REQUIRE(p->images_last, "run a forward first");
+      if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) return nrd_tc_stem_fwd(p, p->images_last, st);   // rewrites x_0 in place (same values)
       return stem_fwd_any(p->images_last, p->conv1_wp, PRM(P_C1B), p->dxb, p->idx0, B, C, dt, st);
     case NRD_OP_STEM_BWD:
       NRD_REQUIRE(p->images_last, "run a forward first");
+      if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) return nrd_tc_stem_bwd(p, p->images_last, p->dxa, st);
       return stem_bwd_any(p->images_last, p->dxa, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st);
     case NRD_OP_FWD_BLOCKS:
       NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent forward not available for this plan");

@@ -81,10 +81,14 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
 /* NRD_OPT_PERSIST_BWD (default 1): the same for the backward of the residual blocks: dL/dx stays in registers, dy in
  * shared memory, the weight-gradient accumulators in TMEM for the whole stack; 0 = per-block kernels. */
 #define NRD_OPT_PERSIST_BWD 3
+/* NRD_OPT_TC_STEM (default 1): stem forward / weight gradient as tcgen05 implicit GEMMs with the im2col operand built in
+ * shared memory (bf16 plans, C = 32); 0 = the CUDA-core stem kernels. */
+#define NRD_OPT_TC_STEM 4
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
  * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch (ping),
- * 6 = dx scratch (pong), 7 = wgrad per-CTA partials [ctas][9][C][C], 8 = BN-stat per-CTA partials [ctas][2][C] */
+ * 6 = dx scratch (pong), 7 = wgrad per-CTA partials [ctas][9][C][C], 8 = BN-stat per-CTA partials [ctas][2][C],
+ * 9 = stem weight-gradient per-CTA partials [ctas][28][C] (27 taps + bias) */
 int nrd_plan_tensor(nrd_plan* plan, int what, int k, void** ptr, size_t* bytes);
 
 /* Re-derive the packed weight copies (tap-major / transposed / bf16 / NHWC-ordered fc1) from the

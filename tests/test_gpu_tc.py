@@ -151,3 +151,34 @@ def test_persistent_backward_matches_per_block_kernels(B):
     for k in res[0][1]:
         a, b = res[0][1][k], res[1][1][k]
         assert rell2(b, a) < 1e-2 and cosine(b, a) > 0.9999, (k, rell2(b, a), cosine(b, a))
+
+
+@pytest.mark.parametrize("B", [1, 37, 256, 300])
+def test_tensor_core_stem_matches_torch_and_cuda_core_stem(B):
+    """Stem forward / weight gradient as tcgen05 implicit GEMMs (im2col built in shared memory, pooling across the four
+    accumulators of a TMEM lane) against torch on the same bf16-rounded image and weights (<= one bf16 rounding step) and
+    against our CUDA-core stem (fp32 image/weights there: bf16 operand rounding is the only difference)."""
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for tc in (0, 1):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(32, 2, dtype="bf16").to(DEV)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 4, tc))
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        res.append(dict(x0=pl.tensor_view(0, 0).view(torch.bfloat16).float().view(B, 16, 16, 32).cpu().clone(), g=module_grads(m),
+                        w=m.conv1.weight.detach().cpu().clone(), b=m.conv1.bias.detach().cpu().clone()))
+    cc, tc = res
+    ref = F.max_pool2d(torch.relu(F.conv2d(x.cpu().bfloat16().double(), tc["w"].bfloat16().double(), tc["b"].double(), padding=1)), 2)
+    assert relmax(tc["x0"].permute(0, 3, 1, 2), ref) < 2 ** -8 * 1.05
+    assert rell2(tc["x0"], cc["x0"]) < 1e-2
+    # weight-gradient kernel alone, both implementations on the SAME x0 / argmax / incoming gradient (left by the last run)
+    part = {}
+    for name, opt in (("cc", 0), ("tc", 1)):
+        check(lib.nrd_plan_set_option(pl.handle, 4, opt))
+        pl.tensor_view(9, 0).zero_()
+        check(lib.nrd_plan_run_op(pl.handle, 6, 0, st()), "stem bwd")
+        torch.cuda.synchronize()
+        part[name] = pl.tensor_view(9, 0).view(torch.float32).view(-1, 28, 32).double().sum(0).cpu()
+    assert rell2(part["tc"], part["cc"]) < 1e-2 and cosine(part["tc"], part["cc"]) > 0.9999, rell2(part["tc"], part["cc"])
