@@ -95,6 +95,7 @@ struct nrd_plan {
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
   unsigned long long* gbar; // grid-barrier counters (one per cooperative kernel type)
   void* trace;            // optional device buffer for in-kernel clock64 stamps (profiling aid; NULL = off)
+  int dbg_skip_stores;    // profiling experiment (NRD_OPT_TRACE value 2)
   void* trace_bwd;        // same for the persistent backward (lives in the pooled-gradient-free part of the dy scratch)
 };
 

@@ -1457,7 +1457,8 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_PERSIST_FWD: p->persist_fwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_BWD: p->persist_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_TC_STEM: p->use_tc_stem = value ? 1 : 0; return NRD_OK;
-    case NRD_OPT_TRACE: p->trace = value ? (void*)p->dxb : nullptr; p->trace_bwd = value ? (void*)p->dy : nullptr; return NRD_OK;   // stamps land in the dx pong / dy scratch
+    case NRD_OPT_TRACE: p->dbg_skip_stores = (value == 2);
+      p->trace = value ? (void*)p->dxb : nullptr; p->trace_bwd = value ? (void*)p->dy : nullptr; return NRD_OK;   // stamps land in the dx pong / dy scratch
     default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
   }
 }
