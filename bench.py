@@ -61,7 +61,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "25",
                                           "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -248,8 +248,11 @@ def main():
             v["share"] = round(v["us"] * v["per_step"] / tot, 3)
         dom = max(breakdown, key=lambda k: breakdown[k]["us"] * breakdown[k]["per_step"])
         d = breakdown[dom]
+        # DRAM bytes per launch from the committed ncu --set full capture (profiles/r01_step_v6_persistent.md), same config only
+        ncu_traffic = {"bwd_blocks(persistent)": 88448256 + 3574272, "fwd_blocks(persistent)": 4270848 + 29913600}
+        traffic = ncu_traffic.get(dom) if (B, C, NB, args.dtype) == (256, 32, 10, "bf16") else None
         roof = {"bound": "hbm", "kernel": dom, "achieved": d["gbs"], "peak": hbm, "unit": "GB/s", "frac": round(d["gbs"] / hbm, 4),
-                "traffic": None, "peak_source": peak_kind, "launch_us": d["us"], "algo_bytes_per_launch": d["algo_bytes"],
+                "traffic": traffic, "peak_source": peak_kind, "launch_us": d["us"], "algo_bytes_per_launch": d["algo_bytes"],
                 "impl": "tcgen05" if lib.nrd_plan_conv_impl(step.plan.handle) == 1 else "cuda_core"}
         t_roof_us = B * max(flops_per_image(C, NB) / (tflops * 1e12), bytes_per_image(C, NB, s_act) / (hbm * 1e9)) * 1e6
         step_roof = {"t_roof_us": round(t_roof_us, 1), "t_step_us": round(ms_total / args.steps * 1e3, 1),
