@@ -33,6 +33,22 @@ template <int C> struct Cfg {
   static constexpr int NST = 2;                                 // work-item stages
 };
 
+// 16 values per lane -> after the call lanes 2c and 2c+1 both hold the sum over the 32 lanes of v[c] (c = lane >> 1)
+__device__ __forceinline__ float warp_col_sum16(float (&v)[16], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 2; off >>= 1) {
+    const bool upper = (lane & off) != 0;
+    const int n = off >> 1;
+#pragma unroll
+    for (int i = 0; i < n; ++i) {
+      float send = upper ? v[i] : v[i + n];
+      float keep = upper ? v[i + n] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
 // 1/sqrt(x) to fp32 accuracy without the fp64 sqrt/div software sequences (hundreds of cycles on the per-block critical path):
 // hardware rsqrt + one Newton step
 __device__ __forceinline__ float fast_invstd(double var_plus_eps) {
@@ -579,7 +595,7 @@ struct PersistBwdArgs {
   long long* trace;           // optional clock64 stamps (profiling aid), or NULL
 };
 
-__global__ void __launch_bounds__(320, 1)
+__global__ void __launch_bounds__(576, 1)
 k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_constant__ CUtensorMap tmWd, PersistBwdArgs a) {
   constexpr int C = 32;
   using K = Cfg<C>;
@@ -600,11 +616,12 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   const uint32_t tmem_slot = bar0 + 8u * 12;
   constexpr int BAR_BYTES = 8 * 14;
   constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
-  float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [8 warps][2][C] = 512 floats
-  float* coef = red + 512;                                               // [3C] = gamma*invstd | mean(dz) | mean(dz*xhat)
+  float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][2][C] = 1024 floats
+  float* coef = red + 1024;                                               // [3C] = gamma*invstd | mean(dz) | mean(dz*xhat)
   float* bnp2 = coef + 96;                                               // 2 x 64 floats (scale/shift pairs, double-buffered) + 128 floats (dy coefficients)
-  double* dsum = reinterpret_cast<double*>(bnp2 + 256);                  // [1024]
-  uint4* ybuf = reinterpret_cast<uint4*>(dsum + 1024);                   // [2 tiles][4 chunks][256 threads]: each thread's y_k rows (cp.async)                   // [1024]
+  double* dsum = reinterpret_cast<double*>(bnp2 + 256);                  // [32 row classes][2C] = 2048
+  double* dsum2 = dsum + 2048;                                           // [4][2C]
+  uint4* ybuf = reinterpret_cast<uint4*>(dsum2 + 256);                   // [4 chunks][512 threads]: each thread's y_k row (cp.async)                   // [1024]
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -623,7 +640,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     tma_prefetch_desc(&tmXall); tma_prefetch_desc(&tmWd);
     mbar_init(wfull, 1); mbar_init(wdone, 1);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(xready(s), 1); mbar_init(dyready(s), 128); mbar_init(wfree(s), 1);
+      mbar_init(xready(s), 1); mbar_init(dyready(s), 256); mbar_init(wfree(s), 1);
       mbar_init(dxfull(s, 0), 1); mbar_init(dxfull(s, 1), 1);
     }
     fence_barrier_init();
@@ -691,42 +708,36 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       umma_commit(wdone);
     }
   } else {
-    // ===== epilogue: group s = image slot, q = TMEM lane quarter; thread = pixel (m*128 + q*32 + lane) of its image =====
-    const int ew = warp - 2, s = ew >> 2, q = warp & 3, et = threadIdx.x - 64;
+    // ===== epilogue: 16 warps; warp = (image slot s, tile m of that image, TMEM lane quarter q); thread = one pixel =====
+    const int ew = warp - 2, s = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
     const bool active = s < nslots;
     const int img = (s == 0) ? img0 : img1;
     uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
+    const int p = q * 32 + lane, pi = m * 8 + (p >> 4), pj = p & 15;
+    const size_t gp = ((size_t)img * NRD_PIX + pi * 16 + pj) * C;             // this thread's pixel
+    const int P1 = (pi + 1) * 16 + pj;                                         // its index inside an operand copy (row-haloed)
+    const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C;
     unsigned long long gbar_target = 0;
     if (et == 0) gbar_target = nrd_grid_barrier_base(a.gbar, gridDim.x);
-    uint32_t gpk[2][16];                              // dL/d(out) of this thread's two pixels, bf16 pairs
-    size_t gp[2];
+    uint32_t gpk[16];                                 // dL/d(out) of this thread's pixel, bf16 pairs
 #pragma unroll
-    for (int m = 0; m < 2; ++m) {
-      const int p = q * 32 + lane, i = m * 8 + (p >> 4), j = p & 15;
-      gp[m] = ((size_t)img * NRD_PIX + i * 16 + j) * C;
-#pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {
-        uint4 v = active ? reinterpret_cast<const uint4*>(a.g_in + gp[m])[ch] : make_uint4(0, 0, 0, 0);
-        gpk[m][ch * 4 + 0] = v.x; gpk[m][ch * 4 + 1] = v.y; gpk[m][ch * 4 + 2] = v.z; gpk[m][ch * 4 + 3] = v.w;
-      }
+    for (int ch = 0; ch < 4; ++ch) {
+      uint4 v = active ? reinterpret_cast<const uint4*>(a.g_in + gp)[ch] : make_uint4(0, 0, 0, 0);
+      gpk[ch * 4 + 0] = v.x; gpk[ch * 4 + 1] = v.y; gpk[ch * 4 + 2] = v.z; gpk[ch * 4 + 3] = v.w;
     }
     float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, et < C: running dgamma / dbeta over the blocks
-    // y_k of this thread's two pixels: prefetched one block ahead with cp.async into this thread's own shared-memory slots
+    // y_k of this thread's pixel: prefetched one block ahead with cp.async into this thread's own shared-memory slots
     const uint32_t ybuf_s = smem_u32(ybuf);
     auto load_y = [&](int k) {
       const bf16* yk = a.ys + (size_t)k * a.act_elems;
 #pragma unroll
-      for (int m = 0; m < 2; ++m)
-#pragma unroll
-        for (int ch = 0; ch < 4; ++ch)
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ybuf_s + (uint32_t)(((m * 4 + ch) * 256 + et) * 16)),
-                       "l"(reinterpret_cast<const uint4*>(yk + gp[m]) + ch) : "memory");
+      for (int ch = 0; ch < 4; ++ch)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ybuf_s + (uint32_t)((ch * 512 + et) * 16)),
+                     "l"(reinterpret_cast<const uint4*>(yk + gp) + ch) : "memory");
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    auto y_pair = [&](int m, int pe) -> float2 {      // channels 2*pe, 2*pe+1 of tile m's pixel
-      const uint32_t w = reinterpret_cast<const uint32_t*>(ybuf + ((m * 4 + (pe >> 2)) * 256 + et))[pe & 3];
-      return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
-    };
+    // y of 8 channels (chunk ch) of this thread's pixel: one conflict-free LDS.128 from the thread's own slots
+    auto y_chunk = [&](int ch) -> uint4 { return ybuf[ch * 512 + et]; };
     if (active) load_y(a.NB - 1);
     for (int it = 0; it < a.NB; ++it) {
       const int k = a.NB - 1 - it;
@@ -741,67 +752,77 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         d[0] = a.scale_shift[(size_t)k * 2 * C + et]; d[1] = a.scale_shift[(size_t)k * 2 * C + C + et];
       }
       asm volatile("cp.async.wait_group 0;" ::: "memory");
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      // ---- phase A: per-channel sums of dz and dz*y over this warp's pixels ----
-      float s1 = 0.f, s2 = 0.f;
+      asm volatile("bar.sync 1, 512;" ::: "memory");
+      if (tr) tr[7] = clock64();
+      // ---- phase A: per-channel sums of dz and dz*y over this warp's 32 pixels ----
+      float s1[2] = {0.f, 0.f}, s2[2] = {0.f, 0.f};          // per 16-channel half: lanes 2c, 2c+1 hold channel 16*half + c
       if (active) {
 #pragma unroll
-        for (int m = 0; m < 2; ++m) {
-          float t[32];
+        for (int hf = 0; hf < 2; ++hf) {
+          float t1[16], t2[16];
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {
-            const float2 y2 = y_pair(m, e);
-            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][e]));
-            const float4 ss = ssp[e];
-            t[2 * e] = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f;
-            t[2 * e + 1] = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
-          }
-          s1 += warp_col_sum(t, lane);
+          for (int c2 = 0; c2 < 2; ++c2) {
+            const uint4 yv = y_chunk(hf * 2 + c2);
+            const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {              // dz * y (dz recomputed: keeps the live register set small)
-            const float2 y2 = y_pair(m, e);
-            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][e]));
-            const float4 ss = ssp[e];
-            t[2 * e] = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x * y2.x : 0.f;
-            t[2 * e + 1] = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y * y2.y : 0.f;
+            for (int e = 0; e < 4; ++e) {
+              const int pe = (hf * 2 + c2) * 4 + e, i = c2 * 8 + 2 * e;
+              const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&yw[e]));
+              const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[pe]));
+              const float4 ss = ssp[pe];
+              const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
+              t1[i] = d0; t1[i + 1] = d1; t2[i] = d0 * y2.x; t2[i + 1] = d1 * y2.y;
+            }
           }
-          s2 += warp_col_sum(t, lane);
+          s1[hf] = warp_col_sum16(t1, lane);
+          s2[hf] = warp_col_sum16(t2, lane);
         }
       }
       if (tr) tr[1] = clock64();
-      red[(ew * 2 + 0) * C + lane] = s1; red[(ew * 2 + 1) * C + lane] = s2;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if ((lane & 1) == 0) {
+        const int c = lane >> 1;
+        red[(ew * 2 + 0) * C + c] = s1[0]; red[(ew * 2 + 0) * C + 16 + c] = s1[1];
+        red[(ew * 2 + 1) * C + c] = s2[0]; red[(ew * 2 + 1) * C + 16 + c] = s2[1];
+      }
+      asm volatile("bar.sync 1, 512;" ::: "memory");
       float* part = a.partial + (size_t)(it & 1) * 512 * 2 * C;
       if (et < 2 * C) {
         float t = 0.f;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) t += red[w * 2 * C + et];
+        for (int w = 0; w < 16; ++w) t += red[w * 2 * C + et];
         part[(size_t)blockIdx.x * 2 * C + et] = t;
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[2] = clock64();
       if (et == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
       if (tr) tr[3] = clock64();
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, 512;" ::: "memory");
       {
         const int c4 = et & 15, r = et >> 4;
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-        float4 v[10];
+        float4 v[5];
 #pragma unroll
-        for (int u = 0; u < 10; ++u) {
-          const int row = r + u * 16;
+        for (int u = 0; u < 5; ++u) {
+          const int row = r + u * 32;
           v[u] = (row < (int)gridDim.x) ? __ldcg(reinterpret_cast<const float4*>(part + (size_t)row * 2 * C) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
-        for (int u = 0; u < 10; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
+        for (int u = 0; u < 5; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
         double* d = dsum + (size_t)r * 2 * C + c4 * 4;
         d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (et < C) {
-        double db = 0.0, dgy = 0.0;
+      asm volatile("bar.sync 1, 512;" ::: "memory");
+      if (et < 4 * 2 * C) {
+        const int col = et & (2 * C - 1), g = et >> 6;
+        double t = 0.0;
 #pragma unroll
-        for (int r = 0; r < 16; ++r) { db += dsum[r * 2 * C + et]; dgy += dsum[r * 2 * C + C + et]; }
+        for (int r = 0; r < 8; ++r) t += dsum[(size_t)(g * 8 + r) * 2 * C + col];
+        dsum2[g * 2 * C + col] = t;
+      }
+      asm volatile("bar.sync 1, 512;" ::: "memory");
+      if (et < C) {
+        const double db = dsum2[et] + dsum2[2 * C + et] + dsum2[4 * C + et] + dsum2[6 * C + et];
+        const double dgy = dsum2[C + et] + dsum2[3 * C + et] + dsum2[5 * C + et] + dsum2[7 * C + et];
         const double mean = (double)a.saved[(size_t)k * 2 * C + et], is = (double)a.saved[(size_t)k * 2 * C + C + et];
         const double dg = is * (dgy - mean * db);       // sum dz*xhat = invstd * (sum dz*y - mean * sum dz)
         db_acc += (float)db; dg_acc += (float)dg;       // same order as the per-block path: k = NB-1 first
@@ -809,63 +830,58 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         float* d = reinterpret_cast<float*>(cfp) + (et >> 1) * 8 + (et & 1) * 4;
         d[0] = (float)a_; d[1] = (float)(-a_ * c_ * is); d[2] = (float)(a_ * c_ * is * mean - a_ * b_); d[3] = 0.f;
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[4] = clock64();
       if (active) {
         // ---- phase B: dy -> the three operand copies (once the previous block's MMAs no longer read them) ----
         if (it > 0) mbar_wait(wfree(s), (uint32_t)((it - 1) & 1));
 #pragma unroll
-        for (int m = 0; m < 2; ++m) {
-          const int p = q * 32 + lane, i = m * 8 + (p >> 4), j = p & 15;
-          const int P1 = (i + 1) * 16 + j;
+        for (int ch = 0; ch < 4; ++ch) {
+          uint4 ok;
+          __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
 #pragma unroll
-          for (int ch = 0; ch < 4; ++ch) {
-            uint4 ok;
-            __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
+          const uint4 yv = y_chunk(ch);
+          const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int pe = ch * 4 + e;
-              const float2 y2 = y_pair(m, pe);
-              const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][pe]));
-              const float4 ss = ssp[pe], c0 = cfp[pe * 2], c1 = cfp[pe * 2 + 1];
-              const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
-              oh[e] = __floats2bfloat162_rn(fmaf(d0, c0.x, fmaf(y2.x, c0.y, c0.z)), fmaf(d1, c1.x, fmaf(y2.y, c1.y, c1.z)));
-            }
-            *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
-            if (j < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
-            if (j > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
+          for (int e = 0; e < 4; ++e) {
+            const int pe = ch * 4 + e;
+            const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&yw[e]));
+            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[pe]));
+            const float4 ss = ssp[pe], c0 = cfp[pe * 2], c1 = cfp[pe * 2 + 1];
+            const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
+            oh[e] = __floats2bfloat162_rn(fmaf(d0, c0.x, fmaf(y2.x, c0.y, c0.z)), fmaf(d1, c1.x, fmaf(y2.y, c1.y, c1.z)));
           }
+          *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
+          if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
+          if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
         }
         fence_proxy_async();
         mbar_arrive(dyready(s));
         if (tr) tr[5] = clock64();
-        if (k > 0) load_y(k - 1);          // y_k is dead: fetch the next block's rows while the dgrad MMAs run
+        if (k > 0) load_y(k - 1);          // y_k is dead: fetch the next block's row while the dgrad MMAs run
         // ---- phase C: dx_k = dgrad + g ----
+        mbar_wait(dxfull(s, m), (uint32_t)(it & 1));
+        tc_fence_after();
+        float v[32];
+        tmem_ld32(my_tmem, v);
 #pragma unroll
-        for (int m = 0; m < 2; ++m) {
-          mbar_wait(dxfull(s, m), (uint32_t)(it & 1));
-          tc_fence_after();
-          float v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C, v);
+        for (int e = 0; e < 16; ++e) {
+          const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[e]));
+          const __nv_bfloat162 o = __floats2bfloat162_rn(v[2 * e] + g2.x, v[2 * e + 1] + g2.y);
+          gpk[e] = *reinterpret_cast<const uint32_t*>(&o);
+        }
+        if (k == 0) {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {
-            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[m][e]));
-            const __nv_bfloat162 o = __floats2bfloat162_rn(v[2 * e] + g2.x, v[2 * e + 1] + g2.y);
-            gpk[m][e] = *reinterpret_cast<const uint32_t*>(&o);
-          }
-          if (k == 0) {
-#pragma unroll
-            for (int ch = 0; ch < 4; ++ch)
-              reinterpret_cast<uint4*>(a.dx0_out + gp[m])[ch] = make_uint4(gpk[m][ch * 4], gpk[m][ch * 4 + 1], gpk[m][ch * 4 + 2], gpk[m][ch * 4 + 3]);
-          }
+          for (int ch = 0; ch < 4; ++ch)
+            reinterpret_cast<uint4*>(a.dx0_out + gp)[ch] = make_uint4(gpk[ch * 4], gpk[ch * 4 + 1], gpk[ch * 4 + 2], gpk[ch * 4 + 3]);
         }
         if (tr) tr[6] = clock64();
-        tc_fence_before();      // the accumulators are in registers: the next block's dgrad may overwrite them (ordered by dyready)
+        tc_fence_before();      // the accumulator is in registers: the next block's dgrad may overwrite it (ordered by dyready)
       }
     }
     if (blockIdx.x == 0 && et < C) { a.dgamma[et] = dg_acc; a.dbeta[et] = db_acc; }
     // ---- weight-gradient partial of this CTA: accumulator rows (j, co), columns ci ----
-    if (s == 0) {
+    if (s == 0 && m == 0) {
       mbar_wait(wdone, 0);
       tc_fence_after();
       float* outp = a.wpartial + (size_t)blockIdx.x * 9 * C * C;
@@ -1060,7 +1076,7 @@ constexpr size_t persist_smem() {
 }
 
 constexpr size_t persist_bwd_smem() {
-  return 1024 + 2 * 4 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 112 + (512 + 96 + 256) * sizeof(float) + 1024 * sizeof(double) + 2 * 4 * 256 * 16 + 64;
+  return 1024 + 2 * 4 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 112 + (1024 + 96 + 256) * sizeof(float) + (2048 + 256) * sizeof(double) + 4 * 512 * 16 + 64;
 }
 
 static int items(const nrd_plan* p) { return p->B * (p->C == 32 ? 1 : 2); }
@@ -1182,7 +1198,7 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_in, void* dx0_out, cudaStr
   a.partial = p->stats_partial; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
-  NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist, dim3(conv_grid(p)), dim3(320), args, persist_bwd_smem(), st));
+  NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(), st));
   nrd_count_launch();
   return NRD_OK;
 }

@@ -35,4 +35,4 @@ for cta in (0, grid - 1):
     print(f"BWD CTA {cta}:")
     for it in range(10):
         t = trb[cta, it]
-        print("  it=%d " % it + " ".join(f"{namesb[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next=+{int(trb[cta,it+1,0]-t[0])}" if it < 9 else ""))
+        print("  it=%d " % it + f"sync={int(t[7]-t[0]):6d} " + " ".join(f"{namesb[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next=+{int(trb[cta,it+1,0]-t[0])}" if it < 9 else ""))
