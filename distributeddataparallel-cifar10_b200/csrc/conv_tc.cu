@@ -430,6 +430,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C;
     unsigned long long gbar_target = 0;
     if (et == 0) gbar_target = nrd_grid_barrier_base(a.gbar, gridDim.x);   // before this CTA's first arrival
+    const float gamma_r = (et < C) ? a.gamma[et] : 0.f, beta_r = (et < C) ? a.beta[et] : 0.f;   // off the per-block critical path
     for (int k = 0; k < a.NB; ++k) {
       long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + k) * 8 : nullptr;
       if (tr) tr[0] = clock64();
@@ -507,7 +508,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         double var = Q * inv_count - mean * mean;
         if (var < 0.0) var = 0.0;
         const float invstd = fast_invstd(var + (double)NRD_BN_EPS);
-        const float sc = a.gamma[et] * invstd, sh = a.beta[et] - (float)mean * sc;
+        const float sc = gamma_r * invstd, sh = beta_r - (float)mean * sc;
         ss_sm[et] = sc; ss_sm[C + et] = sh;
         if (blockIdx.x == 0) {
           a.saved[(size_t)k * 2 * C + et] = (float)mean; a.saved[(size_t)k * 2 * C + C + et] = invstd;
@@ -592,6 +593,7 @@ struct PersistBwdArgs {
   int B, NB;
   size_t act_elems;
   double inv_count;
+  int dbg_skip;               // profiling experiment only (results garbage)
   long long* trace;           // optional clock64 stamps (profiling aid), or NULL
 };
 
@@ -613,7 +615,8 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   auto wfree = [&](int s) { return bar0 + 8u * (5 + s); };
   auto dxfull = [&](int s, int m) { return bar0 + 8u * (7 + s * 2 + m); };
   const uint32_t wdone = bar0 + 8u * 11;
-  const uint32_t tmem_slot = bar0 + 8u * 12;
+  const uint32_t epi_idle = bar0 + 8u * 12;
+  const uint32_t tmem_slot = bar0 + 8u * 13;
   constexpr int BAR_BYTES = 8 * 14;
   constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
   float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][2][C] = 1024 floats
@@ -638,7 +641,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   fence_proxy_async();
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmXall); tma_prefetch_desc(&tmWd);
-    mbar_init(wfull, 1); mbar_init(wdone, 1);
+    mbar_init(wfull, 1); mbar_init(wdone, 1); mbar_init(epi_idle, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(xready(s), 1); mbar_init(dyready(s), 256); mbar_init(wfree(s), 1);
       mbar_init(dxfull(s, 0), 1); mbar_init(dxfull(s, 1), 1);
@@ -739,20 +742,27 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     // y of 8 channels (chunk ch) of this thread's pixel: one conflict-free LDS.128 from the thread's own slots
     auto y_chunk = [&](int ch) -> uint4 { return ybuf[ch * 512 + et]; };
     if (active) load_y(a.NB - 1);
+    auto write_ssp = [&](int it2) {                  // scale/shift pairs of block NB-1-it2 -> buffer it2 & 1 (threads et < C)
+      const int k2 = a.NB - 1 - it2;
+      float* d = bnp2 + (it2 & 1) * 64 + (et >> 1) * 4 + (et & 1) * 2;
+      d[0] = a.scale_shift[(size_t)k2 * 2 * C + et]; d[1] = a.scale_shift[(size_t)k2 * 2 * C + C + et];
+    };
+    if (et < C) write_ssp(0);
+    const float gamma_r = (et < C) ? a.gamma[et] : 0.f;
+    asm volatile("bar.sync 1, 512;" ::: "memory");
     for (int it = 0; it < a.NB; ++it) {
       const int k = a.NB - 1 - it;
-      long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + it) * 8 : nullptr;
+      long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + it) * 16 : nullptr;
       if (tr) tr[0] = clock64();
       // per channel pair e (channels 2e, 2e+1): ssp[e] = {scale, shift, scale', shift'} (double-buffered: a slower thread may
       // still be in phase B of the previous block); cfp[e] = {A1, A2, A3, -, A1', A2', A3', -} with dy = dz*A1 + y*A2 + A3
       float4* ssp = reinterpret_cast<float4*>(bnp2 + (it & 1) * 64);
       float4* cfp = reinterpret_cast<float4*>(bnp2 + 128);
-      if (et < C) {
-        float* d = reinterpret_cast<float*>(ssp) + (et >> 1) * 4 + (et & 1) * 2;
-        d[0] = a.scale_shift[(size_t)k * 2 * C + et]; d[1] = a.scale_shift[(size_t)k * 2 * C + C + et];
-      }
+      // no CTA barrier here: ssp for this block was written one block ahead (below, after the grid barrier), y comes from this
+      // thread's own cp.async slots, so the warps of the first image start phase A while the second image's dgrad still runs
+      // saved statistics of this block for the combine below: fetched now, far ahead of their use on the critical path
+      const float mean_r = (et < C) ? a.saved[(size_t)k * 2 * C + et] : 0.f, is_r = (et < C) ? a.saved[(size_t)k * 2 * C + C + et] : 0.f;
       asm volatile("cp.async.wait_group 0;" ::: "memory");
-      asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[7] = clock64();
       // ---- phase A: per-channel sums of dz and dz*y over this warp's 32 pixels ----
       float s1[2] = {0.f, 0.f}, s2[2] = {0.f, 0.f};          // per 16-channel half: lanes 2c, 2c+1 hold channel 16*half + c
@@ -774,8 +784,11 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
               t1[i] = d0; t1[i + 1] = d1; t2[i] = d0 * y2.x; t2[i + 1] = d1 * y2.y;
             }
           }
+          if (tr) tr[8 + hf * 3] = clock64();
           s1[hf] = warp_col_sum16(t1, lane);
+          if (tr) tr[9 + hf * 3] = clock64();
           s2[hf] = warp_col_sum16(t2, lane);
+          if (tr) tr[10 + hf * 3] = clock64();
         }
       }
       if (tr) tr[1] = clock64();
@@ -794,9 +807,13 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[2] = clock64();
-      if (et == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
+      if (et == 0) {
+        gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target);
+      }
       if (tr) tr[3] = clock64();
       asm volatile("bar.sync 1, 512;" ::: "memory");
+      // every thread is past phase B of the previous block: its scale/shift buffer may now take the NEXT block's values
+      if (et < C && it + 1 < a.NB) write_ssp(it + 1);
       {
         const int c4 = et & 15, r = et >> 4;
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
@@ -823,10 +840,10 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       if (et < C) {
         const double db = dsum2[et] + dsum2[2 * C + et] + dsum2[4 * C + et] + dsum2[6 * C + et];
         const double dgy = dsum2[C + et] + dsum2[3 * C + et] + dsum2[5 * C + et] + dsum2[7 * C + et];
-        const double mean = (double)a.saved[(size_t)k * 2 * C + et], is = (double)a.saved[(size_t)k * 2 * C + C + et];
+        const double mean = (double)mean_r, is = (double)is_r;
         const double dg = is * (dgy - mean * db);       // sum dz*xhat = invstd * (sum dz*y - mean * sum dz)
         db_acc += (float)db; dg_acc += (float)dg;       // same order as the per-block path: k = NB-1 first
-        const double a_ = (double)a.gamma[et] * is, b_ = db * a.inv_count, c_ = dg * a.inv_count;
+        const double a_ = (double)gamma_r * is, b_ = db * a.inv_count, c_ = dg * a.inv_count;
         float* d = reinterpret_cast<float*>(cfp) + (et >> 1) * 8 + (et & 1) * 4;
         d[0] = (float)a_; d[1] = (float)(-a_ * c_ * is); d[2] = (float)(a_ * c_ * is * mean - a_ * b_); d[3] = 0.f;
       }
@@ -858,7 +875,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         fence_proxy_async();
         mbar_arrive(dyready(s));
         if (tr) tr[5] = clock64();
-        if (k > 0) load_y(k - 1);          // y_k is dead: fetch the next block's row while the dgrad MMAs run
+        if (k > 0 && !a.dbg_skip) load_y(k - 1);          // y_k is dead: fetch the next block's row while the dgrad MMAs run
         // ---- phase C: dx_k = dgrad + g ----
         mbar_wait(dxfull(s, m), (uint32_t)(it & 1));
         tc_fence_after();
@@ -1196,7 +1213,7 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_in, void* dx0_out, cudaStr
   a.dgamma = p->grads + p->off[3]; a.dbeta = p->grads + p->off[4];
   a.ys = (const bf16*)p->ys; a.g_in = (const bf16*)g_in; a.dx0_out = (bf16*)dx0_out;
   a.partial = p->stats_partial; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
-  a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
+  a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.dbg_skip = p->dbg_skip_stores; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(), st));
   nrd_count_launch();

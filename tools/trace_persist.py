@@ -29,10 +29,10 @@ for cta in (0, 1, grid - 1):
 y = torch.randint(0, 10, (B,), device=dev)
 out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
 torch.cuda.synchronize()
-trb = pl.tensor_view(2, 0).view(torch.int64)[: grid * 10 * 8].view(grid, 10, 8).cpu()
+trb = pl.tensor_view(2, 0).view(torch.int64)[: grid * 10 * 16].view(grid, 10, 16).cpu()
 namesb = ["start", "phaseA", "pre-barrier", "post-barrier", "combined", "phaseB(dy ready)", "phaseC(dx)"]
 for cta in (0, grid - 1):
     print(f"BWD CTA {cta}:")
     for it in range(10):
         t = trb[cta, it]
-        print("  it=%d " % it + f"sync={int(t[7]-t[0]):6d} " + " ".join(f"{namesb[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next=+{int(trb[cta,it+1,0]-t[0])}" if it < 9 else ""))
+        print("  it=%d " % it + f"sync={int(t[7]-t[0]):6d} " + " ".join(f"{namesb[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next=+{int(trb[cta,it+1,0]-t[0])}" if it < 9 else "") + "  A:" + ",".join(str(int(t[i]-t[7])) for i in range(8, 14)))
