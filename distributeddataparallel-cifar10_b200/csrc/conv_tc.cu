@@ -331,7 +331,8 @@ struct PersistFwdArgs {
   long long* nbt;
   bf16* xs;                // x_0 .. x_NB   (x_0 is read through the tensor map)
   bf16* ys;                // y_0 .. y_NB-1
-  float* partial;          // two buffers of [gridDim.x][2C] at +0 and +512*2C floats
+  float* partial;          // (unused by the persistent kernel; kept for the per-block kernels)
+  unsigned long long* acc; // [NB][2C] 64-bit fixed-point accumulators, zeroed before the launch
   unsigned long long* gbar;
   int B, NB;
   size_t act_elems;        // B*256*C
@@ -464,45 +465,25 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       if (tr) tr[2] = clock64();
       red[(ew * 2 + 0) * C + lane] = ssum; red[(ew * 2 + 1) * C + lane] = qsum;
       asm volatile("bar.sync 1, 512;" ::: "memory");
-      float* part = a.partial + (size_t)(k & 1) * 512 * 2 * C;
+      // cross-CTA sum WITHOUT a partial matrix: every CTA adds its 2C per-channel sums as 64-bit fixed point (2^-32) into one
+      // accumulator row per block.  Integer addition is associative, so the result is bit-identical whatever order the CTAs
+      // arrive in; the grid barrier then only has to publish 2C numbers instead of gridDim.x rows.
+      unsigned long long* acc = a.acc + (size_t)k * 2 * C;
       if (et < 2 * C) {
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 16; ++w) t += red[w * 2 * C + et];      // fixed order over the 16 epilogue warps
-        part[(size_t)blockIdx.x * 2 * C + et] = t;
+        atomicAdd(acc + et, (unsigned long long)__double2ll_rn((double)t * 4294967296.0));
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[3] = clock64();
       if (et == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
       if (tr) tr[4] = clock64();
       asm volatile("bar.sync 1, 512;" ::: "memory");
-      {
-        // [gridDim.x][2C] -> column sums in fp64, fixed order: 16 float4 column chunks x 32 row classes, then 4 groups of 8
-        const int c4 = et & 15, r = et >> 4;
-        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-        float4 v[5];                                    // gridDim.x <= 148 => at most 5 rows per class: all loads in flight at once
-#pragma unroll
-        for (int u = 0; u < 5; ++u) {
-          const int row = r + u * 32;
-          v[u] = (row < (int)gridDim.x) ? __ldcg(reinterpret_cast<const float4*>(part + (size_t)row * 2 * C) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-#pragma unroll
-        for (int u = 0; u < 5; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
-        double* d = dsum + (size_t)r * 2 * C + c4 * 4;
-        d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
-      }
-      asm volatile("bar.sync 1, 512;" ::: "memory");
-      if (et < 4 * 2 * C) {
-        const int col = et & (2 * C - 1), g = et >> 6;
-        double t = 0.0;
-#pragma unroll
-        for (int r = 0; r < 8; ++r) t += dsum[(size_t)(g * 8 + r) * 2 * C + col];
-        dsum2[g * 2 * C + col] = t;
-      }
+      if (et < 2 * C) dsum2[et] = (double)(long long)__ldcg(acc + et) * (1.0 / 4294967296.0);
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (et < C) {
-        const double S = dsum2[et] + dsum2[2 * C + et] + dsum2[4 * C + et] + dsum2[6 * C + et];
-        const double Q = dsum2[C + et] + dsum2[3 * C + et] + dsum2[5 * C + et] + dsum2[7 * C + et];
+        const double S = dsum2[et], Q = dsum2[C + et];
         const double inv_count = a.inv_count;
         const double mean = S * inv_count;
         double var = Q * inv_count - mean * mean;
@@ -587,7 +568,7 @@ struct PersistBwdArgs {
   const bf16* ys;             // y_0 .. y_NB-1
   const bf16* g_in;           // dL/dx_NB
   bf16* dx0_out;              // dL/dx_0
-  float* partial;             // two buffers of [gridDim.x][2C] at +0 and +512*2C floats
+  unsigned long long* acc;    // [NB][2C] 64-bit fixed-point accumulators, zeroed before the launch
   float* wpartial;            // [gridDim.x][9][C][C]
   unsigned long long* gbar;
   int B, NB;
@@ -798,12 +779,13 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         red[(ew * 2 + 1) * C + c] = s2[0]; red[(ew * 2 + 1) * C + 16 + c] = s2[1];
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
-      float* part = a.partial + (size_t)(it & 1) * 512 * 2 * C;
+      // cross-CTA sum as 64-bit fixed point (2^-40) atomics into one accumulator row per block: order-independent, bit-exact
+      unsigned long long* acc = a.acc + (size_t)it * 2 * C;
       if (et < 2 * C) {
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 16; ++w) t += red[w * 2 * C + et];
-        part[(size_t)blockIdx.x * 2 * C + et] = t;
+        atomicAdd(acc + et, (unsigned long long)__double2ll_rn((double)t * 1099511627776.0));
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[2] = clock64();
@@ -814,32 +796,10 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       asm volatile("bar.sync 1, 512;" ::: "memory");
       // every thread is past phase B of the previous block: its scale/shift buffer may now take the NEXT block's values
       if (et < C && it + 1 < a.NB) write_ssp(it + 1);
-      {
-        const int c4 = et & 15, r = et >> 4;
-        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-        float4 v[5];
-#pragma unroll
-        for (int u = 0; u < 5; ++u) {
-          const int row = r + u * 32;
-          v[u] = (row < (int)gridDim.x) ? __ldcg(reinterpret_cast<const float4*>(part + (size_t)row * 2 * C) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-#pragma unroll
-        for (int u = 0; u < 5; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
-        double* d = dsum + (size_t)r * 2 * C + c4 * 4;
-        d[0] = a0; d[1] = a1; d[2] = a2; d[3] = a3;
-      }
-      asm volatile("bar.sync 1, 512;" ::: "memory");
-      if (et < 4 * 2 * C) {
-        const int col = et & (2 * C - 1), g = et >> 6;
-        double t = 0.0;
-#pragma unroll
-        for (int r = 0; r < 8; ++r) t += dsum[(size_t)(g * 8 + r) * 2 * C + col];
-        dsum2[g * 2 * C + col] = t;
-      }
+      if (et < 2 * C) dsum2[et] = (double)(long long)__ldcg(acc + et) * (1.0 / 1099511627776.0);
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (et < C) {
-        const double db = dsum2[et] + dsum2[2 * C + et] + dsum2[4 * C + et] + dsum2[6 * C + et];
-        const double dgy = dsum2[C + et] + dsum2[3 * C + et] + dsum2[5 * C + et] + dsum2[7 * C + et];
+        const double db = dsum2[et], dgy = dsum2[C + et];
         const double mean = (double)mean_r, is = (double)is_r;
         const double dg = is * (dgy - mean * db);       // sum dz*xhat = invstd * (sum dz*y - mean * sum dz)
         db_acc += (float)db; dg_acc += (float)dg;       // same order as the per-block path: k = NB-1 first
@@ -856,7 +816,6 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         for (int ch = 0; ch < 4; ++ch) {
           uint4 ok;
           __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
-#pragma unroll
           const uint4 yv = y_chunk(ch);
           const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
 #pragma unroll
@@ -1195,7 +1154,8 @@ int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st) {
   PersistFwdArgs a;
   a.gamma = p->params + p->off[3]; a.beta = p->params + p->off[4];
   a.saved = p->saved_stats; a.scale_shift = p->scale_shift; a.running = p->bn_running; a.nbt = (long long*)p->nbt;
-  a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_FWD;
+  a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.acc = p->bn_acc; a.gbar = p->gbar + NRD_GBAR_PERSIST_FWD;
+  NRD_CHECK_CUDA(cudaMemsetAsync(p->bn_acc, 0, (size_t)p->NB * 2 * p->C * sizeof(unsigned long long), st));
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace; a.dbg_skip_stores = p->dbg_skip_stores;
   a.inv_count = 1.0 / ((double)p->B * NRD_PIX); a.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
   void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&a};
@@ -1212,7 +1172,8 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_in, void* dx0_out, cudaStr
   a.gamma = p->params + p->off[3]; a.scale_shift = p->scale_shift; a.saved = p->saved_stats;
   a.dgamma = p->grads + p->off[3]; a.dbeta = p->grads + p->off[4];
   a.ys = (const bf16*)p->ys; a.g_in = (const bf16*)g_in; a.dx0_out = (bf16*)dx0_out;
-  a.partial = p->stats_partial; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
+  a.acc = p->bn_acc + (size_t)32 * 2 * 64; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
+  NRD_CHECK_CUDA(cudaMemsetAsync(a.acc, 0, (size_t)p->NB * 2 * p->C * sizeof(unsigned long long), st));
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.dbg_skip = p->dbg_skip_stores; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(), st));

@@ -93,6 +93,7 @@ struct nrd_plan {
   int fuse_bn_bwd;        // BN+ReLU backward as one cooperative kernel when it fits shared memory
   int tc_persist_fwd;     // all NB blocks of the forward in ONE cooperative kernel (C=32, <= 2 images per CTA)
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
+  unsigned long long* bn_acc; // fixed-point BN-sum accumulators of the persistent kernels: fwd [32][128] then bwd [32][128]
   unsigned long long* gbar; // grid-barrier counters (one per cooperative kernel type)
   void* trace;            // optional device buffer for in-kernel clock64 stamps (profiling aid; NULL = off)
   int dbg_skip_stores;    // profiling experiment (NRD_OPT_TRACE value 2)

@@ -1389,6 +1389,7 @@ static void carve(nrd_plan* p, char* base, size_t* total) {
   p->wtc_fwd = cv.take<bf16>((size_t)9 * C * C * 2);
   p->wtc_dgrad = cv.take<bf16>((size_t)9 * C * C * 2);
   p->gbar = cv.take<unsigned long long>(256);
+  p->bn_acc = cv.take<unsigned long long>((size_t)2 * 32 * 128 * sizeof(unsigned long long));
   *total = cv.off;
 }
 
