@@ -7,6 +7,7 @@ LIB_PATH = os.path.join(HERE, "libnrd.so")
 
 NRD_F32, NRD_BF16 = 0, 1
 CONV_CUDA_CORE, CONV_TCGEN05, CONV_TCGEN05_UNFUSED = 0, 1, 2
+OPT_FUSE_BN_BWD, OPT_PERSIST_FWD, OPT_TRACE, OPT_PERSIST_BWD, OPT_TC_STEM, OPT_RESERVE_SMS = range(6)
 
 
 class NrdError(RuntimeError):
@@ -34,6 +35,7 @@ _PROTOS = {
     "nrd_plan_set_conv_impl": (i32, [vp, i32]),
     "nrd_plan_conv_impl": (i32, [vp]),
     "nrd_plan_set_option": (i32, [vp, i32, i32]),
+    "nrd_plan_set_bn_sync": (i32, [vp, vp, f32, f32]),
     "nrd_plan_tensor": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)]),
     "nrd_pack_weights": (i32, [vp, vp]),
     "nrd_forward": (i32, [vp, vp, vp, i32, vp]),

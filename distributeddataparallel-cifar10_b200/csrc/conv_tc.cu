@@ -1056,7 +1056,7 @@ constexpr size_t persist_bwd_smem() {
 }
 
 static int items(const nrd_plan* p) { return p->B * (p->C == 32 ? 1 : 2); }
-static int conv_grid(const nrd_plan* p) { int t = items(p); return t < NRD_NUM_SMS ? t : NRD_NUM_SMS; }
+static int conv_grid(const nrd_plan* p) { int t = items(p), sms = NRD_NUM_SMS - p->reserve_sms; return t < sms ? t : sms; }
 
 template <typename F> static int set_attr(F* fn, size_t smem) {
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -1089,10 +1089,8 @@ int nrd_tc_plan_init(nrd_plan* p) {
     NRD_TRY(set_attr(k_tc_conv<64, 2>, conv_smem<64, 2>())); NRD_TRY(set_attr(k_tc_wgrad<64>, wgrad_smem<64>()));
   }
   // fused block forward: every CTA keeps all its accumulators in TMEM (512 columns) and all CTAs must be co-resident
-  const int grid = conv_grid(p), per_cta = (items(p) + grid - 1) / grid * (rows / 8);
-  p->tc_fused_fwd = (per_cta * p->C <= 512) ? 1 : 0;
-  p->tc_persist_fwd = (p->C == 32 && p->B <= 2 * NRD_NUM_SMS) ? 1 : 0;
-  if (p->tc_persist_fwd) {
+  nrd_tc_refresh_limits(p);
+  if (p->C == 32) {
     NRD_TRY(set_attr(k_tc_fwd_persist, persist_smem()));
     NRD_TRY(set_attr(k_tc_bwd_persist, persist_bwd_smem()));
     // all saved x_k as ONE 5-D tensor {C, W, H, N, k}: the block index is just the last TMA coordinate
@@ -1107,6 +1105,14 @@ int nrd_tc_plan_init(nrd_plan* p) {
   }
   p->tc_ready = 1;
   return NRD_OK;
+}
+
+// which cooperative kernels fit, given the grid (148 SMs minus the ones left free for a concurrent collective)
+void nrd_tc_refresh_limits(nrd_plan* p) {
+  const int rows = p->C == 32 ? 16 : 8;
+  const int grid = conv_grid(p), per_cta = (items(p) + grid - 1) / grid * (rows / 8);
+  p->tc_fused_fwd = (per_cta * p->C <= 512) ? 1 : 0;
+  p->tc_persist_fwd = (p->C == 32 && p->B <= 2 * grid) ? 1 : 0;
 }
 
 int nrd_tc_stats_blocks(const nrd_plan* p) { return conv_grid(p); }

@@ -86,6 +86,10 @@ struct nrd_plan {
   CUtensorMap tm_wf, tm_wd;
   CUtensorMap tm_xall;    // all x_k as one 5-D tensor (persistent backward)
   int tc_ready;
+  int reserve_sms;        // option: SMs the cooperative kernels leave free (a concurrent NCCL kernel needs somewhere to run)
+  float* bn_sync;         // optional [2C] slot in front of the gradient vector: BN running stats ride the body bucket's all-reduce
+  float bn_sync_contrib;  // what this rank adds to the slot: world_size on rank 0, 0 elsewhere
+  float bn_sync_inv_world;
   int tc_stem;            // tensor-core stem kernels available (bf16, C = 32)
   int use_tc_stem;        // option
   int persist_fwd;        // option: use the persistent block-stack forward when available
@@ -124,6 +128,19 @@ static __device__ __forceinline__ void nrd_grid_barrier(unsigned long long* ctr,
     }
   }
 }
+// DDP buffer sync folded into the gradient exchange (nrd_plan_set_bn_sync): the stem forward, the first kernel of a training
+// step, overwrites the running stats with rank 0's values of the previous step (slot = world_size * value after the
+// all-reduce), exactly where DDP's broadcast in front of the forward would.
+struct nrd_bn_sync_args { const float* slot; float* running; float inv_world; int n; };
+static __device__ __forceinline__ void nrd_bn_sync_apply(const nrd_bn_sync_args& a) {
+  if (a.slot && blockIdx.x == 0 && blockIdx.y == 0)
+    for (int j = threadIdx.x; j < a.n; j += blockDim.x) a.running[j] = a.slot[j] * a.inv_world;
+}
+static inline nrd_bn_sync_args nrd_bn_sync_of(const nrd_plan* p, int training) {
+  nrd_bn_sync_args a = {nullptr, nullptr, 0.f, 0};
+  if (p && training && p->bn_sync) { a.slot = p->bn_sync; a.running = p->bn_running; a.inv_world = p->bn_sync_inv_world; a.n = 2 * p->C; }
+  return a;
+}
 #define NRD_GBAR_BLOCK_FWD 0
 #define NRD_GBAR_PERSIST_FWD 1
 #define NRD_GBAR_BN_BWD 2
@@ -131,11 +148,12 @@ static __device__ __forceinline__ void nrd_grid_barrier(unsigned long long* ctr,
 
 // tcgen05 path (conv_tc.cu)
 int nrd_tc_plan_init(nrd_plan* p);
+void nrd_tc_refresh_limits(nrd_plan* p);
 int nrd_tc_conv_fwd(nrd_plan* p, int k, cudaStream_t st);                       // y_k = conv(x_k) + stats partials
 int nrd_tc_conv_dgrad(nrd_plan* p, const void* g, void* dx_out, cudaStream_t st); // dx = dgrad(dy) + g
 int nrd_tc_conv_wgrad(nrd_plan* p, int k, int first, cudaStream_t st);          // partial (+)= wgrad(x_k, dy)
 int nrd_tc_stem_init(nrd_plan* p);
-int nrd_tc_stem_fwd(nrd_plan* p, const float* images, cudaStream_t st);
+int nrd_tc_stem_fwd(nrd_plan* p, const float* images, int training, cudaStream_t st);
 int nrd_tc_stem_bwd(nrd_plan* p, const float* images, const void* g0, cudaStream_t st);   // per-CTA partials only
 int nrd_tc_stats_blocks(const nrd_plan* p);
 int nrd_tc_wgrad_blocks(const nrd_plan* p);

@@ -93,8 +93,9 @@ __global__ void k_pack_weights(const float* __restrict__ rb_w, const float* __re
 // ------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void k_stem_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27][C]*/,
-                           const float* __restrict__ bias, T* __restrict__ x0, uint8_t* __restrict__ idx0, int C) {
+                           const float* __restrict__ bias, T* __restrict__ x0, uint8_t* __restrict__ idx0, int C, nrd_bn_sync_args bs) {
   extern __shared__ float sm[];
+  nrd_bn_sync_apply(bs);
   float* tile = sm;                 // [3][10][35], padded to 1056 floats so wsm stays 16-B aligned
   float* wsm = sm + 1056;           // [27][C]
   float* bsm = wsm + 27 * C;        // [C]
@@ -216,8 +217,12 @@ __global__ void __launch_bounds__(256) k_stem_bwd(const float* __restrict__ img,
 
 // conv-weight and stem partials in ONE launch: CTAs [0, 9C*C/32) reduce the conv partials, the rest the stem partials
 __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ wpartial, int wblk, const float* __restrict__ spartial, int sblk,
-                                                     int C, float* __restrict__ dw, float* __restrict__ dw1, float* __restrict__ db1) {
+                                                     int C, float* __restrict__ dw, float* __restrict__ dw1, float* __restrict__ db1,
+                                                     float* __restrict__ bn_sync, const float* __restrict__ running, float contrib) {
   __shared__ double red[8][33];
+  // DDP buffer sync riding the body bucket: rank 0 contributes world_size * running, the others exact zeros
+  if (bn_sync && blockIdx.x == gridDim.x - 1)
+    for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) bn_sync[j] = contrib != 0.f ? running[j] * contrib : 0.f;
   const int o = threadIdx.x & 31, r = threadIdx.x >> 5, nconv = 9 * C * C / 32;
   const bool conv = (int)blockIdx.x < nconv;
   const int i = (conv ? blockIdx.x : blockIdx.x - nconv) * 32 + o, n = conv ? 9 * C * C : 28 * C, nblk = conv ? wblk : sblk;
@@ -1184,11 +1189,12 @@ static int bn_relu_bwd_any(const void* g, const void* y, const float* ss, const 
   return NRD_OK;
 }
 
-static int stem_fwd_any(const float* img, const float* wp, const float* bias, void* x0, uint8_t* idx0, int B, int C, int dt, cudaStream_t st) {
+static int stem_fwd_any(const float* img, const float* wp, const float* bias, void* x0, uint8_t* idx0, int B, int C, int dt, cudaStream_t st,
+                        nrd_bn_sync_args bs = nrd_bn_sync_args{nullptr, nullptr, 0.f, 0}) {
   dim3 grid(4, B); int threads = 64 * (C / 8);
   size_t smem = (1056 + 27 * C + C) * sizeof(float);
-  if (dt == NRD_F32) k_stem_fwd<float><<<grid, threads, smem, st>>>(img, wp, bias, (float*)x0, idx0, C);
-  else k_stem_fwd<bf16><<<grid, threads, smem, st>>>(img, wp, bias, (bf16*)x0, idx0, C);
+  if (dt == NRD_F32) k_stem_fwd<float><<<grid, threads, smem, st>>>(img, wp, bias, (float*)x0, idx0, C, bs);
+  else k_stem_fwd<bf16><<<grid, threads, smem, st>>>(img, wp, bias, (bf16*)x0, idx0, C, bs);
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1458,10 +1464,24 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_PERSIST_FWD: p->persist_fwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_BWD: p->persist_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_TC_STEM: p->use_tc_stem = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_RESERVE_SMS:
+      NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
+      p->reserve_sms = value;
+      if (p->tc_ready) nrd_tc_refresh_limits(p);
+      return NRD_OK;
     case NRD_OPT_TRACE: p->dbg_skip_stores = (value == 2);
       p->trace = value ? (void*)p->dxb : nullptr; p->trace_bwd = value ? (void*)p->dy : nullptr; return NRD_OK;   // stamps land in the dx pong / dy scratch
     default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
   }
+}
+
+extern "C" int nrd_plan_set_bn_sync(nrd_plan* p, float* slot, float contrib, float inv_world) {
+  NRD_REQUIRE(p, "null plan");
+  NRD_REQUIRE(slot == nullptr || slot + 2 * p->C == p->grads, "nrd_plan_set_bn_sync: the slot must be the 2C floats right in front of the gradient vector");
+  p->bn_sync = slot;
+  p->bn_sync_contrib = contrib;
+  p->bn_sync_inv_world = inv_world;
+  return NRD_OK;
 }
 
 extern "C" int nrd_plan_conv_impl(const nrd_plan* p) { return p ? p->conv_impl : NRD_EINVAL; }
@@ -1519,8 +1539,8 @@ extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int 
   const int B = p->B, C = p->C, NB = p->NB, dt = p->dtype;
   const size_t act = p->act_elems * p->esz;
   p->images_last = images;
-  if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_fwd(p, images, st));
-  else NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st));
+  if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_fwd(p, images, training, st));
+  else NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st, nrd_bn_sync_of(p, training)));
   if (!training) { k_bn_eval_coeffs<<<1, 64, 0, st>>>(p->bn_running, PRM(P_BNG), PRM(P_BNB), C, p->scale_shift); LAUNCH_CHECK(); }
   const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_fwd;
   if (persist) NRD_TRY(nrd_tc_forward_blocks(p, st));
@@ -1609,7 +1629,8 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_bwd(p, p->images_last, g, st));
   else NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
   k_body_reduce<<<9 * C * C / 32 + 28 * C / 32, 256, 0, st>>>(p->wgrad_partial, p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B),
-                                                           p->stem_partial, stem_bwd_blocks(B), C, GRD(P_RBW), GRD(P_C1W), GRD(P_C1B));
+                                                           p->stem_partial, stem_bwd_blocks(B), C, GRD(P_RBW), GRD(P_C1W), GRD(P_C1B),
+                                                           p->bn_sync, p->bn_running, p->bn_sync_contrib);
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1652,7 +1673,7 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       return conv_fwd_any(p->dy, p->w_dgrad, p->dxb, B, C, dt, nullptr, p->dxa, st);
     case NRD_OP_STEM_FWD:
       NRD_REQUIRE(p->images_last, "run a forward first");
-      if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) return nrd_tc_stem_fwd(p, p->images_last, st);   // rewrites x_0 in place (same values)
+      if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) return nrd_tc_stem_fwd(p, p->images_last, 0, st);   // rewrites x_0 in place (same values)
       return stem_fwd_any(p->images_last, p->conv1_wp, PRM(P_C1B), p->dxb, p->idx0, B, C, dt, st);
     case NRD_OP_STEM_BWD:
       NRD_REQUIRE(p->images_last, "run a forward first");

@@ -75,8 +75,9 @@ constexpr int STAGE_B = 8 * TILE_BYTES;                 // backward stage: 4 A t
 // ============================================================================================
 __global__ void __launch_bounds__(288, 1)
 k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27][32] fp32*/, const float* __restrict__ bias,
-              bf16* __restrict__ x0, uint8_t* __restrict__ idx0, int B) {
+              bf16* __restrict__ x0, uint8_t* __restrict__ idx0, int B, nrd_bn_sync_args bs) {
   extern __shared__ uint8_t smem_raw[];
+  nrd_bn_sync_apply(bs);
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
   uint8_t* a_gen = gen;                                            // 2 stages x 4 tiles
@@ -344,9 +345,9 @@ int nrd_tc_stem_init(nrd_plan* p) {
 
 static int stem_grid(const nrd_plan* p) { return p->B < NRD_NUM_SMS ? p->B : NRD_NUM_SMS; }
 
-int nrd_tc_stem_fwd(nrd_plan* p, const float* images, cudaStream_t st) {
+int nrd_tc_stem_fwd(nrd_plan* p, const float* images, int training, cudaStream_t st) {
   NRD_REQUIRE(p->tc_stem, "tensor-core stem not available for this plan");
-  k_stem_tc_fwd<<<stem_grid(p), 288, stem_fwd_smem(), st>>>(images, p->conv1_wp, p->params + p->off[1], (bf16*)p->xs, p->idx0, p->B);
+  k_stem_tc_fwd<<<stem_grid(p), 288, stem_fwd_smem(), st>>>(images, p->conv1_wp, p->params + p->off[1], (bf16*)p->xs, p->idx0, p->B, nrd_bn_sync_of(p, training));
   nrd_count_launch();
   NRD_CHECK_CUDA(cudaGetLastError());
   return NRD_OK;

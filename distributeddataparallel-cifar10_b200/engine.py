@@ -108,7 +108,10 @@ class Engine:
             raise RuntimeError("NetResDeep (B200) runs on CUDA devices only: there is no CPU fallback")
         n = self.offsets[9]
         flat = torch.empty(n, dtype=torch.float32, device=device)
-        grads = torch.zeros(n, dtype=torch.float32, device=device)
+        # gradient exchange buffer: [2C BN-sync slot | body bucket | head bucket]; the slot lets rank 0's running stats
+        # ride the body bucket's all-reduce (graph.TrainStep) instead of a broadcast in front of every forward
+        self.xchg = torch.zeros(2 * self.C + n, dtype=torch.float32, device=device)
+        grads = self.xchg[2 * self.C:]
         for p, o in zip(ps, self.offsets):
             view = flat[o:o + p.numel()].view(p.shape)
             view.copy_(p.data.float())
@@ -127,6 +130,10 @@ class Engine:
 
     def grad_views(self) -> List[torch.Tensor]:
         return [self.flat_grads[o:o + p.numel()].view(p.shape) for p, o in zip(self.params(), self.offsets)]
+
+    def body_bucket_with_bn_slot(self) -> torch.Tensor:
+        """BN-sync slot + body bucket as ONE contiguous all-reduce operand."""
+        return self.xchg[:2 * self.C + self.offsets[N_BODY]]
 
     def bucket_slices(self):
         """(body, head) element ranges of the flat vectors."""

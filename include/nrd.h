@@ -84,7 +84,19 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
 /* NRD_OPT_TC_STEM (default 1): stem forward / weight gradient as tcgen05 implicit GEMMs with the im2col operand built in
  * shared memory (bf16 plans, C = 32); 0 = the CUDA-core stem kernels. */
 #define NRD_OPT_TC_STEM 4
+/* NRD_OPT_RESERVE_SMS (default 0): the cooperative kernels use 148 - value SMs.  They fill an SM's shared memory, so a
+ * collective launched beside them (the head bucket's all-reduce, parallel.py) can only run on SMs they leave free. */
+#define NRD_OPT_RESERVE_SMS 5
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
+/* DDP's per-forward buffer broadcast (torch DDP `broadcast_buffers`, reached from main.py:63 and run in front of every
+ * forward, main.py:33) folded into the gradient exchange: `slot` = the 2C floats directly in front of `grads` (so slot +
+ * body bucket are ONE contiguous all-reduce), `contrib` = world_size on rank 0 and 0 elsewhere, `inv_world` = 1/world_size.
+ * nrd_backward_body() writes running_stats * contrib into the slot; after the SUM all-reduce it holds world_size * (rank
+ * 0's stats) on every rank, and the next training nrd_forward() starts by storing slot * inv_world into the running
+ * stats -- what the broadcast would have delivered, bit-exact for a power-of-two world size.  Between steps every rank
+ * still sees its OWN running stats, as with the reference.  The caller initialises the slot (world_size * current stats)
+ * before the first step.  slot = NULL (default) turns it off. */
+int nrd_plan_set_bn_sync(nrd_plan* plan, float* slot, float contrib, float inv_world);
 /* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
  * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch (ping),
  * 6 = dx scratch (pong), 7 = wgrad per-CTA partials [ctas][9][C][C], 8 = BN-stat per-CTA partials [ctas][2][C],
