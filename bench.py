@@ -11,7 +11,8 @@ gradient exchange, SGD update), replayed as one CUDA graph.  Workload = BASELINE
   value     images/s, whole job, batch resident in HBM, device-timed (CUDA events per step, summed;
             max over ranks); L2 is flushed between steps (256 MiB write, untimed).
   e2e       same metric through the public API from PINNED HOST buffers: per step an H2D copy of the
-            batch, the step, and a D2H read of the loss (wall clock around K steps, max over ranks).
+            batch (TrainStep.iterate: issued one step ahead on a copy stream), the step, and a D2H read
+            of the loss with a host sync (wall clock around K steps, max over ranks).
   roofline  dominant kernel class of the step, timed alone with CUDA events on the launching stream
             (nrd_plan_run_op), algorithmic HBM bytes / duration against MEASURED_PEAKS.json.
   cpu_baseline  the oracle's port of the reference CPU step (main_no_ddp.py:45-50, B=64, fp32) timed
@@ -197,14 +198,22 @@ def main():
     # ---- end to end from pinned host memory -------------------------------------------------
     h_imgs = imgs.cpu().pin_memory(); h_labels = labels.cpu().pin_memory()
     h_loss = torch.zeros((), dtype=torch.float32).pin_memory()
-    for _ in range(3):
-        h_loss.copy_(step(h_imgs, h_labels), non_blocking=True); torch.cuda.current_stream().synchronize()
+    class HostBatches:                                      # stands in for main.py:61's DataLoader (pinned host batches)
+        def __init__(self, n): self.n = n
+        def __len__(self): return self.n
+        def __iter__(self): return ((h_imgs, h_labels) for _ in range(self.n))
+
+    def epoch(n):
+        # main.py:31-41 as TrainStep.iterate: launch step t, then start batch t+1's H2D copy beside it, then read the loss
+        tot = 0.0
+        for loss in step.iterate(HostBatches(n)):
+            tot += float(loss)                                  # host value of the step's loss (main.py:41)
+        return tot
+
+    epoch(3)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        loss = step(h_imgs, h_labels)                       # H2D (pinned, async) + graph replay
-        h_loss.copy_(loss, non_blocking=True)               # D2H of the step's loss
-        torch.cuda.current_stream().synchronize()           # the reference's loss.item() sync (main.py:41)
+    epoch(args.steps)                                           # every step's H2D copy (the first one too) is inside
     barrier()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)

@@ -31,6 +31,59 @@ class SyntheticCifar10Loader:
             self._step += 1
 
 
+class DevicePrefetcher:
+    """Wraps a loader that yields HOST batches `(imgs, labels)` (main.py:61's DataLoader; pinned memory makes the copies
+    asynchronous) and yields them on the device, with batch t+1's host-to-device copy issued on a copy stream BEFORE batch
+    t is handed out -- so it runs beside step t's kernels.  The training loop keeps the reference's shape (main.py:31-33:
+    `for imgs, labels in loader: imgs, labels = imgs.to(rank), labels.to(rank)`; `.to` of a resident tensor is free).
+
+    Two device slots are reused in turn: a yielded batch stays valid until the NEXT-BUT-ONE `next()`; work that reads it
+    must have been enqueued on the current stream by then (a training loop does exactly that)."""
+
+    def __init__(self, loader, device, slots: int = 2):
+        self.loader, self.device, self.n = loader, torch.device(device), max(2, slots)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.bufs = [None] * self.n
+        self.ready = [torch.cuda.Event() for _ in range(self.n)]
+
+    def __len__(self):
+        return len(self.loader)
+
+    def _issue(self, slot, batch):
+        imgs, labels = batch
+        if self.bufs[slot] is None or self.bufs[slot][0].shape != imgs.shape:
+            self.bufs[slot] = (torch.empty(imgs.shape, dtype=imgs.dtype, device=self.device),
+                               torch.empty(labels.shape, dtype=labels.dtype, device=self.device))
+        # the slot's previous contents were handed out two batches ago: everything enqueued on the consumer's stream so
+        # far (its readers included) goes first
+        self.copy_stream.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self.copy_stream):
+            self.bufs[slot][0].copy_(imgs, non_blocking=True)
+            self.bufs[slot][1].copy_(labels, non_blocking=True)
+            self.ready[slot].record(self.copy_stream)
+
+    def __iter__(self):
+        it = iter(self.loader)
+        try:
+            nxt = next(it)
+        except StopIteration:
+            return
+        slot = 0
+        self._issue(slot, nxt)
+        while True:
+            cur = slot
+            try:
+                nxt = next(it)
+                slot = (slot + 1) % self.n
+                self._issue(slot, nxt)
+            except StopIteration:
+                nxt = None
+            torch.cuda.current_stream(self.device).wait_event(self.ready[cur])
+            yield self.bufs[cur]
+            if nxt is None:
+                return
+
+
 # ---- host restatement of the generator (tests compare the device batch with it) -------------
 def _philox4x32_10(c0, c1, c2, c3, k0, k1):
     M0, M1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57)

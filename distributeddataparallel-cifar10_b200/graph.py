@@ -29,8 +29,10 @@ class TrainStep:
             raise RuntimeError("TrainStep needs the model on a CUDA device")
         self.device = dev
         self.world = self.ddp.world_size if self.ddp is not None else 1
-        self.imgs = torch.zeros(batch_size, 3, 32, 32, dtype=torch.float32, device=dev)
-        self.labels = torch.zeros(batch_size, dtype=torch.int64, device=dev)
+        # two input slots: `iterate()` fills one over PCIe while the step reads the other; slot 0 is the default
+        self.inputs = [(torch.zeros(batch_size, 3, 32, 32, dtype=torch.float32, device=dev),
+                        torch.zeros(batch_size, dtype=torch.int64, device=dev)) for _ in range(2)]
+        self.imgs, self.labels = self.inputs[0]
         self.logits = torch.empty(batch_size, 10, dtype=torch.float32, device=dev)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.plan = self.eng.plan(batch_size, dev)
@@ -49,10 +51,11 @@ class TrainStep:
                 self.resync_buffers()
             check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8"))),
                   "nrd_plan_set_option")
-        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.graphs = [None, None]              # one captured step per input slot (slot 1 on first use)
+        self.use_graph = use_graph
         self.kernel_launches = None
         if use_graph:
-            self._capture()
+            self._capture(0)
 
     def resync_buffers(self):
         """Rank 0's BN running stats to every rank, and into the slot the next forward starts from.  Called at construction;
@@ -63,12 +66,21 @@ class TrainStep:
                 torch.mul(self.eng.bn_running, float(self.world), out=self.eng.xchg[:2 * self.eng.C])
 
     # the step body, launched on the current stream
-    def _body(self):
+    @property
+    def graph(self):
+        return self.graphs[0]
+
+    @graph.setter
+    def graph(self, g):                     # `step.graph = None` drops every captured step (before communicator teardown)
+        self.graphs = [g, None]
+
+    def _body(self, slot: int = 0):
         eng, pl, st = self.eng, self.plan, _stream_ptr()
+        imgs, labels = self.inputs[slot]
         if self.world > 1 and not self.fold_bn_sync:
             self.ddp._sync_buffers()                                   # C2 (folded into the body bucket otherwise)
-        check(lib.nrd_forward(pl.handle, self.imgs.data_ptr(), self.logits.data_ptr(), 1, st), "nrd_forward")
-        check(lib.nrd_cross_entropy(self.logits.data_ptr(), self.labels.data_ptr(), self.B, 1.0, self.loss.data_ptr(),
+        check(lib.nrd_forward(pl.handle, imgs.data_ptr(), self.logits.data_ptr(), 1, st), "nrd_forward")
+        check(lib.nrd_cross_entropy(self.logits.data_ptr(), labels.data_ptr(), self.B, 1.0, self.loss.data_ptr(),
                                     pl.dlogits.data_ptr(), pl.loss_rows.data_ptr(), st), "nrd_cross_entropy")
         # backward: head weight grads (+ their bucket's all-reduce) on a side stream beside the body backward (C3)
         sum_head = (lambda: self.ddp._allreduce_bucket(1, average=False)) if self.world > 1 else None
@@ -80,19 +92,20 @@ class TrainStep:
         # fused mean + SGD (K16), then re-derive the packed weight copies
         check(lib.nrd_sgd_update_pack(pl.handle, self.lr, 1.0 / self.world, st), "nrd_sgd_update_pack")
 
-    def _capture(self):
+    def _capture(self, slot: int = 0):
         s = torch.cuda.Stream(device=self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
         # snapshot state: warm-up steps on a side stream must not change the model
         keep = (self.eng.flat_params.clone(), self.eng.bn_running.clone(), self.eng.nbt.clone())
         with torch.cuda.stream(s):
             for _ in range(2):
-                self._body()
+                self._body(slot)
         torch.cuda.current_stream(self.device).wait_stream(s)
         torch.cuda.synchronize(self.device)
-        self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph, stream=s):
-            self._body()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            self._body(slot)
+        self.graphs[slot] = g
         self.eng.flat_params.copy_(keep[0]); self.eng.bn_running.copy_(keep[1]); self.eng.nbt.copy_(keep[2])
         if self.fold_bn_sync:
             torch.mul(keep[1], float(self.world), out=self.eng.xchg[:2 * self.eng.C])
@@ -104,12 +117,62 @@ class TrainStep:
         self.labels.copy_(labels, non_blocking=True)
         return self.run()
 
-    def run(self) -> torch.Tensor:
-        """Replay on the static inputs already in `self.imgs` / `self.labels`."""
-        if self.graph is not None:
-            self.graph.replay()
+    def run(self, slot: int = 0) -> torch.Tensor:
+        """Replay on the static inputs already in `self.inputs[slot]` (slot 0 = `self.imgs` / `self.labels`)."""
+        if self.use_graph and self.graphs[slot] is None and self.graphs[0] is not None:
+            self._capture(slot)
+        if self.graphs[slot] is not None:
+            self.graphs[slot].replay()
         else:
-            self._body()
+            self._body(slot)
         self.eng.weights_epoch += 1
         self.plan.packed_version = self.eng._weights_version()
         return self.loss
+
+    def iterate(self, loader):
+        """One pass over `loader` (HOST batches `(imgs, labels)`; pinned memory makes the copies asynchronous), one step per
+        batch: the loop of main.py:31-41.  Yields the step's loss as a pinned HOST scalar tensor, already synchronised (the
+        reference's per-step `loss.item()`, main.py:41), valid until the next iteration.  Order per step: launch the step
+        on the slot that is ready, THEN fetch the next host batch and start its copy into the other slot on a copy stream
+        -- loader work and PCIe traffic run beside the step's kernels instead of in front of them."""
+        dev = self.device
+        main = torch.cuda.current_stream(dev)
+        if self.use_graph and self.graphs[1] is None:
+            self._capture(1)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._ready = [torch.cuda.Event(), torch.cuda.Event()]
+            self._consumed = [torch.cuda.Event(), torch.cuda.Event()]
+            self._h_loss = torch.zeros((), dtype=torch.float32).pin_memory()
+            for e in self._consumed:
+                e.record(main)
+        copy = self._copy_stream
+
+        def issue(slot, batch):
+            imgs, labels = batch
+            if tuple(imgs.shape) != tuple(self.inputs[slot][0].shape):
+                raise ValueError(f"TrainStep was built for batches of {tuple(self.inputs[slot][0].shape)}, got {tuple(imgs.shape)} "
+                                 "(use drop_last=True or a second TrainStep for the ragged tail)")
+            copy.wait_event(self._consumed[slot])        # the step that last read this slot
+            with torch.cuda.stream(copy):
+                self.inputs[slot][0].copy_(imgs, non_blocking=True)
+                self.inputs[slot][1].copy_(labels, non_blocking=True)
+                self._ready[slot].record(copy)
+
+        it = iter(loader)
+        nxt = next(it, None)
+        if nxt is None:
+            return
+        slot = 0
+        issue(slot, nxt)
+        while nxt is not None:
+            main.wait_event(self._ready[slot])
+            self.run(slot)
+            self._consumed[slot].record(main)
+            nxt = next(it, None)
+            if nxt is not None:
+                issue(slot ^ 1, nxt)
+            self._h_loss.copy_(self.loss, non_blocking=True)
+            main.synchronize()
+            yield self._h_loss
+            slot ^= 1

@@ -28,14 +28,23 @@ def setup(rank, world_size):
     dist.init_process_group("nccl", rank=rank, world_size=world_size)   # main.py:24
 
 
-def train_loop(model, train_loader, rank, epochs=99, lr=1e-2, save=True, log=print):
+def train_loop(model, train_loader, rank, epochs=99, lr=1e-2, save=True, log=print, graph=False):
+    """`graph=True`: the same loop as ONE captured CUDA graph per step (graph.TrainStep.iterate: next batch's host-to-device
+    copy beside the running step); needs a fixed batch size (drop_last)."""
     optimizer = optim.SGD(model.parameters(), lr=lr)       # main.py:27
     loss_fn = nrd_nn.CrossEntropyLoss()                    # main.py:28
     start_time = time.time()
     history = []
+    step = None
     for epoch in range(1, epochs + 1):                     # main.py:30
         loss_train = torch.zeros((), device=f"cuda:{rank}")  # device-side accumulation: one sync per epoch, not per step
-        for imgs, labels in train_loader:
+        if graph:
+            if step is None:
+                from .graph import TrainStep
+                step = TrainStep(model, train_loader.batch_size, lr=lr)
+            for loss in step.iterate(train_loader):        # main.py:31-41
+                loss_train += loss.to(loss_train.device)
+        for imgs, labels in (() if graph else train_loader):
             imgs, labels = imgs.to(rank), labels.to(rank)  # main.py:33
             outputs = model(imgs)                          # main.py:34
             loss = loss_fn(outputs, labels)                # main.py:35

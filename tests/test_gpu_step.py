@@ -227,3 +227,46 @@ def test_dropin_train_loop_runs_and_full_size_properties():
         yn = (y3.float().view(-1, 32) - stats[:32]) * stats[32:]
         tol = 1e-4 if dtype == "fp32" else 5e-3
         assert float(yn.mean(0).abs().max()) < tol and float((yn.var(0, unbiased=False) - 1).abs().max()) < 5 * tol
+
+
+def test_device_prefetcher_yields_every_host_batch_in_order():
+    """DevicePrefetcher: batch t+1's copy is in flight while batch t is consumed; with two slots reused in turn the
+    consumer (work enqueued on the current stream before the next-but-one next()) must still see every batch intact."""
+    import ddp_cifar10_b200 as nrd
+    g = torch.Generator().manual_seed(7)
+    host = [(torch.randn(64, 3, 32, 32, generator=g).pin_memory(), torch.randint(0, 10, (64,), generator=g).pin_memory())
+            for _ in range(7)]
+    got = []
+    burn = torch.randn(2048, 2048, device="cuda")
+    for imgs, labels in nrd.DevicePrefetcher(host, "cuda"):
+        assert imgs.is_cuda and labels.is_cuda
+        burn @ burn                                    # keep the consumer's stream busy so copies really overlap it
+        got.append((imgs.clone(), labels.clone()))     # the consumer's read, enqueued on the current stream
+    torch.cuda.synchronize()
+    assert len(got) == len(host)
+    for (gi, gl), (hi, hl) in zip(got, host):
+        assert torch.equal(gi.cpu(), hi) and torch.equal(gl.cpu(), hl)
+    assert list(nrd.DevicePrefetcher([], "cuda")) == []
+
+
+def test_trainstep_iterate_equals_step_by_step():
+    """TrainStep.iterate (two input slots, two captured steps, copies issued a step ahead) == calling the step per batch."""
+    import ddp_cifar10_b200 as nrd
+    g = torch.Generator().manual_seed(11)
+    host = [(torch.randn(16, 3, 32, 32, generator=g).pin_memory(), torch.randint(0, 10, (16,), generator=g).pin_memory())
+            for _ in range(5)]
+    res = []
+    for mode in ("call", "iterate"):
+        torch.manual_seed(3)
+        m = nrd.NetResDeep(32, 10).to("cuda")
+        step = nrd.TrainStep(m, 16, lr=1e-2)
+        if mode == "call":
+            losses = [float(step(x.cuda(), y.cuda())) for x, y in host]
+        else:
+            losses = [float(l) for l in step.iterate(host)]
+            assert [float(l) for l in step.iterate([])] == []
+        res.append((losses, m.engine.flat_params.clone(), m.engine.bn_running.clone(), int(m.engine.nbt)))
+    assert res[0][0] == res[1][0] and len(res[1][0]) == 5
+    assert torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2]) and res[0][3] == res[1][3] == 50
+    with pytest.raises(ValueError):
+        list(step.iterate([(torch.zeros(8, 3, 32, 32), torch.zeros(8, dtype=torch.int64))]))

@@ -84,6 +84,16 @@ def _gloo_worker(rank, W, port, q):
     flat_allreduce_mean_cpu(flat, n_body)
     bufs = torch.full((64,), float(rank))
     dist.broadcast(bufs, src=0)                    # C2: rank 0's BN buffers win
+    # the graph path's folded buffer sync: [2C slot | body bucket] as one SUM all-reduce, rank 0 contributes W * stats
+    torch.manual_seed(100 + rank)
+    running = torch.rand(64) * 3 + 1e-3
+    xchg = torch.zeros(64 + n_body)
+    xchg[:64] = running * float(W) if rank == 0 else 0.0
+    xchg[64:] = rank + 1.0
+    dist.all_reduce(xchg, op=dist.ReduceOp.SUM)
+    folded = xchg[:64] * (1.0 / W)
+    ref = running.clone(); dist.broadcast(ref, src=0)
+    assert torch.equal(folded, ref) and float(xchg[64]) == 3.0      # bit-exact, body bucket untouched by the slot
     q.put((rank, flat[[0, 10175, 10176, 76073]].tolist(), bufs.sum().item()))
     dist.barrier(); dist.destroy_process_group()
 
