@@ -359,10 +359,8 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   const uint32_t tmem_slot = bar0 + 8u * 9;
   constexpr int BAR_BYTES = 8 * 10;
   constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
-  float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][2][C] = 1024 floats
-  float* ss_sm = red + 1024;                                             // [2C]
-  double* dsum = reinterpret_cast<double*>(ss_sm + 64);                  // [32 row classes][2C] = 2048
-  double* dsum2 = dsum + 2048;                                           // [4][2C]
+  float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][sum | sum of squares][16 channels]
+  float* ss_sm = red + 1024;                                             // [2C] scale | shift of the current block
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -373,7 +371,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX0); tma_prefetch_desc(&tmW);
     mbar_init(wfull, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(xfull(s), 1); mbar_init(opready(s), 256); mbar_init(tfull(s, 0), 1); mbar_init(tfull(s, 1), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(xfull(s), 1); mbar_init(opready(s), 512); mbar_init(tfull(s, 0), 1); mbar_init(tfull(s, 1), 1); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -397,14 +395,12 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       constexpr uint32_t idesc = make_idesc(128, C, 0, 0);
       mbar_wait(wfull, 0);
       for (int k = 0; k < a.NB; ++k) {
-        for (int s = 0; s < nslots; ++s) {
+        for (int s = 0; s < nslots; ++s) {        // slot-major: slot 0's MMAs start as soon as ITS operands are rewritten
           if (k == 0) mbar_wait(xfull(s), 0);
           else mbar_wait(opready(s), (uint32_t)((k - 1) & 1));
-        }
-        tc_fence_after();
+          tc_fence_after();
 #pragma unroll
-        for (int m = 0; m < 2; ++m) {
-          for (int s = 0; s < nslots; ++s) {      // tile-major order: both image slots' epilogue groups start pass 1 early
+          for (int m = 0; m < 2; ++m) {
             const uint32_t d_tmem = tmem_base + (s * 2 + m) * C;
 #pragma unroll
             for (int t = 0; t < 9; ++t) {
@@ -420,123 +416,134 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       }
     }
   } else {
-    // ===== epilogue: 16 warps; warp = (image slot s, tile m of that image, TMEM lane quarter q); thread = one pixel =====
-    const int ew = warp - 2, s = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
-    const bool active = s < nslots;
-    const int img = (s == 0) ? img0 : img1;
-    uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
+    // ===== epilogue: 16 warps; warp = (channel half h, tile m, TMEM lane quarter q); thread = one pixel x 16 channels, of =====
+    // ===== image slot 0 and then of slot 1: slot 0's operands are ready (and its MMAs run) while slot 1 is still in pass 2 =====
+    const int ew = warp - 2, h = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
     const int p = q * 32 + lane, pi = m * 8 + (p >> 4), pj = p & 15;
-    const size_t gp = ((size_t)img * NRD_PIX + pi * 16 + pj) * C;             // this thread's pixel
+    const size_t pix_off = (size_t)(pi * 16 + pj) * C + h * 16;                // this thread's 16 channels inside an image
+    const size_t img_off[2] = {(size_t)img0 * NRD_PIX * C + pix_off, (size_t)img1 * NRD_PIX * C + pix_off};
     const int P1 = (pi + 1) * 16 + pj;                                         // its index inside an operand copy (row-haloed)
-    const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C;
+    const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
+    const float* ss_w = ss_sm + h * 16;                                        // this thread's channels: scale at [c], shift at [C + c]
     unsigned long long gbar_target = 0;
     if (et == 0) gbar_target = nrd_grid_barrier_base(a.gbar, gridDim.x);   // before this CTA's first arrival
-    const float gamma_r = (et < C) ? a.gamma[et] : 0.f, beta_r = (et < C) ? a.beta[et] : 0.f;   // off the per-block critical path
+    const float gamma_r = a.gamma[lane], beta_r = a.beta[lane];             // off the per-block critical path (used by warp ew == 0)
     for (int k = 0; k < a.NB; ++k) {
       long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + k) * 8 : nullptr;
       if (tr) tr[0] = clock64();
-      // ---- pass 1: y_k store + per-channel sum / sum of squares of this warp's 32 pixels ----
+      // ---- pass 1: y_k store + per-channel sum / sum of squares of this warp's 32 pixels x 16 channels ----
       float ssum = 0.f, qsum = 0.f;
-      if (active) {
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        if (s >= nslots) break;
         mbar_wait(tfull(s, m), (uint32_t)(k & 1));
         tc_fence_after();
-        if (tr) tr[1] = clock64();
-        float v[32];
-        tmem_ld32(my_tmem, v);
+        if (tr && s == 0) tr[1] = clock64();
+        float v[16];
+        tmem_ld16(my_tmem + s * 2 * C, v);
         {
           // y_k does not depend on the statistics: store it now, off the post-barrier critical path
-          uint4* yrow = reinterpret_cast<uint4*>(a.ys + (size_t)k * a.act_elems + gp);
+          uint4* yrow = reinterpret_cast<uint4*>(a.ys + (size_t)k * a.act_elems + img_off[s]);
 #pragma unroll
-          for (int ch = 0; ch < 4; ++ch) {
+          for (int j = 0; j < 2; ++j) {
             uint4 pk; __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[ch * 8 + 2 * e], v[ch * 8 + 2 * e + 1]);
-            if (!a.dbg_skip_stores) yrow[ch] = pk;
+            for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[j * 8 + 2 * e], v[j * 8 + 2 * e + 1]);
+            if (!a.dbg_skip_stores) yrow[j] = pk;
           }
         }
         {
-          float sq[32];
+          float sq[16];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
-          qsum = warp_col_sum(sq, lane);
+          for (int i = 0; i < 16; ++i) sq[i] = v[i] * v[i];
+          qsum += warp_col_sum16(sq, lane);
         }
-        ssum = warp_col_sum(v, lane);
+        ssum += warp_col_sum16(v, lane);       // lanes 2c, 2c+1: channel h*16 + c
       }
       if (tr) tr[2] = clock64();
-      red[(ew * 2 + 0) * C + lane] = ssum; red[(ew * 2 + 1) * C + lane] = qsum;
+      red[ew * 32 + (lane & 1) * 16 + (lane >> 1)] = (lane & 1) ? qsum : ssum;
       asm volatile("bar.sync 1, 512;" ::: "memory");
       // cross-CTA sum WITHOUT a partial matrix: every CTA adds its 2C per-channel sums as 64-bit fixed point (2^-32) into one
       // accumulator row per block.  Integer addition is associative, so the result is bit-identical whatever order the CTAs
       // arrive in; the grid barrier then only has to publish 2C numbers instead of gridDim.x rows.
       unsigned long long* acc = a.acc + (size_t)k * 2 * C;
       if (et < 2 * C) {
+        const int which = et >> 5, ch = et & 31;
         float t = 0.f;
 #pragma unroll
-        for (int w = 0; w < 16; ++w) t += red[w * 2 * C + et];      // fixed order over the 16 epilogue warps
+        for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];   // fixed order over the 8 warps of the half
         atomicAdd(acc + et, (unsigned long long)__double2ll_rn((double)t * 4294967296.0));
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[3] = clock64();
-      if (et == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
-      if (tr) tr[4] = clock64();
-      asm volatile("bar.sync 1, 512;" ::: "memory");
-      if (et < 2 * C) dsum2[et] = (double)(long long)__ldcg(acc + et) * (1.0 / 4294967296.0);
-      asm volatile("bar.sync 1, 512;" ::: "memory");
-      if (et < C) {
-        const double S = dsum2[et], Q = dsum2[C + et];
-        const double inv_count = a.inv_count;
-        const double mean = S * inv_count;
-        double var = Q * inv_count - mean * mean;
+      // the warp that polls the grid barrier also derives the coefficients (32 lanes = 32 channels: ONE warp's worth of the slow
+      // fp64 pipe) and publishes them with the only CTA-wide barrier after the grid barrier
+      if (ew == 0) {
+        if (lane == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
+        __syncwarp();
+        if (tr) tr[4] = clock64();
+        const double S = (double)(long long)__ldcg(acc + lane) * (1.0 / 4294967296.0);
+        const double Q = (double)(long long)__ldcg(acc + C + lane) * (1.0 / 4294967296.0);
+        const double mean = S * a.inv_count;
+        double var = Q * a.inv_count - mean * mean;
         if (var < 0.0) var = 0.0;
         const float invstd = fast_invstd(var + (double)NRD_BN_EPS);
         const float sc = gamma_r * invstd, sh = beta_r - (float)mean * sc;
-        ss_sm[et] = sc; ss_sm[C + et] = sh;
+        ss_sm[lane] = sc; ss_sm[C + lane] = sh;
         if (blockIdx.x == 0) {
-          a.saved[(size_t)k * 2 * C + et] = (float)mean; a.saved[(size_t)k * 2 * C + C + et] = invstd;
-          a.scale_shift[(size_t)k * 2 * C + et] = sc; a.scale_shift[(size_t)k * 2 * C + C + et] = sh;
+          a.saved[(size_t)k * 2 * C + lane] = (float)mean; a.saved[(size_t)k * 2 * C + C + lane] = invstd;
+          a.scale_shift[(size_t)k * 2 * C + lane] = sc; a.scale_shift[(size_t)k * 2 * C + C + lane] = sh;
           const double unbiased = var * a.unbias;
-          a.running[et] = (1.f - NRD_BN_MOMENTUM) * a.running[et] + NRD_BN_MOMENTUM * (float)mean;
-          a.running[C + et] = (1.f - NRD_BN_MOMENTUM) * a.running[C + et] + NRD_BN_MOMENTUM * (float)unbiased;
-          if (et == 0) *a.nbt += 1;
+          a.running[lane] = (1.f - NRD_BN_MOMENTUM) * a.running[lane] + NRD_BN_MOMENTUM * (float)mean;
+          a.running[C + lane] = (1.f - NRD_BN_MOMENTUM) * a.running[C + lane] + NRD_BN_MOMENTUM * (float)unbiased;
+          if (lane == 0) *a.nbt += 1;
         }
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[5] = clock64();
       // ---- pass 2: x_{k+1} = relu(bn(y_k)) + x_k -> the three operand copies in shared memory, then global ----
-      if (active) {
-        if (k == 0) mbar_wait(xfull(s), 0);      // the TMA-written x_0 copy is read below (residual) by this thread itself
-        uint4 xo[4];
-        float v[32];
-        tmem_ld32(my_tmem, v);
+      uint4 xo[2][2];
 #pragma unroll
-        for (int ch = 0; ch < 4; ++ch) {
+      for (int s = 0; s < 2; ++s) {
+        if (s >= nslots) break;
+        if (k == 0) mbar_wait(xfull(s), 0);      // the TMA-written x_0 copy is read below (residual) by this thread itself
+        uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
+        float v[16];
+        tmem_ld16(my_tmem + s * 2 * C, v);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
           // residual x_k from the centre copy (kx = 1); 16-B chunk ch of pixel P sits at chunk ch ^ ((P>>1)&3) (SWIZZLE_64B)
+          const int ch = h * 2 + j;
           const uint4 xk = *reinterpret_cast<const uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4));
           const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xk);
-          __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&xo[ch]);
+          __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&xo[s][j]);
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const int c = ch * 8 + 2 * e;
+            const int c = j * 8 + 2 * e;
             const float2 yr = __bfloat1622float2(__floats2bfloat162_rn(v[c], v[c + 1]));   // BN sees the STORED y (as backward will)
             const float2 xr = __bfloat1622float2(xh[e]);
-            const float2 sc2 = *reinterpret_cast<const float2*>(ss_sm + c), sh2 = *reinterpret_cast<const float2*>(ss_sm + C + c);
+            const float2 sc2 = *reinterpret_cast<const float2*>(ss_w + c), sh2 = *reinterpret_cast<const float2*>(ss_w + C + c);
             oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, sc2.x, sh2.x), 0.f) + xr.x, fmaxf(fmaf(yr.y, sc2.y, sh2.y), 0.f) + xr.y);
           }
           if (k + 1 < a.NB) {
-            const uint4 ok = xo[ch];
+            const uint4 ok = xo[s][j];
             *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
             if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
             if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
           }
         }
-        // TMEM reads and shared-memory operand writes of this thread are done: release the slot to the MMA warp
+        // TMEM reads and shared-memory operand writes of this thread for slot s are done: release the slot to the MMA warp
         tc_fence_before();
         fence_proxy_async();
         mbar_arrive(opready(s));
-        // x_{k+1} -> global (saved for backward) while the next block's MMAs already run
-        uint4* xrow = reinterpret_cast<uint4*>(a.xs + (size_t)(k + 1) * a.act_elems + gp);
+      }
+      // x_{k+1} -> global (saved for backward) while the next block's MMAs already run
 #pragma unroll
-        for (int ch = 0; ch < 4; ++ch) if (!a.dbg_skip_stores) xrow[ch] = xo[ch];
+      for (int s = 0; s < 2; ++s) {
+        if (s >= nslots) break;
+        uint4* xrow = reinterpret_cast<uint4*>(a.xs + (size_t)(k + 1) * a.act_elems + img_off[s]);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) if (!a.dbg_skip_stores) xrow[j] = xo[s][j];
       }
       if (tr) tr[6] = clock64();
     }

@@ -42,8 +42,10 @@ def train_loop(model, train_loader, rank, epochs=99, lr=1e-2, save=True, log=pri
             if step is None:
                 from .graph import TrainStep
                 step = TrainStep(model, train_loader.batch_size, lr=lr)
+            host_sum = 0.0
             for loss in step.iterate(train_loader):        # main.py:31-41
-                loss_train += loss.to(loss_train.device)
+                host_sum += float(loss)                    # main.py:41: the loss is already on the host
+            loss_train += host_sum
         for imgs, labels in (() if graph else train_loader):
             imgs, labels = imgs.to(rank), labels.to(rank)  # main.py:33
             outputs = model(imgs)                          # main.py:34

@@ -207,6 +207,15 @@ def test_dropin_train_loop_runs_and_full_size_properties():
     loader = nrd.SyntheticCifar10Loader(batch_size=64, steps_per_epoch=4, device=DEV)
     hist = nrd.main_no_ddp.training_loop(m, loader, epochs=2, lr=1e-3, log=lambda *_: None)
     assert len(hist) == 2 and all(np.isfinite(hist))
+    # main.train_loop: the captured-graph loop gives the eager loop's numbers
+    hs = []
+    for graph in (False, True):
+        torch.manual_seed(5)
+        mm = nrd.NetResDeep().to(DEV)
+        loader = nrd.SyntheticCifar10Loader(batch_size=64, steps_per_epoch=3, device=DEV)
+        hs.append((nrd.main.train_loop(mm, loader, 0, epochs=2, lr=1e-2, save=False, log=lambda *_: None, graph=graph),
+                   mm.engine.flat_params.clone()))
+    assert np.allclose(hs[0][0], hs[1][0], rtol=1e-6) and torch.equal(hs[0][1], hs[1][1])
     for dtype in ("fp32", "bf16"):
         res = []
         for _ in range(2):
