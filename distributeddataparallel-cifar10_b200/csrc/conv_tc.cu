@@ -342,7 +342,8 @@ struct PersistFwdArgs {
 };
 
 __global__ void __launch_bounds__(576, 1)
-k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmW, PersistFwdArgs a) {
+k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmXst,
+                 const __grid_constant__ CUtensorMap tmYst, PersistFwdArgs a) {
   constexpr int C = 32;
   using K = Cfg<C>;
   extern __shared__ uint8_t smem_raw[];
@@ -351,14 +352,18 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   constexpr int SLOT_BYTES = 3 * K::BUF_BYTES;                    // 55,296 B: three kx-copies of one image
   const uint32_t a_smem = base;                                   // 2 image slots
   const uint32_t w_smem = a_smem + 2 * SLOT_BYTES;               // 9 taps
-  const uint32_t bar0 = w_smem + 9 * K::WTAP_BYTES;
+  constexpr int YST_BYTES = NRD_PIX * C * 2;                      // 16,384 B: y_k of one image, staged for its TMA store
+  const uint32_t y_smem = w_smem + 9 * K::WTAP_BYTES;             // 2 image slots (1024-B aligned)
+  const uint32_t bar0 = y_smem + 2 * YST_BYTES;
   const uint32_t wfull = bar0;
   auto xfull = [&](int s) { return bar0 + 8u * (1 + s); };
   auto opready = [&](int s) { return bar0 + 8u * (3 + s); };
   auto tfull = [&](int s, int m) { return bar0 + 8u * (5 + s * 2 + m); };
   const uint32_t tmem_slot = bar0 + 8u * 9;
-  constexpr int BAR_BYTES = 8 * 10;
-  constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
+  auto yready = [&](int s) { return bar0 + 8u * (10 + s); };
+  const uint32_t yfree = bar0 + 8u * 12, xfree = bar0 + 8u * 13;
+  constexpr int BAR_BYTES = 8 * 14;
+  constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + 2 * YST_BYTES + BAR_BYTES;
   float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][sum | sum of squares][16 channels]
   float* ss_sm = red + 1024;                                             // [2C] scale | shift of the current block
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
@@ -371,7 +376,11 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX0); tma_prefetch_desc(&tmW);
     mbar_init(wfull, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(xfull(s), 1); mbar_init(opready(s), 512); mbar_init(tfull(s, 0), 1); mbar_init(tfull(s, 1), 1); }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(xfull(s), 1); mbar_init(opready(s), 512); mbar_init(tfull(s, 0), 1); mbar_init(tfull(s, 1), 1); mbar_init(yready(s), 512);
+    }
+    mbar_init(yfree, 1); mbar_init(xfree, 1);
+    tma_prefetch_desc(&tmXst); tma_prefetch_desc(&tmYst);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -389,6 +398,24 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         for (int kx = 0; kx < 3; ++kx)
           tma_load_4d(a_smem + s * SLOT_BYTES + kx * K::BUF_BYTES, &tmX0, xfull(s), 0, kx - 1, -1, s == 0 ? img0 : img1);
       }
+      // ... then this thread is the store engine: y_k from its staging tile and x_{k+1} from the CENTRE operand copy (the same
+      // swizzled bytes the tensor map expects) go to global memory as two bulk tensor stores per image, instead of eight
+      // 16-byte stores per thread
+      for (int k = 0; k < a.NB; ++k) {
+        for (int s = 0; s < nslots; ++s) {
+          mbar_wait(yready(s), (uint32_t)(k & 1));
+          if (!a.dbg_skip_stores) tma_store_5d(&tmYst, y_smem + s * YST_BYTES, 0, 0, 0, s == 0 ? img0 : img1, k);
+        }
+        bulk_commit(); bulk_wait_read0();
+        mbar_arrive(yfree);
+        for (int s = 0; s < nslots; ++s) {
+          mbar_wait(opready(s), (uint32_t)(k & 1));
+          if (!a.dbg_skip_stores) tma_store_5d(&tmXst, a_smem + s * SLOT_BYTES + K::BUF_BYTES + K::IMGROW_BYTES, 0, 0, 0, s == 0 ? img0 : img1, k + 1);
+        }
+        bulk_commit(); bulk_wait_read0();
+        mbar_arrive(xfree);
+      }
+      bulk_wait0();
     }
   } else if (warp == 1) {
     if (lane == 0) {
@@ -420,9 +447,8 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     // ===== image slot 0 and then of slot 1: slot 0's operands are ready (and its MMAs run) while slot 1 is still in pass 2 =====
     const int ew = warp - 2, h = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
     const int p = q * 32 + lane, pi = m * 8 + (p >> 4), pj = p & 15;
-    const size_t pix_off = (size_t)(pi * 16 + pj) * C + h * 16;                // this thread's 16 channels inside an image
-    const size_t img_off[2] = {(size_t)img0 * NRD_PIX * C + pix_off, (size_t)img1 * NRD_PIX * C + pix_off};
     const int P1 = (pi + 1) * 16 + pj;                                         // its index inside an operand copy (row-haloed)
+    const int P0y = pi * 16 + pj;                                              // ... and inside the y staging tile
     const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
     const float* ss_w = ss_sm + h * 16;                                        // this thread's channels: scale at [c], shift at [C + c]
     unsigned long long gbar_target = 0;
@@ -442,15 +468,18 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         float v[16];
         tmem_ld16(my_tmem + s * 2 * C, v);
         {
-          // y_k does not depend on the statistics: store it now, off the post-barrier critical path
-          uint4* yrow = reinterpret_cast<uint4*>(a.ys + (size_t)k * a.act_elems + img_off[s]);
+          // y_k (bf16) into the staging tile, swizzled as the tensor map expects; the store thread sends it off
+          if (s == 0 && k > 0) mbar_wait(yfree, (uint32_t)((k - 1) & 1));     // block k-1's y stores have read the tiles
+          uint8_t* yst = gen_base + (y_smem - base) + s * YST_BYTES;
 #pragma unroll
           for (int j = 0; j < 2; ++j) {
             uint4 pk; __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
 #pragma unroll
             for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[j * 8 + 2 * e], v[j * 8 + 2 * e + 1]);
-            if (!a.dbg_skip_stores) yrow[j] = pk;
+            *reinterpret_cast<uint4*>(yst + P0y * 64 + (((h * 2 + j) ^ ((P0y >> 1) & 3)) << 4)) = pk;
           }
+          fence_proxy_async();
+          mbar_arrive(yready(s));
         }
         {
           float sq[16];
@@ -502,7 +531,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[5] = clock64();
       // ---- pass 2: x_{k+1} = relu(bn(y_k)) + x_k -> the three operand copies in shared memory, then global ----
-      uint4 xo[2][2];
+      if (k > 0) mbar_wait(xfree, (uint32_t)((k - 1) & 1));       // block k-1's x stores have read the centre copies
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         if (s >= nslots) break;
@@ -516,7 +545,8 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
           const int ch = h * 2 + j;
           const uint4 xk = *reinterpret_cast<const uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4));
           const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xk);
-          __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&xo[s][j]);
+          uint4 ok;
+          __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const int c = j * 8 + 2 * e;
@@ -525,25 +555,17 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
             const float2 sc2 = *reinterpret_cast<const float2*>(ss_w + c), sh2 = *reinterpret_cast<const float2*>(ss_w + C + c);
             oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, sc2.x, sh2.x), 0.f) + xr.x, fmaxf(fmaf(yr.y, sc2.y, sh2.y), 0.f) + xr.y);
           }
+          *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;   // also the store's source
           if (k + 1 < a.NB) {
-            const uint4 ok = xo[s][j];
-            *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
             if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
             if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
           }
         }
         // TMEM reads and shared-memory operand writes of this thread for slot s are done: release the slot to the MMA warp
+        // (and the centre copy to the store thread)
         tc_fence_before();
         fence_proxy_async();
         mbar_arrive(opready(s));
-      }
-      // x_{k+1} -> global (saved for backward) while the next block's MMAs already run
-#pragma unroll
-      for (int s = 0; s < 2; ++s) {
-        if (s >= nslots) break;
-        uint4* xrow = reinterpret_cast<uint4*>(a.xs + (size_t)(k + 1) * a.act_elems + img_off[s]);
-#pragma unroll
-        for (int j = 0; j < 2; ++j) if (!a.dbg_skip_stores) xrow[j] = xo[s][j];
       }
       if (tr) tr[6] = clock64();
     }
@@ -1055,7 +1077,7 @@ template <int C> constexpr size_t wgrad_smem() {
 }
 
 constexpr size_t persist_smem() {
-  return 1024 + 2 * 3 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 80 + (1024 + 64) * sizeof(float) + (2048 + 256) * sizeof(double) + 64;
+  return 1024 + 2 * 3 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 2 * NRD_PIX * 32 * 2 + 112 + (1024 + 64) * sizeof(float) + 64;
 }
 
 constexpr size_t persist_bwd_smem() {
@@ -1109,6 +1131,15 @@ int nrd_tc_plan_init(nrd_plan* p) {
     CUresult r = enc(&p->tm_xall, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, p->xs, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { nrd_set_error("cuTensorMapEncodeTiled(x stack) failed: %d", (int)r); return NRD_ECUDA; }
+    // store maps of the persistent forward: one whole image {C, 16, 16} of x_k / y_k per bulk tensor store
+    cuuint32_t sbox[5] = {32, 16, 16, 1, 1};
+    r = enc(&p->tm_xst, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, p->xs, dims, strides, sbox, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { nrd_set_error("cuTensorMapEncodeTiled(x store) failed: %d", (int)r); return NRD_ECUDA; }
+    cuuint64_t ydims[5] = {32, 16, 16, (cuuint64_t)p->B, (cuuint64_t)p->NB};
+    r = enc(&p->tm_yst, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, p->ys, ydims, strides, sbox, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { nrd_set_error("cuTensorMapEncodeTiled(y store) failed: %d", (int)r); return NRD_ECUDA; }
   }
   p->tc_ready = 1;
   return NRD_OK;
@@ -1171,7 +1202,7 @@ int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st) {
   NRD_CHECK_CUDA(cudaMemsetAsync(p->bn_acc, 0, (size_t)p->NB * 2 * p->C * sizeof(unsigned long long), st));
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace; a.dbg_skip_stores = p->dbg_skip_stores;
   a.inv_count = 1.0 / ((double)p->B * NRD_PIX); a.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
-  void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&a};
+  void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_smem(), st));
   nrd_count_launch();
   return NRD_OK;

@@ -85,6 +85,7 @@ struct nrd_plan {
   CUtensorMap tm_dy0;     // dy scratch, plain rows (wgrad)
   CUtensorMap tm_wf, tm_wd;
   CUtensorMap tm_xall;    // all x_k as one 5-D tensor (persistent backward)
+  CUtensorMap tm_xst, tm_yst; // x_k / y_k stacks, whole-image boxes: bulk tensor STORES of the persistent forward
   int tc_ready;
   int reserve_sms;        // option: SMs the cooperative kernels leave free (a concurrent NCCL kernel needs somewhere to run)
   float* bn_sync;         // optional [2C] slot in front of the gradient vector: BN running stats ride the body bucket's all-reduce
