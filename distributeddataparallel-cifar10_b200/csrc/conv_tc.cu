@@ -519,7 +519,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         const float invstd = fast_invstd(var + (double)NRD_BN_EPS);
         const float sc = gamma_r * invstd, sh = beta_r - (float)mean * sc;
         ss_sm[lane] = sc; ss_sm[C + lane] = sh;
-        if (blockIdx.x == 0) {
+        if (blockIdx.x == gridDim.x - 1) {      // the last CTA has the fewest images: the bookkeeping is off the grid's critical path
           a.saved[(size_t)k * 2 * C + lane] = (float)mean; a.saved[(size_t)k * 2 * C + C + lane] = invstd;
           a.scale_shift[(size_t)k * 2 * C + lane] = sc; a.scale_shift[(size_t)k * 2 * C + C + lane] = sh;
           const double unbiased = var * a.unbias;
@@ -653,7 +653,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     tma_prefetch_desc(&tmXall); tma_prefetch_desc(&tmWd);
     mbar_init(wfull, 1); mbar_init(wdone, 1); mbar_init(epi_idle, 1);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(xready(s), 1); mbar_init(dyready(s), 256); mbar_init(wfree(s), 1);
+      mbar_init(xready(s), 1); mbar_init(dyready(s), 512); mbar_init(wfree(s), 1);
       mbar_init(dxfull(s, 0), 1); mbar_init(dxfull(s, 1), 1);
     }
     fence_barrier_init();
@@ -682,7 +682,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     if (lane == 0) {
       // ===== MMA issuer =====
       constexpr uint32_t idesc_d = make_idesc(128, C, 0, 0);      // dgrad: both K-major
-      constexpr uint32_t idesc_w = make_idesc(128, C, 1, 1);      // wgrad: both MN-major
+      constexpr uint32_t idesc_w = make_idesc(128, 3 * C, 1, 1);  // wgrad: both MN-major, N = three kx taps x C
       mbar_wait(wfull, 0);
       for (int it = 0; it < a.NB; ++it) {
         for (int s = 0; s < nslots; ++s) {
@@ -706,14 +706,12 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
           mbar_wait(xready(s), (uint32_t)(it & 1));
           tc_fence_after();
           const uint32_t sb = a_smem + s * SLOT_BYTES;
-          for (int yy = 0; yy < 16; ++yy) {              // K step = image row yy = 16 pixels
-            const uint64_t bd = make_sdesc(sb + DY_BYTES + (yy + 1) * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
-#pragma unroll
-            for (int kxb = 0; kxb < 3; ++kxb) {
-              // accumulator rows (j, co): dy copy kxb, buffer rows yy + j  <=>  tap (ky, kx) = (2 - j, 2 - kxb); j = 3 is junk
-              const uint64_t ad = make_sdesc(sb + kxb * K::BUF_BYTES + yy * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
-              umma_bf16(tmem_base + ACCW + kxb * C, ad, bd, idesc_w, (it > 0 || s > 0 || yy > 0) ? 1u : 0u);
-            }
+          for (int yy = 0; yy < 16; ++yy) {              // K step = image row yy = 16 pixels; ONE MMA per row
+            // A (MN-major): x_k rows yy .. yy+3 of the row-haloed tile stacked along M = (j, ci): vertical tap ky = j (j = 3 junk)
+            // B (MN-major): row yy of the three kx-shifted dy copies stacked along N = (kxb, co): horizontal tap kx = 2 - kxb
+            const uint64_t ad = make_sdesc(sb + DY_BYTES + yy * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
+            const uint64_t bd = make_sdesc(sb + (yy + 1) * K::IMGROW_BYTES, K::BUF_BYTES, K::SBO, K::LAYOUT);
+            umma_bf16(tmem_base + ACCW, ad, bd, idesc_w, (it > 0 || s > 0 || yy > 0) ? 1u : 0u);
           }
           umma_commit(wfree(s));
         }
@@ -721,185 +719,194 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       umma_commit(wdone);
     }
   } else {
-    // ===== epilogue: 16 warps; warp = (image slot s, tile m of that image, TMEM lane quarter q); thread = one pixel =====
-    const int ew = warp - 2, s = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
-    const bool active = s < nslots;
-    const int img = (s == 0) ? img0 : img1;
-    uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
+    // ===== epilogue: 16 warps; warp = (channel half h, tile m, TMEM lane quarter q); thread = one pixel x 16 channels, of =====
+    // ===== image slot 0 and then of slot 1 (slot 0's dgrad MMAs run while slot 1's dy is still being written) =====
+    const int ew = warp - 2, h = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
     const int p = q * 32 + lane, pi = m * 8 + (p >> 4), pj = p & 15;
-    const size_t gp = ((size_t)img * NRD_PIX + pi * 16 + pj) * C;             // this thread's pixel
+    const size_t pix_off = (size_t)(pi * 16 + pj) * C + h * 16;               // this thread's 16 channels inside an image
     const int P1 = (pi + 1) * 16 + pj;                                         // its index inside an operand copy (row-haloed)
-    const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + (s * 2 + m) * C;
+    const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
     unsigned long long gbar_target = 0;
     if (et == 0) gbar_target = nrd_grid_barrier_base(a.gbar, gridDim.x);
-    uint32_t gpk[16];                                 // dL/d(out) of this thread's pixel, bf16 pairs
+    uint32_t gpk[2][8];                               // dL/d(out) of this thread's pixel and channels, per image slot, bf16 pairs
 #pragma unroll
-    for (int ch = 0; ch < 4; ++ch) {
-      uint4 v = active ? reinterpret_cast<const uint4*>(a.g_in + gp)[ch] : make_uint4(0, 0, 0, 0);
-      gpk[ch * 4 + 0] = v.x; gpk[ch * 4 + 1] = v.y; gpk[ch * 4 + 2] = v.z; gpk[ch * 4 + 3] = v.w;
+    for (int s = 0; s < 2; ++s) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (s < nslots) v = reinterpret_cast<const uint4*>(a.g_in + (size_t)(s == 0 ? img0 : img1) * NRD_PIX * C + pix_off)[j];
+        gpk[s][j * 4 + 0] = v.x; gpk[s][j * 4 + 1] = v.y; gpk[s][j * 4 + 2] = v.z; gpk[s][j * 4 + 3] = v.w;
+      }
     }
-    float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, et < C: running dgamma / dbeta over the blocks
-    // y_k of this thread's pixel: prefetched one block ahead with cp.async into this thread's own shared-memory slots
+    float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, warp ew == 0 (lane = channel): running dgamma / dbeta over the blocks
+    // y_k of this thread's pixel: prefetched one block ahead with cp.async into this thread's own shared-memory slots,
+    // one commit group per image slot
     const uint32_t ybuf_s = smem_u32(ybuf);
     auto load_y = [&](int k) {
-      const bf16* yk = a.ys + (size_t)k * a.act_elems;
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ybuf_s + (uint32_t)((ch * 512 + et) * 16)),
-                     "l"(reinterpret_cast<const uint4*>(yk + gp) + ch) : "memory");
-      asm volatile("cp.async.commit_group;" ::: "memory");
+      for (int s = 0; s < 2; ++s) {
+        if (s < nslots) {
+          const bf16* yk = a.ys + (size_t)k * a.act_elems + (size_t)(s == 0 ? img0 : img1) * NRD_PIX * C + pix_off;
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ybuf_s + (uint32_t)(((s * 2 + j) * 512 + et) * 16)),
+                         "l"(reinterpret_cast<const uint4*>(yk) + j) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+      }
     };
-    // y of 8 channels (chunk ch) of this thread's pixel: one conflict-free LDS.128 from the thread's own slots
-    auto y_chunk = [&](int ch) -> uint4 { return ybuf[ch * 512 + et]; };
-    if (active) load_y(a.NB - 1);
-    auto write_ssp = [&](int it2) {                  // scale/shift pairs of block NB-1-it2 -> buffer it2 & 1 (threads et < C)
+    // y of 8 channels (chunk j of slot s) of this thread's pixel: one conflict-free LDS.128 from the thread's own slots
+    auto y_chunk = [&](int s, int j) -> uint4 { return ybuf[(s * 2 + j) * 512 + et]; };
+    load_y(a.NB - 1);
+    auto write_ssp = [&](int it2) {                  // scale/shift pairs of block NB-1-it2 -> buffer it2 & 1 (warp ew == 0, lane = channel)
       const int k2 = a.NB - 1 - it2;
-      float* d = bnp2 + (it2 & 1) * 64 + (et >> 1) * 4 + (et & 1) * 2;
-      d[0] = a.scale_shift[(size_t)k2 * 2 * C + et]; d[1] = a.scale_shift[(size_t)k2 * 2 * C + C + et];
+      float* d = bnp2 + (it2 & 1) * 64 + (lane >> 1) * 4 + (lane & 1) * 2;
+      d[0] = a.scale_shift[(size_t)k2 * 2 * C + lane]; d[1] = a.scale_shift[(size_t)k2 * 2 * C + C + lane];
     };
-    if (et < C) write_ssp(0);
-    const float gamma_r = (et < C) ? a.gamma[et] : 0.f;
+    if (ew == 0) write_ssp(0);
+    const float gamma_r = a.gamma[lane];
     asm volatile("bar.sync 1, 512;" ::: "memory");
+    float4* cfp = reinterpret_cast<float4*>(bnp2 + 128);   // per channel pair: {A1, A2, A3, -, A1', A2', A3', -}, dy = dz*A1 + y*A2 + A3
+    float s1 = 0.f, s2 = 0.f;                              // lanes 2c, 2c+1: sums of dz / dz*y over this warp's pixels, channel 16h + c
+    // ---- phase A of block it for image slot s: per-channel sums of dz and dz*y over this warp's 32 pixels ----
+    auto phase_a = [&](int s, int it) {
+      const float4* ssp = reinterpret_cast<const float4*>(bnp2 + (it & 1) * 64);
+      float t1[16], t2[16];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const uint4 yv = y_chunk(s, j);
+        const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = j * 8 + 2 * e;
+          const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&yw[e]));
+          const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[s][j * 4 + e]));
+          const float4 ss = ssp[h * 8 + j * 4 + e];
+          const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
+          t1[i] = d0; t1[i + 1] = d1; t2[i] = d0 * y2.x; t2[i + 1] = d1 * y2.y;
+        }
+      }
+      s1 += warp_col_sum16(t1, lane);
+      s2 += warp_col_sum16(t2, lane);
+    };
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    phase_a(0, 0);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (nslots > 1) phase_a(1, 0);
     for (int it = 0; it < a.NB; ++it) {
       const int k = a.NB - 1 - it;
       long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + it) * 16 : nullptr;
-      if (tr) tr[0] = clock64();
-      // per channel pair e (channels 2e, 2e+1): ssp[e] = {scale, shift, scale', shift'} (double-buffered: a slower thread may
-      // still be in phase B of the previous block); cfp[e] = {A1, A2, A3, -, A1', A2', A3', -} with dy = dz*A1 + y*A2 + A3
-      float4* ssp = reinterpret_cast<float4*>(bnp2 + (it & 1) * 64);
-      float4* cfp = reinterpret_cast<float4*>(bnp2 + 128);
-      // no CTA barrier here: ssp for this block was written one block ahead (below, after the grid barrier), y comes from this
-      // thread's own cp.async slots, so the warps of the first image start phase A while the second image's dgrad still runs
+      if (tr) { const long long t = clock64(); tr[0] = t; tr[7] = t; tr[1] = t; for (int i = 8; i < 14; ++i) tr[i] = t; }
       // saved statistics of this block for the combine below: fetched now, far ahead of their use on the critical path
-      const float mean_r = (et < C) ? a.saved[(size_t)k * 2 * C + et] : 0.f, is_r = (et < C) ? a.saved[(size_t)k * 2 * C + C + et] : 0.f;
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-      if (tr) tr[7] = clock64();
-      // ---- phase A: per-channel sums of dz and dz*y over this warp's 32 pixels ----
-      float s1[2] = {0.f, 0.f}, s2[2] = {0.f, 0.f};          // per 16-channel half: lanes 2c, 2c+1 hold channel 16*half + c
-      if (active) {
-#pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {
-          float t1[16], t2[16];
-#pragma unroll
-          for (int c2 = 0; c2 < 2; ++c2) {
-            const uint4 yv = y_chunk(hf * 2 + c2);
-            const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int pe = (hf * 2 + c2) * 4 + e, i = c2 * 8 + 2 * e;
-              const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&yw[e]));
-              const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[pe]));
-              const float4 ss = ssp[pe];
-              const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
-              t1[i] = d0; t1[i + 1] = d1; t2[i] = d0 * y2.x; t2[i + 1] = d1 * y2.y;
-            }
-          }
-          if (tr) tr[8 + hf * 3] = clock64();
-          s1[hf] = warp_col_sum16(t1, lane);
-          if (tr) tr[9 + hf * 3] = clock64();
-          s2[hf] = warp_col_sum16(t2, lane);
-          if (tr) tr[10 + hf * 3] = clock64();
-        }
-      }
-      if (tr) tr[1] = clock64();
-      if ((lane & 1) == 0) {
-        const int c = lane >> 1;
-        red[(ew * 2 + 0) * C + c] = s1[0]; red[(ew * 2 + 0) * C + 16 + c] = s1[1];
-        red[(ew * 2 + 1) * C + c] = s2[0]; red[(ew * 2 + 1) * C + 16 + c] = s2[1];
-      }
+      const float mean_r = (ew == 0) ? a.saved[(size_t)k * 2 * C + lane] : 0.f, is_r = (ew == 0) ? a.saved[(size_t)k * 2 * C + C + lane] : 0.f;
+      red[ew * 32 + (lane & 1) * 16 + (lane >> 1)] = (lane & 1) ? s2 : s1;
+      s1 = 0.f; s2 = 0.f;
       asm volatile("bar.sync 1, 512;" ::: "memory");
       // cross-CTA sum as 64-bit fixed point (2^-40) atomics into one accumulator row per block: order-independent, bit-exact
       unsigned long long* acc = a.acc + (size_t)it * 2 * C;
       if (et < 2 * C) {
+        const int which = et >> 5, ch = et & 31;
         float t = 0.f;
 #pragma unroll
-        for (int w = 0; w < 16; ++w) t += red[w * 2 * C + et];
+        for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
         atomicAdd(acc + et, (unsigned long long)__double2ll_rn((double)t * 1099511627776.0));
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[2] = clock64();
-      if (et == 0) {
-        gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target);
-      }
-      if (tr) tr[3] = clock64();
-      asm volatile("bar.sync 1, 512;" ::: "memory");
-      // every thread is past phase B of the previous block: its scale/shift buffer may now take the NEXT block's values
-      if (et < C && it + 1 < a.NB) write_ssp(it + 1);
-      if (et < 2 * C) dsum2[et] = (double)(long long)__ldcg(acc + et) * (1.0 / 1099511627776.0);
-      asm volatile("bar.sync 1, 512;" ::: "memory");
-      if (et < C) {
-        const double db = dsum2[et], dgy = dsum2[C + et];
+      // the warp that polls the grid barrier also derives the dy coefficients (lane = channel) and publishes them (and the NEXT
+      // block's scale/shift pairs: every thread is past phase B of the previous block) with the one CTA barrier that follows
+      if (ew == 0) {
+        if (lane == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
+        __syncwarp();
+        if (tr) tr[3] = clock64();
+        const double db = (double)(long long)__ldcg(acc + lane) * (1.0 / 1099511627776.0);
+        const double dgy = (double)(long long)__ldcg(acc + C + lane) * (1.0 / 1099511627776.0);
+        if (it + 1 < a.NB) write_ssp(it + 1);
         const double mean = (double)mean_r, is = (double)is_r;
         const double dg = is * (dgy - mean * db);       // sum dz*xhat = invstd * (sum dz*y - mean * sum dz)
         db_acc += (float)db; dg_acc += (float)dg;       // same order as the per-block path: k = NB-1 first
         const double a_ = (double)gamma_r * is, b_ = db * a.inv_count, c_ = dg * a.inv_count;
-        float* d = reinterpret_cast<float*>(cfp) + (et >> 1) * 8 + (et & 1) * 4;
+        float* d = reinterpret_cast<float*>(cfp) + (lane >> 1) * 8 + (lane & 1) * 4;
         d[0] = (float)a_; d[1] = (float)(-a_ * c_ * is); d[2] = (float)(a_ * c_ * is * mean - a_ * b_); d[3] = 0.f;
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[4] = clock64();
-      if (active) {
-        // ---- phase B: dy -> the three operand copies (once the previous block's MMAs no longer read them) ----
-        if (it > 0) mbar_wait(wfree(s), (uint32_t)((it - 1) & 1));
+      // ---- phase B: dy -> the three operand copies (once the previous block's wgrad MMAs no longer read them) ----
+      {
+        const float4* ssp = reinterpret_cast<const float4*>(bnp2 + (it & 1) * 64);
 #pragma unroll
-        for (int ch = 0; ch < 4; ++ch) {
-          uint4 ok;
-          __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
-          const uint4 yv = y_chunk(ch);
-          const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
+        for (int s = 0; s < 2; ++s) {
+          if (s >= nslots) break;
+          if (it > 0) mbar_wait(wfree(s), (uint32_t)((it - 1) & 1));
+          uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int pe = ch * 4 + e;
-            const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&yw[e]));
-            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[pe]));
-            const float4 ss = ssp[pe], c0 = cfp[pe * 2], c1 = cfp[pe * 2 + 1];
-            const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
-            oh[e] = __floats2bfloat162_rn(fmaf(d0, c0.x, fmaf(y2.x, c0.y, c0.z)), fmaf(d1, c1.x, fmaf(y2.y, c1.y, c1.z)));
+          for (int j = 0; j < 2; ++j) {
+            const int ch = h * 2 + j;
+            uint4 ok;
+            __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
+            const uint4 yv = y_chunk(s, j);
+            const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int pe = ch * 4 + e;
+              const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&yw[e]));
+              const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[s][j * 4 + e]));
+              const float4 ss = ssp[pe], c0 = cfp[pe * 2], c1 = cfp[pe * 2 + 1];
+              const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
+              oh[e] = __floats2bfloat162_rn(fmaf(d0, c0.x, fmaf(y2.x, c0.y, c0.z)), fmaf(d1, c1.x, fmaf(y2.y, c1.y, c1.z)));
+            }
+            *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
+            if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
+            if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
           }
-          *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
-          if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
-          if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
+          fence_proxy_async();
+          mbar_arrive(dyready(s));
         }
-        fence_proxy_async();
-        mbar_arrive(dyready(s));
-        if (tr) tr[5] = clock64();
-        if (k > 0 && !a.dbg_skip) load_y(k - 1);          // y_k is dead: fetch the next block's row while the dgrad MMAs run
-        // ---- phase C: dx_k = dgrad + g ----
+      }
+      if (tr) tr[5] = clock64();
+      if (k > 0 && !a.dbg_skip) load_y(k - 1);          // y_k is dead: fetch the next block's rows while the dgrad MMAs run
+      // ---- phase C: dx_k = dgrad + g, then straight on to phase A of the next block for the same image ----
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        if (s >= nslots) break;
         mbar_wait(dxfull(s, m), (uint32_t)(it & 1));
         tc_fence_after();
-        float v[32];
-        tmem_ld32(my_tmem, v);
+        float v[16];
+        tmem_ld16(my_tmem + s * 2 * C, v);
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[e]));
+        for (int e = 0; e < 8; ++e) {
+          const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gpk[s][e]));
           const __nv_bfloat162 o = __floats2bfloat162_rn(v[2 * e] + g2.x, v[2 * e + 1] + g2.y);
-          gpk[e] = *reinterpret_cast<const uint32_t*>(&o);
+          gpk[s][e] = *reinterpret_cast<const uint32_t*>(&o);
         }
-        if (k == 0) {
-#pragma unroll
-          for (int ch = 0; ch < 4; ++ch)
-            reinterpret_cast<uint4*>(a.dx0_out + gp)[ch] = make_uint4(gpk[ch * 4], gpk[ch * 4 + 1], gpk[ch * 4 + 2], gpk[ch * 4 + 3]);
-        }
-        if (tr) tr[6] = clock64();
         tc_fence_before();      // the accumulator is in registers: the next block's dgrad may overwrite it (ordered by dyready)
+        if (k == 0) {
+          uint4* dst = reinterpret_cast<uint4*>(a.dx0_out + (size_t)(s == 0 ? img0 : img1) * NRD_PIX * C + pix_off);
+#pragma unroll
+          for (int j = 0; j < 2; ++j) dst[j] = make_uint4(gpk[s][j * 4], gpk[s][j * 4 + 1], gpk[s][j * 4 + 2], gpk[s][j * 4 + 3]);
+        } else if (!a.dbg_skip) {
+          if (s == 0) asm volatile("cp.async.wait_group 1;" ::: "memory");
+          else asm volatile("cp.async.wait_group 0;" ::: "memory");
+          phase_a(s, it + 1);
+        }
       }
+      if (tr) tr[6] = clock64();
     }
-    if (blockIdx.x == 0 && et < C) { a.dgamma[et] = dg_acc; a.dbeta[et] = db_acc; }
-    // ---- weight-gradient partial of this CTA: accumulator rows (j, co), columns ci ----
-    if (s == 0 && m == 0) {
+    if (blockIdx.x == 0 && ew == 0) { a.dgamma[lane] = dg_acc; a.dbeta[lane] = db_acc; }
+    // ---- weight-gradient partial of this CTA: accumulator lanes (j, ci), columns (kxb, co) ----
+    if (h == 0 && m == 0) {
       mbar_wait(wdone, 0);
       tc_fence_after();
       float* outp = a.wpartial + (size_t)blockIdx.x * 9 * C * C;
-      const int jrow = q, co = lane;
+      const int j = q, ci = lane;
 #pragma unroll
       for (int kxb = 0; kxb < 3; ++kxb) {
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ACCW + kxb * C, v);
-        if (jrow < 3) {
-          const int tap = (2 - jrow) * 3 + (2 - kxb);
-          float4* dst = reinterpret_cast<float4*>(outp + ((size_t)tap * C + co) * C);      // [tap][co][ci]
+        if (j < 3) {
+          float* dst = outp + (size_t)(j * 3 + (2 - kxb)) * C * C + ci;                     // [tap = (ky, kx)][co][ci]
 #pragma unroll
-          for (int c4 = 0; c4 < 8; ++c4) dst[c4] = make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
+          for (int co = 0; co < 32; ++co) dst[co * C] = v[co];
         }
       }
     }
