@@ -39,6 +39,7 @@ _PROTOS = {
     "nrd_plan_tensor": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)]),
     "nrd_pack_weights": (i32, [vp, vp]),
     "nrd_forward": (i32, [vp, vp, vp, i32, vp]),
+    "nrd_forward_loss": (i32, [vp, vp, vp, f32, vp, vp, vp, vp, vp]),
     "nrd_cross_entropy": (i32, [vp, vp, i32, f32, vp, vp, vp, vp]),
     "nrd_cross_entropy_static": (i32, [vp, vp, i32, f32, vp, vp, vp]),
     "nrd_backward": (i32, [vp, vp, vp]),

@@ -595,7 +595,8 @@ struct PersistBwdArgs {
   const float* saved;         // [NB][2C] mean | invstd
   float* dgamma; float* dbeta;
   const bf16* ys;             // y_0 .. y_NB-1
-  const bf16* g_in;           // dL/dx_NB
+  const bf16* g_pool;         // dL/d(pooled) [B,8,8,C], expanded through pool-2's argmax while loading (dL/dx_NB never exists)
+  const uint8_t* idx2;        // pool-2 argmax [B,8,8,C] (position 0..3 inside the 2x2 window)
   bf16* dx0_out;              // dL/dx_0
   unsigned long long* acc;    // [NB][2C] 64-bit fixed-point accumulators, zeroed before the launch
   float* wpartial;            // [gridDim.x][9][C][C]
@@ -734,7 +735,24 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         uint4 v = make_uint4(0, 0, 0, 0);
-        if (s < nslots) v = reinterpret_cast<const uint4*>(a.g_in + (size_t)(s == 0 ? img0 : img1) * NRD_PIX * C + pix_off)[j];
+        if (s < nslots) {
+          {
+            // max-pool backward on the fly: the pooled gradient goes to the window position the forward picked
+            const size_t po = ((size_t)(s == 0 ? img0 : img1) * 64 + (pi >> 1) * 8 + (pj >> 1)) * C + h * 16 + j * 8;
+            const uint4 gp4 = *reinterpret_cast<const uint4*>(a.g_pool + po);
+            const uint2 id = *reinterpret_cast<const uint2*>(a.idx2 + po);
+            const uint32_t sel = (uint32_t)((pi & 1) * 2 + (pj & 1));
+            const uint32_t gw[4] = {gp4.x, gp4.y, gp4.z, gp4.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t ib = (e < 2 ? id.x : id.y) >> ((e & 1) * 16);
+              const uint32_t lo = ((ib & 0xffu) == sel) ? 0x0000ffffu : 0u, hi = (((ib >> 8) & 0xffu) == sel) ? 0xffff0000u : 0u;
+              o[e] = gw[e] & (lo | hi);
+            }
+            v = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+        }
         gpk[s][j * 4 + 0] = v.x; gpk[s][j * 4 + 1] = v.y; gpk[s][j * 4 + 2] = v.z; gpk[s][j * 4 + 3] = v.w;
       }
     }
@@ -1217,12 +1235,12 @@ int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st) {
 
 // all NB residual blocks of the backward in ONE cooperative launch: g_in = dL/dx_NB -> dx0_out = dL/dx_0, dgamma, dbeta,
 // per-CTA weight-gradient partials (reduced by k_wgrad_reduce)
-int nrd_tc_backward_blocks(nrd_plan* p, const void* g_in, void* dx0_out, cudaStream_t st) {
+int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cudaStream_t st) {
   NRD_REQUIRE(p->tc_ready && p->tc_persist_fwd, "persistent block-stack backward not available for this plan");
   PersistBwdArgs a;
   a.gamma = p->params + p->off[3]; a.scale_shift = p->scale_shift; a.saved = p->saved_stats;
   a.dgamma = p->grads + p->off[3]; a.dbeta = p->grads + p->off[4];
-  a.ys = (const bf16*)p->ys; a.g_in = (const bf16*)g_in; a.dx0_out = (bf16*)dx0_out;
+  a.ys = (const bf16*)p->ys; a.g_pool = (const bf16*)g_pooled; a.idx2 = p->idx2; a.dx0_out = (bf16*)dx0_out;
   a.acc = p->bn_acc + (size_t)32 * 2 * 64; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
   NRD_CHECK_CUDA(cudaMemsetAsync(a.acc, 0, (size_t)p->NB * 2 * p->C * sizeof(unsigned long long), st));
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.dbg_skip = p->dbg_skip_stores; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);

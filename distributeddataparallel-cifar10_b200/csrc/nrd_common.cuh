@@ -52,6 +52,7 @@ struct nrd_plan {
   int64_t* nbt;
   int64_t off[10];
   const float* images_last;  // images of the last nrd_forward (stem backward reads them)
+  const char* dx0_last;      // dL/dx_0 of the last nrd_backward_body (which of the two dx scratch buffers holds it)
   // workspace carve-up
   char* xs;            // (NB+1) saved block inputs x_k, NHWC T
   char* ys;            // NB saved conv outputs y_k, NHWC T
@@ -159,5 +160,6 @@ int nrd_tc_stem_bwd(nrd_plan* p, const float* images, const void* g0, cudaStream
 int nrd_tc_stats_blocks(const nrd_plan* p);
 int nrd_tc_wgrad_blocks(const nrd_plan* p);
 int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st);                        // x_0 -> all y_k, x_{k+1}: one launch
-int nrd_tc_backward_blocks(nrd_plan* p, const void* g_in, void* dx0_out, cudaStream_t st);   // all blocks' backward: one launch
+int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cudaStream_t st);   // all blocks' backward, one launch;
+                                                                            // g_pooled = dL/d(pooled) [B,8,8,C]
 int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st);                      // y_k, x_{k+1}, BN stats + EMA, one launch

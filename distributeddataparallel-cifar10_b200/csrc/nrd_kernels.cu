@@ -803,6 +803,67 @@ __global__ void __launch_bounds__(256) k_fc2_fwd(const float* __restrict__ part,
   }
 }
 
+// k_fc2_fwd + softmax cross-entropy (forward and gradient) in one launch: each CTA finishes its 8 rows (loss row, dlogits);
+// the CTA that arrives last at a counter sums the B loss rows in k_ce's fixed order, so the mean is bit-identical to k_ce's.
+__global__ void __launch_bounds__(256) k_fc2_ce(const float* __restrict__ part, int nsplit, const float* __restrict__ b1,
+                                                const float* __restrict__ w2, const float* __restrict__ b2,
+                                                float* __restrict__ h1, float* __restrict__ logits, int B,
+                                                const int64_t* __restrict__ labels, float gscale, float* __restrict__ loss_rows,
+                                                float* __restrict__ dlogits, float* __restrict__ loss, unsigned int* __restrict__ counter) {
+  __shared__ float hs[8][33];
+  __shared__ float ls[8][NRD_NCLS];
+  __shared__ double red[256];
+  __shared__ int last;
+  const int tid = threadIdx.x, r = tid >> 5, j = tid & 31, b = blockIdx.x * 8 + r;
+  float h = 0.f;
+  if (b < B) {
+    for (int s = 0; s < nsplit; ++s) h += part[((size_t)s * B + b) * NRD_FC1_OUT + j];
+    h = fmaxf(h + b1[j], 0.f);
+    h1[(size_t)b * NRD_FC1_OUT + j] = h;
+  }
+  hs[r][j] = h;
+  __syncthreads();
+  if (tid < 8 * NRD_NCLS) {
+    const int rr = tid / NRD_NCLS, c = tid % NRD_NCLS, bb = blockIdx.x * 8 + rr;
+    float sacc = b2[c];
+#pragma unroll
+    for (int jj = 0; jj < NRD_FC1_OUT; ++jj) sacc = fmaf(hs[rr][jj], w2[c * NRD_FC1_OUT + jj], sacc);
+    ls[rr][c] = sacc;
+    if (bb < B) logits[(size_t)bb * NRD_NCLS + c] = sacc;
+  }
+  __syncthreads();
+  if (tid < 8) {
+    const int bb = blockIdx.x * 8 + tid;
+    if (bb < B) {
+      float v[NRD_NCLS], m = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = ls[tid][c]; m = fmaxf(m, v[c]); }
+      float s = 0.f;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
+      const long long lab64 = labels[bb];
+      const bool lab_ok = lab64 >= 0 && lab64 < NRD_NCLS;          // an out-of-range label poisons the loss, never the address
+      const int lab = lab_ok ? (int)lab64 : 0;
+      const float inv = 1.f / s, sc = gscale / (float)B;
+      loss_rows[bb] = lab_ok ? logf(s) + m - ls[tid][lab] : NAN;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) dlogits[bb * NRD_NCLS + c] = lab_ok ? (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc : NAN;
+    }
+    __threadfence();
+  }
+  __syncthreads();
+  if (tid == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1 : 0;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  double acc = 0.0;
+  for (int bb = tid; bb < B; bb += 256) acc += (double)__ldcg(loss_rows + bb);
+  red[tid] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
+  if (tid == 0) { *loss = (float)(red[0] / B); *counter = 0u; }
+}
+
 // softmax cross-entropy, forward and gradient, one CTA: per-row loss (kept in loss_rows) and dlogits =
 // (softmax - onehot) * grad_scale / B, then the mean loss by a fixed-shape tree over the CTA (deterministic).
 __global__ void __launch_bounds__(256) k_ce(const float* __restrict__ logits, const int64_t* __restrict__ labels, int B, float gscale,
@@ -816,14 +877,16 @@ __global__ void __launch_bounds__(256) k_ce(const float* __restrict__ logits, co
     float s = 0.f;
 #pragma unroll
     for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
-    const int lab = (int)labels[b];
+    const long long lab64 = labels[b];
+    const bool lab_ok = lab64 >= 0 && lab64 < NRD_NCLS;            // an out-of-range label poisons the loss, never the address
+    const int lab = lab_ok ? (int)lab64 : 0;
     const float inv = 1.f / s, sc = gscale / (float)B;
-    const float l = logf(s) + m - logits[b * NRD_NCLS + lab];
+    const float l = lab_ok ? logf(s) + m - logits[b * NRD_NCLS + lab] : NAN;
     loss_rows[b] = l;
     acc += (double)l;
     if (dlogits) {
 #pragma unroll
-      for (int c = 0; c < NRD_NCLS; ++c) dlogits[b * NRD_NCLS + c] = (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc;
+      for (int c = 0; c < NRD_NCLS; ++c) dlogits[b * NRD_NCLS + c] = lab_ok ? (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc : NAN;
     }
   }
   red[threadIdx.x] = acc;
@@ -969,6 +1032,42 @@ __global__ void __launch_bounds__(256) k_fc1_dgrad_unpool(const float* __restric
         gx[(((size_t)b * 16 + 2 * ph + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + c] = from_f<T>(q == id ? s[r] : 0.f);
     }
   }
+}
+
+// The same without the scatter: d(pooled) [B,8,8,C] only.  The persistent backward expands it through pool-2's argmax while it
+// loads its gradient registers, so the 4x larger (and 3/4 zero) dL/dx_NB never exists in memory.
+template <typename T>
+__global__ void __launch_bounds__(256) k_fc1_dgrad_pooled(const float* __restrict__ dlogits, const float* __restrict__ h1,
+                                                          const float* __restrict__ w2, const float* __restrict__ w1t,
+                                                          T* __restrict__ dp, int B, int C) {
+  __shared__ float d[8][NRD_FC1_OUT];
+  __shared__ float dl[8 * NRD_NCLS], w2s[NRD_NCLS * NRD_FC1_OUT];
+  const int K = 64 * C, per_b = K / 256, b0 = (blockIdx.x / per_b) * 8, i = (blockIdx.x % per_b) * 256 + threadIdx.x;
+  for (int q = threadIdx.x; q < NRD_NCLS * NRD_FC1_OUT; q += 256) w2s[q] = w2[q];
+  if (threadIdx.x < 8 * NRD_NCLS) {
+    const int r = threadIdx.x / NRD_NCLS;
+    dl[threadIdx.x] = (b0 + r < B) ? dlogits[(size_t)b0 * NRD_NCLS + threadIdx.x] : 0.f;
+  }
+  __syncthreads();
+  {
+    const int r = threadIdx.x >> 5, j = threadIdx.x & 31;
+    d[r][j] = (b0 + r < B) ? dh1_elem(dl + r * NRD_NCLS, w2s, j, h1[(size_t)(b0 + r) * NRD_FC1_OUT + j]) : 0.f;
+  }
+  __syncthreads();
+  float s[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) s[r] = 0.f;
+  const float4* wrow = reinterpret_cast<const float4*>(w1t + (size_t)i * NRD_FC1_OUT);
+#pragma unroll
+  for (int j4 = 0; j4 < 8; ++j4) {
+    const float4 w = wrow[j4];
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+      s[r] += d[r][j4 * 4] * w.x + d[r][j4 * 4 + 1] * w.y + d[r][j4 * 4 + 2] * w.z + d[r][j4 * 4 + 3] * w.w;
+  }
+#pragma unroll
+  for (int r = 0; r < 8; ++r)
+    if (b0 + r < B) dp[(size_t)(b0 + r) * K + i] = from_f<T>(s[r]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1532,7 +1631,22 @@ extern "C" int nrd_sgd_update_pack(nrd_plan* p, float lr, float inv_world, void*
   return NRD_OK;
 }
 
+static int forward_impl(nrd_plan* p, const float* images, float* logits, int training, void* stream, const int64_t* labels,
+                        float grad_scale, float* loss_out, float* dlogits, float* loss_rows);
+
 extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int training, void* stream) {
+  return forward_impl(p, images, logits, training, stream, nullptr, 0.f, nullptr, nullptr, nullptr);
+}
+
+// training forward + CrossEntropyLoss forward/backward: the loss rides the last kernel of the forward (one launch less)
+extern "C" int nrd_forward_loss(nrd_plan* p, const float* images, const int64_t* labels, float grad_scale, float* logits,
+                                float* loss_out, float* dlogits, float* row_scratch, void* stream) {
+  NRD_REQUIRE(labels && loss_out && dlogits && row_scratch, "nrd_forward_loss: null pointer");
+  return forward_impl(p, images, logits, 1, stream, labels, grad_scale, loss_out, dlogits, row_scratch);
+}
+
+static int forward_impl(nrd_plan* p, const float* images, float* logits, int training, void* stream, const int64_t* labels,
+                        float grad_scale, float* loss_out, float* dlogits, float* loss_rows) {
   NRD_REQUIRE(p && images && logits, "nrd_forward: null pointer");
   NRD_CHECK_CUDA(cudaSetDevice(p->device));
   cudaStream_t st = (cudaStream_t)stream;
@@ -1566,7 +1680,11 @@ extern "C" int nrd_forward(nrd_plan* p, const float* images, float* logits, int 
   if (dt == NRD_F32) k_pool_fc1_fwd_part<float><<<g1, 256, 0, st>>>((const float*)(p->xs + act * NB), (float*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C);
   else k_pool_fc1_fwd_part<bf16><<<g1, 256, 0, st>>>((const bf16*)(p->xs + act * NB), (bf16*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C);
   LAUNCH_CHECK();
-  k_fc2_fwd<<<(B + 7) / 8, 256, 0, st>>>(p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B);
+  if (labels)
+    k_fc2_ce<<<(B + 7) / 8, 256, 0, st>>>(p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B, labels, grad_scale,
+                                         loss_rows, dlogits, loss_out, reinterpret_cast<unsigned int*>(p->gbar + 16));
+  else
+    k_fc2_fwd<<<(B + 7) / 8, 256, 0, st>>>(p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B);
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1602,11 +1720,12 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   const size_t act = p->act_elems * p->esz;
   char* g = p->dxa; char* gn = p->dxb;
   const int K = 64 * C;
-  if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (float*)g, B, C);
+  const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd;
+  if (persist) k_fc1_dgrad_pooled<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, (bf16*)g, B, C);
+  else if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (float*)g, B, C);
   else k_fc1_dgrad_unpool<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (bf16*)g, B, C);
   LAUNCH_CHECK();
   // residual blocks, last to first; the shared block's grads accumulate over the NB applications
-  const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd;
   if (persist) {
     NRD_TRY(nrd_tc_backward_blocks(p, g, gn, st));
     char* t = g; g = gn; gn = t;
@@ -1626,6 +1745,7 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
     }
     char* t = g; g = gn; gn = t;
   }
+  p->dx0_last = g;
   if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_bwd(p, p->images_last, g, st));
   else NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
   k_body_reduce<<<9 * C * C / 32 + 28 * C / 32, 256, 0, st>>>(p->wgrad_partial, p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B),
@@ -1638,8 +1758,7 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
 extern "C" int nrd_train_step(nrd_plan* p, const float* images, const int64_t* labels, float lr, float* logits, float* loss_out,
                               void* stream) {
   NRD_REQUIRE(p && images && labels && logits && loss_out, "nrd_train_step: null pointer");
-  NRD_TRY(nrd_forward(p, images, logits, 1, stream));
-  NRD_TRY(nrd_cross_entropy(logits, labels, p->B, 1.0f, loss_out, p->dlogits, p->loss_rows, stream));
+  NRD_TRY(nrd_forward_loss(p, images, labels, 1.0f, logits, loss_out, p->dlogits, p->loss_rows, stream));
   NRD_TRY(nrd_backward(p, p->dlogits, stream));
   return nrd_sgd_update_pack(p, lr, 1.0f, stream);
 }
@@ -1677,8 +1796,9 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       return stem_fwd_any(p->images_last, p->conv1_wp, PRM(P_C1B), p->dxb, p->idx0, B, C, dt, st);
     case NRD_OP_STEM_BWD:
       NRD_REQUIRE(p->images_last, "run a forward first");
-      if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) return nrd_tc_stem_bwd(p, p->images_last, p->dxa, st);
-      return stem_bwd_any(p->images_last, p->dxa, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st);
+      NRD_REQUIRE(p->dx0_last, "run a backward first");
+      if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) return nrd_tc_stem_bwd(p, p->images_last, p->dx0_last, st);
+      return stem_bwd_any(p->images_last, p->dx0_last, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st);
     case NRD_OP_FWD_BLOCKS:
       NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent forward not available for this plan");
       return nrd_tc_forward_blocks(p, st);

@@ -79,9 +79,8 @@ class TrainStep:
         imgs, labels = self.inputs[slot]
         if self.world > 1 and not self.fold_bn_sync:
             self.ddp._sync_buffers()                                   # C2 (folded into the body bucket otherwise)
-        check(lib.nrd_forward(pl.handle, imgs.data_ptr(), self.logits.data_ptr(), 1, st), "nrd_forward")
-        check(lib.nrd_cross_entropy(self.logits.data_ptr(), labels.data_ptr(), self.B, 1.0, self.loss.data_ptr(),
-                                    pl.dlogits.data_ptr(), pl.loss_rows.data_ptr(), st), "nrd_cross_entropy")
+        check(lib.nrd_forward_loss(pl.handle, imgs.data_ptr(), labels.data_ptr(), 1.0, self.logits.data_ptr(), self.loss.data_ptr(),
+                                   pl.dlogits.data_ptr(), pl.loss_rows.data_ptr(), st), "nrd_forward_loss")
         # backward: head weight grads (+ their bucket's all-reduce) on a side stream beside the body backward (C3)
         sum_head = (lambda: self.ddp._allreduce_bucket(1, average=False)) if self.world > 1 else None
         sum_body = None
@@ -153,6 +152,13 @@ class TrainStep:
             if tuple(imgs.shape) != tuple(self.inputs[slot][0].shape):
                 raise ValueError(f"TrainStep was built for batches of {tuple(self.inputs[slot][0].shape)}, got {tuple(imgs.shape)} "
                                  "(use drop_last=True or a second TrainStep for the ragged tail)")
+            if imgs.is_cuda or labels.is_cuda:
+                # device-resident batch (e.g. SyntheticCifar10Loader): its producer runs on the current stream, so the copy
+                # goes there too (nothing to overlap: there is no PCIe transfer)
+                self.inputs[slot][0].copy_(imgs, non_blocking=True)
+                self.inputs[slot][1].copy_(labels, non_blocking=True)
+                self._ready[slot].record(main)
+                return
             copy.wait_event(self._consumed[slot])        # the step that last read this slot
             with torch.cuda.stream(copy):
                 self.inputs[slot][0].copy_(imgs, non_blocking=True)

@@ -121,6 +121,10 @@ int nrd_pack_weights(nrd_plan* plan, void* stream);
  * nrd_train_step = main.py:34-39 for one rank without the allreduce: forward, loss, backward,
  *   update (inv_world = 1) and weight re-pack; loss_out: fp32 scalar on the device. */
 int nrd_forward(nrd_plan* plan, const float* images, float* logits, int training, void* stream);
+/* main.py:34-35 in one call: training forward, then loss and dlogits exactly as nrd_cross_entropy computes them (bit
+ * for bit), with the loss folded into the forward's last kernel.  row_scratch: B floats. */
+int nrd_forward_loss(nrd_plan* plan, const float* images, const int64_t* labels, float grad_scale, float* logits,
+                     float* loss_out, float* dlogits, float* row_scratch, void* stream);
 int nrd_cross_entropy(const float* logits, const int64_t* labels, int B, float grad_scale,
                       float* loss_out, float* dlogits, float* row_scratch /* [B] */, void* stream);
 /* nrd_cross_entropy_static: the same computation for callers that cannot allocate device memory and

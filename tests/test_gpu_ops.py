@@ -151,6 +151,12 @@ def test_cross_entropy_and_sgd_and_generator():
     lr = logits.double().requires_grad_(True)
     ref = F.cross_entropy(lr, labels); ref.backward()
     assert abs(float(loss) - float(ref)) < 1e-6 * max(1, abs(float(ref))) and relmax(dl, lr.grad) < 1e-5
+    # an out-of-range label (torch raises a device assert there) poisons the loss with NaN but never the address
+    bad = labels.clone(); bad[5] = 1 << 40; bad[7] = -3
+    badd = bad.to(DEV)
+    check(lib.nrd_cross_entropy(ld.data_ptr(), badd.data_ptr(), B, 1.0, loss.data_ptr(), dl.data_ptr(), rows.data_ptr(), st()))
+    torch.cuda.synchronize()
+    assert np.isnan(float(loss)) and bool(torch.isnan(rows[5])) and bool(torch.isnan(dl[7]).all()) and bool(torch.isfinite(dl[6]).all())
     # fused mean + SGD
     p = torch.randn(1000, generator=g); gr = torch.randn(1000, generator=g)
     pd, gd = dev_f32(p), dev_f32(gr)
