@@ -372,6 +372,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   const int img0 = blockIdx.x, img1 = blockIdx.x + gridDim.x;
   const int nslots = (img1 < a.B) ? 2 : 1;
   constexpr uint32_t TMEM_COLS = 128;                              // 2 slots x 2 tiles x 32 columns
+  nrd_pdl_launch();                                                // the head kernels behind us may be scheduled (they wait for our exit)
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX0); tma_prefetch_desc(&tmW);
@@ -643,6 +644,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   const int nslots = (img1 < a.B) ? 2 : 1;
   constexpr uint32_t TMEM_COLS = 256;                              // dgrad 2x2x32 columns + wgrad 3x32 columns
   constexpr uint32_t ACCW = 128;
+  nrd_pdl_launch();                                                // the stem backward behind us may be scheduled (it waits for our exit)
 
   // the halo rows / columns of the dy copies are the convolution padding: zero everything once, never write them again
   for (int i = threadIdx.x; i < 2 * DY_BYTES / 16; i += blockDim.x) {

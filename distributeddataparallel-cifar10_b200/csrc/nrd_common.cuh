@@ -88,6 +88,7 @@ struct nrd_plan {
   CUtensorMap tm_xall;    // all x_k as one 5-D tensor (persistent backward)
   CUtensorMap tm_xst, tm_yst; // x_k / y_k stacks, whole-image boxes: bulk tensor STORES of the persistent forward
   int tc_ready;
+  int pdl;                // option: programmatic dependent launch between the small kernels of the step
   int reserve_sms;        // option: SMs the cooperative kernels leave free (a concurrent NCCL kernel needs somewhere to run)
   float* bn_sync;         // optional [2C] slot in front of the gradient vector: BN running stats ride the body bucket's all-reduce
   float bn_sync_contrib;  // what this rank adds to the slot: world_size on rank 0, 0 elsewhere
@@ -105,6 +106,23 @@ struct nrd_plan {
   int dbg_skip_stores;    // profiling experiment (NRD_OPT_TRACE value 2)
   void* trace_bwd;        // same for the persistent backward (lives in the pooled-gradient-free part of the dy scratch)
 };
+
+// Programmatic dependent launch: a kernel launched with nrd_launch_pdl() may start (be scheduled, run its prologue) while its
+// predecessor on the stream is still running; it must call nrd_pdl_wait() before touching anything the predecessor (or any
+// kernel before that) writes.  Producers call nrd_pdl_launch() as early as they like: it only lets the dependent grid be
+// scheduled.  Without the launch attribute both are no-ops.  Stream capture keeps the programmatic edge in the graph.
+static __device__ __forceinline__ void nrd_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+static __device__ __forceinline__ void nrd_pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+static inline cudaError_t nrd_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 
 // Grid-wide barrier for cooperative launches (all CTAs co-resident).  ONE 64-bit monotonic counter per kernel type and plan:
 // an arrival is a release-add of 1, waiting is an acquire-poll until the counter reaches this episode's target.  The counter

@@ -220,6 +220,8 @@ __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ w
                                                      int C, float* __restrict__ dw, float* __restrict__ dw1, float* __restrict__ db1,
                                                      float* __restrict__ bn_sync, const float* __restrict__ running, float contrib) {
   __shared__ double red[8][33];
+  nrd_pdl_launch();
+  nrd_pdl_wait();
   // DDP buffer sync riding the body bucket: rank 0 contributes world_size * running, the others exact zeros
   if (bn_sync && blockIdx.x == gridDim.x - 1)
     for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) bn_sync[j] = contrib != 0.f ? running[j] * contrib : 0.f;
@@ -740,8 +742,10 @@ __global__ void __launch_bounds__(256) k_pool_fc1_fwd_part(const T* __restrict__
   __shared__ __align__(16) float ws[128 * 32];
   __shared__ float ps[32 * 129];
   const int tid = threadIdx.x, b0 = blockIdx.x * 32, k0 = blockIdx.y * 128, K = 64 * C;
-  for (int i = tid; i < 128 * 32 / 4; i += 256)
+  nrd_pdl_launch();
+  for (int i = tid; i < 128 * 32 / 4; i += 256)        // weights: untouched since the last optimizer step, safe before the wait
     reinterpret_cast<float4*>(ws)[i] = reinterpret_cast<const float4*>(w1t + (size_t)k0 * 32)[i];
+  nrd_pdl_wait();
   for (int i = tid; i < 32 * 16; i += 256) {          // 32 rows x 16 eight-channel chunks of the slice
     const int r = i >> 4, c8 = i & 15, b = b0 + r;
     const int kk = k0 + c8 * 8, hw = kk / C, c = kk % C, ph = hw >> 3, pw = hw & 7;
@@ -784,6 +788,8 @@ __global__ void __launch_bounds__(256) k_fc2_fwd(const float* __restrict__ part,
                                                  float* __restrict__ h1, float* __restrict__ logits, int B) {
   __shared__ float hs[8][33];
   const int tid = threadIdx.x, r = tid >> 5, j = tid & 31, b = blockIdx.x * 8 + r;
+  nrd_pdl_launch();
+  nrd_pdl_wait();
   float h = 0.f;
   if (b < B) {
     for (int s = 0; s < nsplit; ++s) h += part[((size_t)s * B + b) * NRD_FC1_OUT + j];
@@ -815,6 +821,8 @@ __global__ void __launch_bounds__(256) k_fc2_ce(const float* __restrict__ part, 
   __shared__ double red[256];
   __shared__ int last;
   const int tid = threadIdx.x, r = tid >> 5, j = tid & 31, b = blockIdx.x * 8 + r;
+  nrd_pdl_launch();
+  nrd_pdl_wait();
   float h = 0.f;
   if (b < B) {
     for (int s = 0; s < nsplit; ++s) h += part[((size_t)s * B + b) * NRD_FC1_OUT + j];
@@ -999,7 +1007,9 @@ __global__ void __launch_bounds__(256) k_fc1_dgrad_unpool(const float* __restric
   __shared__ float d[8][NRD_FC1_OUT];
   __shared__ float dl[8 * NRD_NCLS], w2s[NRD_NCLS * NRD_FC1_OUT];
   const int K = 64 * C, per_b = K / 256, b0 = (blockIdx.x / per_b) * 8, i = (blockIdx.x % per_b) * 256 + threadIdx.x;
+  nrd_pdl_launch();
   for (int q = threadIdx.x; q < NRD_NCLS * NRD_FC1_OUT; q += 256) w2s[q] = w2[q];
+  nrd_pdl_wait();
   if (threadIdx.x < 8 * NRD_NCLS) {
     const int r = threadIdx.x / NRD_NCLS;
     dl[threadIdx.x] = (b0 + r < B) ? dlogits[(size_t)b0 * NRD_NCLS + threadIdx.x] : 0.f;
@@ -1043,7 +1053,9 @@ __global__ void __launch_bounds__(256) k_fc1_dgrad_pooled(const float* __restric
   __shared__ float d[8][NRD_FC1_OUT];
   __shared__ float dl[8 * NRD_NCLS], w2s[NRD_NCLS * NRD_FC1_OUT];
   const int K = 64 * C, per_b = K / 256, b0 = (blockIdx.x / per_b) * 8, i = (blockIdx.x % per_b) * 256 + threadIdx.x;
+  nrd_pdl_launch();
   for (int q = threadIdx.x; q < NRD_NCLS * NRD_FC1_OUT; q += 256) w2s[q] = w2[q];
+  nrd_pdl_wait();
   if (threadIdx.x < 8 * NRD_NCLS) {
     const int r = threadIdx.x / NRD_NCLS;
     dl[threadIdx.x] = (b0 + r < B) ? dlogits[(size_t)b0 * NRD_NCLS + threadIdx.x] : 0.f;
@@ -1085,6 +1097,7 @@ __global__ void k_sgd_pack(float* __restrict__ p, const float* __restrict__ g, f
                            float* __restrict__ w_fwd, float* __restrict__ w_dgrad, bf16* __restrict__ wtc_fwd, bf16* __restrict__ wtc_dgrad,
                            float* __restrict__ w1p, float* __restrict__ conv1_wp) {
   (void)offp;
+  nrd_pdl_wait();
   const long long n_rb = (long long)C * C * 9, n_fc1 = (long long)NRD_FC1_OUT * 64 * C, n_c1 = (long long)C * 27;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float w = fmaf(-step_scale, g[i], p[i]);
@@ -1531,6 +1544,7 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->persist_fwd = 1;
   p->persist_bwd = 1;
   p->use_tc_stem = 1;
+  p->pdl = 5;     // measured: the consumers of the two persistent kernels (bit 1) lose 13 us when made programmatic dependents
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
   e = cudaMemset(p->gbar, 0, 256);
@@ -1563,6 +1577,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_PERSIST_FWD: p->persist_fwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PERSIST_BWD: p->persist_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_TC_STEM: p->use_tc_stem = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_PDL: p->pdl = value; return NRD_OK;
     case NRD_OPT_RESERVE_SMS:
       NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
       p->reserve_sms = value;
@@ -1624,9 +1639,9 @@ extern "C" int nrd_sgd_update_pack(nrd_plan* p, float lr, float inv_world, void*
   NRD_REQUIRE(p, "null plan");
   NRD_CHECK_CUDA(cudaSetDevice(p->device));
   const long long n = p->off[9];
-  k_sgd_pack<<<grid_for((size_t)n, 256, NRD_NUM_SMS * 2), 256, 0, (cudaStream_t)stream>>>(
-      p->params, p->grads, lr * inv_world, p->C, nullptr, p->off[P_C1W], p->off[P_RBW], p->off[P_FC1W], n, p->w_fwd, p->w_dgrad,
-      p->wtc_fwd, p->wtc_dgrad, p->w1p, p->conv1_wp);
+  NRD_CHECK_CUDA(nrd_launch_pdl(k_sgd_pack, dim3(grid_for((size_t)n, 256, NRD_NUM_SMS * 2)), dim3(256), 0, (cudaStream_t)stream, (p->pdl >> 2) & 1,
+                                p->params, p->grads, lr * inv_world, p->C, nullptr, p->off[P_C1W], p->off[P_RBW], p->off[P_FC1W], n, p->w_fwd,
+                                p->w_dgrad, p->wtc_fwd, p->wtc_dgrad, p->w1p, p->conv1_wp));
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1677,14 +1692,15 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
   }
   const int K = 64 * C;
   const dim3 g1((B + 31) / 32, K / 128);
-  if (dt == NRD_F32) k_pool_fc1_fwd_part<float><<<g1, 256, 0, st>>>((const float*)(p->xs + act * NB), (float*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C);
-  else k_pool_fc1_fwd_part<bf16><<<g1, 256, 0, st>>>((const bf16*)(p->xs + act * NB), (bf16*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C);
+  if (dt == NRD_F32) NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<float>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const float*)(p->xs + act * NB), (float*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
+  else NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<bf16>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const bf16*)(p->xs + act * NB), (bf16*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
   LAUNCH_CHECK();
   if (labels)
-    k_fc2_ce<<<(B + 7) / 8, 256, 0, st>>>(p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B, labels, grad_scale,
-                                         loss_rows, dlogits, loss_out, reinterpret_cast<unsigned int*>(p->gbar + 16));
+    NRD_CHECK_CUDA(nrd_launch_pdl(k_fc2_ce, dim3((B + 7) / 8), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B),
+                                  p->h1, logits, B, labels, grad_scale, loss_rows, dlogits, loss_out, reinterpret_cast<unsigned int*>(p->gbar + 16)));
   else
-    k_fc2_fwd<<<(B + 7) / 8, 256, 0, st>>>(p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B);
+    NRD_CHECK_CUDA(nrd_launch_pdl(k_fc2_fwd, dim3((B + 7) / 8), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B),
+                                  p->h1, logits, B));
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1721,7 +1737,8 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   char* g = p->dxa; char* gn = p->dxb;
   const int K = 64 * C;
   const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd;
-  if (persist) k_fc1_dgrad_pooled<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, (bf16*)g, B, C);
+  if (persist) NRD_CHECK_CUDA(nrd_launch_pdl(k_fc1_dgrad_pooled<bf16>, dim3(((B + 7) / 8) * (K / 256)), dim3(256), 0, st, p->pdl & 1, dlogits, p->h1,
+                                             PRM(P_FC2W), p->w1p, (bf16*)g, B, C));
   else if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (float*)g, B, C);
   else k_fc1_dgrad_unpool<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (bf16*)g, B, C);
   LAUNCH_CHECK();
@@ -1748,9 +1765,9 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   p->dx0_last = g;
   if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_bwd(p, p->images_last, g, st));
   else NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
-  k_body_reduce<<<9 * C * C / 32 + 28 * C / 32, 256, 0, st>>>(p->wgrad_partial, p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B),
-                                                           p->stem_partial, stem_bwd_blocks(B), C, GRD(P_RBW), GRD(P_C1W), GRD(P_C1B),
-                                                           p->bn_sync, p->bn_running, p->bn_sync_contrib);
+  NRD_CHECK_CUDA(nrd_launch_pdl(k_body_reduce, dim3(9 * C * C / 32 + 28 * C / 32), dim3(256), 0, st, (p->pdl >> 2) & 1, p->wgrad_partial,
+                                p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B), p->stem_partial, stem_bwd_blocks(B), C,
+                                GRD(P_RBW), GRD(P_C1W), GRD(P_C1B), p->bn_sync, p->bn_running, p->bn_sync_contrib));
   LAUNCH_CHECK();
   return NRD_OK;
 }

@@ -229,6 +229,8 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  nrd_pdl_launch();
+  nrd_pdl_wait();          // set-up above overlaps the predecessor's tail; dL/dx_0 is read below
   const uint32_t tmem_base = *tmem_slot_gen;
   const int nimg = (B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
@@ -356,7 +358,8 @@ int nrd_tc_stem_fwd(nrd_plan* p, const float* images, int training, cudaStream_t
 // per-CTA partials [stem_grid][28][32] into p->stem_partial (same layout the CUDA-core path writes; reduced by the caller)
 int nrd_tc_stem_bwd(nrd_plan* p, const float* images, const void* g0, cudaStream_t st) {
   NRD_REQUIRE(p->tc_stem, "tensor-core stem not available for this plan");
-  k_stem_tc_bwd<<<stem_grid(p), 288, stem_bwd_smem(), st>>>(images, (const bf16*)g0, (const bf16*)p->xs, p->idx0, p->stem_partial, p->B);
+  NRD_CHECK_CUDA(nrd_launch_pdl(k_stem_tc_bwd, dim3(stem_grid(p)), dim3(288), stem_bwd_smem(), st, (p->pdl >> 1) & 1, images, (const bf16*)g0, (const bf16*)p->xs,
+                                (const uint8_t*)p->idx0, p->stem_partial, p->B));
   nrd_count_launch();
   NRD_CHECK_CUDA(cudaGetLastError());
   return NRD_OK;

@@ -41,6 +41,8 @@ class _Plan:
                                   eng.flat_params.data_ptr(), eng.flat_grads.data_ptr(), eng.bn_running.data_ptr(),
                                   eng.nbt.data_ptr()), "nrd_plan_create")
         self.handle = h
+        if "NRD_PDL" in os.environ:                        # A/B switch for measurements (bit mask, see nrd.h)
+            check(lib.nrd_plan_set_option(h, _lib.OPT_PDL, int(os.environ["NRD_PDL"])), "nrd_plan_set_option")
         self.dlogits = torch.empty(B, 10, dtype=torch.float32, device=eng.device)
         self.loss_rows = torch.empty(B, dtype=torch.float32, device=eng.device)
         self.packed_version = -1

@@ -87,6 +87,10 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
 /* NRD_OPT_RESERVE_SMS (default 0): the cooperative kernels use 148 - value SMs.  They fill an SM's shared memory, so a
  * collective launched beside them (the head bucket's all-reduce, parallel.py) can only run on SMs they leave free. */
 #define NRD_OPT_RESERVE_SMS 5
+/* NRD_OPT_PDL (bit mask, default 5): kernels launched with programmatic stream serialization, i.e. already resident with
+ * their prologue done when the predecessor's last CTA retires.  bit 0: loss and fc1-dgrad kernels, bit 2: body gradient
+ * reduce and optimizer kernels, bit 1: the kernels right behind the two persistent kernels (measured slower: off). */
+#define NRD_OPT_PDL 6
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* DDP's per-forward buffer broadcast (torch DDP `broadcast_buffers`, reached from main.py:63 and run in front of every
  * forward, main.py:33) folded into the gradient exchange: `slot` = the 2C floats directly in front of `grads` (so slot +
