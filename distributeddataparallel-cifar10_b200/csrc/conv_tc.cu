@@ -372,6 +372,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   const int img0 = blockIdx.x, img1 = blockIdx.x + gridDim.x;
   const int nslots = (img1 < a.B) ? 2 : 1;
   constexpr uint32_t TMEM_COLS = 128;                              // 2 slots x 2 tiles x 32 columns
+  if (a.trace && threadIdx.x == 64) a.trace[(size_t)blockIdx.x * a.NB * 8 + 7] = clock64();      // kernel entry
   nrd_pdl_launch();                                                // the head kernels behind us may be scheduled (they wait for our exit)
 
   if (warp == 0 && lane == 0) {
@@ -452,8 +453,6 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     const int P0y = pi * 16 + pj;                                              // ... and inside the y staging tile
     const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
     const float* ss_w = ss_sm + h * 16;                                        // this thread's channels: scale at [c], shift at [C + c]
-    unsigned long long gbar_target = 0;
-    if (et == 0) gbar_target = nrd_grid_barrier_base(a.gbar, gridDim.x);   // before this CTA's first arrival
     const float gamma_r = a.gamma[lane], beta_r = a.beta[lane];             // off the per-block critical path (used by warp ew == 0)
     for (int k = 0; k < a.NB; ++k) {
       long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + k) * 8 : nullptr;
@@ -493,27 +492,25 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       if (tr) tr[2] = clock64();
       red[ew * 32 + (lane & 1) * 16 + (lane >> 1)] = (lane & 1) ? qsum : ssum;
       asm volatile("bar.sync 1, 512;" ::: "memory");
-      // cross-CTA sum WITHOUT a partial matrix: every CTA adds its 2C per-channel sums as 64-bit fixed point (2^-32) into one
-      // accumulator row per block.  Integer addition is associative, so the result is bit-identical whatever order the CTAs
-      // arrive in; the grid barrier then only has to publish 2C numbers instead of gridDim.x rows.
+      // cross-CTA sum WITHOUT a partial matrix and WITHOUT a separate barrier: every CTA adds its 2C per-channel sums as fixed
+      // point (2^-24) into one word per statistic that also counts the contributors (nrd_common.cuh); integer addition is
+      // associative, so the result is bit-identical whatever order the CTAs arrive in
       unsigned long long* acc = a.acc + (size_t)k * 2 * C;
       if (et < 2 * C) {
         const int which = et >> 5, ch = et & 31;
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];   // fixed order over the 8 warps of the half
-        atomicAdd(acc + et, (unsigned long long)__double2ll_rn((double)t * 4294967296.0));
+        nrd_acc_add(acc + et, t, 16777216.0);
       }
-      asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[3] = clock64();
-      // the warp that polls the grid barrier also derives the coefficients (32 lanes = 32 channels: ONE warp's worth of the slow
-      // fp64 pipe) and publishes them with the only CTA-wide barrier after the grid barrier
+      // one warp (lane = channel) polls its channels' words until every CTA has contributed, derives the coefficients (ONE
+      // warp's worth of the slow fp64 pipe) and publishes them with the only CTA-wide barrier of the wait
       if (ew == 0) {
-        if (lane == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
-        __syncwarp();
+        unsigned long long ws, wq;
+        nrd_acc_wait2(acc + lane, acc + C + lane, gridDim.x, ws, wq);
         if (tr) tr[4] = clock64();
-        const double S = (double)(long long)__ldcg(acc + lane) * (1.0 / 4294967296.0);
-        const double Q = (double)(long long)__ldcg(acc + C + lane) * (1.0 / 4294967296.0);
+        const double S = nrd_acc_value(ws, gridDim.x, 1.0 / 16777216.0), Q = nrd_acc_value(wq, gridDim.x, 1.0 / 16777216.0);
         const double mean = S * a.inv_count;
         double var = Q * a.inv_count - mean * mean;
         if (var < 0.0) var = 0.0;
@@ -574,6 +571,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   tc_fence_before();
   __syncthreads();
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+  if (a.trace && threadIdx.x == 64) a.trace[((size_t)blockIdx.x * a.NB + a.NB - 1) * 8 + 7] = clock64();   // kernel exit
 }
 
 // ============================================================================================
@@ -644,6 +642,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   const int nslots = (img1 < a.B) ? 2 : 1;
   constexpr uint32_t TMEM_COLS = 256;                              // dgrad 2x2x32 columns + wgrad 3x32 columns
   constexpr uint32_t ACCW = 128;
+  if (a.trace && threadIdx.x == 64) a.trace[(size_t)blockIdx.x * a.NB * 16 + 14] = clock64();     // kernel entry
   nrd_pdl_launch();                                                // the stem backward behind us may be scheduled (it waits for our exit)
 
   // the halo rows / columns of the dy copies are the convolution padding: zero everything once, never write them again
@@ -729,8 +728,6 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     const size_t pix_off = (size_t)(pi * 16 + pj) * C + h * 16;               // this thread's 16 channels inside an image
     const int P1 = (pi + 1) * 16 + pj;                                         // its index inside an operand copy (row-haloed)
     const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
-    unsigned long long gbar_target = 0;
-    if (et == 0) gbar_target = nrd_grid_barrier_base(a.gbar, gridDim.x);
     uint32_t gpk[2][8];                               // dL/d(out) of this thread's pixel and channels, per image slot, bf16 pairs
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
@@ -822,25 +819,24 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       red[ew * 32 + (lane & 1) * 16 + (lane >> 1)] = (lane & 1) ? s2 : s1;
       s1 = 0.f; s2 = 0.f;
       asm volatile("bar.sync 1, 512;" ::: "memory");
-      // cross-CTA sum as 64-bit fixed point (2^-40) atomics into one accumulator row per block: order-independent, bit-exact
+      // cross-CTA sum: fixed point (2^-36) + contributor count in one word per statistic (nrd_common.cuh): order-independent,
+      // bit-exact, and no separate grid barrier
       unsigned long long* acc = a.acc + (size_t)it * 2 * C;
       if (et < 2 * C) {
         const int which = et >> 5, ch = et & 31;
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
-        atomicAdd(acc + et, (unsigned long long)__double2ll_rn((double)t * 1099511627776.0));
+        nrd_acc_add(acc + et, t, 68719476736.0);
       }
-      asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tr) tr[2] = clock64();
-      // the warp that polls the grid barrier also derives the dy coefficients (lane = channel) and publishes them (and the NEXT
+      // one warp (lane = channel) polls its channels' words, derives the dy coefficients and publishes them (and the NEXT
       // block's scale/shift pairs: every thread is past phase B of the previous block) with the one CTA barrier that follows
       if (ew == 0) {
-        if (lane == 0) { gbar_target += gridDim.x; nrd_grid_barrier(a.gbar, gbar_target); }
-        __syncwarp();
+        unsigned long long wb, wg;
+        nrd_acc_wait2(acc + lane, acc + C + lane, gridDim.x, wb, wg);
         if (tr) tr[3] = clock64();
-        const double db = (double)(long long)__ldcg(acc + lane) * (1.0 / 1099511627776.0);
-        const double dgy = (double)(long long)__ldcg(acc + C + lane) * (1.0 / 1099511627776.0);
+        const double db = nrd_acc_value(wb, gridDim.x, 1.0 / 68719476736.0), dgy = nrd_acc_value(wg, gridDim.x, 1.0 / 68719476736.0);
         if (it + 1 < a.NB) write_ssp(it + 1);
         const double mean = (double)mean_r, is = (double)is_r;
         const double dg = is * (dgy - mean * db);       // sum dz*xhat = invstd * (sum dz*y - mean * sum dz)
@@ -934,6 +930,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+  if (a.trace && threadIdx.x == 64) a.trace[((size_t)blockIdx.x * a.NB + a.NB - 1) * 16 + 15] = clock64();   // kernel exit
 }
 
 // ============================================================================================

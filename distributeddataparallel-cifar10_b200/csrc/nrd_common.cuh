@@ -161,6 +161,44 @@ static inline nrd_bn_sync_args nrd_bn_sync_of(const nrd_plan* p, int training) {
   if (p && training && p->bn_sync) { a.slot = p->bn_sync; a.running = p->bn_running; a.inv_world = p->bn_sync_inv_world; a.n = 2 * p->C; }
   return a;
 }
+// BN sums of the persistent kernels: ONE 64-bit word per channel statistic carries both the cross-CTA sum and the arrival
+// count, so waiting for "all CTAs have contributed" and fetching the sum are the same load, and no CTA waits for its own
+// atomics to be acknowledged before it signals (that is what a separate barrier counter costs).
+//   bits 56..63  number of CTAs that have added (grid <= 255)
+//   bits  0..55  sum of (fixed-point contribution + NRD_ACC_BIAS): the bias keeps every contribution positive so the low
+//                field never borrows from / carries into the count; integer addition = order-independent, bit-exact.
+// A contribution is clamped to +-(2^46 - 1) fixed-point units (see the scale at each use).
+#define NRD_ACC_CNT1 (1ull << 56)
+#define NRD_ACC_BIAS (1ull << 46)
+static __device__ __forceinline__ void nrd_acc_add(unsigned long long* word, float v, double scale) {
+  long long f = __double2ll_rn((double)v * scale);
+  const long long lim = (long long)NRD_ACC_BIAS - 1;
+  f = f > lim ? lim : (f < -lim ? -lim : f);
+  atomicAdd(word, NRD_ACC_CNT1 + NRD_ACC_BIAS + (unsigned long long)f);
+}
+static __device__ __forceinline__ unsigned long long nrd_acc_peek(const unsigned long long* word) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(word) : "memory");
+  return v;
+}
+static __device__ __forceinline__ double nrd_acc_value(unsigned long long w, unsigned int nblocks, double inv_scale) {
+  return (double)((long long)(w & (NRD_ACC_CNT1 - 1)) - (long long)((unsigned long long)nblocks * NRD_ACC_BIAS)) * inv_scale;
+}
+// one warp waits until both of each lane's words are complete (all lanes leave together); a ~2 s spin traps
+static __device__ __forceinline__ void nrd_acc_wait2(const unsigned long long* w0, const unsigned long long* w1, unsigned int nblocks,
+                                                     unsigned long long& v0, unsigned long long& v1) {
+  long long t0 = 0;
+  int spins = 0;
+  while (true) {
+    v0 = nrd_acc_peek(w0); v1 = nrd_acc_peek(w1);
+    const bool done = (v0 >> 56) == nblocks && (v1 >> 56) == nblocks;
+    if (__all_sync(0xffffffffu, done)) break;
+    if (++spins > 1024) {
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > 4000000000LL) __trap();
+    }
+  }
+}
 #define NRD_GBAR_BLOCK_FWD 0
 #define NRD_GBAR_PERSIST_FWD 1
 #define NRD_GBAR_BN_BWD 2

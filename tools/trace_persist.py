@@ -24,6 +24,7 @@ for cta in (0, 1, grid - 1):
     for k in range(10):
         t = tr[cta, k]
         print("  k=%d " % k + " ".join(f"{names[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next_start=+{int(tr[cta,k+1,0]-t[0])}" if k < 9 else ""))
+    print(f"  kernel entry -> first block start {int(tr[cta,0,0]-tr[cta,0,7])}, last pass 2 -> kernel exit {int(tr[cta,9,7]-tr[cta,9,6])}, whole kernel {int(tr[cta,9,7]-tr[cta,0,7])} cycles")
 
 # ---- backward ----
 y = torch.randint(0, 10, (B,), device=dev)
@@ -36,3 +37,19 @@ for cta in (0, grid - 1):
     for it in range(10):
         t = trb[cta, it]
         print("  it=%d " % it + f"sync={int(t[7]-t[0]):6d} " + " ".join(f"{namesb[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next=+{int(trb[cta,it+1,0]-t[0])}" if it < 9 else "") + "  A:" + ",".join(str(int(t[i]-t[7])) for i in range(8, 14)))
+    print(f"  kernel entry -> first block start {int(trb[cta,0,0]-trb[cta,0,14])}, last phase C -> kernel exit {int(trb[cta,9,15]-trb[cta,9,6])}, whole kernel {int(trb[cta,9,15]-trb[cta,0,14])} cycles")
+
+# ---- who is late?  wait = post-barrier - pre-barrier per CTA (the last arriver waits least) ----
+if os.environ.get("TRACE_WAITS"):
+    import numpy as np
+    for name, t, i0, i1, seg in (("fwd", tr, 3, 4, [(0, 2, "start->pass1"), (2, 3, "pass1->atomics"), (4, 5, "combine"), (5, 6, "pass2")]),
+                                 ("bwd", trb, 2, 3, [(0, 2, "start->atomics"), (3, 4, "combine"), (4, 5, "phaseB"), (5, 6, "phaseC+A")])):
+        w = (t[:, 2:9, i1] - t[:, 2:9, i0]).float().mean(1).numpy()
+        order = np.argsort(w)
+        print(f"{name}: mean wait per CTA over blocks 2..8: min {w.min():.0f} (CTA {order[0]}), median {np.median(w):.0f}, max {w.max():.0f} (CTA {order[-1]})")
+        print("   least-waiting CTAs:", [(int(c), int(w[c])) for c in order[:12]])
+        two = w[: 2 * 148 - 256 if False else 108]
+        print(f"   2-image CTAs (0..107): mean wait {w[:108].mean():.0f}; 1-image CTAs: mean wait {w[108:].mean():.0f}")
+        for a_, b_, nm in seg:
+            d_ = (t[:, 2:9, b_] - t[:, 2:9, a_]).float().mean(1).numpy()
+            print(f"   {nm}: 2-image CTAs mean {d_[:108].mean():.0f} min {d_[:108].min():.0f} max {d_[:108].max():.0f} (CTA {int(np.argmax(d_[:108]))})")
