@@ -454,6 +454,15 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
     const float* ss_w = ss_sm + h * 16;                                        // this thread's channels: scale at [c], shift at [C + c]
     const float gamma_r = a.gamma[lane], beta_r = a.beta[lane];             // off the per-block critical path (used by warp ew == 0)
+    // the LAST row of the previous launch could not be cleaned inside that launch (its readers were still polling): do it now,
+    // long before anyone adds to it -- every CTA reaches that row only after seeing this CTA's contribution to row 0, which
+    // is issued after the fence
+    if (blockIdx.x == 0 && ew == 0) {
+      unsigned long long* last = a.acc + (size_t)(a.NB - 1) * NRD_ACC_ROW;
+#pragma unroll
+      for (int r = 0; r < NRD_ACC_REPL; ++r) { last[NRD_ACC_IDX(r, lane)] = 0ull; last[NRD_ACC_IDX(r, C + lane)] = 0ull; }
+      __threadfence();
+    }
     for (int k = 0; k < a.NB; ++k) {
       long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + k) * 8 : nullptr;
       if (tr) tr[0] = clock64();
@@ -495,21 +504,26 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       // cross-CTA sum WITHOUT a partial matrix and WITHOUT a separate barrier: every CTA adds its 2C per-channel sums as fixed
       // point (2^-24) into one word per statistic that also counts the contributors (nrd_common.cuh); integer addition is
       // associative, so the result is bit-identical whatever order the CTAs arrive in
-      unsigned long long* acc = a.acc + (size_t)k * 2 * C;
+      unsigned long long* acc = a.acc + (size_t)k * NRD_ACC_ROW;      // [replica][2C] words, NRD_ACC_WS apart
       if (et < 2 * C) {
         const int which = et >> 5, ch = et & 31;
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];   // fixed order over the 8 warps of the half
-        nrd_acc_add(acc + et, t, 16777216.0);
+        nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 16777216.0);
       }
       if (tr) tr[3] = clock64();
       // one warp (lane = channel) polls its channels' words until every CTA has contributed, derives the coefficients (ONE
       // warp's worth of the slow fp64 pipe) and publishes them with the only CTA-wide barrier of the wait
       if (ew == 0) {
         unsigned long long ws, wq;
-        nrd_acc_wait2(acc + lane, acc + C + lane, gridDim.x, ws, wq);
+        nrd_acc_wait2(acc + NRD_ACC_IDX(0, lane), acc + NRD_ACC_IDX(0, C + lane), gridDim.x, ws, wq);
         if (tr) tr[4] = clock64();
+        // every CTA has contributed to this row, so every CTA is done reading the previous one: clean it for the next launch
+        if (blockIdx.x == 0 && k > 0) {
+#pragma unroll
+          for (int r = 0; r < NRD_ACC_REPL; ++r) { (acc - NRD_ACC_ROW)[NRD_ACC_IDX(r, lane)] = 0ull; (acc - NRD_ACC_ROW)[NRD_ACC_IDX(r, C + lane)] = 0ull; }
+        }
         const double S = nrd_acc_value(ws, gridDim.x, 1.0 / 16777216.0), Q = nrd_acc_value(wq, gridDim.x, 1.0 / 16777216.0);
         const double mean = S * a.inv_count;
         double var = Q * a.inv_count - mean * mean;
@@ -782,6 +796,15 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     };
     if (ew == 0) write_ssp(0);
     const float gamma_r = a.gamma[lane];
+    // the LAST row of the previous launch could not be cleaned inside that launch (its readers were still polling): do it now,
+    // long before anyone adds to it -- every CTA reaches that row only after seeing this CTA's contribution to row 0, which
+    // is issued after the fence
+    if (blockIdx.x == 0 && ew == 0) {
+      unsigned long long* last = a.acc + (size_t)(a.NB - 1) * NRD_ACC_ROW;
+#pragma unroll
+      for (int r = 0; r < NRD_ACC_REPL; ++r) { last[NRD_ACC_IDX(r, lane)] = 0ull; last[NRD_ACC_IDX(r, C + lane)] = 0ull; }
+      __threadfence();
+    }
     asm volatile("bar.sync 1, 512;" ::: "memory");
     float4* cfp = reinterpret_cast<float4*>(bnp2 + 128);   // per channel pair: {A1, A2, A3, -, A1', A2', A3', -}, dy = dz*A1 + y*A2 + A3
     float s1 = 0.f, s2 = 0.f;                              // lanes 2c, 2c+1: sums of dz / dz*y over this warp's pixels, channel 16h + c
@@ -821,21 +844,25 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       asm volatile("bar.sync 1, 512;" ::: "memory");
       // cross-CTA sum: fixed point (2^-36) + contributor count in one word per statistic (nrd_common.cuh): order-independent,
       // bit-exact, and no separate grid barrier
-      unsigned long long* acc = a.acc + (size_t)it * 2 * C;
+      unsigned long long* acc = a.acc + (size_t)it * NRD_ACC_ROW;     // [replica][2C] words, NRD_ACC_WS apart
       if (et < 2 * C) {
         const int which = et >> 5, ch = et & 31;
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
-        nrd_acc_add(acc + et, t, 68719476736.0);
+        nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0);
       }
       if (tr) tr[2] = clock64();
       // one warp (lane = channel) polls its channels' words, derives the dy coefficients and publishes them (and the NEXT
       // block's scale/shift pairs: every thread is past phase B of the previous block) with the one CTA barrier that follows
       if (ew == 0) {
         unsigned long long wb, wg;
-        nrd_acc_wait2(acc + lane, acc + C + lane, gridDim.x, wb, wg);
+        nrd_acc_wait2(acc + NRD_ACC_IDX(0, lane), acc + NRD_ACC_IDX(0, C + lane), gridDim.x, wb, wg);
         if (tr) tr[3] = clock64();
+        if (blockIdx.x == 0 && it > 0) {       // the previous row is dead (see the forward kernel): clean it for the next launch
+#pragma unroll
+          for (int r = 0; r < NRD_ACC_REPL; ++r) { (acc - NRD_ACC_ROW)[NRD_ACC_IDX(r, lane)] = 0ull; (acc - NRD_ACC_ROW)[NRD_ACC_IDX(r, C + lane)] = 0ull; }
+        }
         const double db = nrd_acc_value(wb, gridDim.x, 1.0 / 68719476736.0), dgy = nrd_acc_value(wg, gridDim.x, 1.0 / 68719476736.0);
         if (it + 1 < a.NB) write_ssp(it + 1);
         const double mean = (double)mean_r, is = (double)is_r;
@@ -1223,7 +1250,6 @@ int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st) {
   a.gamma = p->params + p->off[3]; a.beta = p->params + p->off[4];
   a.saved = p->saved_stats; a.scale_shift = p->scale_shift; a.running = p->bn_running; a.nbt = (long long*)p->nbt;
   a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.acc = p->bn_acc; a.gbar = p->gbar + NRD_GBAR_PERSIST_FWD;
-  NRD_CHECK_CUDA(cudaMemsetAsync(p->bn_acc, 0, (size_t)p->NB * 2 * p->C * sizeof(unsigned long long), st));
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace; a.dbg_skip_stores = p->dbg_skip_stores;
   a.inv_count = 1.0 / ((double)p->B * NRD_PIX); a.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
   void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
@@ -1240,8 +1266,7 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cud
   a.gamma = p->params + p->off[3]; a.scale_shift = p->scale_shift; a.saved = p->saved_stats;
   a.dgamma = p->grads + p->off[3]; a.dbeta = p->grads + p->off[4];
   a.ys = (const bf16*)p->ys; a.g_pool = (const bf16*)g_pooled; a.idx2 = p->idx2; a.dx0_out = (bf16*)dx0_out;
-  a.acc = p->bn_acc + (size_t)32 * 2 * 64; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
-  NRD_CHECK_CUDA(cudaMemsetAsync(a.acc, 0, (size_t)p->NB * 2 * p->C * sizeof(unsigned long long), st));
+  a.acc = p->bn_acc + (size_t)32 * NRD_ACC_ROW; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.dbg_skip = p->dbg_skip_stores; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(), st));

@@ -100,7 +100,8 @@ struct nrd_plan {
   int fuse_bn_bwd;        // BN+ReLU backward as one cooperative kernel when it fits shared memory
   int tc_persist_fwd;     // all NB blocks of the forward in ONE cooperative kernel (C=32, <= 2 images per CTA)
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
-  unsigned long long* bn_acc; // fixed-point BN-sum accumulators of the persistent kernels: fwd [32][128] then bwd [32][128]
+  unsigned long long* bn_acc; // BN-sum words of the persistent kernels: fwd [32 blocks][NRD_ACC_REPL][64] then bwd, same shape;
+                              // zero between launches (the kernels clean up behind themselves)
   unsigned long long* gbar; // grid-barrier counters (one per cooperative kernel type)
   void* trace;            // optional device buffer for in-kernel clock64 stamps (profiling aid; NULL = off)
   int dbg_skip_stores;    // profiling experiment (NRD_OPT_TRACE value 2)
@@ -182,16 +183,35 @@ static __device__ __forceinline__ unsigned long long nrd_acc_peek(const unsigned
   return v;
 }
 static __device__ __forceinline__ double nrd_acc_value(unsigned long long w, unsigned int nblocks, double inv_scale) {
-  return (double)((long long)(w & (NRD_ACC_CNT1 - 1)) - (long long)((unsigned long long)nblocks * NRD_ACC_BIAS)) * inv_scale;
+  return (double)((long long)w - (long long)((unsigned long long)nblocks * NRD_ACC_BIAS)) * inv_scale;   // w: summed low fields
 }
-// one warp waits until both of each lane's words are complete (all lanes leave together); a ~2 s spin traps
-static __device__ __forceinline__ void nrd_acc_wait2(const unsigned long long* w0, const unsigned long long* w1, unsigned int nblocks,
-                                                     unsigned long long& v0, unsigned long long& v1) {
+// Atomics on ONE address retire at ~27 cycles each in the L2 slice: 108 CTAs arriving together would queue for ~3000 cycles.
+// Every statistic therefore has NRD_ACC_REPL replica words (CTA i adds to replica i % NRD_ACC_REPL, rows of `stride` words
+// apart); the waiting warp reads all replicas, adds the counts and the low fields (still pure integer arithmetic).
+#define NRD_ACC_REPL 1
+// words of one row are NRD_ACC_WS words (128 B) apart: every statistic has its own L2 line, so the ~9500 atomics that
+// arrive within a few hundred cycles spread over 64 lines / L2 slices instead of queueing on 4
+#define NRD_ACC_WS 16
+#define NRD_ACC_IDX(r, e) (((r) * 64 + (e)) * NRD_ACC_WS)
+#define NRD_ACC_ROW (NRD_ACC_REPL * 64 * NRD_ACC_WS)          // words per block row
+// one warp waits until both of each lane's statistics are complete (all lanes leave together); a ~2 s spin traps.
+// v0 / v1 return the summed low fields (feed them to nrd_acc_value).
+static __device__ __forceinline__ void nrd_acc_wait2(const unsigned long long* w0, const unsigned long long* w1,
+                                                     unsigned int nblocks, unsigned long long& v0, unsigned long long& v1) {
   long long t0 = 0;
   int spins = 0;
   while (true) {
-    v0 = nrd_acc_peek(w0); v1 = nrd_acc_peek(w1);
-    const bool done = (v0 >> 56) == nblocks && (v1 >> 56) == nblocks;
+    unsigned long long r0[NRD_ACC_REPL], r1[NRD_ACC_REPL];
+#pragma unroll
+    for (int r = 0; r < NRD_ACC_REPL; ++r) { r0[r] = nrd_acc_peek(w0 + NRD_ACC_IDX(r, 0)); r1[r] = nrd_acc_peek(w1 + NRD_ACC_IDX(r, 0)); }
+    unsigned long long c0 = 0, c1 = 0;
+    v0 = 0; v1 = 0;
+#pragma unroll
+    for (int r = 0; r < NRD_ACC_REPL; ++r) {
+      c0 += r0[r] >> 56; c1 += r1[r] >> 56;
+      v0 += r0[r] & (NRD_ACC_CNT1 - 1); v1 += r1[r] & (NRD_ACC_CNT1 - 1);
+    }
+    const bool done = c0 == nblocks && c1 == nblocks;
     if (__all_sync(0xffffffffu, done)) break;
     if (++spins > 1024) {
       if (t0 == 0) t0 = clock64();

@@ -1507,7 +1507,7 @@ static void carve(nrd_plan* p, char* base, size_t* total) {
   p->wtc_fwd = cv.take<bf16>((size_t)9 * C * C * 2);
   p->wtc_dgrad = cv.take<bf16>((size_t)9 * C * C * 2);
   p->gbar = cv.take<unsigned long long>(256);
-  p->bn_acc = cv.take<unsigned long long>((size_t)2 * 32 * 128 * sizeof(unsigned long long));
+  p->bn_acc = cv.take<unsigned long long>((size_t)2 * 32 * NRD_ACC_ROW * sizeof(unsigned long long));
   *total = cv.off;
 }
 
@@ -1549,6 +1549,8 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
   e = cudaMemset(p->gbar, 0, 256);
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaMemset(grid barrier): %s", cudaGetErrorString(e)); return NRD_ECUDA; }
+  e = cudaMemset(p->bn_acc, 0, (size_t)2 * 32 * NRD_ACC_ROW * sizeof(unsigned long long));   // the persistent kernels keep it zero
+  if (e != cudaSuccess) { delete p; nrd_set_error("cudaMemset(BN accumulators): %s", cudaGetErrorString(e)); return NRD_ECUDA; }
   if (dtype == NRD_BF16) {
     r = nrd_tc_plan_init(p);
     if (r != NRD_OK) { delete p; return r; }   // no silent fallback: the bf16 product path IS the tcgen05 path

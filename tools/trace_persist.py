@@ -46,6 +46,8 @@ if os.environ.get("TRACE_WAITS"):
                                  ("bwd", trb, 2, 3, [(0, 2, "start->atomics"), (3, 4, "combine"), (4, 5, "phaseB"), (5, 6, "phaseC+A")])):
         w = (t[:, 2:9, i1] - t[:, 2:9, i0]).float().mean(1).numpy()
         order = np.argsort(w)
+        wb = (t[:108, :, i1] - t[:108, :, i0]).numpy()
+        print("   per block, 2-image CTAs: min wait", [int(x) for x in wb.min(0)], "argmin", [int(x) for x in wb.argmin(0)], "median", [int(x) for x in np.median(wb, 0)])
         print(f"{name}: mean wait per CTA over blocks 2..8: min {w.min():.0f} (CTA {order[0]}), median {np.median(w):.0f}, max {w.max():.0f} (CTA {order[-1]})")
         print("   least-waiting CTAs:", [(int(c), int(w[c])) for c in order[:12]])
         two = w[: 2 * 148 - 256 if False else 108]
