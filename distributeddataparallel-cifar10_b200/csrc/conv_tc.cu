@@ -510,7 +510,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];   // fixed order over the 8 warps of the half
-        nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 16777216.0);
+        nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 16777216.0, gridDim.x);
       }
       if (tr) tr[3] = clock64();
       // one warp (lane = channel) polls its channels' words until every CTA has contributed, derives the coefficients (ONE
@@ -700,7 +700,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       constexpr uint32_t idesc_d = make_idesc(128, C, 0, 0);      // dgrad: both K-major
       constexpr uint32_t idesc_w = make_idesc(128, 3 * C, 1, 1);  // wgrad: both MN-major, N = three kx taps x C
       mbar_wait(wfull, 0);
-      for (int it = 0; it < a.NB; ++it) {
+      auto dgrad = [&](int it) {
         for (int s = 0; s < nslots; ++s) {
           mbar_wait(dyready(s), (uint32_t)(it & 1));
           tc_fence_after();
@@ -718,7 +718,10 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
             umma_commit(dxfull(s, m));
           }
         }
+      };
+      auto wgrad = [&](int it) {
         for (int s = 0; s < nslots; ++s) {
+          mbar_wait(dyready(s), (uint32_t)(it & 1));
           mbar_wait(xready(s), (uint32_t)(it & 1));
           tc_fence_after();
           const uint32_t sb = a_smem + s * SLOT_BYTES;
@@ -731,8 +734,12 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
           }
           umma_commit(wfree(s));
         }
-      }
+      };
+      for (int it = 0; it + 1 < a.NB; ++it) { dgrad(it); wgrad(it); }
+      // last block: weight gradient first, so the partial store runs under the last dgrad instead of after it
+      wgrad(a.NB - 1);
       umma_commit(wdone);
+      dgrad(a.NB - 1);
     }
   } else {
     // ===== epilogue: 16 warps; warp = (channel half h, tile m, TMEM lane quarter q); thread = one pixel x 16 channels, of =====
@@ -742,6 +749,26 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     const size_t pix_off = (size_t)(pi * 16 + pj) * C + h * 16;               // this thread's 16 channels inside an image
     const int P1 = (pi + 1) * 16 + pj;                                         // its index inside an operand copy (row-haloed)
     const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
+    float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, warp ew == 0 (lane = channel): running dgamma / dbeta over the blocks
+    // y_k of this thread's pixel: prefetched one block ahead with cp.async into this thread's own shared-memory slots,
+    // one commit group per image slot
+    const uint32_t ybuf_s = smem_u32(ybuf);
+    auto load_y = [&](int k) {
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        if (s < nslots) {
+          const bf16* yk = a.ys + (size_t)k * a.act_elems + (size_t)(s == 0 ? img0 : img1) * NRD_PIX * C + pix_off;
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ybuf_s + (uint32_t)(((s * 2 + j) * 512 + et) * 16)),
+                         "l"(reinterpret_cast<const uint4*>(yk) + j) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+      }
+    };
+    // y of 8 channels (chunk j of slot s) of this thread's pixel: one conflict-free LDS.128 from the thread's own slots
+    auto y_chunk = [&](int s, int j) -> uint4 { return ybuf[(s * 2 + j) * 512 + et]; };
+    load_y(a.NB - 1);                                 // the longest latency of the prologue (DRAM) goes first
     uint32_t gpk[2][8];                               // dL/d(out) of this thread's pixel and channels, per image slot, bf16 pairs
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
@@ -769,26 +796,6 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         gpk[s][j * 4 + 0] = v.x; gpk[s][j * 4 + 1] = v.y; gpk[s][j * 4 + 2] = v.z; gpk[s][j * 4 + 3] = v.w;
       }
     }
-    float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, warp ew == 0 (lane = channel): running dgamma / dbeta over the blocks
-    // y_k of this thread's pixel: prefetched one block ahead with cp.async into this thread's own shared-memory slots,
-    // one commit group per image slot
-    const uint32_t ybuf_s = smem_u32(ybuf);
-    auto load_y = [&](int k) {
-#pragma unroll
-      for (int s = 0; s < 2; ++s) {
-        if (s < nslots) {
-          const bf16* yk = a.ys + (size_t)k * a.act_elems + (size_t)(s == 0 ? img0 : img1) * NRD_PIX * C + pix_off;
-#pragma unroll
-          for (int j = 0; j < 2; ++j)
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ybuf_s + (uint32_t)(((s * 2 + j) * 512 + et) * 16)),
-                         "l"(reinterpret_cast<const uint4*>(yk) + j) : "memory");
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-      }
-    };
-    // y of 8 channels (chunk j of slot s) of this thread's pixel: one conflict-free LDS.128 from the thread's own slots
-    auto y_chunk = [&](int s, int j) -> uint4 { return ybuf[(s * 2 + j) * 512 + et]; };
-    load_y(a.NB - 1);
     auto write_ssp = [&](int it2) {                  // scale/shift pairs of block NB-1-it2 -> buffer it2 & 1 (warp ew == 0, lane = channel)
       const int k2 = a.NB - 1 - it2;
       float* d = bnp2 + (it2 & 1) * 64 + (lane >> 1) * 4 + (lane & 1) * 2;
@@ -850,7 +857,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
-        nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0);
+        nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0, gridDim.x);
       }
       if (tr) tr[2] = clock64();
       // one warp (lane = channel) polls its channels' words, derives the dy coefficients and publishes them (and the NEXT
@@ -908,6 +915,23 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       }
       if (tr) tr[5] = clock64();
       if (k > 0 && !a.dbg_skip) load_y(k - 1);          // y_k is dead: fetch the next block's rows while the dgrad MMAs run
+      // ---- weight-gradient partial of this CTA: accumulator lanes (j, ci), columns (kxb, co) ----
+      if (it == a.NB - 1 && h == 0 && m == 0) {
+        mbar_wait(wdone, 0);
+        tc_fence_after();
+        float* outp = a.wpartial + (size_t)blockIdx.x * 9 * C * C;
+        const int j = q, ci = lane;
+  #pragma unroll
+        for (int kxb = 0; kxb < 3; ++kxb) {
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ACCW + kxb * C, v);
+          if (j < 3) {
+            float* dst = outp + (size_t)(j * 3 + (2 - kxb)) * C * C + ci;                     // [tap = (ky, kx)][co][ci]
+  #pragma unroll
+            for (int co = 0; co < 32; ++co) dst[co * C] = v[co];
+          }
+        }
+      }
       // ---- phase C: dx_k = dgrad + g, then straight on to phase A of the next block for the same image ----
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
@@ -936,23 +960,6 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       if (tr) tr[6] = clock64();
     }
     if (blockIdx.x == 0 && ew == 0) { a.dgamma[lane] = dg_acc; a.dbeta[lane] = db_acc; }
-    // ---- weight-gradient partial of this CTA: accumulator lanes (j, ci), columns (kxb, co) ----
-    if (h == 0 && m == 0) {
-      mbar_wait(wdone, 0);
-      tc_fence_after();
-      float* outp = a.wpartial + (size_t)blockIdx.x * 9 * C * C;
-      const int j = q, ci = lane;
-#pragma unroll
-      for (int kxb = 0; kxb < 3; ++kxb) {
-        float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ACCW + kxb * C, v);
-        if (j < 3) {
-          float* dst = outp + (size_t)(j * 3 + (2 - kxb)) * C * C + ci;                     // [tap = (ky, kx)][co][ci]
-#pragma unroll
-          for (int co = 0; co < 32; ++co) dst[co * C] = v[co];
-        }
-      }
-    }
   }
   tc_fence_before();
   __syncthreads();

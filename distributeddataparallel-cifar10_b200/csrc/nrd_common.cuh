@@ -52,6 +52,8 @@ struct nrd_plan {
   int64_t* nbt;
   int64_t off[10];
   const float* images_last;  // images of the last nrd_forward (stem backward reads them)
+  const float* dp_for;       // dlogits pointer whose d(pooled) nrd_forward_loss already computed (consumed by nrd_backward_body)
+  int fuse_head_tail;        // option: fc2 + loss + fc1 dgrad in one launch inside nrd_forward_loss
   const char* dx0_last;      // dL/dx_0 of the last nrd_backward_body (which of the two dx scratch buffers holds it)
   // workspace carve-up
   char* xs;            // (NB+1) saved block inputs x_k, NHWC T
@@ -171,11 +173,15 @@ static inline nrd_bn_sync_args nrd_bn_sync_of(const nrd_plan* p, int training) {
 // A contribution is clamped to +-(2^46 - 1) fixed-point units (see the scale at each use).
 #define NRD_ACC_CNT1 (1ull << 56)
 #define NRD_ACC_BIAS (1ull << 46)
-static __device__ __forceinline__ void nrd_acc_add(unsigned long long* word, float v, double scale) {
+// The atomic RETURNS the old word on purpose: measured (tools/barrier_rate.cu), a round of returning atomics completes in
+// ~2050 cycles on 148 CTAs against ~3000 for fire-and-forget reductions (REDs seem to drain behind the polling loads).  The
+// returned count doubles as a check that the row was clean (a dirty row would otherwise make every CTA spin to the trap).
+static __device__ __forceinline__ void nrd_acc_add(unsigned long long* word, float v, double scale, unsigned int nblocks) {
   long long f = __double2ll_rn((double)v * scale);
   const long long lim = (long long)NRD_ACC_BIAS - 1;
   f = f > lim ? lim : (f < -lim ? -lim : f);
-  atomicAdd(word, NRD_ACC_CNT1 + NRD_ACC_BIAS + (unsigned long long)f);
+  const unsigned long long old = atomicAdd(word, NRD_ACC_CNT1 + NRD_ACC_BIAS + (unsigned long long)f);
+  if ((old >> 56) >= nblocks) __trap();
 }
 static __device__ __forceinline__ unsigned long long nrd_acc_peek(const unsigned long long* word) {
   unsigned long long v;

@@ -1082,6 +1082,101 @@ __global__ void __launch_bounds__(256) k_fc1_dgrad_pooled(const float* __restric
     if (b0 + r < B) dp[(size_t)(b0 + r) * K + i] = from_f<T>(s[r]);
 }
 
+// k_fc2_ce and k_fc1_dgrad_pooled as ONE launch: every CTA of the dgrad grid (8 batch rows x 256 columns of d(pooled)) first
+// redoes the tiny fc2 + cross-entropy of its 8 rows (320 + 80 MACs per row) instead of waiting for a kernel that does it
+// once; the CTAs of column group 0 also publish h1, logits, loss rows and dlogits, and the last of them to finish sums the
+// loss.  Same arithmetic, same order as the two kernels it replaces: results are bit-identical.
+template <typename T>
+__global__ void __launch_bounds__(256) k_head_tail(const float* __restrict__ part, int nsplit, const float* __restrict__ b1,
+                                                   const float* __restrict__ w2, const float* __restrict__ b2,
+                                                   float* __restrict__ h1, float* __restrict__ logits, int B,
+                                                   const int64_t* __restrict__ labels, float gscale, float* __restrict__ loss_rows,
+                                                   float* __restrict__ dlogits, float* __restrict__ loss, unsigned int* __restrict__ counter,
+                                                   const float* __restrict__ w1t, T* __restrict__ dp, int C) {
+  __shared__ float hs[8][33];
+  __shared__ float ls[8][NRD_NCLS];
+  __shared__ float d[8][NRD_FC1_OUT];
+  __shared__ float dl[8 * NRD_NCLS], w2s[NRD_NCLS * NRD_FC1_OUT];
+  __shared__ double red[256];
+  __shared__ int last;
+  const int tid = threadIdx.x, K = 64 * C, per_b = K / 256, b0 = (blockIdx.x / per_b) * 8, cg = blockIdx.x % per_b, i = cg * 256 + tid;
+  const int r = tid >> 5, j = tid & 31, b = b0 + r;
+  nrd_pdl_launch();
+  for (int q = tid; q < NRD_NCLS * NRD_FC1_OUT; q += 256) w2s[q] = w2[q];
+  nrd_pdl_wait();
+  float h = 0.f;
+  if (b < B) {
+    for (int s = 0; s < nsplit; ++s) h += part[((size_t)s * B + b) * NRD_FC1_OUT + j];
+    h = fmaxf(h + b1[j], 0.f);
+    if (cg == 0) h1[(size_t)b * NRD_FC1_OUT + j] = h;
+  }
+  hs[r][j] = h;
+  __syncthreads();
+  if (tid < 8 * NRD_NCLS) {
+    const int rr = tid / NRD_NCLS, c = tid % NRD_NCLS, bb = b0 + rr;
+    float sacc = b2[c];
+#pragma unroll
+    for (int jj = 0; jj < NRD_FC1_OUT; ++jj) sacc = fmaf(hs[rr][jj], w2s[c * NRD_FC1_OUT + jj], sacc);
+    ls[rr][c] = sacc;
+    if (cg == 0 && bb < B) logits[(size_t)bb * NRD_NCLS + c] = sacc;
+  }
+  __syncthreads();
+  if (tid < 8) {
+    const int bb = b0 + tid;
+#pragma unroll
+    for (int c = 0; c < NRD_NCLS; ++c) dl[tid * NRD_NCLS + c] = 0.f;
+    if (bb < B) {
+      float v[NRD_NCLS], m = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = ls[tid][c]; m = fmaxf(m, v[c]); }
+      float s = 0.f;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
+      const long long lab64 = labels[bb];
+      const bool lab_ok = lab64 >= 0 && lab64 < NRD_NCLS;          // an out-of-range label poisons the loss, never the address
+      const int lab = lab_ok ? (int)lab64 : 0;
+      const float inv = 1.f / s, sc = gscale / (float)B;
+      if (cg == 0) loss_rows[bb] = lab_ok ? logf(s) + m - ls[tid][lab] : NAN;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) {
+        const float g = lab_ok ? (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc : NAN;
+        dl[tid * NRD_NCLS + c] = g;
+        if (cg == 0) dlogits[bb * NRD_NCLS + c] = g;
+      }
+    }
+    if (cg == 0) __threadfence();
+  }
+  __syncthreads();
+  d[r][j] = (b < B) ? dh1_elem(dl + r * NRD_NCLS, w2s, j, hs[r][j]) : 0.f;
+  __syncthreads();
+  float s8[8];
+#pragma unroll
+  for (int rr = 0; rr < 8; ++rr) s8[rr] = 0.f;
+  const float4* wrow = reinterpret_cast<const float4*>(w1t + (size_t)i * NRD_FC1_OUT);
+#pragma unroll
+  for (int j4 = 0; j4 < 8; ++j4) {
+    const float4 w = wrow[j4];
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr)
+      s8[rr] += d[rr][j4 * 4] * w.x + d[rr][j4 * 4 + 1] * w.y + d[rr][j4 * 4 + 2] * w.z + d[rr][j4 * 4 + 3] * w.w;
+  }
+#pragma unroll
+  for (int rr = 0; rr < 8; ++rr)
+    if (b0 + rr < B) dp[(size_t)(b0 + rr) * K + i] = from_f<T>(s8[rr]);
+  if (cg != 0) return;
+  // mean loss: the last row group to get here sums the B loss rows in k_ce's fixed order
+  if (tid == 0) last = (atomicAdd(counter, 1u) == (unsigned)((B + 7) / 8) - 1) ? 1 : 0;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  double acc = 0.0;
+  for (int bb = tid; bb < B; bb += 256) acc += (double)__ldcg(loss_rows + bb);
+  red[tid] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
+  if (tid == 0) { *loss = (float)(red[0] / B); *counter = 0u; }
+}
+
 // ------------------------------------------------------------------------------------------
 // fused DDP mean + SGD step: p <- p - lr * inv_world * g                      (main.py:27,39,63)
 // ------------------------------------------------------------------------------------------
@@ -1544,6 +1639,7 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->persist_fwd = 1;
   p->persist_bwd = 1;
   p->use_tc_stem = 1;
+  p->fuse_head_tail = 1;
   p->pdl = 5;     // measured: the consumers of the two persistent kernels (bit 1) lose 13 us when made programmatic dependents
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
@@ -1580,6 +1676,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_PERSIST_BWD: p->persist_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_TC_STEM: p->use_tc_stem = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PDL: p->pdl = value; return NRD_OK;
+    case NRD_OPT_HEAD_TAIL: p->fuse_head_tail = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_RESERVE_SMS:
       NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
       p->reserve_sms = value;
@@ -1697,7 +1794,14 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
   if (dt == NRD_F32) NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<float>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const float*)(p->xs + act * NB), (float*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
   else NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<bf16>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const bf16*)(p->xs + act * NB), (bf16*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
   LAUNCH_CHECK();
-  if (labels)
+  p->dp_for = nullptr;
+  if (labels && dt == NRD_BF16 && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd && p->fuse_head_tail) {
+    // the backward's first kernel rides along: d(pooled) is ready when nrd_backward_body(dlogits) is called
+    NRD_CHECK_CUDA(nrd_launch_pdl(k_head_tail<bf16>, dim3(((B + 7) / 8) * (K / 256)), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B),
+                                  PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B, labels, grad_scale, loss_rows, dlogits, loss_out,
+                                  reinterpret_cast<unsigned int*>(p->gbar + 16), p->w1p, (bf16*)p->dxa, C));
+    p->dp_for = dlogits;
+  } else if (labels)
     NRD_CHECK_CUDA(nrd_launch_pdl(k_fc2_ce, dim3((B + 7) / 8), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B),
                                   p->h1, logits, B, labels, grad_scale, loss_rows, dlogits, loss_out, reinterpret_cast<unsigned int*>(p->gbar + 16)));
   else
@@ -1739,7 +1843,8 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   char* g = p->dxa; char* gn = p->dxb;
   const int K = 64 * C;
   const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd;
-  if (persist) NRD_CHECK_CUDA(nrd_launch_pdl(k_fc1_dgrad_pooled<bf16>, dim3(((B + 7) / 8) * (K / 256)), dim3(256), 0, st, p->pdl & 1, dlogits, p->h1,
+  if (persist && p->dp_for == dlogits) p->dp_for = nullptr;      // nrd_forward_loss already left d(pooled) in the dx scratch
+  else if (persist) NRD_CHECK_CUDA(nrd_launch_pdl(k_fc1_dgrad_pooled<bf16>, dim3(((B + 7) / 8) * (K / 256)), dim3(256), 0, st, p->pdl & 1, dlogits, p->h1,
                                              PRM(P_FC2W), p->w1p, (bf16*)g, B, C));
   else if (dt == NRD_F32) k_fc1_dgrad_unpool<float><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (float*)g, B, C);
   else k_fc1_dgrad_unpool<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (bf16*)g, B, C);

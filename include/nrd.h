@@ -91,6 +91,9 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
  * their prologue done when the predecessor's last CTA retires.  bit 0: loss and fc1-dgrad kernels, bit 2: body gradient
  * reduce and optimizer kernels, bit 1: the kernels right behind the two persistent kernels (measured slower: off). */
 #define NRD_OPT_PDL 6
+/* NRD_OPT_HEAD_TAIL (default 1): nrd_forward_loss also computes the backward's first product, dL/d(pooled), in the same
+ * launch as fc2 and the loss; nrd_backward_body(dlogits) with the pointer nrd_forward_loss filled then starts at the blocks. */
+#define NRD_OPT_HEAD_TAIL 7
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* DDP's per-forward buffer broadcast (torch DDP `broadcast_buffers`, reached from main.py:63 and run in front of every
  * forward, main.py:33) folded into the gradient exchange: `slot` = the 2C floats directly in front of `grads` (so slot +
