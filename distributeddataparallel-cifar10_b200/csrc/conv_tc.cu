@@ -339,6 +339,9 @@ struct PersistFwdArgs {
   double inv_count, unbias; // 1/(B*256), n/(n-1)
   long long* trace;        // optional [gridDim.x][NB][8] clock64 stamps of epilogue thread 0 (profiling aid), or NULL
   int dbg_skip_stores;     // profiling experiment only: drop the global y/x stores (results are then garbage)
+  bf16* pooled;            // [B,8,8,C] maxpool2 of x_NB and its arg-max (position 0..3 in the window), written by the last
+  uint8_t* idx2;           // block's pass 2; NULL = leave the pooling to the head kernel
+  int poll_ns;
 };
 
 __global__ void __launch_bounds__(576, 1)
@@ -510,14 +513,14 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];   // fixed order over the 8 warps of the half
-        nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 16777216.0, gridDim.x);
+        nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 16777216.0), gridDim.x);   // wait for the return: measured faster
       }
       if (tr) tr[3] = clock64();
       // one warp (lane = channel) polls its channels' words until every CTA has contributed, derives the coefficients (ONE
       // warp's worth of the slow fp64 pipe) and publishes them with the only CTA-wide barrier of the wait
       if (ew == 0) {
         unsigned long long ws, wq;
-        nrd_acc_wait2(acc + NRD_ACC_IDX(0, lane), acc + NRD_ACC_IDX(0, C + lane), gridDim.x, ws, wq);
+        nrd_acc_wait2(acc + NRD_ACC_IDX(0, lane), acc + NRD_ACC_IDX(0, C + lane), gridDim.x, ws, wq, a.poll_ns);
         if (tr) tr[4] = clock64();
         // every CTA has contributed to this row, so every CTA is done reading the previous one: clean it for the next launch
         if (blockIdx.x == 0 && k > 0) {
@@ -571,6 +574,34 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
           if (k + 1 < a.NB) {
             if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
             if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
+          } else if (a.pooled) {
+            // last block: max-pool 2x2 of the network body's output right here.  A warp holds two image rows (lanes 0..15 and
+            // 16..31), so the window of the even/even pixel is lanes l, l^1, l^16, l^17 = positions 0..3; first maximum wins
+            // (k_pool_fc1_fwd_part's rule).  The even/even lane writes 8 pooled channels and their arg-max bytes.
+            const uint32_t own[4] = {ok.x, ok.y, ok.z, ok.w};
+            uint32_t pk[4]; uint32_t ib[2] = {0u, 0u};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t o1 = __shfl_xor_sync(0xffffffffu, own[e], 1), o2 = __shfl_xor_sync(0xffffffffu, own[e], 16),
+                             o3 = __shfl_xor_sync(0xffffffffu, own[e], 17);
+              const uint32_t w4[4] = {own[e], o1, o2, o3};
+              float2 mx = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w4[0]));
+              uint32_t i0 = 0, i1 = 0;
+#pragma unroll
+              for (int qq = 1; qq < 4; ++qq) {
+                const float2 vv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w4[qq]));
+                if (vv.x > mx.x) { mx.x = vv.x; i0 = qq; }
+                if (vv.y > mx.y) { mx.y = vv.y; i1 = qq; }
+              }
+              const __nv_bfloat162 pm = __floats2bfloat162_rn(mx.x, mx.y);      // exact: the maxima are bf16 values
+              pk[e] = *reinterpret_cast<const uint32_t*>(&pm);
+              ib[e >> 1] |= (i0 | (i1 << 8)) << ((e & 1) * 16);
+            }
+            if (((pi | pj) & 1) == 0) {
+              const size_t po = ((size_t)(s == 0 ? img0 : img1) * 64 + (pi >> 1) * 8 + (pj >> 1)) * C + ch * 8;
+              *reinterpret_cast<uint4*>(a.pooled + po) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              *reinterpret_cast<uint2*>(a.idx2 + po) = make_uint2(ib[0], ib[1]);
+            }
           }
         }
         // TMEM reads and shared-memory operand writes of this thread for slot s are done: release the slot to the MMA warp
@@ -619,6 +650,7 @@ struct PersistBwdArgs {
   double inv_count;
   int dbg_skip;               // profiling experiment only (results garbage)
   long long* trace;           // optional clock64 stamps (profiling aid), or NULL
+  int poll_ns;
 };
 
 __global__ void __launch_bounds__(576, 1)
@@ -857,14 +889,14 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
-        nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0, gridDim.x);
+        nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0), gridDim.x);   // wait for the return: measured faster
       }
       if (tr) tr[2] = clock64();
       // one warp (lane = channel) polls its channels' words, derives the dy coefficients and publishes them (and the NEXT
       // block's scale/shift pairs: every thread is past phase B of the previous block) with the one CTA barrier that follows
       if (ew == 0) {
         unsigned long long wb, wg;
-        nrd_acc_wait2(acc + NRD_ACC_IDX(0, lane), acc + NRD_ACC_IDX(0, C + lane), gridDim.x, wb, wg);
+        nrd_acc_wait2(acc + NRD_ACC_IDX(0, lane), acc + NRD_ACC_IDX(0, C + lane), gridDim.x, wb, wg, a.poll_ns);
         if (tr) tr[3] = clock64();
         if (blockIdx.x == 0 && it > 0) {       // the previous row is dead (see the forward kernel): clean it for the next launch
 #pragma unroll
@@ -1251,13 +1283,14 @@ int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st) {
 }
 
 // all NB residual blocks in ONE cooperative launch (C = 32, <= 2 images per CTA)
-int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st) {
+int nrd_tc_forward_blocks(nrd_plan* p, int pool, cudaStream_t st) {
   NRD_REQUIRE(p->tc_ready && p->tc_persist_fwd, "persistent block-stack forward not available for this plan");
   PersistFwdArgs a;
   a.gamma = p->params + p->off[3]; a.beta = p->params + p->off[4];
   a.saved = p->saved_stats; a.scale_shift = p->scale_shift; a.running = p->bn_running; a.nbt = (long long*)p->nbt;
   a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.acc = p->bn_acc; a.gbar = p->gbar + NRD_GBAR_PERSIST_FWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace; a.dbg_skip_stores = p->dbg_skip_stores;
+  a.pooled = pool ? (bf16*)p->pooled : nullptr; a.idx2 = p->idx2; a.poll_ns = p->poll_ns;
   a.inv_count = 1.0 / ((double)p->B * NRD_PIX); a.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
   void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_smem(), st));
@@ -1272,7 +1305,7 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cud
   PersistBwdArgs a;
   a.gamma = p->params + p->off[3]; a.scale_shift = p->scale_shift; a.saved = p->saved_stats;
   a.dgamma = p->grads + p->off[3]; a.dbeta = p->grads + p->off[4];
-  a.ys = (const bf16*)p->ys; a.g_pool = (const bf16*)g_pooled; a.idx2 = p->idx2; a.dx0_out = (bf16*)dx0_out;
+  a.ys = (const bf16*)p->ys; a.g_pool = (const bf16*)g_pooled; a.idx2 = p->idx2; a.poll_ns = p->poll_ns; a.dx0_out = (bf16*)dx0_out;
   a.acc = p->bn_acc + (size_t)32 * NRD_ACC_ROW; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.dbg_skip = p->dbg_skip_stores; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};

@@ -53,6 +53,7 @@ struct nrd_plan {
   int64_t off[10];
   const float* images_last;  // images of the last nrd_forward (stem backward reads them)
   const float* dp_for;       // dlogits pointer whose d(pooled) nrd_forward_loss already computed (consumed by nrd_backward_body)
+  int fuse_pool;             // option: the persistent forward's last block also does the max-pool in front of fc1
   int fuse_head_tail;        // option: fc2 + loss + fc1 dgrad in one launch inside nrd_forward_loss
   const char* dx0_last;      // dL/dx_0 of the last nrd_backward_body (which of the two dx scratch buffers holds it)
   // workspace carve-up
@@ -90,6 +91,7 @@ struct nrd_plan {
   CUtensorMap tm_xall;    // all x_k as one 5-D tensor (persistent backward)
   CUtensorMap tm_xst, tm_yst; // x_k / y_k stacks, whole-image boxes: bulk tensor STORES of the persistent forward
   int tc_ready;
+  int poll_ns;            // experiment knob (env NRD_POLL_NS at plan creation): back-off between polls of the BN exchange
   int pdl;                // option: programmatic dependent launch between the small kernels of the step
   int reserve_sms;        // option: SMs the cooperative kernels leave free (a concurrent NCCL kernel needs somewhere to run)
   float* bn_sync;         // optional [2C] slot in front of the gradient vector: BN running stats ride the body bucket's all-reduce
@@ -176,11 +178,15 @@ static inline nrd_bn_sync_args nrd_bn_sync_of(const nrd_plan* p, int training) {
 // The atomic RETURNS the old word on purpose: measured (tools/barrier_rate.cu), a round of returning atomics completes in
 // ~2050 cycles on 148 CTAs against ~3000 for fire-and-forget reductions (REDs seem to drain behind the polling loads).  The
 // returned count doubles as a check that the row was clean (a dirty row would otherwise make every CTA spin to the trap).
-static __device__ __forceinline__ void nrd_acc_add(unsigned long long* word, float v, double scale, unsigned int nblocks) {
+static __device__ __forceinline__ unsigned long long nrd_acc_add(unsigned long long* word, float v, double scale) {
   long long f = __double2ll_rn((double)v * scale);
   const long long lim = (long long)NRD_ACC_BIAS - 1;
   f = f > lim ? lim : (f < -lim ? -lim : f);
-  const unsigned long long old = atomicAdd(word, NRD_ACC_CNT1 + NRD_ACC_BIAS + (unsigned long long)f);
+  return atomicAdd(word, NRD_ACC_CNT1 + NRD_ACC_BIAS + (unsigned long long)f);
+}
+// checking right away, i.e. waiting for the atomic's return before the first poll, measured 2.5 us per kernel FASTER than
+// polling beside the outstanding atomic
+static __device__ __forceinline__ void nrd_acc_check(unsigned long long old, unsigned int nblocks) {
   if ((old >> 56) >= nblocks) __trap();
 }
 static __device__ __forceinline__ unsigned long long nrd_acc_peek(const unsigned long long* word) {
@@ -203,7 +209,7 @@ static __device__ __forceinline__ double nrd_acc_value(unsigned long long w, uns
 // one warp waits until both of each lane's statistics are complete (all lanes leave together); a ~2 s spin traps.
 // v0 / v1 return the summed low fields (feed them to nrd_acc_value).
 static __device__ __forceinline__ void nrd_acc_wait2(const unsigned long long* w0, const unsigned long long* w1,
-                                                     unsigned int nblocks, unsigned long long& v0, unsigned long long& v1) {
+                                                     unsigned int nblocks, unsigned long long& v0, unsigned long long& v1, int poll_ns = 0) {
   long long t0 = 0;
   int spins = 0;
   while (true) {
@@ -219,6 +225,7 @@ static __device__ __forceinline__ void nrd_acc_wait2(const unsigned long long* w
     }
     const bool done = c0 == nblocks && c1 == nblocks;
     if (__all_sync(0xffffffffu, done)) break;
+    if (poll_ns) __nanosleep(poll_ns);
     if (++spins > 1024) {
       if (t0 == 0) t0 = clock64();
       else if (clock64() - t0 > 4000000000LL) __trap();
@@ -241,7 +248,8 @@ int nrd_tc_stem_fwd(nrd_plan* p, const float* images, int training, cudaStream_t
 int nrd_tc_stem_bwd(nrd_plan* p, const float* images, const void* g0, cudaStream_t st);   // per-CTA partials only
 int nrd_tc_stats_blocks(const nrd_plan* p);
 int nrd_tc_wgrad_blocks(const nrd_plan* p);
-int nrd_tc_forward_blocks(nrd_plan* p, cudaStream_t st);                        // x_0 -> all y_k, x_{k+1}: one launch
+int nrd_tc_forward_blocks(nrd_plan* p, int pool, cudaStream_t st);              // x_0 -> all y_k, x_{k+1}: one launch
+                                                                                // (pool: also maxpool2(x_NB) -> pooled, idx2)
 int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cudaStream_t st);   // all blocks' backward, one launch;
                                                                             // g_pooled = dL/d(pooled) [B,8,8,C]
 int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st);                      // y_k, x_{k+1}, BN stats + EMA, one launch

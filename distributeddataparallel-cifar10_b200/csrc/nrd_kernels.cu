@@ -2,6 +2,7 @@
 // non-GEMM op of the bf16 path).  Activations are NHWC, T = float | bf16; parameters, gradients,
 // BN statistics and all accumulation are fp32 (fp64 for the final cross-CTA combines).
 // Every cross-CTA reduction is two-stage with a fixed summation order => bitwise reproducible.
+#include <stdlib.h>
 #include "nrd_common.cuh"
 #include <stdarg.h>
 
@@ -766,6 +767,39 @@ __global__ void __launch_bounds__(256) k_pool_fc1_fwd_part(const T* __restrict__
       for (int j = 0; j < 8; ++j) pb[j] = (uint8_t)mi[j];
       *reinterpret_cast<uint2*>(idx2 + (size_t)b * K + kk) = pk;
     }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ps[r * 129 + c8 * 8 + j] = m[j];
+  }
+  __syncthreads();
+  const int r = tid >> 3, jq = tid & 7;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 8
+  for (int k = 0; k < 128; ++k) {
+    const float pv = ps[r * 129 + k];
+    const float4 w = *reinterpret_cast<const float4*>(ws + k * 32 + jq * 4);
+    a0 = fmaf(pv, w.x, a0); a1 = fmaf(pv, w.y, a1); a2 = fmaf(pv, w.z, a2); a3 = fmaf(pv, w.w, a3);
+  }
+  if (b0 + r < B)
+    *reinterpret_cast<float4*>(part + ((size_t)blockIdx.y * B + b0 + r) * NRD_FC1_OUT + jq * 4) = make_float4(a0, a1, a2, a3);
+}
+
+// the same split-K fc1 when the pooling has already been done (persistent forward): reads pooled [B,8,8,C]
+template <typename T>
+__global__ void __launch_bounds__(256) k_fc1_fwd_part(const T* __restrict__ pooled, const float* __restrict__ w1t, float* __restrict__ part,
+                                                      int B, int C) {
+  __shared__ __align__(16) float ws[128 * 32];
+  __shared__ float ps[32 * 129];
+  const int tid = threadIdx.x, b0 = blockIdx.x * 32, k0 = blockIdx.y * 128, K = 64 * C;
+  nrd_pdl_launch();
+  for (int i = tid; i < 128 * 32 / 4; i += 256)
+    reinterpret_cast<float4*>(ws)[i] = reinterpret_cast<const float4*>(w1t + (size_t)k0 * 32)[i];
+  nrd_pdl_wait();
+  for (int i = tid; i < 32 * 16; i += 256) {
+    const int r = i >> 4, c8 = i & 15, b = b0 + r;
+    float m[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m[j] = 0.f;
+    if (b < B) ld8(pooled + (size_t)b * K + k0 + c8 * 8, m);
 #pragma unroll
     for (int j = 0; j < 8; ++j) ps[r * 129 + c8 * 8 + j] = m[j];
   }
@@ -1640,6 +1674,8 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->persist_bwd = 1;
   p->use_tc_stem = 1;
   p->fuse_head_tail = 1;
+  p->fuse_pool = 0;          // measured 1 us slower per step than pooling in the fc1 kernel (it sits on the blocks' critical path)
+  { const char* e = getenv("NRD_POLL_NS"); p->poll_ns = e ? atoi(e) : 0; }
   p->pdl = 5;     // measured: the consumers of the two persistent kernels (bit 1) lose 13 us when made programmatic dependents
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); return NRD_ECUDA; }
@@ -1677,6 +1713,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_TC_STEM: p->use_tc_stem = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_PDL: p->pdl = value; return NRD_OK;
     case NRD_OPT_HEAD_TAIL: p->fuse_head_tail = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_FUSE_POOL: p->fuse_pool = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_RESERVE_SMS:
       NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
       p->reserve_sms = value;
@@ -1771,7 +1808,8 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
   else NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st, nrd_bn_sync_of(p, training)));
   if (!training) { k_bn_eval_coeffs<<<1, 64, 0, st>>>(p->bn_running, PRM(P_BNG), PRM(P_BNB), C, p->scale_shift); LAUNCH_CHECK(); }
   const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_fwd;
-  if (persist) NRD_TRY(nrd_tc_forward_blocks(p, st));
+  const bool pool_in_blocks = persist && p->fuse_pool;
+  if (persist) NRD_TRY(nrd_tc_forward_blocks(p, pool_in_blocks ? 1 : 0, st));       // ... and the max-pool behind the last block
   for (int k = 0; k < (persist ? 0 : NB); ++k) {
     char* xk = p->xs + act * k; char* yk = p->ys + act * k; char* xn = p->xs + act * (k + 1);
     float* ss = training ? p->scale_shift + (size_t)k * 2 * C : p->scale_shift;
@@ -1791,7 +1829,8 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
   }
   const int K = 64 * C;
   const dim3 g1((B + 31) / 32, K / 128);
-  if (dt == NRD_F32) NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<float>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const float*)(p->xs + act * NB), (float*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
+  if (pool_in_blocks) NRD_CHECK_CUDA(nrd_launch_pdl(k_fc1_fwd_part<bf16>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const bf16*)p->pooled, p->w1p, p->fc1_part, B, C));
+  else if (dt == NRD_F32) NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<float>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const float*)(p->xs + act * NB), (float*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
   else NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<bf16>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const bf16*)(p->xs + act * NB), (bf16*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
   LAUNCH_CHECK();
   p->dp_for = nullptr;
@@ -1925,7 +1964,7 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       return stem_bwd_any(p->images_last, p->dx0_last, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st);
     case NRD_OP_FWD_BLOCKS:
       NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent forward not available for this plan");
-      return nrd_tc_forward_blocks(p, st);
+      return nrd_tc_forward_blocks(p, 0, st);
     case NRD_OP_BWD_BLOCKS:
       NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent backward not available for this plan");
       return nrd_tc_backward_blocks(p, p->dxa, p->dxb, st);

@@ -94,6 +94,9 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
 /* NRD_OPT_HEAD_TAIL (default 1): nrd_forward_loss also computes the backward's first product, dL/d(pooled), in the same
  * launch as fc2 and the loss; nrd_backward_body(dlogits) with the pointer nrd_forward_loss filled then starts at the blocks. */
 #define NRD_OPT_HEAD_TAIL 7
+/* NRD_OPT_FUSE_POOL (default 0: measured 1 us per step slower): the persistent forward max-pools its last block's output itself (warp shuffles over the
+ * 2x2 window) and fc1 reads the pooled tensor, instead of a head kernel re-reading x_NB. */
+#define NRD_OPT_FUSE_POOL 8
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* DDP's per-forward buffer broadcast (torch DDP `broadcast_buffers`, reached from main.py:63 and run in front of every
  * forward, main.py:33) folded into the gradient exchange: `slot` = the 2C floats directly in front of `grads` (so slot +

@@ -182,3 +182,21 @@ def test_tensor_core_stem_matches_torch_and_cuda_core_stem(B):
         torch.cuda.synchronize()
         part[name] = pl.tensor_view(9, 0).view(torch.float32).view(-1, 28, 32).double().sum(0).cpu()
     assert rell2(part["tc"], part["cc"]) < 1e-2 and cosine(part["tc"], part["cc"]) > 0.9999, rell2(part["tc"], part["cc"])
+
+
+def test_pool_fused_into_persistent_forward_is_bitwise_the_head_kernels_pool():
+    """NRD_OPT_FUSE_POOL: the last block of the persistent forward max-pools its own output (warp shuffles, first maximum
+    wins) and fc1 reads the pooled tensor: pooled values, arg-max bytes, logits and gradients equal the default path's."""
+    B = 200
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for fuse in (0, 1):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(32, 10, dtype="bf16").to(DEV)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 8, fuse))
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        torch.cuda.synchronize()
+        res.append((out.detach().clone(), pl.tensor_view(3, 0).clone(), m.engine.flat_grads.clone()))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2])
