@@ -257,8 +257,8 @@ def main():
             v["share"] = round(v["us"] * v["per_step"] / tot, 3)
         dom = max(breakdown, key=lambda k: breakdown[k]["us"] * breakdown[k]["per_step"])
         d = breakdown[dom]
-        # DRAM bytes per launch from the committed ncu --set full capture (profiles/r01_step_v6_persistent.md), same config only
-        ncu_traffic = {"bwd_blocks(persistent)": 88448256 + 3574272, "fwd_blocks(persistent)": 4270848 + 29913600}
+        # DRAM bytes per launch from the committed ncu --set full capture (profiles/r01_step_v9_final.md), same config only
+        ncu_traffic = {"bwd_blocks(persistent)": 85643776 + 3396096, "fwd_blocks(persistent)": 4361472 + 32077056}
         traffic = ncu_traffic.get(dom) if (B, C, NB, args.dtype) == (256, 32, 10, "bf16") else None
         roof = {"bound": "hbm", "kernel": dom, "achieved": d["gbs"], "peak": hbm, "unit": "GB/s", "frac": round(d["gbs"] / hbm, 4),
                 "traffic": traffic, "peak_source": peak_kind, "launch_us": d["us"], "algo_bytes_per_launch": d["algo_bytes"],
