@@ -273,7 +273,7 @@ def main():
                 "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
                 "config": {"workload": f"NetResDeep C={C} NB={NB} DDP train step (BASELINE configs[1]), per-rank batch {B}",
                            "global_batch": B * world, "parallelism": f"dp{world}", "l2": "flushed between steps (256 MiB write, untimed)",
-                           "graph": not args.no_graph, "lr": 1e-2},
+                           "graph": not args.no_graph, "body_exchange": ("p2p" if getattr(step, "p2p", False) else ("nccl" if world > 1 else None)), "lr": 1e-2},
                 "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps) if launches_per_step else None,
                 "launches_per_step": launches_per_step, "clocks": clocks, "roofline": roof, "step_roofline": step_roof,
                 "breakdown": breakdown, "loss_last": loss_last}

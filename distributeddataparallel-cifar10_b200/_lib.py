@@ -36,6 +36,11 @@ _PROTOS = {
     "nrd_plan_conv_impl": (i32, [vp]),
     "nrd_plan_set_option": (i32, [vp, i32, i32]),
     "nrd_plan_set_bn_sync": (i32, [vp, vp, f32, f32]),
+    "nrd_exchange_bytes": (sz, [i32, i32]),
+    "nrd_exchange_alloc": (i32, [i32, sz, C.POINTER(vp), vp]),
+    "nrd_exchange_open": (i32, [i32, vp, C.POINTER(vp)]),
+    "nrd_exchange_release": (i32, [vp, i32]),
+    "nrd_plan_set_exchange": (i32, [vp, i32, i32, C.POINTER(vp)]),
     "nrd_plan_tensor": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)]),
     "nrd_pack_weights": (i32, [vp, vp]),
     "nrd_forward": (i32, [vp, vp, vp, i32, vp]),

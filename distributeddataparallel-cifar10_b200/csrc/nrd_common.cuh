@@ -44,6 +44,75 @@ void nrd_set_error(const char* fmt, ...);
     if (r__ != NRD_OK) return r__;                                                             \
   } while (0)
 
+// ---- gradient exchange over NVLink peer memory (graph path of DDP, one node, <= 8 ranks) ----------------------------------
+// Every rank owns one exchange buffer, mapped into every other rank's address space (CUDA IPC):
+//   data   [2 parities][world][nx] floats   slot (parity, r) = what rank r produced in a step of that parity
+//   ctrl   u64 words (NRD_XCHG_*): per bucket (body, head) flags [2][NRD_XCHG_MAX_WORLD] = epoch of the data rank r put in
+//          slot (parity, r), and the producing kernel's local epoch and arrival counter
+// nx = 2C (BN running-stat slot) + all gradients in flat order.  Body bucket: the kernel that finishes the body gradients
+// (k_body_reduce) stores every value straight into slot (parity, own rank) of ALL ranks' buffers and its last CTA publishes
+// the epoch in every rank's flag.  Head bucket: k_xchg_push_head does the same for fc1/fc2 gradients on the side stream,
+// under the body backward.  The optimizer kernel (k_sgd_pack) waits for the world's flags in its OWN buffer and sums the
+// slots in rank order: one NVLink write latency instead of a collective launch, no NCCL kernel competing for SMs, and a sum
+// order that is the same on every rank.  Two parities: a rank one step ahead never overwrites data a peer is still reading.
+#define NRD_XCHG_MAX_WORLD 8
+#define NRD_XCHG_BUCKET_WORDS (2 * NRD_XCHG_MAX_WORLD + 2)      // flags[2][8], epoch, arrive
+#define NRD_XCHG_EPOCH (2 * NRD_XCHG_MAX_WORLD)
+#define NRD_XCHG_ARRIVE (2 * NRD_XCHG_MAX_WORLD + 1)
+#define NRD_XCHG_CTRL_WORDS (2 * NRD_XCHG_BUCKET_WORDS)         // bucket 0 = body, bucket 1 = head
+struct nrd_xchg_args {
+  float* peer[NRD_XCHG_MAX_WORLD];
+  int world, rank, nx;          // world == 0: exchange off
+};
+static __host__ __device__ __forceinline__ size_t nrd_xchg_flags_off(int world, int nx) {
+  return (((size_t)2 * world * nx * sizeof(float)) + 127) & ~(size_t)127;
+}
+static __host__ __device__ __forceinline__ size_t nrd_xchg_bytes(int world, int nx) {
+  return nrd_xchg_flags_off(world, nx) + NRD_XCHG_CTRL_WORDS * sizeof(unsigned long long);
+}
+static __device__ __forceinline__ unsigned long long* nrd_xchg_flags(float* base, int world, int nx, int bucket = 0) {
+  return reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(base) + nrd_xchg_flags_off(world, nx)) + bucket * NRD_XCHG_BUCKET_WORDS;
+}
+// last step of a producing kernel (every thread calls it after its peer stores): the CTA that arrives last publishes `epoch`
+// in every rank's flag of this bucket and records it locally
+static __device__ __forceinline__ void nrd_xchg_publish(const nrd_xchg_args& x, int bucket, unsigned long long epoch) {
+  __threadfence_system();                     // this thread's peer stores are performed before the CTA reports in
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long* ctrl = nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, bucket);
+    unsigned int* arrive = reinterpret_cast<unsigned int*>(ctrl + NRD_XCHG_ARRIVE);
+    if (atomicAdd(arrive, 1u) == gridDim.x * gridDim.y - 1) {
+      *arrive = 0u;
+      __threadfence_system();
+      for (int p = 0; p < x.world; ++p) {
+        unsigned long long* f = nrd_xchg_flags(x.peer[p], x.world, x.nx, bucket) + (epoch & 1) * NRD_XCHG_MAX_WORLD + x.rank;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(epoch) : "memory");
+      }
+      ctrl[NRD_XCHG_EPOCH] = epoch;
+    }
+  }
+}
+// consumer: threads 0 .. world-1 of the CTA wait for the world's flags of a bucket in the own buffer; returns the epoch
+static __device__ __forceinline__ unsigned long long nrd_xchg_wait(const nrd_xchg_args& x, int bucket, int t) {
+  unsigned long long* ctrl = nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, bucket);
+  const unsigned long long epoch = ctrl[NRD_XCHG_EPOCH];       // set by this step's producer (ordered before us by the stream)
+  if (t >= 0 && t < x.world) {
+    const unsigned long long* f = ctrl + (epoch & 1) * NRD_XCHG_MAX_WORLD + t;
+    unsigned long long v;
+    long long t0 = 0;
+    int spins = 0;
+    while (true) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+      if (v >= epoch) break;
+      if (++spins > 4096) {
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > 60000000000LL) __trap();      // ~30 s: a peer is gone
+      }
+    }
+  }
+  return epoch;
+}
+
 struct nrd_plan {
   int device, B, C, NB, dtype, conv_impl;
   size_t esz;       // activation element size
@@ -91,6 +160,7 @@ struct nrd_plan {
   CUtensorMap tm_xall;    // all x_k as one 5-D tensor (persistent backward)
   CUtensorMap tm_xst, tm_yst; // x_k / y_k stacks, whole-image boxes: bulk tensor STORES of the persistent forward
   int tc_ready;
+  nrd_xchg_args xchg;     // peer-memory gradient exchange (nrd_plan_set_exchange); world == 0: off
   int poll_ns;            // experiment knob (env NRD_POLL_NS at plan creation): back-off between polls of the BN exchange
   int pdl;                // option: programmatic dependent launch between the small kernels of the step
   int reserve_sms;        // option: SMs the cooperative kernels leave free (a concurrent NCCL kernel needs somewhere to run)

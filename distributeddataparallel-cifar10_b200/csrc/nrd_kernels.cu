@@ -216,16 +216,34 @@ __global__ void __launch_bounds__(256) k_stem_bwd(const float* __restrict__ img,
   }
 }
 
-// conv-weight and stem partials in ONE launch: CTAs [0, 9C*C/32) reduce the conv partials, the rest the stem partials
+// conv-weight and stem partials in ONE launch: CTAs [0, 9C*C/32) reduce the conv partials, the rest the stem partials.
+// With the peer-memory exchange on (x.world > 0) every finished gradient is also stored into this rank's slot of EVERY rank's
+// exchange buffer, the last CTA adds the BN gradients (written by the persistent backward) and the BN running-stat slot, and
+// whichever CTA finishes last publishes the epoch in every rank's flag (nrd_common.cuh).
 __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ wpartial, int wblk, const float* __restrict__ spartial, int sblk,
                                                      int C, float* __restrict__ dw, float* __restrict__ dw1, float* __restrict__ db1,
-                                                     float* __restrict__ bn_sync, const float* __restrict__ running, float contrib) {
+                                                     float* __restrict__ bn_sync, const float* __restrict__ running, float contrib,
+                                                     nrd_xchg_args x, const float* grads_base, int off_bng, int off_rbw, int off_c1w) {
   __shared__ double red[8][33];
   nrd_pdl_launch();
   nrd_pdl_wait();
+  const bool px = x.world > 0;
+  // bumped by the last CTA, after every CTA has read it
+  const unsigned long long epoch = px ? nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, 0)[NRD_XCHG_EPOCH] + 1 : 0;
+  const size_t slot = px ? ((size_t)(epoch & 1) * x.world + x.rank) * x.nx : 0;
+  auto push = [&](size_t idx, float v) {
+    for (int p = 0; p < x.world; ++p) x.peer[p][slot + idx] = v;
+  };
   // DDP buffer sync riding the body bucket: rank 0 contributes world_size * running, the others exact zeros
-  if (bn_sync && blockIdx.x == gridDim.x - 1)
-    for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) bn_sync[j] = contrib != 0.f ? running[j] * contrib : 0.f;
+  if (blockIdx.x == gridDim.x - 1) {
+    for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
+      if (bn_sync || px) {
+        const float v = contrib != 0.f ? running[j] * contrib : 0.f;
+        if (bn_sync) bn_sync[j] = v;
+        if (px) { push(j, v); push(2 * C + off_bng + j, grads_base[off_bng + j]); }   // ... and dgamma | dbeta
+      }
+    }
+  }
   const int o = threadIdx.x & 31, r = threadIdx.x >> 5, nconv = 9 * C * C / 32;
   const bool conv = (int)blockIdx.x < nconv;
   const int i = (conv ? blockIdx.x : blockIdx.x - nconv) * 32 + o, n = conv ? 9 * C * C : 28 * C, nblk = conv ? wblk : sblk;
@@ -239,9 +257,32 @@ __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ w
     double tot = 0.0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) tot += red[k][o];
-    if (conv) { const int t = i / (C * C), co = (i / C) % C, ci = i % C; dw[((size_t)co * C + ci) * 9 + t] = (float)tot; }
-    else { const int k = i / C, co = i % C; if (k < 27) dw1[co * 27 + k] = (float)tot; else db1[co] = (float)tot; }
+    float* q;
+    if (conv) { const int t = i / (C * C), co = (i / C) % C, ci = i % C; q = dw + ((size_t)co * C + ci) * 9 + t; }
+    else { const int k = i / C, co = i % C; q = k < 27 ? dw1 + co * 27 + k : db1 + co; }
+    *q = (float)tot;
+    // the slot keeps THIS kernel's order (conv [tap][co][ci], conv1 [tap][co]): a warp's 32 values are 128 contiguous bytes per
+    // peer instead of 32 scattered 4-byte NVLink writes; k_sgd_pack applies the permutation when it reads (locally)
+    if (px) push(2 * C + (conv ? off_rbw + i : (i < 27 * C ? off_c1w + i : (size_t)(q - grads_base))), (float)tot);
   }
+  if (px) nrd_xchg_publish(x, 0, epoch);
+}
+
+// head bucket of the peer-memory exchange: this rank's fc1 / fc2 gradients (flat range [lo, hi)) into its slot of every
+// rank's buffer; runs on the side stream behind the head weight-gradient kernels, i.e. under the body backward
+__global__ void __launch_bounds__(256) k_xchg_push_head(nrd_xchg_args x, const float* __restrict__ grads, int lo, int hi, int C) {
+  const unsigned long long epoch = nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, 1)[NRD_XCHG_EPOCH] + 1;
+  const size_t slot = ((size_t)(epoch & 1) * x.world + x.rank) * x.nx + 2 * C;
+  const int n4 = (hi - lo) / 4;                       // lo, 2C and nx are multiples of 4: 16-byte stores
+  for (int v4 = blockIdx.x * blockDim.x + threadIdx.x; v4 < n4; v4 += gridDim.x * blockDim.x) {
+    const float4 v = *reinterpret_cast<const float4*>(grads + lo + v4 * 4);
+    for (int p = 0; p < x.world; ++p) *reinterpret_cast<float4*>(x.peer[p] + slot + lo + v4 * 4) = v;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (hi - lo) - n4 * 4) {
+    const int i = lo + n4 * 4 + threadIdx.x;
+    for (int p = 0; p < x.world; ++p) x.peer[p][slot + i] = grads[i];
+  }
+  nrd_xchg_publish(x, 1, epoch);
 }
 
 // CTA = 32 outputs x 8 row classes, fixed-order combine
@@ -1221,15 +1262,46 @@ __global__ void k_sgd(float* __restrict__ p, const float* __restrict__ g, size_t
 
 // p <- p - step_scale * g over the whole flat vector AND the packed copies of the three tensors that have them, one launch
 // (off[] = flat offsets of the 9 tensors; index order as k_pack_weights)
-__global__ void k_sgd_pack(float* __restrict__ p, const float* __restrict__ g, float step_scale, int C, const long long* __restrict__ offp,
+__global__ void k_sgd_pack(float* __restrict__ p, float* g, float step_scale, int C, const long long* __restrict__ offp,
                            long long o_c1w, long long o_rbw, long long o_fc1w, long long n,
                            float* __restrict__ w_fwd, float* __restrict__ w_dgrad, bf16* __restrict__ wtc_fwd, bf16* __restrict__ wtc_dgrad,
-                           float* __restrict__ w1p, float* __restrict__ conv1_wp) {
+                           float* __restrict__ w1p, float* __restrict__ conv1_wp, nrd_xchg_args x, float* bn_sync) {
   (void)offp;
   nrd_pdl_wait();
+  // peer-memory exchange: every gradient is the rank-ordered sum of the world's slots in OUR buffer (body bucket [0, o_fc1w)
+  // and head bucket [o_fc1w, n) arrive separately)
+  const bool px = x.world > 0;
+  const float* slots = nullptr;
+  const float* slots_head = nullptr;
+  if (px) {
+    float* own = x.peer[x.rank];
+    const unsigned long long e_body = nrd_xchg_wait(x, 0, (int)threadIdx.x);
+    const unsigned long long e_head = nrd_xchg_wait(x, 1, (int)threadIdx.x - 32);
+    __syncthreads();
+    slots = own + (size_t)(e_body & 1) * x.world * x.nx;
+    slots_head = own + (size_t)(e_head & 1) * x.world * x.nx;
+    if (blockIdx.x == 0 && bn_sync)
+      for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
+        float sres = 0.f;
+        for (int r = 0; r < x.world; ++r) sres += __ldcg(slots + (size_t)r * x.nx + j);
+        bn_sync[j] = sres;
+      }
+  }
   const long long n_rb = (long long)C * C * 9, n_fc1 = (long long)NRD_FC1_OUT * 64 * C, n_c1 = (long long)C * 27;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const float w = fmaf(-step_scale, g[i], p[i]);
+    float gi;
+    if (px) {
+      const float* sl = i < o_fc1w ? slots : slots_head;
+      long long si = i;                            // slot index: k_body_reduce's order for the two conv weights
+      if (i >= o_rbw && i < o_rbw + n_rb) { const int q = (int)(i - o_rbw), co = q / (C * 9), r9 = q % (C * 9), ci = r9 / 9, t = r9 % 9; si = o_rbw + ((long long)t * C + co) * C + ci; }
+      else if (i >= o_c1w && i < o_c1w + n_c1) { const int q = (int)(i - o_c1w), co = q / 27, k = q % 27; si = o_c1w + (long long)k * C + co; }
+      gi = 0.f;
+      for (int r = 0; r < x.world; ++r) gi += __ldcg(sl + (size_t)r * x.nx + 2 * C + si);
+      g[i] = gi;                                   // .grad keeps holding the world's sum, as after the all-reduce
+    } else {
+      gi = g[i];
+    }
+    const float w = fmaf(-step_scale, gi, p[i]);
     p[i] = w;
     if (i >= o_rbw && i < o_rbw + n_rb) {
       const int q = (int)(i - o_rbw), co = q / (C * 9), r = q % (C * 9), ci = r / 9, t = r % 9;
@@ -1734,6 +1806,54 @@ extern "C" int nrd_plan_set_bn_sync(nrd_plan* p, float* slot, float contrib, flo
   return NRD_OK;
 }
 
+// ---- peer-memory gradient exchange: buffers and wiring -------------------------------------------------------------------
+extern "C" size_t nrd_exchange_bytes(int C, int world) {
+  int64_t off[10];
+  if (world < 2 || world > NRD_XCHG_MAX_WORLD || nrd_param_offsets(C, off) != NRD_OK) return 0;
+  return nrd_xchg_bytes(world, (2 * C + (int)off[9] + 3) & ~3);
+}
+
+// The exchange buffer is the one piece of device memory the library allocates itself: it must be a whole cudaMalloc
+// allocation to be exportable with cudaIpcGetMemHandle (a sub-range of a framework's caching allocator is not).
+extern "C" int nrd_exchange_alloc(int device, size_t bytes, void** ptr, void* ipc_handle_64) {
+  NRD_REQUIRE(ptr && ipc_handle_64 && bytes > 0, "nrd_exchange_alloc: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  NRD_CHECK_CUDA(cudaSetDevice(device));
+  NRD_CHECK_CUDA(cudaMalloc(ptr, bytes));
+  NRD_CHECK_CUDA(cudaMemset(*ptr, 0, bytes));
+  NRD_CHECK_CUDA(cudaDeviceSynchronize());
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, *ptr);
+  if (e != cudaSuccess) { cudaFree(*ptr); *ptr = nullptr; nrd_set_error("cudaIpcGetMemHandle: %s", cudaGetErrorString(e)); return NRD_ECUDA; }
+  memcpy(ipc_handle_64, &h, 64);
+  return NRD_OK;
+}
+
+extern "C" int nrd_exchange_open(int device, const void* ipc_handle_64, void** ptr) {
+  NRD_REQUIRE(ptr && ipc_handle_64, "nrd_exchange_open: null pointer");
+  NRD_CHECK_CUDA(cudaSetDevice(device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, ipc_handle_64, 64);
+  NRD_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return NRD_OK;
+}
+
+extern "C" int nrd_exchange_release(void* ptr, int opened) {
+  if (!ptr) return NRD_OK;
+  if (opened) NRD_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+  else NRD_CHECK_CUDA(cudaFree(ptr));
+  return NRD_OK;
+}
+
+extern "C" int nrd_plan_set_exchange(nrd_plan* p, int rank, int world, void* const* bufs) {
+  NRD_REQUIRE(p, "null plan");
+  if (world == 0 || !bufs) { memset(&p->xchg, 0, sizeof(p->xchg)); return NRD_OK; }
+  NRD_REQUIRE(world >= 2 && world <= NRD_XCHG_MAX_WORLD && rank >= 0 && rank < world, "nrd_plan_set_exchange: world %d / rank %d out of range", world, rank);
+  for (int r = 0; r < world; ++r) { NRD_REQUIRE(bufs[r], "nrd_plan_set_exchange: null buffer for rank %d", r); p->xchg.peer[r] = (float*)bufs[r]; }
+  p->xchg.world = world; p->xchg.rank = rank; p->xchg.nx = (2 * p->C + (int)p->off[9] + 3) & ~3;
+  return NRD_OK;
+}
+
 extern "C" int nrd_plan_conv_impl(const nrd_plan* p) { return p ? p->conv_impl : NRD_EINVAL; }
 
 extern "C" int nrd_plan_tensor(nrd_plan* p, int what, int k, void** ptr, size_t* bytes) {
@@ -1777,7 +1897,7 @@ extern "C" int nrd_sgd_update_pack(nrd_plan* p, float lr, float inv_world, void*
   const long long n = p->off[9];
   NRD_CHECK_CUDA(nrd_launch_pdl(k_sgd_pack, dim3(grid_for((size_t)n, 256, NRD_NUM_SMS * 2)), dim3(256), 0, (cudaStream_t)stream, (p->pdl >> 2) & 1,
                                 p->params, p->grads, lr * inv_world, p->C, nullptr, p->off[P_C1W], p->off[P_RBW], p->off[P_FC1W], n, p->w_fwd,
-                                p->w_dgrad, p->wtc_fwd, p->wtc_dgrad, p->w1p, p->conv1_wp));
+                                p->w_dgrad, p->wtc_fwd, p->wtc_dgrad, p->w1p, p->conv1_wp, p->xchg, p->bn_sync));
   LAUNCH_CHECK();
   return NRD_OK;
 }
@@ -1864,6 +1984,10 @@ extern "C" int nrd_backward_head(nrd_plan* p, const float* dlogits, void* stream
   LAUNCH_CHECK();
   k_fc1_wgrad_reduce<<<(NRD_FC1_OUT * 64 * C + 255) / 256, 256, 0, st>>>(p->fc1w_partial, nsplit, C, GRD(P_FC1W));
   LAUNCH_CHECK();
+  if (p->xchg.world > 0) {      // peer-memory exchange: the head bucket leaves now, under the body backward
+    k_xchg_push_head<<<32, 256, 0, st>>>(p->xchg, p->grads, (int)p->off[P_FC1W], (int)p->off[9], C);
+    LAUNCH_CHECK();
+  }
   return NRD_OK;
 }
 
@@ -1913,7 +2037,8 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   else NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
   NRD_CHECK_CUDA(nrd_launch_pdl(k_body_reduce, dim3(9 * C * C / 32 + 28 * C / 32), dim3(256), 0, st, (p->pdl >> 2) & 1, p->wgrad_partial,
                                 p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B), p->stem_partial, stem_bwd_blocks(B), C,
-                                GRD(P_RBW), GRD(P_C1W), GRD(P_C1B), p->bn_sync, p->bn_running, p->bn_sync_contrib));
+                                GRD(P_RBW), GRD(P_C1W), GRD(P_C1B), p->bn_sync, p->bn_running, p->bn_sync_contrib, p->xchg, (const float*)p->grads,
+                                (int)p->off[P_BNG], (int)p->off[P_RBW], (int)p->off[P_C1W]));
   LAUNCH_CHECK();
   return NRD_OK;
 }

@@ -37,18 +37,30 @@ class TrainStep:
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.plan = self.eng.plan(batch_size, dev)
         self.eng.ensure_packed(self.plan)
-        # DDP on the graph path: (1) rank 0's BN running stats ride the body bucket's all-reduce of the PREVIOUS step
-        # instead of a broadcast in front of every forward (same values: the buffers do not change in between; exact
-        # for power-of-two world sizes, otherwise the broadcast stays); (2) the persistent kernels leave a few SMs
-        # free so the head bucket's all-reduce really runs beside the body backward.
-        self.fold_bn_sync = (self.world > 1 and self.ddp.broadcast_buffers and (self.world & (self.world - 1)) == 0
-                             and os.environ.get("NRD_FOLD_BN_SYNC", "1") != "0")
+        # DDP on the graph path:
+        # (1) gradients are exchanged over NVLink peer memory by our own kernels (nrd_plan_set_exchange: the producing
+        #     kernels store into every rank's buffer, the optimizer kernel sums the world's slots in rank order; the head
+        #     bucket leaves on the side stream under the body backward).  Without peer access (or beyond 8 ranks) the two
+        #     buckets are NCCL all-reduces, the head one on the side stream;
+        # (2) rank 0's BN running stats ride that exchange of the PREVIOUS step instead of a broadcast in front of every
+        #     forward (same values: the buffers do not change in between);
+        # (3) the persistent kernels leave a few SMs free so the head bucket's all-reduce really runs beside them.
+        self.p2p = False
+        self.fold_bn_sync = False
+        self.slot_scale = 1.0
         if self.world > 1:
             rank = dist.get_rank(self.ddp.process_group)
+            if os.environ.get("NRD_P2P", "1") != "0" and self.world <= 8:
+                self.p2p = self._setup_exchange(rank)
+            pow2 = (self.world & (self.world - 1)) == 0
+            self.fold_bn_sync = (self.ddp.broadcast_buffers and (self.p2p or pow2) and os.environ.get("NRD_FOLD_BN_SYNC", "1") != "0")
             if self.fold_bn_sync:
-                check(lib.nrd_plan_set_bn_sync(self.plan.handle, self.eng.xchg.data_ptr(), float(self.world) if rank == 0 else 0.0,
-                                               1.0 / self.world), "nrd_plan_set_bn_sync")
+                # all-reduce: rank 0 contributes world * stats (exact for powers of two); peer exchange: the stats themselves
+                self.slot_scale = 1.0 if self.p2p else float(self.world)
+                check(lib.nrd_plan_set_bn_sync(self.plan.handle, self.eng.xchg.data_ptr(), self.slot_scale if rank == 0 else 0.0,
+                                               1.0 / self.slot_scale), "nrd_plan_set_bn_sync")
                 self.resync_buffers()
+            # the head bucket's kernel (NCCL all-reduce or our push kernel) has to fit beside the persistent kernels
             check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8"))),
                   "nrd_plan_set_option")
         self.graphs = [None, None]              # one captured step per input slot (slot 1 on first use)
@@ -57,13 +69,51 @@ class TrainStep:
         if use_graph:
             self._capture(0)
 
+    def _setup_exchange(self, rank: int) -> bool:
+        """Exchange buffers for the body bucket: allocate ours, swap CUDA IPC handles over the process group, map the peers'.
+        Returns False (on every rank alike) when any rank cannot, e.g. no peer access between the devices."""
+        import ctypes as C
+        W, dev = self.world, self.device
+        nbytes = lib.nrd_exchange_bytes(self.eng.C, W)
+        ptr, handle = C.c_void_p(), (C.c_ubyte * 64)()
+        ok = nbytes > 0 and lib.nrd_exchange_alloc(dev.index, nbytes, C.byref(ptr), handle) == 0
+        handles = [None] * W
+        dist.all_gather_object(handles, bytes(handle) if ok else None, group=self.ddp.process_group)
+        ptrs = (C.c_void_p * W)()
+        opened = []
+        if all(h is not None for h in handles):
+            for r in range(W):
+                if r == rank:
+                    ptrs[r] = ptr.value
+                    continue
+                q = C.c_void_p()
+                hb = (C.c_ubyte * 64).from_buffer_copy(handles[r])
+                if lib.nrd_exchange_open(dev.index, hb, C.byref(q)) != 0:
+                    ok = False
+                    break
+                ptrs[r] = q.value
+                opened.append(q.value)
+        else:
+            ok = False
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.ddp.process_group)
+        if int(flag) == 0:
+            for q in opened:
+                lib.nrd_exchange_release(q, 1)
+            if ptr.value:
+                lib.nrd_exchange_release(ptr, 0)
+            return False
+        check(lib.nrd_plan_set_exchange(self.plan.handle, rank, W, ptrs), "nrd_plan_set_exchange")
+        self._exchange = (ptr, opened)          # kept mapped for the life of the process (captured graphs point into them)
+        return True
+
     def resync_buffers(self):
         """Rank 0's BN running stats to every rank, and into the slot the next forward starts from.  Called at construction;
         call it again after changing the buffers outside the step (load_state_dict)."""
         if self.world > 1 and self.ddp.broadcast_buffers:
             self.ddp._sync_buffers()
             if self.fold_bn_sync:
-                torch.mul(self.eng.bn_running, float(self.world), out=self.eng.xchg[:2 * self.eng.C])
+                torch.mul(self.eng.bn_running, self.slot_scale, out=self.eng.xchg[:2 * self.eng.C])
 
     # the step body, launched on the current stream
     @property
@@ -82,11 +132,14 @@ class TrainStep:
         check(lib.nrd_forward_loss(pl.handle, imgs.data_ptr(), labels.data_ptr(), 1.0, self.logits.data_ptr(), self.loss.data_ptr(),
                                    pl.dlogits.data_ptr(), pl.loss_rows.data_ptr(), st), "nrd_forward_loss")
         # backward: head weight grads (+ their bucket's all-reduce) on a side stream beside the body backward (C3)
-        sum_head = (lambda: self.ddp._allreduce_bucket(1, average=False)) if self.world > 1 else None
+        # peer-memory exchange: both buckets travel inside nrd_backward_head / nrd_backward_body, no collective here
+        sum_head = (lambda: self.ddp._allreduce_bucket(1, average=False)) if (self.world > 1 and not self.p2p) else None
         sum_body = None
-        if self.world > 1:
+        if self.world > 1 and not self.p2p:
             sum_body = ((lambda: dist.all_reduce(eng.body_bucket_with_bn_slot(), op=dist.ReduceOp.SUM, group=self.ddp.process_group))
                         if self.fold_bn_sync else (lambda: self.ddp._allreduce_bucket(0, average=False)))
+        if os.environ.get("NRD_DIAG_NO_EXCHANGE") == "1":          # timing diagnosis only: every rank trains alone
+            sum_head = sum_body = None
         eng.backward(pl, pl.dlogits, sum_head, sum_body)
         # fused mean + SGD (K16), then re-derive the packed weight copies
         check(lib.nrd_sgd_update_pack(pl.handle, self.lr, 1.0 / self.world, st), "nrd_sgd_update_pack")
@@ -107,7 +160,7 @@ class TrainStep:
         self.graphs[slot] = g
         self.eng.flat_params.copy_(keep[0]); self.eng.bn_running.copy_(keep[1]); self.eng.nbt.copy_(keep[2])
         if self.fold_bn_sync:
-            torch.mul(keep[1], float(self.world), out=self.eng.xchg[:2 * self.eng.C])
+            torch.mul(keep[1], self.slot_scale, out=self.eng.xchg[:2 * self.eng.C])
         check(lib.nrd_pack_weights(self.plan.handle, _stream_ptr()), "nrd_pack_weights")
         torch.cuda.synchronize(self.device)
 

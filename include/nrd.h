@@ -107,6 +107,19 @@ int nrd_plan_set_option(nrd_plan* plan, int option, int value);
  * still sees its OWN running stats, as with the reference.  The caller initialises the slot (world_size * current stats)
  * before the first step.  slot = NULL (default) turns it off. */
 int nrd_plan_set_bn_sync(nrd_plan* plan, float* slot, float contrib, float inv_world);
+/* Gradient exchange over NVLink peer memory for the body bucket (one node, 2..8 ranks), replacing the all-reduce that DDP's
+ * reducer runs after the last gradient (reached from main.py:38 through the hooks main.py:63 installs).  Every rank
+ * allocates one exchange buffer (nrd_exchange_bytes / nrd_exchange_alloc: a cudaMalloc allocation, exported as a 64-byte CUDA
+ * IPC handle), the ranks swap handles with any transport they like, open each other's buffers (nrd_exchange_open) and hand
+ * the table (own pointer at index `rank`) to nrd_plan_set_exchange.  From then on nrd_backward_body() stores the body
+ * gradients (and the BN slot of nrd_plan_set_bn_sync, which it then needs contrib = 1 on rank 0 and inv_world = 1 for) into
+ * every rank's buffer and nrd_sgd_update_pack() sums the world's contributions in rank order before the update, so the
+ * caller all-reduces only the head bucket.  Every rank must run the same sequence of steps.  world = 0 turns it off. */
+size_t nrd_exchange_bytes(int C, int world);
+int nrd_exchange_alloc(int device, size_t bytes, void** ptr, void* ipc_handle_64);
+int nrd_exchange_open(int device, const void* ipc_handle_64, void** ptr);
+int nrd_exchange_release(void* ptr, int opened);
+int nrd_plan_set_exchange(nrd_plan* plan, int rank, int world, void* const* bufs);
 /* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
  * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch (ping),
  * 6 = dx scratch (pong), 7 = wgrad per-CTA partials [ctas][9][C][C], 8 = BN-stat per-CTA partials [ctas][2][C],
