@@ -204,9 +204,10 @@ def main():
         def __iter__(self): return ((h_imgs, h_labels) for _ in range(self.n))
 
     def epoch(n):
-        # main.py:31-41 as TrainStep.iterate: launch step t, then start batch t+1's H2D copy beside it, then read the loss
+        # main.py:31-41 as TrainStep.iterate: launch step t, then start batch t+1's H2D copy beside it, then read the loss of
+        # step t-1 (look-ahead 1: every step's loss still reaches the host, in order, one launch later)
         tot = 0.0
-        for loss in step.iterate(HostBatches(n)):
+        for loss in step.iterate(HostBatches(n), lookahead=1):
             tot += float(loss)                                  # host value of the step's loss (main.py:41)
         return tot
 
@@ -220,7 +221,7 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e = {"value": world * B * args.steps / float(t), "unit": "images/s",
-           "h2d_bytes_per_step": h_imgs.numel() * 4 + h_labels.numel() * 8, "d2h_bytes_per_step": 4,
+           "h2d_bytes_per_step": h_imgs.numel() * 4 + h_labels.numel() * 8, "d2h_bytes_per_step": 4, "loss_lookahead": 1,
            "ms_per_step": float(t) / args.steps * 1e3}
 
     # ---- per-kernel-class timing + roofline (rank 0) ------------------------------------------

@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ w
                                                      int C, float* __restrict__ dw, float* __restrict__ dw1, float* __restrict__ db1,
                                                      float* __restrict__ bn_sync, const float* __restrict__ running, float contrib,
                                                      nrd_xchg_args x, const float* grads_base, int off_bng, int off_rbw, int off_c1w) {
-  __shared__ double red[8][33];
+  __shared__ float red[8][33];
   nrd_pdl_launch();
   nrd_pdl_wait();
   const bool px = x.world > 0;
@@ -248,22 +248,24 @@ __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ w
   const bool conv = (int)blockIdx.x < nconv;
   const int i = (conv ? blockIdx.x : blockIdx.x - nconv) * 32 + o, n = conv ? 9 * C * C : 28 * C, nblk = conv ? wblk : sblk;
   const float* part = conv ? wpartial : spartial;
-  double s = 0.0;
+  // fp32, fixed order (8 row classes, each its partials in order): deterministic, and the partials are fp32 sums already --
+  // the fp64 pipe made this kernel twice as long
+  float s = 0.f;
 #pragma unroll 8
-  for (int b = r; b < nblk; b += 8) s += (double)__ldcg(part + (size_t)b * n + i);
+  for (int b = r; b < nblk; b += 8) s += __ldcg(part + (size_t)b * n + i);
   red[r][o] = s;
   __syncthreads();
   if (r == 0) {
-    double tot = 0.0;
+    float tot = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) tot += red[k][o];
     float* q;
     if (conv) { const int t = i / (C * C), co = (i / C) % C, ci = i % C; q = dw + ((size_t)co * C + ci) * 9 + t; }
     else { const int k = i / C, co = i % C; q = k < 27 ? dw1 + co * 27 + k : db1 + co; }
-    *q = (float)tot;
+    *q = tot;
     // the slot keeps THIS kernel's order (conv [tap][co][ci], conv1 [tap][co]): a warp's 32 values are 128 contiguous bytes per
     // peer instead of 32 scattered 4-byte NVLink writes; k_sgd_pack applies the permutation when it reads (locally)
-    if (px) push(2 * C + (conv ? off_rbw + i : (i < 27 * C ? off_c1w + i : (size_t)(q - grads_base))), (float)tot);
+    if (px) push(2 * C + (conv ? off_rbw + i : (i < 27 * C ? off_c1w + i : (size_t)(q - grads_base))), tot);
   }
   if (px) nrd_xchg_publish(x, 0, epoch);
 }
@@ -1178,6 +1180,14 @@ __global__ void __launch_bounds__(256) k_head_tail(const float* __restrict__ par
   const int r = tid >> 5, j = tid & 31, b = b0 + r;
   nrd_pdl_launch();
   for (int q = tid; q < NRD_NCLS * NRD_FC1_OUT; q += 256) w2s[q] = w2[q];
+  // this thread's fc1 weight row (column i of d(pooled)): weights are untouched since the last optimizer step, so the 128 bytes
+  // are fetched before the wait, under the predecessor's tail, instead of in front of the dgrad loop
+  float4 wreg[8];
+  {
+    const float4* wrow = reinterpret_cast<const float4*>(w1t + (size_t)i * NRD_FC1_OUT);
+#pragma unroll
+    for (int j4 = 0; j4 < 8; ++j4) wreg[j4] = wrow[j4];
+  }
   nrd_pdl_wait();
   float h = 0.f;
   if (b < B) {
@@ -1227,10 +1237,9 @@ __global__ void __launch_bounds__(256) k_head_tail(const float* __restrict__ par
   float s8[8];
 #pragma unroll
   for (int rr = 0; rr < 8; ++rr) s8[rr] = 0.f;
-  const float4* wrow = reinterpret_cast<const float4*>(w1t + (size_t)i * NRD_FC1_OUT);
 #pragma unroll
   for (int j4 = 0; j4 < 8; ++j4) {
-    const float4 w = wrow[j4];
+    const float4 w = wreg[j4];
 #pragma unroll
     for (int rr = 0; rr < 8; ++rr)
       s8[rr] += d[rr][j4 * 4] * w.x + d[rr][j4 * 4 + 1] * w.y + d[rr][j4 * 4 + 2] * w.z + d[rr][j4 * 4 + 3] * w.w;

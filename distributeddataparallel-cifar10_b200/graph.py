@@ -181,12 +181,16 @@ class TrainStep:
         self.plan.packed_version = self.eng._weights_version()
         return self.loss
 
-    def iterate(self, loader):
+    def iterate(self, loader, lookahead: int = 0):
         """One pass over `loader` (HOST batches `(imgs, labels)`; pinned memory makes the copies asynchronous), one step per
         batch: the loop of main.py:31-41.  Yields the step's loss as a pinned HOST scalar tensor, already synchronised (the
         reference's per-step `loss.item()`, main.py:41), valid until the next iteration.  Order per step: launch the step
         on the slot that is ready, THEN fetch the next host batch and start its copy into the other slot on a copy stream
-        -- loader work and PCIe traffic run beside the step's kernels instead of in front of them."""
+        -- loader work and PCIe traffic run beside the step's kernels instead of in front of them.
+
+        `lookahead=1`: step t's loss is handed out after step t+1 has been LAUNCHED (same values, same order, one step
+        later), so the GPU never waits for the host between steps; the price is that breaking out of the loop at step t
+        leaves step t+1 applied as well."""
         dev = self.device
         main = torch.cuda.current_stream(dev)
         if self.use_graph and self.graphs[1] is None:
@@ -195,7 +199,8 @@ class TrainStep:
             self._copy_stream = torch.cuda.Stream(device=dev)
             self._ready = [torch.cuda.Event(), torch.cuda.Event()]
             self._consumed = [torch.cuda.Event(), torch.cuda.Event()]
-            self._h_loss = torch.zeros((), dtype=torch.float32).pin_memory()
+            self._h_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._loss_done = [torch.cuda.Event(), torch.cuda.Event()]
             for e in self._consumed:
                 e.record(main)
         copy = self._copy_stream
@@ -224,14 +229,27 @@ class TrainStep:
             return
         slot = 0
         issue(slot, nxt)
+        k, pending = 0, None
         while nxt is not None:
             main.wait_event(self._ready[slot])
             self.run(slot)
             self._consumed[slot].record(main)
+            self._h_loss[k].copy_(self.loss, non_blocking=True)
+            self._loss_done[k].record(main)
             nxt = next(it, None)
             if nxt is not None:
                 issue(slot ^ 1, nxt)
-            self._h_loss.copy_(self.loss, non_blocking=True)
-            main.synchronize()
-            yield self._h_loss
+            if lookahead and nxt is not None:
+                if pending is not None:
+                    self._loss_done[pending].synchronize()
+                    yield self._h_loss[pending]
+                pending = k
+            else:
+                if pending is not None:
+                    self._loss_done[pending].synchronize()
+                    yield self._h_loss[pending]
+                    pending = None
+                self._loss_done[k].synchronize()
+                yield self._h_loss[k]
             slot ^= 1
+            k ^= 1

@@ -43,7 +43,7 @@ def train_loop(model, train_loader, rank, epochs=99, lr=1e-2, save=True, log=pri
                 from .graph import TrainStep
                 step = TrainStep(model, train_loader.batch_size, lr=lr)
             host_sum = 0.0
-            for loss in step.iterate(train_loader):        # main.py:31-41
+            for loss in step.iterate(train_loader, lookahead=1):   # main.py:31-41 (no early exit here: look-ahead is free)
                 host_sum += float(loss)                    # main.py:41: the loss is already on the host
             loss_train += host_sum
         for imgs, labels in (() if graph else train_loader):

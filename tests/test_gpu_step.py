@@ -275,7 +275,14 @@ def test_trainstep_iterate_equals_step_by_step():
             losses = [float(l) for l in step.iterate(host)]
             assert [float(l) for l in step.iterate([])] == []
         res.append((losses, m.engine.flat_params.clone(), m.engine.bn_running.clone(), int(m.engine.nbt)))
-    assert res[0][0] == res[1][0] and len(res[1][0]) == 5
+    for mode in ("lookahead",):
+        torch.manual_seed(3)
+        m = nrd.NetResDeep(32, 10).to("cuda")
+        step = nrd.TrainStep(m, 16, lr=1e-2)
+        losses = [float(l) for l in step.iterate(host, lookahead=1)]     # same values, same order, handed out one launch later
+        assert [float(l) for l in step.iterate(host[:1], lookahead=1)] != []
+        res.append((losses, m.engine.flat_params.clone(), m.engine.bn_running.clone(), int(m.engine.nbt)))
+    assert res[0][0] == res[1][0] == losses and len(res[1][0]) == 5
     assert torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2]) and res[0][3] == res[1][3] == 50
     with pytest.raises(ValueError):
         list(step.iterate([(torch.zeros(8, 3, 32, 32), torch.zeros(8, dtype=torch.int64))]))
