@@ -342,6 +342,12 @@ struct PersistFwdArgs {
   bf16* pooled;            // [B,8,8,C] maxpool2 of x_NB and its arg-max (position 0..3 in the window), written by the last
   uint8_t* idx2;           // block's pass 2; NULL = leave the pooling to the head kernel
   int poll_ns;
+  // fused stem (NRD_OPT_FUSE_STEM): x_0 = maxpool2(relu(conv1(images) + b)) computed here instead of loaded; NULL = off
+  const float* images;     // [B,3,32,32] fp32
+  const float* conv1_wp;   // [27][C] fp32
+  const float* conv1_b;    // [C]
+  uint8_t* idx0;           // [B,16,16,C] stem pool arg-max
+  nrd_bn_sync_args bs;     // DDP buffer sync that the stem kernel would have applied
 };
 
 __global__ void __launch_bounds__(576, 1)
@@ -365,16 +371,25 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   const uint32_t tmem_slot = bar0 + 8u * 9;
   auto yready = [&](int s) { return bar0 + 8u * (10 + s); };
   const uint32_t yfree = bar0 + 8u * 12, xfree = bar0 + 8u * 13;
-  constexpr int BAR_BYTES = 8 * 14;
+  const uint32_t st_afull = bar0 + 8u * 14, st_tfull = bar0 + 8u * 15;   // fused stem: im2col tiles written / accumulators ready
+  const uint32_t st_x0free = bar0 + 8u * 16;                             // ... x_0's bulk store has read the centre copies
+  constexpr int BAR_BYTES = 8 * 18;
   constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + 2 * YST_BYTES + BAR_BYTES;
   float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][sum | sum of squares][16 channels]
   float* ss_sm = red + 1024;                                             // [2C] scale | shift of the current block
+  // fused stem scratch: W1 tile (1024-B aligned), bias, two zero-padded fp32 images; the four im2col tiles of a half image
+  // alias the y staging tiles (free until block 0's pass 1)
+  constexpr int STEM_OFF = (MISC_OFF + (1024 + 64) * 4 + 1023) & ~1023;
+  uint8_t* st_w_gen = gen_base + STEM_OFF;                               // [32 co][32 taps] bf16, SWIZZLE_64B rows
+  float* st_bias = reinterpret_cast<float*>(st_w_gen + 2048);
+  float* st_img = st_bias + 32;                                          // [2][3][34][40] fp32
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int img0 = blockIdx.x, img1 = blockIdx.x + gridDim.x;
   const int nslots = (img1 < a.B) ? 2 : 1;
-  constexpr uint32_t TMEM_COLS = 128;                              // 2 slots x 2 tiles x 32 columns
+  constexpr uint32_t TMEM_COLS = 256;                              // 2 slots x 2 tiles x 32 columns + 4 stem window accumulators
+  const bool fuse_stem = a.images != nullptr;
   if (a.trace && threadIdx.x == 64) a.trace[(size_t)blockIdx.x * a.NB * 8 + 7] = clock64();      // kernel entry
   nrd_pdl_launch();                                                // the head kernels behind us may be scheduled (they wait for our exit)
 
@@ -385,8 +400,42 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       mbar_init(xfull(s), 1); mbar_init(opready(s), 512); mbar_init(tfull(s, 0), 1); mbar_init(tfull(s, 1), 1); mbar_init(yready(s), 512);
     }
     mbar_init(yfree, 1); mbar_init(xfree, 1);
+    mbar_init(st_afull, 512); mbar_init(st_tfull, 1); mbar_init(st_x0free, 1);
+    if (fuse_stem) { mbar_init(xfull(0), 512); mbar_init(xfull(1), 512); }      // x_0 is written by the epilogue threads, not by TMA
     tma_prefetch_desc(&tmXst); tma_prefetch_desc(&tmYst);
     fence_barrier_init();
+  }
+  if (fuse_stem) {
+    // the operand copies' halo rows / edge columns are the convolution padding (TMA zero-fills them on the loading path) and
+    // the padded images' borders are conv1's: zero everything once
+    for (int i = threadIdx.x; i < 2 * SLOT_BYTES / 16; i += blockDim.x) reinterpret_cast<uint4*>(gen_base)[i] = make_uint4(0, 0, 0, 0);
+    // images first (the longest latency of the prologue): interior by cp.async, borders zeroed by plain stores (disjoint)
+    if (threadIdx.x >= 64) {
+      const uint32_t im_s = smem_u32(st_img);
+      for (int c = threadIdx.x - 64; c < nslots * 768; c += 512) {                 // 768 16-byte chunks per image
+        const int s_ = c / 768, qq = c % 768, ci = qq >> 8, r = (qq >> 3) & 31, c4 = qq & 7;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(im_s + (uint32_t)((s_ * 4080 + (ci * 34 + r + 1) * 40 + 4 + c4 * 4) * 4)),
+                     "l"(a.images + (size_t)(s_ == 0 ? img0 : img1) * 3072 + ci * 1024 + r * 32 + c4 * 4) : "memory");
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int i = threadIdx.x; i < 2 * 3 * 34 * 40; i += blockDim.x) {
+      const int r = (i / 40) % 34, c = i % 40;
+      if (r == 0 || r == 33 || c < 4 || c >= 36) st_img[i] = 0.f;
+    }
+    if (threadIdx.x < 128) {                                       // W1 -> bf16 K-major rows; row co, chunk ch = taps ch*8..+7
+      const int co = threadIdx.x >> 2, ch = threadIdx.x & 3;
+      uint32_t pk[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int t0 = ch * 8 + 2 * e;
+        const __nv_bfloat162 hh = __floats2bfloat162_rn(t0 < 27 ? a.conv1_wp[t0 * C + co] : 0.f, t0 + 1 < 27 ? a.conv1_wp[(t0 + 1) * C + co] : 0.f);
+        pk[e] = *reinterpret_cast<const uint32_t*>(&hh);
+      }
+      *reinterpret_cast<uint4*>(st_w_gen + co * 64 + ((ch ^ ((co >> 1) & 3)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    }
+    if (threadIdx.x < 32) st_bias[threadIdx.x] = a.conv1_b[threadIdx.x];
+    fence_proxy_async();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
@@ -398,10 +447,21 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     if (lane == 0) {
       mbar_expect_tx(wfull, 9 * K::WTAP_BYTES);
       for (int t = 0; t < 9; ++t) tma_load_2d(w_smem + t * K::WTAP_BYTES, &tmW, wfull, t * C, 0);
-      for (int s = 0; s < nslots; ++s) {
-        mbar_expect_tx(xfull(s), SLOT_BYTES);
-        for (int kx = 0; kx < 3; ++kx)
-          tma_load_4d(a_smem + s * SLOT_BYTES + kx * K::BUF_BYTES, &tmX0, xfull(s), 0, kx - 1, -1, s == 0 ? img0 : img1);
+      if (!fuse_stem) {
+        for (int s = 0; s < nslots; ++s) {
+          mbar_expect_tx(xfull(s), SLOT_BYTES);
+          for (int kx = 0; kx < 3; ++kx)
+            tma_load_4d(a_smem + s * SLOT_BYTES + kx * K::BUF_BYTES, &tmX0, xfull(s), 0, kx - 1, -1, s == 0 ? img0 : img1);
+        }
+      } else {
+        // fused stem: x_0 was produced on chip; it still goes to global memory (block 0's weight gradient and the stem
+        // backward read it), straight from the centre copies
+        for (int s = 0; s < nslots; ++s) {
+          mbar_wait(xfull(s), 0);
+          tma_store_5d(&tmXst, a_smem + s * SLOT_BYTES + K::BUF_BYTES + K::IMGROW_BYTES, 0, 0, 0, s == 0 ? img0 : img1, 0);
+        }
+        bulk_commit(); bulk_wait_read0();
+        mbar_arrive(st_x0free);
       }
       // ... then this thread is the store engine: y_k from its staging tile and x_{k+1} from the CENTRE operand copy (the same
       // swizzled bytes the tensor map expects) go to global memory as two bulk tensor stores per image, instead of eight
@@ -425,6 +485,23 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(128, C, 0, 0);
+      if (fuse_stem) {
+        // stem: per half image, D_w[pooled pixel][co] = im2col_w[pooled pixel][27 taps -> 32] x W1, one accumulator per
+        // position w of the 2x2 pooling window (the epilogue takes the maximum over the four)
+        const uint32_t tiles = y_smem, w1 = base + STEM_OFF;
+        const uint64_t bd = make_sdesc(w1, 16, K::SBO, K::LAYOUT);
+        for (int i = 0; i < 2 * nslots; ++i) {
+          mbar_wait(st_afull, (uint32_t)(i & 1));
+          tc_fence_after();
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            const uint64_t ad = make_sdesc(tiles + w * 8192, 16, K::SBO, K::LAYOUT);
+            umma_bf16(tmem_base + 128 + w * C, ad, bd, idesc, 0);
+            umma_bf16(tmem_base + 128 + w * C, ad + 2, bd + 2, idesc, 1);
+          }
+          umma_commit(st_tfull);
+        }
+      }
       mbar_wait(wfull, 0);
       for (int k = 0; k < a.NB; ++k) {
         for (int s = 0; s < nslots; ++s) {        // slot-major: slot 0's MMAs start as soon as ITS operands are rewritten
@@ -465,6 +542,89 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
 #pragma unroll
       for (int r = 0; r < NRD_ACC_REPL; ++r) { last[NRD_ACC_IDX(r, lane)] = 0ull; last[NRD_ACC_IDX(r, C + lane)] = 0ull; }
       __threadfence();
+    }
+    if (fuse_stem) {
+      // ===== fused stem: x_0 = maxpool2(relu(conv1(image) + b)) of this CTA's images, straight into the operand copies =====
+      constexpr int IMG_ROW = 40, IMG_FLOATS = 3 * 34 * IMG_ROW;     // zero-padded rows -1..32, data column c at index 4 + c
+      if (blockIdx.x == gridDim.x - 1 && ew == 0 && a.bs.slot) {     // DDP buffer sync, by the thread that does the EMA later
+        a.bs.running[lane] = a.bs.slot[lane] * a.bs.inv_world; a.bs.running[C + lane] = a.bs.slot[C + lane] * a.bs.inv_world;
+      }
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      asm volatile("bar.sync 1, 512;" ::: "memory");
+      long long* trs = (a.trace && et == 0) ? a.trace + (size_t)gridDim.x * a.NB * 8 + (size_t)blockIdx.x * 16 : nullptr;   // stem stamps
+      if (trs) trs[0] = clock64();
+      uint8_t* tiles = gen_base + (y_smem - base);
+      for (int i = 0; i < 2 * nslots; ++i) {
+        const int s_ = i >> 1, hh = i & 1;
+        const float* im = st_img + s_ * IMG_FLOATS;
+        if (i > 0) mbar_wait(st_tfull, (uint32_t)((i - 1) & 1));     // the previous half's MMAs have read the tiles
+        {
+          // builder: thread = (pooled pixel bp of the half, window position w): one 64-byte im2col row (27 taps, bf16)
+          const int bp = et & 127, w = et >> 7, pr = 8 * hh + (bp >> 4), pc = bp & 15, dy = w >> 1, dx = w & 1;
+          float kv[32];
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+              for (int kx = 0; kx < 3; ++kx) kv[ci * 9 + ky * 3 + kx] = im[(ci * 34 + 2 * pr + dy + ky) * IMG_ROW + 3 + 2 * pc + dx + kx];
+          kv[27] = kv[28] = kv[29] = kv[30] = kv[31] = 0.f;
+          uint8_t* row = tiles + w * 8192 + bp * 64;
+          const int sw = (bp >> 1) & 3;
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const __nv_bfloat162 hv = __floats2bfloat162_rn(kv[ch * 8 + 2 * e], kv[ch * 8 + 2 * e + 1]);
+              pk[e] = *reinterpret_cast<const uint32_t*>(&hv);
+            }
+            *reinterpret_cast<uint4*>(row + ((ch ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          }
+        }
+        fence_proxy_async();
+        mbar_arrive(st_afull);
+        if (trs) trs[1 + i * 3] = clock64();
+        if (m == hh) {
+          // epilogue of the half (the warps whose pixel tile it is; the others already build the next half's tiles): this
+          // thread's pooled pixel x 16 channels; maximum over the four accumulators, first one wins
+          mbar_wait(st_tfull, (uint32_t)(i & 1));
+          tc_fence_after();
+          if (trs) trs[2 + i * 3] = clock64();
+          float mx[16]; uint32_t mi[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            float v[16];
+            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + 128 + w * C + h * 16, v);
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+              if (w == 0) mx[c] = v[c];
+              else if (v[c] > mx[c]) { mx[c] = v[c]; mi[c >> 2] = (mi[c >> 2] & ~(0xFFu << (8 * (c & 3)))) | ((uint32_t)w << (8 * (c & 3))); }
+            }
+          }
+          tc_fence_before();
+          uint8_t* slot_gen = gen_base + s_ * SLOT_BYTES;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int ch = h * 2 + j;
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = j * 8 + 2 * e;
+              const __nv_bfloat162 hv = __floats2bfloat162_rn(fmaxf(mx[c] + st_bias[h * 16 + c], 0.f), fmaxf(mx[c + 1] + st_bias[h * 16 + c + 1], 0.f));
+              pk[e] = *reinterpret_cast<const uint32_t*>(&hv);
+            }
+            const uint4 ok = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
+            if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
+            if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
+          }
+          *reinterpret_cast<uint4*>(a.idx0 + ((size_t)(s_ == 0 ? img0 : img1) * NRD_PIX + hh * 128 + p) * C + h * 16) = make_uint4(mi[0], mi[1], mi[2], mi[3]);
+          if (trs) trs[3 + i * 3] = clock64();
+        }
+      }
+      fence_proxy_async();
+      for (int s_ = 0; s_ < nslots; ++s_) mbar_arrive(xfull(s_));
     }
     for (int k = 0; k < a.NB; ++k) {
       long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + k) * 8 : nullptr;
@@ -547,6 +707,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       if (tr) tr[5] = clock64();
       // ---- pass 2: x_{k+1} = relu(bn(y_k)) + x_k -> the three operand copies in shared memory, then global ----
       if (k > 0) mbar_wait(xfree, (uint32_t)((k - 1) & 1));       // block k-1's x stores have read the centre copies
+      else if (fuse_stem) mbar_wait(st_x0free, 0);
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         if (s >= nslots) break;
@@ -1167,7 +1328,8 @@ template <int C> constexpr size_t wgrad_smem() {
 }
 
 constexpr size_t persist_smem() {
-  return 1024 + 2 * 3 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 2 * NRD_PIX * 32 * 2 + 112 + (1024 + 64) * sizeof(float) + 64;
+  return 1024 + 2 * 3 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 2 * NRD_PIX * 32 * 2 + 144 + (1024 + 64) * sizeof(float) + 64 +
+         1024 + 2048 + 128 + 2 * 3 * 34 * 40 * sizeof(float);     // + fused stem: alignment, W1 tile, bias, two padded images
 }
 
 constexpr size_t persist_bwd_smem() {
@@ -1283,7 +1445,7 @@ int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st) {
 }
 
 // all NB residual blocks in ONE cooperative launch (C = 32, <= 2 images per CTA)
-int nrd_tc_forward_blocks(nrd_plan* p, int pool, cudaStream_t st) {
+int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int training, cudaStream_t st) {
   NRD_REQUIRE(p->tc_ready && p->tc_persist_fwd, "persistent block-stack forward not available for this plan");
   PersistFwdArgs a;
   a.gamma = p->params + p->off[3]; a.beta = p->params + p->off[4];
@@ -1291,6 +1453,7 @@ int nrd_tc_forward_blocks(nrd_plan* p, int pool, cudaStream_t st) {
   a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.acc = p->bn_acc; a.gbar = p->gbar + NRD_GBAR_PERSIST_FWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace; a.dbg_skip_stores = p->dbg_skip_stores;
   a.pooled = pool ? (bf16*)p->pooled : nullptr; a.idx2 = p->idx2; a.poll_ns = p->poll_ns;
+  a.images = stem_images; a.conv1_wp = p->conv1_wp; a.conv1_b = p->params + p->off[1]; a.idx0 = p->idx0; a.bs = nrd_bn_sync_of(p, training);
   a.inv_count = 1.0 / ((double)p->B * NRD_PIX); a.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
   void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_smem(), st));

@@ -1755,6 +1755,7 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->persist_bwd = 1;
   p->use_tc_stem = 1;
   p->fuse_head_tail = 1;
+  p->fuse_stem = 0;          // measured: as long as the stem kernel it replaces (its four half images run one after the other)
   p->fuse_pool = 0;          // measured 1 us slower per step than pooling in the fc1 kernel (it sits on the blocks' critical path)
   { const char* e = getenv("NRD_POLL_NS"); p->poll_ns = e ? atoi(e) : 0; }
   p->pdl = 5;     // measured: the consumers of the two persistent kernels (bit 1) lose 13 us when made programmatic dependents
@@ -1795,6 +1796,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_PDL: p->pdl = value; return NRD_OK;
     case NRD_OPT_HEAD_TAIL: p->fuse_head_tail = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_FUSE_POOL: p->fuse_pool = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_FUSE_STEM: p->fuse_stem = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_RESERVE_SMS:
       NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
       p->reserve_sms = value;
@@ -1933,12 +1935,14 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
   const int B = p->B, C = p->C, NB = p->NB, dt = p->dtype;
   const size_t act = p->act_elems * p->esz;
   p->images_last = images;
-  if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_fwd(p, images, training, st));
+  const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_fwd;
+  const bool stem_in_blocks = persist && p->fuse_stem && p->tc_stem && p->use_tc_stem;
+  if (stem_in_blocks) {}                                         // x_0 is produced inside the persistent kernel
+  else if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_fwd(p, images, training, st));
   else NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st, nrd_bn_sync_of(p, training)));
   if (!training) { k_bn_eval_coeffs<<<1, 64, 0, st>>>(p->bn_running, PRM(P_BNG), PRM(P_BNB), C, p->scale_shift); LAUNCH_CHECK(); }
-  const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_fwd;
   const bool pool_in_blocks = persist && p->fuse_pool;
-  if (persist) NRD_TRY(nrd_tc_forward_blocks(p, pool_in_blocks ? 1 : 0, st));       // ... and the max-pool behind the last block
+  if (persist) NRD_TRY(nrd_tc_forward_blocks(p, pool_in_blocks ? 1 : 0, stem_in_blocks ? images : nullptr, training, st));       // ... and the max-pool behind the last block
   for (int k = 0; k < (persist ? 0 : NB); ++k) {
     char* xk = p->xs + act * k; char* yk = p->ys + act * k; char* xn = p->xs + act * (k + 1);
     float* ss = training ? p->scale_shift + (size_t)k * 2 * C : p->scale_shift;
@@ -2098,7 +2102,7 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       return stem_bwd_any(p->images_last, p->dx0_last, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st);
     case NRD_OP_FWD_BLOCKS:
       NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent forward not available for this plan");
-      return nrd_tc_forward_blocks(p, 0, st);
+      return nrd_tc_forward_blocks(p, 0, nullptr, 0, st);
     case NRD_OP_BWD_BLOCKS:
       NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent backward not available for this plan");
       return nrd_tc_backward_blocks(p, p->dxa, p->dxb, st);

@@ -97,6 +97,10 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
 /* NRD_OPT_FUSE_POOL (default 0: measured 1 us per step slower): the persistent forward max-pools its last block's output itself (warp shuffles over the
  * 2x2 window) and fc1 reads the pooled tensor, instead of a head kernel re-reading x_NB. */
 #define NRD_OPT_FUSE_POOL 8
+/* NRD_OPT_FUSE_STEM (default 0: bit-identical, measured no faster than the stem kernel it replaces): the persistent forward computes x_0 = maxpool2(relu(conv1(images)+b)) itself (im2col tiles
+ * built by its 512 epilogue threads, 8 tcgen05.mma per half image, result written straight into the operand copies):
+ * no stem launch, no x_0 load. */
+#define NRD_OPT_FUSE_STEM 9
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* DDP's per-forward buffer broadcast (torch DDP `broadcast_buffers`, reached from main.py:63 and run in front of every
  * forward, main.py:33) folded into the gradient exchange: `slot` = the 2C floats directly in front of `grads` (so slot +

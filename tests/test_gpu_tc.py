@@ -200,3 +200,23 @@ def test_pool_fused_into_persistent_forward_is_bitwise_the_head_kernels_pool():
         torch.cuda.synchronize()
         res.append((out.detach().clone(), pl.tensor_view(3, 0).clone(), m.engine.flat_grads.clone()))
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2])
+
+
+@pytest.mark.parametrize("B", [1, 100, 256, 296])
+def test_stem_fused_into_persistent_forward_is_bitwise_the_stem_kernel(B):
+    """NRD_OPT_FUSE_STEM: x_0 computed inside the persistent forward (same im2col tiles, same MMAs, same max / first-arg-max
+    rule as k_stem_tc_fwd): x_0, logits, BN buffers and every gradient (the stem's goes through the arg-max) are equal."""
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for fuse in (0, 1):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(32, 10, dtype="bf16").to(DEV)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 9, fuse))
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        torch.cuda.synchronize()
+        bn = m.resblocks[0].batch_norm
+        res.append((out.detach().clone(), pl.tensor_view(0, 0).clone(), m.engine.flat_grads.clone(), bn.running_mean.clone(), bn.running_var.clone()))
+    for a_, b_ in zip(res[0], res[1]):
+        assert torch.equal(a_, b_)

@@ -26,6 +26,12 @@ for cta in (0, 1, grid - 1):
         print("  k=%d " % k + " ".join(f"{names[i]}={int(t[i]-t[0]):6d}" for i in range(1, 7)) + (f"  next_start=+{int(tr[cta,k+1,0]-t[0])}" if k < 9 else ""))
     print(f"  kernel entry -> first block start {int(tr[cta,0,0]-tr[cta,0,7])}, last pass 2 -> kernel exit {int(tr[cta,9,7]-tr[cta,9,6])}, whole kernel {int(tr[cta,9,7]-tr[cta,0,7])} cycles")
 
+st = pl.tensor_view(6, 0).view(torch.int64)[grid * 10 * 8: grid * 10 * 8 + grid * 16].view(grid, 16).cpu()
+if int(st[0, 0]) != 0:
+    e = int(tr[0, 0, 7])
+    print("fused stem, CTA 0 (cycles since kernel entry): images in smem", int(st[0, 0]) - e,
+          " per half [built, accumulators ready, epilogue done]:", [[int(st[0, 1 + i * 3 + j]) - e for j in range(3)] for i in range(4)])
+
 # ---- backward ----
 y = torch.randint(0, 10, (B,), device=dev)
 out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
