@@ -631,6 +631,15 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       if (tr) tr[0] = clock64();
       // ---- pass 1: y_k store + per-channel sum / sum of squares of this warp's 32 pixels x 16 channels ----
       float ssum = 0.f, qsum = 0.f;
+      uint4 ypk[2];
+      auto stage_y = [&](int s) {      // ypk -> slot s's staging tile (swizzled as the tensor map expects); the store thread sends it off
+        if (s == 0 && k > 0) mbar_wait(yfree, (uint32_t)((k - 1) & 1));     // block k-1's y stores have read the tiles
+        uint8_t* yst = gen_base + (y_smem - base) + s * YST_BYTES;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) *reinterpret_cast<uint4*>(yst + P0y * 64 + (((h * 2 + j) ^ ((P0y >> 1) & 3)) << 4)) = ypk[j];
+        fence_proxy_async();
+        mbar_arrive(yready(s));
+      };
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         if (s >= nslots) break;
@@ -639,20 +648,14 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         if (tr && s == 0) tr[1] = clock64();
         float v[16];
         tmem_ld16(my_tmem + s * 2 * C, v);
-        {
-          // y_k (bf16) into the staging tile, swizzled as the tensor map expects; the store thread sends it off
-          if (s == 0 && k > 0) mbar_wait(yfree, (uint32_t)((k - 1) & 1));     // block k-1's y stores have read the tiles
-          uint8_t* yst = gen_base + (y_smem - base) + s * YST_BYTES;
+        // y_k (bf16) for the staging tile; the LAST slot's goes there only after the statistics have left (off the critical path)
 #pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            uint4 pk; __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+        for (int j = 0; j < 2; ++j) {
+          __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&ypk[j]);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[j * 8 + 2 * e], v[j * 8 + 2 * e + 1]);
-            *reinterpret_cast<uint4*>(yst + P0y * 64 + (((h * 2 + j) ^ ((P0y >> 1) & 3)) << 4)) = pk;
-          }
-          fence_proxy_async();
-          mbar_arrive(yready(s));
+          for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[j * 8 + 2 * e], v[j * 8 + 2 * e + 1]);
         }
+        if (s + 1 < nslots) stage_y(s);
         {
           float sq[16];
 #pragma unroll
@@ -675,6 +678,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];   // fixed order over the 8 warps of the half
         nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 16777216.0), gridDim.x);   // wait for the return: measured faster
       }
+      stage_y(nslots - 1);
       if (tr) tr[3] = clock64();
       // one warp (lane = channel) polls its channels' words until every CTA has contributed, derives the coefficients (ONE
       // warp's worth of the slow fp64 pipe) and publishes them with the only CTA-wide barrier of the wait
