@@ -7,7 +7,7 @@ LIB_PATH = os.path.join(HERE, "libnrd.so")
 
 NRD_F32, NRD_BF16 = 0, 1
 CONV_CUDA_CORE, CONV_TCGEN05, CONV_TCGEN05_UNFUSED = 0, 1, 2
-OPT_FUSE_BN_BWD, OPT_PERSIST_FWD, OPT_TRACE, OPT_PERSIST_BWD, OPT_TC_STEM, OPT_RESERVE_SMS, OPT_PDL, OPT_HEAD_TAIL, OPT_FUSE_POOL, OPT_FUSE_STEM = range(10)
+OPT_FUSE_BN_BWD, OPT_PERSIST_FWD, OPT_TRACE, OPT_PERSIST_BWD, OPT_TC_STEM, OPT_RESERVE_SMS, OPT_PDL, OPT_HEAD_TAIL, OPT_FUSE_POOL, OPT_FUSE_STEM, OPT_ONE_COPY = range(11)
 
 
 class NrdError(RuntimeError):

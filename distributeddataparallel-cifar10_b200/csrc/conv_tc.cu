@@ -350,6 +350,11 @@ struct PersistFwdArgs {
   nrd_bn_sync_args bs;     // DDP buffer sync that the stem kernel would have applied
 };
 
+// ONE = 1: ONE operand copy per image, [18 rows][18 pixels][64 B] with a row AND column halo, instead of three kx-shifted
+// copies: SWIZZLE_64B is a function of the shared-memory address, so a tap is just a descriptor start (ky*18 + kx pixels
+// further, tools/umma_shift_test.cu) and a pixel tile is 16 image rows x 8 columns (8-row groups one 18-pixel pitch apart).
+// A third of the operand writes in pass 2, a third of the shared memory.
+template <int ONE>
 __global__ void __launch_bounds__(576, 1)
 k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmXst,
                  const __grid_constant__ CUtensorMap tmYst, PersistFwdArgs a) {
@@ -358,12 +363,15 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
-  constexpr int SLOT_BYTES = 3 * K::BUF_BYTES;                    // 55,296 B: three kx-copies of one image
+  constexpr int PITCH = 18;                                       // ONE: pixels per operand row (16 + column halo)
+  constexpr int SLOT_BYTES = ONE ? 21 * 1024 : 3 * K::BUF_BYTES;  // 18*18*64 = 20,736 B rounded up / 55,296 B: three kx-copies
   const uint32_t a_smem = base;                                   // 2 image slots
   const uint32_t w_smem = a_smem + 2 * SLOT_BYTES;               // 9 taps
   constexpr int YST_BYTES = NRD_PIX * C * 2;                      // 16,384 B: y_k of one image, staged for its TMA store
   const uint32_t y_smem = w_smem + 9 * K::WTAP_BYTES;             // 2 image slots (1024-B aligned)
-  const uint32_t bar0 = y_smem + 2 * YST_BYTES;
+  // ONE: x_{k+1} is staged like y_k for its bulk store (a haloed 18 x 18 box cannot be the source of a tensor store)
+  const uint32_t xst_smem = y_smem + 2 * YST_BYTES;
+  const uint32_t bar0 = xst_smem + (ONE ? 2 * YST_BYTES : 0);
   const uint32_t wfull = bar0;
   auto xfull = [&](int s) { return bar0 + 8u * (1 + s); };
   auto opready = [&](int s) { return bar0 + 8u * (3 + s); };
@@ -374,7 +382,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
   const uint32_t st_afull = bar0 + 8u * 14, st_tfull = bar0 + 8u * 15;   // fused stem: im2col tiles written / accumulators ready
   const uint32_t st_x0free = bar0 + 8u * 16;                             // ... x_0's bulk store has read the centre copies
   constexpr int BAR_BYTES = 8 * 18;
-  constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + 2 * YST_BYTES + BAR_BYTES;
+  constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + (ONE ? 4 : 2) * YST_BYTES + BAR_BYTES;
   float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][sum | sum of squares][16 channels]
   float* ss_sm = red + 1024;                                             // [2C] scale | shift of the current block
   // fused stem scratch: W1 tile (1024-B aligned), bias, two zero-padded fp32 images; the four im2col tiles of a half image
@@ -449,16 +457,21 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
       for (int t = 0; t < 9; ++t) tma_load_2d(w_smem + t * K::WTAP_BYTES, &tmW, wfull, t * C, 0);
       if (!fuse_stem) {
         for (int s = 0; s < nslots; ++s) {
-          mbar_expect_tx(xfull(s), SLOT_BYTES);
-          for (int kx = 0; kx < 3; ++kx)
-            tma_load_4d(a_smem + s * SLOT_BYTES + kx * K::BUF_BYTES, &tmX0, xfull(s), 0, kx - 1, -1, s == 0 ? img0 : img1);
+          if (ONE) {
+            mbar_expect_tx(xfull(s), PITCH * PITCH * 64);
+            tma_load_4d(a_smem + s * SLOT_BYTES, &tmX0, xfull(s), 0, -1, -1, s == 0 ? img0 : img1);     // box 18 x 18: halo zero-filled
+          } else {
+            mbar_expect_tx(xfull(s), SLOT_BYTES);
+            for (int kx = 0; kx < 3; ++kx)
+              tma_load_4d(a_smem + s * SLOT_BYTES + kx * K::BUF_BYTES, &tmX0, xfull(s), 0, kx - 1, -1, s == 0 ? img0 : img1);
+          }
         }
       } else {
         // fused stem: x_0 was produced on chip; it still goes to global memory (block 0's weight gradient and the stem
         // backward read it), straight from the centre copies
         for (int s = 0; s < nslots; ++s) {
           mbar_wait(xfull(s), 0);
-          tma_store_5d(&tmXst, a_smem + s * SLOT_BYTES + K::BUF_BYTES + K::IMGROW_BYTES, 0, 0, 0, s == 0 ? img0 : img1, 0);
+          tma_store_5d(&tmXst, ONE ? xst_smem + s * YST_BYTES : a_smem + s * SLOT_BYTES + K::BUF_BYTES + K::IMGROW_BYTES, 0, 0, 0, s == 0 ? img0 : img1, 0);
         }
         bulk_commit(); bulk_wait_read0();
         mbar_arrive(st_x0free);
@@ -475,7 +488,8 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         mbar_arrive(yfree);
         for (int s = 0; s < nslots; ++s) {
           mbar_wait(opready(s), (uint32_t)(k & 1));
-          if (!a.dbg_skip_stores) tma_store_5d(&tmXst, a_smem + s * SLOT_BYTES + K::BUF_BYTES + K::IMGROW_BYTES, 0, 0, 0, s == 0 ? img0 : img1, k + 1);
+          if (!a.dbg_skip_stores)
+            tma_store_5d(&tmXst, ONE ? xst_smem + s * YST_BYTES : a_smem + s * SLOT_BYTES + K::BUF_BYTES + K::IMGROW_BYTES, 0, 0, 0, s == 0 ? img0 : img1, k + 1);
         }
         bulk_commit(); bulk_wait_read0();
         mbar_arrive(xfree);
@@ -513,8 +527,10 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
             const uint32_t d_tmem = tmem_base + (s * 2 + m) * C;
 #pragma unroll
             for (int t = 0; t < 9; ++t) {
-              const uint32_t a_addr = a_smem + s * SLOT_BYTES + (t % 3) * K::BUF_BYTES + (m * 8 + t / 3) * K::IMGROW_BYTES;
-              const uint64_t ad = make_sdesc(a_addr, 16, K::SBO, K::LAYOUT);
+              // ONE: tile m = columns 8m..8m+7 of all 16 rows; tap (ky, kx) starts ky rows and kx pixels into the haloed copy
+              const uint32_t a_addr = ONE ? a_smem + s * SLOT_BYTES + ((t / 3) * PITCH + m * 8 + (t % 3)) * 64
+                                          : a_smem + s * SLOT_BYTES + (t % 3) * K::BUF_BYTES + (m * 8 + t / 3) * K::IMGROW_BYTES;
+              const uint64_t ad = make_sdesc(a_addr, 16, ONE ? PITCH * 64 : K::SBO, K::LAYOUT);
               const uint64_t bd = make_sdesc(w_smem + t * K::WTAP_BYTES, 16, K::SBO, K::LAYOUT);
 #pragma unroll
               for (int kk = 0; kk < K::KSTEPS; ++kk) umma_bf16(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (t | kk) != 0);
@@ -528,8 +544,10 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     // ===== epilogue: 16 warps; warp = (channel half h, tile m, TMEM lane quarter q); thread = one pixel x 16 channels, of =====
     // ===== image slot 0 and then of slot 1: slot 0's operands are ready (and its MMAs run) while slot 1 is still in pass 2 =====
     const int ew = warp - 2, h = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
-    const int p = q * 32 + lane, pi = m * 8 + (p >> 4), pj = p & 15;
-    const int P1 = (pi + 1) * 16 + pj;                                         // its index inside an operand copy (row-haloed)
+    // pixel of this thread = row of its TMEM lane in tile m: 8 rows x 16 columns per tile, or (ONE) 16 rows x 8 columns
+    const int p = q * 32 + lane, pi = ONE ? q * 4 + (lane >> 3) : m * 8 + (p >> 4), pj = ONE ? m * 8 + (lane & 7) : (p & 15);
+    const int P1 = ONE ? (pi + 1) * PITCH + pj + 1 : (pi + 1) * 16 + pj;       // its index inside the (centre) operand copy
+    constexpr int CEN = ONE ? 0 : K::BUF_BYTES;                                // byte offset of the centre copy in a slot
     const int P0y = pi * 16 + pj;                                              // ... and inside the y staging tile
     const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
     const float* ss_w = ss_sm + h * 16;                                        // this thread's channels: scale at [c], shift at [C + c]
@@ -615,9 +633,12 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
               pk[e] = *reinterpret_cast<const uint32_t*>(&hv);
             }
             const uint4 ok = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
-            if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
-            if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
+            // the stem's accumulator rows are pooled pixels in row-major order of the half image (8 rows x 16 columns)
+            const int sj = p & 15, P1s = ONE ? (hh * 8 + (p >> 4) + 1) * PITCH + sj + 1 : (hh * 8 + (p >> 4) + 1) * 16 + sj;
+            *reinterpret_cast<uint4*>(slot_gen + CEN + P1s * 64 + ((ch ^ ((P1s >> 1) & 3)) << 4)) = ok;
+            if (ONE) { const int P0s = (hh * 8 + (p >> 4)) * 16 + sj; *reinterpret_cast<uint4*>(gen_base + (xst_smem - base) + s_ * YST_BYTES + P0s * 64 + ((ch ^ ((P0s >> 1) & 3)) << 4)) = ok; }
+            if (!ONE && sj < 15) { const int P0 = P1s + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
+            if (!ONE && sj > 0) { const int P2 = P1s - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
           }
           *reinterpret_cast<uint4*>(a.idx0 + ((size_t)(s_ == 0 ? img0 : img1) * NRD_PIX + hh * 128 + p) * C + h * 16) = make_uint4(mi[0], mi[1], mi[2], mi[3]);
           if (trs) trs[3 + i * 3] = clock64();
@@ -723,7 +744,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         for (int j = 0; j < 2; ++j) {
           // residual x_k from the centre copy (kx = 1); 16-B chunk ch of pixel P sits at chunk ch ^ ((P>>1)&3) (SWIZZLE_64B)
           const int ch = h * 2 + j;
-          const uint4 xk = *reinterpret_cast<const uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4));
+          const uint4 xk = *reinterpret_cast<const uint4*>(slot_gen + CEN + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4));
           const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xk);
           uint4 ok;
           __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
@@ -735,11 +756,12 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
             const float2 sc2 = *reinterpret_cast<const float2*>(ss_w + c), sh2 = *reinterpret_cast<const float2*>(ss_w + C + c);
             oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, sc2.x, sh2.x), 0.f) + xr.x, fmaxf(fmaf(yr.y, sc2.y, sh2.y), 0.f) + xr.y);
           }
-          *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;   // also the store's source
-          if (k + 1 < a.NB) {
+          *reinterpret_cast<uint4*>(slot_gen + CEN + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;   // (!ONE: also the store's source)
+          if (ONE) *reinterpret_cast<uint4*>(gen_base + (xst_smem - base) + s * YST_BYTES + P0y * 64 + ((ch ^ ((P0y >> 1) & 3)) << 4)) = ok;
+          if (!ONE && k + 1 < a.NB) {
             if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
             if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
-          } else if (a.pooled) {
+          } else if (k + 1 == a.NB && a.pooled) {
             // last block: max-pool 2x2 of the network body's output right here.  A warp holds two image rows (lanes 0..15 and
             // 16..31), so the window of the even/even pixel is lanes l, l^1, l^16, l^17 = positions 0..3; first maximum wins
             // (k_pool_fc1_fwd_part's rule).  The even/even lane writes 8 pooled channels and their arg-max bytes.
@@ -747,8 +769,8 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
             uint32_t pk[4]; uint32_t ib[2] = {0u, 0u};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              const uint32_t o1 = __shfl_xor_sync(0xffffffffu, own[e], 1), o2 = __shfl_xor_sync(0xffffffffu, own[e], 16),
-                             o3 = __shfl_xor_sync(0xffffffffu, own[e], 17);
+              const uint32_t o1 = __shfl_xor_sync(0xffffffffu, own[e], 1), o2 = __shfl_xor_sync(0xffffffffu, own[e], ONE ? 8 : 16),
+                             o3 = __shfl_xor_sync(0xffffffffu, own[e], ONE ? 9 : 17);      // next row: 8 lanes on (ONE), else 16
               const uint32_t w4[4] = {own[e], o1, o2, o3};
               float2 mx = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w4[0]));
               uint32_t i0 = 0, i1 = 0;
@@ -1331,8 +1353,8 @@ template <int C> constexpr size_t wgrad_smem() {
   return 1024 + WCfg<C>::NSS * WCfg<C>::STAGE_BYTES + WCfg<C>::SLACK + 8 * (2 * WCfg<C>::NSS + 2) + 64;
 }
 
-constexpr size_t persist_smem() {
-  return 1024 + 2 * 3 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 2 * NRD_PIX * 32 * 2 + 144 + (1024 + 64) * sizeof(float) + 64 +
+constexpr size_t persist_smem(int one) {
+  return 1024 + 2 * (one ? 21 * 1024 : 3 * Cfg<32>::BUF_BYTES) + 9 * Cfg<32>::WTAP_BYTES + (one ? 4 : 2) * NRD_PIX * 32 * 2 + 144 + (1024 + 64) * sizeof(float) + 64 +
          1024 + 2048 + 128 + 2 * 3 * 34 * 40 * sizeof(float);     // + fused stem: alignment, W1 tile, bias, two padded images
 }
 
@@ -1376,7 +1398,8 @@ int nrd_tc_plan_init(nrd_plan* p) {
   // fused block forward: every CTA keeps all its accumulators in TMEM (512 columns) and all CTAs must be co-resident
   nrd_tc_refresh_limits(p);
   if (p->C == 32) {
-    NRD_TRY(set_attr(k_tc_fwd_persist, persist_smem()));
+    NRD_TRY(set_attr(k_tc_fwd_persist<0>, persist_smem(0)));
+    NRD_TRY(set_attr(k_tc_fwd_persist<1>, persist_smem(1)));
     NRD_TRY(set_attr(k_tc_bwd_persist, persist_bwd_smem()));
     // all saved x_k as ONE 5-D tensor {C, W, H, N, k}: the block index is just the last TMA coordinate
     PFN_encodeTiled enc = get_encode();
@@ -1392,6 +1415,14 @@ int nrd_tc_plan_init(nrd_plan* p) {
     r = enc(&p->tm_xst, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, p->xs, dims, strides, sbox, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { nrd_set_error("cuTensorMapEncodeTiled(x store) failed: %d", (int)r); return NRD_ECUDA; }
+    {   // one-copy layout: x_0 WITH its halo, 18 x 18 pixels (zero-filled by the load)
+      cuuint64_t d4[4] = {32, 16, 16, (cuuint64_t)p->B};
+      cuuint64_t s4[3] = {64, 1024, 16384};
+      cuuint32_t b4[4] = {32, 18, 18, 1}, e4[4] = {1, 1, 1, 1};
+      r = enc(&p->tm_x18, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, p->xs, d4, s4, b4, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) { nrd_set_error("cuTensorMapEncodeTiled(x_0, haloed) failed: %d", (int)r); return NRD_ECUDA; }
+    }
     cuuint64_t ydims[5] = {32, 16, 16, (cuuint64_t)p->B, (cuuint64_t)p->NB};
     r = enc(&p->tm_yst, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, p->ys, ydims, strides, sbox, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1459,8 +1490,9 @@ int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int t
   a.pooled = pool ? (bf16*)p->pooled : nullptr; a.idx2 = p->idx2; a.poll_ns = p->poll_ns;
   a.images = stem_images; a.conv1_wp = p->conv1_wp; a.conv1_b = p->params + p->off[1]; a.idx0 = p->idx0; a.bs = nrd_bn_sync_of(p, training);
   a.inv_count = 1.0 / ((double)p->B * NRD_PIX); a.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
-  void* args[] = {(void*)&p->tm_x[0], (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
-  NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_smem(), st));
+  void* args[] = {(void*)(p->one_copy ? &p->tm_x18 : &p->tm_x[0]), (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
+  if (p->one_copy) NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist<1>, dim3(conv_grid(p)), dim3(576), args, persist_smem(1), st));
+  else NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist<0>, dim3(conv_grid(p)), dim3(576), args, persist_smem(0), st));
   nrd_count_launch();
   return NRD_OK;
 }
