@@ -840,6 +840,9 @@ struct PersistBwdArgs {
   int poll_ns;
 };
 
+// ONE = 1: dy lives in ONE row- and column-haloed copy per image (see k_tc_fwd_persist): dgrad taps are pixel-granular
+// descriptor starts, the weight gradient's three kx taps are N groups ONE pixel apart (LBO = 64 B)
+template <int ONE>
 __global__ void __launch_bounds__(576, 1)
 k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_constant__ CUtensorMap tmWd, PersistBwdArgs a) {
   constexpr int C = 32;
@@ -847,7 +850,8 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
-  constexpr int DY_BYTES = 3 * K::BUF_BYTES;                      // three kx-copies of dy
+  constexpr int PITCH = 18;
+  constexpr int DY_BYTES = ONE ? 21 * 1024 : 3 * K::BUF_BYTES;    // one haloed copy (18*18*64 B rounded up) / three kx-copies of dy
   constexpr int SLOT_BYTES = DY_BYTES + K::BUF_BYTES;             // + row-haloed x_k tile
   const uint32_t a_smem = base;
   const uint32_t w_smem = a_smem + 2 * SLOT_BYTES;
@@ -928,8 +932,9 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
             const uint32_t d_tmem = tmem_base + (s * 2 + m) * C;
 #pragma unroll
             for (int t = 0; t < 9; ++t) {
-              const uint32_t a_addr = a_smem + s * SLOT_BYTES + (t % 3) * K::BUF_BYTES + (m * 8 + t / 3) * K::IMGROW_BYTES;
-              const uint64_t ad = make_sdesc(a_addr, 16, K::SBO, K::LAYOUT);
+              const uint32_t a_addr = ONE ? a_smem + s * SLOT_BYTES + ((t / 3) * PITCH + m * 8 + (t % 3)) * 64
+                                          : a_smem + s * SLOT_BYTES + (t % 3) * K::BUF_BYTES + (m * 8 + t / 3) * K::IMGROW_BYTES;
+              const uint64_t ad = make_sdesc(a_addr, 16, ONE ? PITCH * 64 : K::SBO, K::LAYOUT);
               const uint64_t bd = make_sdesc(w_smem + t * K::WTAP_BYTES, 16, K::SBO, K::LAYOUT);
 #pragma unroll
               for (int kk = 0; kk < K::KSTEPS; ++kk) umma_bf16(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc_d, (t | kk) != 0);
@@ -948,7 +953,8 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
             // A (MN-major): x_k rows yy .. yy+3 of the row-haloed tile stacked along M = (j, ci): vertical tap ky = j (j = 3 junk)
             // B (MN-major): row yy of the three kx-shifted dy copies stacked along N = (kxb, co): horizontal tap kx = 2 - kxb
             const uint64_t ad = make_sdesc(sb + DY_BYTES + yy * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
-            const uint64_t bd = make_sdesc(sb + (yy + 1) * K::IMGROW_BYTES, K::BUF_BYTES, K::SBO, K::LAYOUT);
+            const uint64_t bd = ONE ? make_sdesc(sb + (yy + 1) * PITCH * 64, 64, K::SBO, K::LAYOUT)          // N groups one pixel apart
+                                    : make_sdesc(sb + (yy + 1) * K::IMGROW_BYTES, K::BUF_BYTES, K::SBO, K::LAYOUT);
             umma_bf16(tmem_base + ACCW, ad, bd, idesc_w, (it > 0 || s > 0 || yy > 0) ? 1u : 0u);
           }
           umma_commit(wfree(s));
@@ -964,9 +970,10 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     // ===== epilogue: 16 warps; warp = (channel half h, tile m, TMEM lane quarter q); thread = one pixel x 16 channels, of =====
     // ===== image slot 0 and then of slot 1 (slot 0's dgrad MMAs run while slot 1's dy is still being written) =====
     const int ew = warp - 2, h = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
-    const int p = q * 32 + lane, pi = m * 8 + (p >> 4), pj = p & 15;
+    // pixel of this thread = row of its TMEM lane in tile m: 8 rows x 16 columns per tile, or (ONE) 16 rows x 8 columns
+    const int pi = ONE ? q * 4 + (lane >> 3) : m * 8 + ((q * 32 + lane) >> 4), pj = ONE ? m * 8 + (lane & 7) : (lane & 15);
     const size_t pix_off = (size_t)(pi * 16 + pj) * C + h * 16;               // this thread's 16 channels inside an image
-    const int P1 = (pi + 1) * 16 + pj;                                         // its index inside an operand copy (row-haloed)
+    const int P1 = ONE ? (pi + 1) * PITCH + pj + 1 : (pi + 1) * 16 + pj;       // its index inside the (centre) dy copy
     const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + s * 2C
     float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, warp ew == 0 (lane = channel): running dgamma / dbeta over the blocks
     // y_k of this thread's pixel: prefetched one block ahead with cp.async into this thread's own shared-memory slots,
@@ -1124,9 +1131,9 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
               const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
               oh[e] = __floats2bfloat162_rn(fmaf(d0, c0.x, fmaf(y2.x, c0.y, c0.z)), fmaf(d1, c1.x, fmaf(y2.y, c1.y, c1.z)));
             }
-            *reinterpret_cast<uint4*>(slot_gen + K::BUF_BYTES + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
-            if (pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
-            if (pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
+            *reinterpret_cast<uint4*>(slot_gen + (ONE ? 0 : K::BUF_BYTES) + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4)) = ok;
+            if (!ONE && pj < 15) { const int P0 = P1 + 1; *reinterpret_cast<uint4*>(slot_gen + P0 * 64 + ((ch ^ ((P0 >> 1) & 3)) << 4)) = ok; }
+            if (!ONE && pj > 0) { const int P2 = P1 - 1; *reinterpret_cast<uint4*>(slot_gen + 2 * K::BUF_BYTES + P2 * 64 + ((ch ^ ((P2 >> 1) & 3)) << 4)) = ok; }
           }
           fence_proxy_async();
           mbar_arrive(dyready(s));
@@ -1358,8 +1365,8 @@ constexpr size_t persist_smem(int one) {
          1024 + 2048 + 128 + 2 * 3 * 34 * 40 * sizeof(float);     // + fused stem: alignment, W1 tile, bias, two padded images
 }
 
-constexpr size_t persist_bwd_smem() {
-  return 1024 + 2 * 4 * Cfg<32>::BUF_BYTES + 9 * Cfg<32>::WTAP_BYTES + 112 + (1024 + 96 + 256) * sizeof(float) + (2048 + 256) * sizeof(double) + 4 * 512 * 16 + 64;
+constexpr size_t persist_bwd_smem(int one) {
+  return 1024 + 2 * ((one ? 21 * 1024 : 3 * Cfg<32>::BUF_BYTES) + Cfg<32>::BUF_BYTES) + 9 * Cfg<32>::WTAP_BYTES + 112 + (1024 + 96 + 256) * sizeof(float) + (2048 + 256) * sizeof(double) + 4 * 512 * 16 + 64;
 }
 
 static int items(const nrd_plan* p) { return p->B * (p->C == 32 ? 1 : 2); }
@@ -1400,7 +1407,8 @@ int nrd_tc_plan_init(nrd_plan* p) {
   if (p->C == 32) {
     NRD_TRY(set_attr(k_tc_fwd_persist<0>, persist_smem(0)));
     NRD_TRY(set_attr(k_tc_fwd_persist<1>, persist_smem(1)));
-    NRD_TRY(set_attr(k_tc_bwd_persist, persist_bwd_smem()));
+    NRD_TRY(set_attr(k_tc_bwd_persist<0>, persist_bwd_smem(0)));
+    NRD_TRY(set_attr(k_tc_bwd_persist<1>, persist_bwd_smem(1)));
     // all saved x_k as ONE 5-D tensor {C, W, H, N, k}: the block index is just the last TMA coordinate
     PFN_encodeTiled enc = get_encode();
     cuuint64_t dims[5] = {32, 16, 16, (cuuint64_t)p->B, (cuuint64_t)(p->NB + 1)};
@@ -1490,8 +1498,8 @@ int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int t
   a.pooled = pool ? (bf16*)p->pooled : nullptr; a.idx2 = p->idx2; a.poll_ns = p->poll_ns;
   a.images = stem_images; a.conv1_wp = p->conv1_wp; a.conv1_b = p->params + p->off[1]; a.idx0 = p->idx0; a.bs = nrd_bn_sync_of(p, training);
   a.inv_count = 1.0 / ((double)p->B * NRD_PIX); a.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
-  void* args[] = {(void*)(p->one_copy ? &p->tm_x18 : &p->tm_x[0]), (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
-  if (p->one_copy) NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist<1>, dim3(conv_grid(p)), dim3(576), args, persist_smem(1), st));
+  void* args[] = {(void*)((p->one_copy & 1) ? &p->tm_x18 : &p->tm_x[0]), (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
+  if (p->one_copy & 1) NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist<1>, dim3(conv_grid(p)), dim3(576), args, persist_smem(1), st));
   else NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_persist<0>, dim3(conv_grid(p)), dim3(576), args, persist_smem(0), st));
   nrd_count_launch();
   return NRD_OK;
@@ -1508,7 +1516,8 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cud
   a.acc = p->bn_acc + (size_t)32 * NRD_ACC_ROW; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.dbg_skip = p->dbg_skip_stores; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
-  NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(), st));
+  if (p->one_copy & 2) NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist<1>, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(1), st));
+  else NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist<0>, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(0), st));
   nrd_count_launch();
   return NRD_OK;
 }

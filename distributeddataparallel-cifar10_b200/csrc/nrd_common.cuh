@@ -160,7 +160,7 @@ struct nrd_plan {
   CUtensorMap tm_wf, tm_wd;
   CUtensorMap tm_xall;    // all x_k as one 5-D tensor (persistent backward)
   CUtensorMap tm_x18;     // x_0 with an 18 x 18 (haloed) box: the one-copy operand layout
-  int one_copy;           // option: ONE haloed operand copy per image in the persistent kernels instead of three shifted ones
+  int one_copy;           // option (bit 0 forward, bit 1 backward): ONE haloed operand copy per image instead of three shifted ones
   CUtensorMap tm_xst, tm_yst; // x_k / y_k stacks, whole-image boxes: bulk tensor STORES of the persistent forward
   int tc_ready;
   nrd_xchg_args xchg;     // peer-memory gradient exchange (nrd_plan_set_exchange); world == 0: off

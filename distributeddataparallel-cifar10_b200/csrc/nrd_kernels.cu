@@ -1755,7 +1755,7 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->persist_bwd = 1;
   p->use_tc_stem = 1;
   p->fuse_head_tail = 1;
-  p->one_copy = 1;
+  p->one_copy = 1;           // forward only: in the backward the one-pixel-apart N groups of the weight gradient measured 2 us slower
   p->fuse_stem = 0;          // measured: as long as the stem kernel it replaces (its four half images run one after the other)
   p->fuse_pool = 0;          // measured 1 us slower per step than pooling in the fc1 kernel (it sits on the blocks' critical path)
   { const char* e = getenv("NRD_POLL_NS"); p->poll_ns = e ? atoi(e) : 0; }
@@ -1798,7 +1798,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_HEAD_TAIL: p->fuse_head_tail = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_FUSE_POOL: p->fuse_pool = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_FUSE_STEM: p->fuse_stem = value ? 1 : 0; return NRD_OK;
-    case NRD_OPT_ONE_COPY: p->one_copy = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_ONE_COPY: p->one_copy = value & 3; return NRD_OK;
     case NRD_OPT_RESERVE_SMS:
       NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
       p->reserve_sms = value;

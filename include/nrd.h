@@ -101,8 +101,9 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
  * built by its 512 epilogue threads, 8 tcgen05.mma per half image, result written straight into the operand copies):
  * no stem launch, no x_0 load. */
 #define NRD_OPT_FUSE_STEM 9
-/* NRD_OPT_ONE_COPY (default 1): the persistent kernels keep ONE row- and column-haloed operand copy per image (a tap is a
- * pixel-granular descriptor start) instead of three kx-shifted copies. */
+/* NRD_OPT_ONE_COPY (bit mask, default 1): bit 0 = the persistent forward, bit 1 = the persistent backward keep ONE row- and
+ * column-haloed operand copy per image (a tap is a pixel-granular descriptor start) instead of three kx-shifted copies.
+ * Measured: forward -1 us; backward +2 us (its weight-gradient MMAs read N groups one pixel apart), hence off there. */
 #define NRD_OPT_ONE_COPY 10
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* DDP's per-forward buffer broadcast (torch DDP `broadcast_buffers`, reached from main.py:63 and run in front of every

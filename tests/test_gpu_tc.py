@@ -220,3 +220,28 @@ def test_stem_fused_into_persistent_forward_is_bitwise_the_stem_kernel(B):
         res.append((out.detach().clone(), pl.tensor_view(0, 0).clone(), m.engine.flat_grads.clone(), bn.running_mean.clone(), bn.running_var.clone()))
     for a_, b_ in zip(res[0], res[1]):
         assert torch.equal(a_, b_)
+
+
+@pytest.mark.parametrize("B", [3, 256])
+def test_one_copy_operand_layouts_match_three_copy_layouts(B):
+    """NRD_OPT_ONE_COPY: one haloed operand copy (pixel-granular descriptor starts, 16 x 8 pixel tiles) in the persistent forward
+    (bit 0) and backward (bit 1) against the three kx-shifted copies: the same products per output element; only the grouping
+    of the fp32 BN partial sums differs (different pixels per warp)."""
+    g = torch.Generator().manual_seed(40 + B)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for mode in (0, 1, 3):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(32, 10, dtype="bf16").to(DEV)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 10, mode))
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        torch.cuda.synchronize()
+        res.append((out.detach().clone(), module_grads(m)))
+    for other in res[1:]:
+        assert rell2(other[0], res[0][0]) < 2e-3
+        for k in res[0][1]:
+            assert rell2(other[1][k], res[0][1][k]) < 4e-2 and cosine(other[1][k], res[0][1][k]) > 0.999, k
+    # forward layout fixed: the backward layouts see identical inputs and must agree closely
+    for k in res[1][1]:
+        assert rell2(res[2][1][k], res[1][1][k]) < 1e-2 and cosine(res[2][1][k], res[1][1][k]) > 0.9999, k
