@@ -258,8 +258,8 @@ def main():
             v["share"] = round(v["us"] * v["per_step"] / tot, 3)
         dom = max(breakdown, key=lambda k: breakdown[k]["us"] * breakdown[k]["per_step"])
         d = breakdown[dom]
-        # DRAM bytes per launch from the committed ncu --set full capture (profiles/r01_step_v9_final.md), same config only
-        ncu_traffic = {"bwd_blocks(persistent)": 85643776 + 3396096, "fwd_blocks(persistent)": 4361472 + 32077056}
+        # DRAM bytes per launch from the committed ncu --set full capture (profiles/r01_step_v10_final.md), same config only
+        ncu_traffic = {"bwd_blocks(persistent)": 85645056 + 3553280, "fwd_blocks(persistent)": 4365056 + 32791552}
         traffic = ncu_traffic.get(dom) if (B, C, NB, args.dtype) == (256, 32, 10, "bf16") else None
         roof = {"bound": "hbm", "kernel": dom, "achieved": d["gbs"], "peak": hbm, "unit": "GB/s", "frac": round(d["gbs"] / hbm, 4),
                 "traffic": traffic, "peak_source": peak_kind, "launch_us": d["us"], "algo_bytes_per_launch": d["algo_bytes"],
