@@ -315,13 +315,16 @@ k_tc_conv(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 // ============================================================================================
 // Persistent forward over ALL residual blocks (C = 32, at most 2 images per CTA, cooperative launch).
 // The block's convolution of an image depends only on that image, so each CTA keeps its images' block input on chip for
-// the whole stack: x_0 comes in by TMA (3 kx-shifted, row-haloed copies), and for every block
-//     MMA warp     36 tcgen05.mma per image from the shared-memory copies -> 2 accumulators (TMEM) per image
-//     pass 1       BN partial sums straight from TMEM (fp32), per-CTA row -> global, ONE grid barrier, fixed-order combine
-//     pass 2       y_k (bf16) and x_{k+1} = relu(bn(y_k)) + x_k -> global (saved for backward) AND x_{k+1} written back
-//                  into the three swizzled operand copies in shared memory = the next block's A operand
+// the whole stack: x_0 comes in by TMA (one haloed copy, or 3 kx-shifted row-haloed copies: template parameter ONE), and per block
+//     MMA warp     36 tcgen05.mma per image from the shared-memory copy/copies -> 2 accumulators (TMEM) per image
+//     pass 1       BN sums straight from TMEM (fp32) -> CTA sum -> returning atomics on count-carrying words (nrd_common.cuh);
+//                  y_k (bf16) staged in shared memory for a bulk tensor store
+//     exchange     one warp polls its channels' words until every CTA has contributed, derives scale / shift
+//     pass 2       x_{k+1} = relu(bn(y_k)) + x_k written (swizzled) into the operand copy/copies = the next block's A operand
+//                  (and, ONE, into a staging tile); the store thread sends it to global memory (saved for backward)
 // so between blocks nothing is re-read from global memory and there is one launch instead of NB (or 3*NB).
-// 576 threads: warp 0 TMA, warp 1 MMA, 16 epilogue warps = (image slot, 128-pixel tile, TMEM lane quarter): one pixel per thread.
+// 576 threads: warp 0 TMA loads + bulk stores, warp 1 MMA, 16 epilogue warps = (channel half, pixel tile, TMEM lane quarter):
+// one pixel x 16 channels per thread, image slot 0 then slot 1.
 // ============================================================================================
 struct PersistFwdArgs {
   const float* gamma; const float* beta;
@@ -810,14 +813,17 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
 // Persistent backward over ALL residual blocks (C = 32, at most 2 images per CTA, cooperative launch).
 // dL/dx of an image never leaves the SM: it lives in the epilogue threads' registers (bf16 pairs, the same rounding the
 // per-block kernels apply when they store it).  Per block k = NB-1 .. 0 and image:
-//   phase A   read y_k (global, one 64-B pixel row per thread); dz = g*[bn(y)>0]; per-channel sums of dz and dz*xhat
-//             (warp transpose-reduce) -> per-CTA row -> ONE grid barrier -> fixed-order fp64 combine -> coefficients
+//   phase A   y_k of the thread's pixel (cp.async, one block ahead); dz = g*[bn(y)>0]; per-channel sums of dz and dz*y
+//             (warp transpose-reduce) -> CTA sum -> returning atomics on count-carrying words -> one warp polls, derives
+//             the dy coefficients (no separate grid barrier)
 //   phase B   dy = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)) written (bf16, swizzled) into three kx-shifted,
-//             row-haloed copies in shared memory = the A operand of BOTH convolution gradients
-//   MMA       dgrad: 36 tcgen05.mma (K-major dy copies x flipped weights) -> 2 accumulators per image
-//             wgrad: 48 tcgen05.mma (MN-major dy copies stacked 4 vertical taps deep x MN-major x_k tile from TMA) into 3
-//             accumulators that persist over all blocks and both images: ONE partial store per CTA per step
-//   phase C   dx_k = dgrad + g -> registers (-> global only for k = 0)
+//             row-haloed copies in shared memory (or ONE haloed copy: template parameter) = operand of BOTH gradients
+//   MMA       dgrad: 36 tcgen05.mma per image (K-major dy x flipped weights) -> 2 accumulators per image
+//             wgrad: 16 tcgen05.mma per image, both operands MN-major: A = 4 vertical taps of the row-haloed x_k tile (TMA)
+//             stacked along M, B = the three kx-shifted dy rows stacked along N = 96; ONE accumulator set that persists over
+//             all blocks and both images: one partial store per CTA per step, issued under the last block's dgrad
+//   phase C   dx_k = dgrad + g -> registers (-> global only for k = 0), then straight into phase A of the next block
+// dL/dx_NB itself is built from dL/d(pooled) through pool-2's arg-max while the registers are loaded.
 // HBM traffic per block: y_k and x_k read once; nothing written.
 // ============================================================================================
 struct PersistBwdArgs {
@@ -862,7 +868,6 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   auto wfree = [&](int s) { return bar0 + 8u * (5 + s); };
   auto dxfull = [&](int s, int m) { return bar0 + 8u * (7 + s * 2 + m); };
   const uint32_t wdone = bar0 + 8u * 11;
-  const uint32_t epi_idle = bar0 + 8u * 12;
   const uint32_t tmem_slot = bar0 + 8u * 13;
   constexpr int BAR_BYTES = 8 * 14;
   constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
@@ -890,7 +895,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   fence_proxy_async();
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmXall); tma_prefetch_desc(&tmWd);
-    mbar_init(wfull, 1); mbar_init(wdone, 1); mbar_init(epi_idle, 1);
+    mbar_init(wfull, 1); mbar_init(wdone, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(xready(s), 1); mbar_init(dyready(s), 512); mbar_init(wfree(s), 1);
       mbar_init(dxfull(s, 0), 1); mbar_init(dxfull(s, 1), 1);
