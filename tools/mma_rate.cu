@@ -8,7 +8,7 @@
 
 void nrd_set_error(const char*, ...) {}
 
-struct Variant { int layout; int row_bytes; int sbo; int kstep_off; int N; int a_mn; int lbo; };
+struct Variant { int layout; int row_bytes; int sbo; int kstep_off; int N; int a_mn; int lbo; int b_mn; int b_lbo; };
 
 __global__ void __launch_bounds__(128, 1) k_rate(Variant v, int nmma, long long* out) {
   extern __shared__ uint8_t smem_raw[];
@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(128, 1) k_rate(Variant v, int nmma, long long*
   tc_fence_before(); __syncthreads(); tc_fence_after();
   const uint32_t tmem = *tslot_gen;
   if (warp == 1 && lane == 0) {
-    const uint32_t idesc = make_idesc(128, v.N, v.a_mn, 0);
+    const uint32_t idesc = make_idesc(128, v.N, v.a_mn, v.b_mn);
     const uint32_t a0 = base, b0 = base + 160 * 1024;
     // descriptors precomputed: the timed loop is nothing but tcgen05.mma instructions (18 per round, as one conv tile)
     uint64_t ad[18], bd[18];
@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(128, 1) k_rate(Variant v, int nmma, long long*
       const int t = i >> 1, kk = i & 1;
       const uint32_t a_addr = a0 + (t % 3) * (18 * 16 * v.row_bytes) + (t / 3) * 16 * v.row_bytes + kk * v.kstep_off;
       ad[i] = make_sdesc(a_addr, v.lbo, v.sbo, v.layout);
-      bd[i] = make_sdesc(b0 + t * 2048 + kk * 32, 16, 512, 4);
+      bd[i] = v.b_mn ? make_sdesc(base + 96 * 1024 + i * 1152, v.b_lbo, 512, 4) : make_sdesc(b0 + t * 2048 + kk * 32, 16, 512, 4);
     }
     long long t0 = clock64();
     for (int r = 0; r < nmma / 18; ++r) {
@@ -65,6 +65,9 @@ int main() {
       {"SW32  K-major N=64", {6, 32, 256, 18 * 16 * 32 * 3, 64, 0, 16}},
       {"SW32  K-major N=128", {6, 32, 256, 18 * 16 * 32 * 3, 128, 0, 16}},
       {"SW64  MN-major A (wgrad, LBO=1024) N=32", {4, 64, 512, 1024, 32, 1, 1024}},
+      {"wgrad: MN-major A, MN-major B N=96, groups 18432 B apart", {4, 64, 512, 1024, 96, 1, 1024, 1, 18432}},
+      {"wgrad: MN-major A, MN-major B N=96, groups 64 B apart", {4, 64, 512, 1024, 96, 1, 1024, 1, 64}},
+      {"wgrad: MN-major A, MN-major B N=96, groups 1152 B apart", {4, 64, 512, 1024, 96, 1, 1024, 1, 1152}},
   };
   const int nmma = 1800;
   for (auto& e : vs) {
