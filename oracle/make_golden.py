@@ -126,3 +126,4 @@ if __name__ == "__main__":
     single(64, 3, 4, 2, "step_c64_nb3_b4")              # wide-channel variant (config 4 family)
     single(32, 10, 64, 12, "curve_c32_nb10_b64_lr1e-2", light=True)  # degenerate lr=1e-2 curve, config 1
     ddp(32, 10, 8, 2, "ddp_w2_c32_nb10_b8")
+    ddp(32, 10, 4, 4, "ddp_w4_c32_nb10_b4")             # four ranks: the mean over more than two contributions
