@@ -35,6 +35,7 @@ _PROTOS = {
     "nrd_plan_set_conv_impl": (i32, [vp, i32]),
     "nrd_plan_conv_impl": (i32, [vp]),
     "nrd_plan_set_option": (i32, [vp, i32, i32]),
+    "nrd_plan_status": (i32, [vp, C.POINTER(u32), i32, vp]),
     "nrd_plan_set_bn_sync": (i32, [vp, vp, f32, f32]),
     "nrd_exchange_bytes": (sz, [i32, i32]),
     "nrd_exchange_alloc": (i32, [i32, sz, C.POINTER(vp), vp]),

@@ -351,6 +351,7 @@ struct PersistFwdArgs {
   const float* conv1_b;    // [C]
   uint8_t* idx0;           // [B,16,16,C] stem pool arg-max
   nrd_bn_sync_args bs;     // DDP buffer sync that the stem kernel would have applied
+  unsigned int* status;    // the plan's sticky status word (nrd_acc_add)
 };
 
 // ONE = 1: ONE operand copy per image, [18 rows][18 pixels][64 B] with a row AND column halo, instead of three kx-shifted
@@ -700,7 +701,7 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];   // fixed order over the 8 warps of the half
-        nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 16777216.0), gridDim.x);   // wait for the return: measured faster
+        nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 16777216.0, a.status), gridDim.x);   // wait for the return: measured faster
       }
       stage_y(nslots - 1);
       if (tr) tr[3] = clock64();
@@ -844,6 +845,7 @@ struct PersistBwdArgs {
   int dbg_skip;               // profiling experiment only (results garbage)
   long long* trace;           // optional clock64 stamps (profiling aid), or NULL
   int poll_ns;
+  unsigned int* status;       // the plan's sticky status word (nrd_acc_add)
 };
 
 // ONE = 1: dy lives in ONE row- and column-haloed copy per image (see k_tc_fwd_persist): dgrad taps are pixel-granular
@@ -1088,7 +1090,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
-        nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0), gridDim.x);   // wait for the return: measured faster
+        nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0, a.status), gridDim.x);   // wait for the return: measured faster
       }
       if (tr) tr[2] = clock64();
       // one warp (lane = channel) polls its channels' words, derives the dy coefficients and publishes them (and the NEXT
@@ -1450,7 +1452,7 @@ void nrd_tc_refresh_limits(nrd_plan* p) {
   const int rows = p->C == 32 ? 16 : 8;
   const int grid = conv_grid(p), per_cta = (items(p) + grid - 1) / grid * (rows / 8);
   p->tc_fused_fwd = (per_cta * p->C <= 512) ? 1 : 0;
-  p->tc_persist_fwd = (p->C == 32 && p->B <= 2 * grid) ? 1 : 0;
+  p->tc_persist_fwd = (p->C == 32 && p->B <= 2 * grid && p->NB >= 2) ? 1 : 0;   // NB = 1: the row cleaned at kernel start would be the live row 0
 }
 
 int nrd_tc_stats_blocks(const nrd_plan* p) { return conv_grid(p); }
@@ -1501,6 +1503,7 @@ int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int t
   a.xs = (bf16*)p->xs; a.ys = (bf16*)p->ys; a.partial = p->stats_partial; a.acc = p->bn_acc; a.gbar = p->gbar + NRD_GBAR_PERSIST_FWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace; a.dbg_skip_stores = p->dbg_skip_stores;
   a.pooled = pool ? (bf16*)p->pooled : nullptr; a.idx2 = p->idx2; a.poll_ns = p->poll_ns;
+  a.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS);
   a.images = stem_images; a.conv1_wp = p->conv1_wp; a.conv1_b = p->params + p->off[1]; a.idx0 = p->idx0; a.bs = nrd_bn_sync_of(p, training);
   a.inv_count = 1.0 / ((double)p->B * NRD_PIX); a.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
   void* args[] = {(void*)((p->one_copy & 1) ? &p->tm_x18 : &p->tm_x[0]), (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&a};
@@ -1520,6 +1523,7 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cud
   a.ys = (const bf16*)p->ys; a.g_pool = (const bf16*)g_pooled; a.idx2 = p->idx2; a.poll_ns = p->poll_ns; a.dx0_out = (bf16*)dx0_out;
   a.acc = p->bn_acc + (size_t)32 * NRD_ACC_ROW; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.dbg_skip = p->dbg_skip_stores; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
+  a.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS);
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
   if (p->one_copy & 2) NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist<1>, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(1), st));
   else NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist<0>, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(0), st));

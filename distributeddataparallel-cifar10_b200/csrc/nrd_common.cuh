@@ -63,6 +63,7 @@ void nrd_set_error(const char* fmt, ...);
 struct nrd_xchg_args {
   float* peer[NRD_XCHG_MAX_WORLD];
   int world, rank, nx;          // world == 0: exchange off
+  long long timeout_cycles;     // how long a consumer spins for a peer's flag before it gives up (nrd_plan_set_exchange)
 };
 static __host__ __device__ __forceinline__ size_t nrd_xchg_flags_off(int world, int nx) {
   return (((size_t)2 * world * nx * sizeof(float)) + 127) & ~(size_t)127;
@@ -106,7 +107,7 @@ static __device__ __forceinline__ unsigned long long nrd_xchg_wait(const nrd_xch
       if (v >= epoch) break;
       if (++spins > 4096) {
         if (t0 == 0) t0 = clock64();
-        else if (clock64() - t0 > 60000000000LL) __trap();      // ~30 s: a peer is gone
+        else if (clock64() - t0 > x.timeout_cycles) __trap();   // default ~10 min (NCCL's default watchdog): a peer is gone
       }
     }
   }
@@ -251,10 +252,19 @@ static inline nrd_bn_sync_args nrd_bn_sync_of(const nrd_plan* p, int training) {
 // The atomic RETURNS the old word on purpose: measured (tools/barrier_rate.cu), a round of returning atomics completes in
 // ~2050 cycles on 148 CTAs against ~3000 for fire-and-forget reductions (REDs seem to drain behind the polling loads).  The
 // returned count doubles as a check that the row was clean (a dirty row would otherwise make every CTA spin to the trap).
-static __device__ __forceinline__ unsigned long long nrd_acc_add(unsigned long long* word, float v, double scale) {
-  long long f = __double2ll_rn((double)v * scale);
+// `status` is the plan's sticky status word (NRD_STATUS_*, read by nrd_plan_status): a contribution that does not fit (or is
+// not finite) is still clamped -- the count field must stay intact or every CTA would spin to the trap -- but the step is
+// marked, so wrong statistics never pass silently.
+#define NRD_STATUS_BN_SATURATED 1u     // a per-CTA BN sum left the fixed-point range (forward: |sum| >= 2^22, backward: >= 2^10)
+#define NRD_STATUS_BN_NONFINITE 2u     // a per-CTA BN sum was NaN / Inf
+static __device__ __forceinline__ unsigned long long nrd_acc_add(unsigned long long* word, float v, double scale, unsigned int* status) {
   const long long lim = (long long)NRD_ACC_BIAS - 1;
-  f = f > lim ? lim : (f < -lim ? -lim : f);
+  long long f;
+  if (!isfinite(v)) { f = 0; atomicOr(status, NRD_STATUS_BN_NONFINITE); }
+  else {
+    f = __double2ll_rn((double)v * scale);
+    if (f > lim || f < -lim) { f = f > lim ? lim : -lim; atomicOr(status, NRD_STATUS_BN_SATURATED); }
+  }
   return atomicAdd(word, NRD_ACC_CNT1 + NRD_ACC_BIAS + (unsigned long long)f);
 }
 // checking right away, i.e. waiting for the atomic's return before the first poll, measured 2.5 us per kernel FASTER than
@@ -309,6 +319,8 @@ static __device__ __forceinline__ void nrd_acc_wait2(const unsigned long long* w
 #define NRD_GBAR_PERSIST_FWD 1
 #define NRD_GBAR_BN_BWD 2
 #define NRD_GBAR_PERSIST_BWD 3
+#define NRD_GBAR_HEAD_COUNTER 16       // word of the gbar block used as the head kernels' arrival counter
+#define NRD_GBAR_STATUS 24             // word of the gbar block that holds the sticky status flags
 
 // tcgen05 path (conv_tc.cu)
 int nrd_tc_plan_init(nrd_plan* p);

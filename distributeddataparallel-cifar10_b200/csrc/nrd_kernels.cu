@@ -1801,6 +1801,14 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_ONE_COPY: p->one_copy = value & 3; return NRD_OK;
     case NRD_OPT_RESERVE_SMS:
       NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
+      if (value != p->reserve_sms) {
+        // the grid of the cooperative kernels changes: their monotonic barrier counters recover the launch's base as
+        // v - v % grid, which only holds while the grid never changes -- start them from zero again (nothing of this plan
+        // may be in flight or being captured when an option is set)
+        NRD_CHECK_CUDA(cudaSetDevice(p->device));
+        NRD_CHECK_CUDA(cudaDeviceSynchronize());
+        NRD_CHECK_CUDA(cudaMemset(p->gbar, 0, 4 * sizeof(unsigned long long)));
+      }
       p->reserve_sms = value;
       if (p->tc_ready) nrd_tc_refresh_limits(p);
       return NRD_OK;
@@ -1864,10 +1872,34 @@ extern "C" int nrd_plan_set_exchange(nrd_plan* p, int rank, int world, void* con
   NRD_REQUIRE(world >= 2 && world <= NRD_XCHG_MAX_WORLD && rank >= 0 && rank < world, "nrd_plan_set_exchange: world %d / rank %d out of range", world, rank);
   for (int r = 0; r < world; ++r) { NRD_REQUIRE(bufs[r], "nrd_plan_set_exchange: null buffer for rank %d", r); p->xchg.peer[r] = (float*)bufs[r]; }
   p->xchg.world = world; p->xchg.rank = rank; p->xchg.nx = (2 * p->C + (int)p->off[9] + 3) & ~3;
+  {
+    // how long the optimizer kernel waits for a peer's gradients before it traps the context: 10 minutes by default (the
+    // default of the NCCL watchdog this exchange replaces), NRD_XCHG_TIMEOUT_S overrides; converted with the SM clock rate
+    const char* e = getenv("NRD_XCHG_TIMEOUT_S");
+    double secs = e ? atof(e) : 600.0;
+    if (!(secs > 0.0)) secs = 600.0;
+    int khz = 0;
+    if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, p->device) != cudaSuccess || khz <= 0) khz = 2000000;
+    p->xchg.timeout_cycles = (long long)(secs * 1e3 * (double)khz);
+  }
   return NRD_OK;
 }
 
 extern "C" int nrd_plan_conv_impl(const nrd_plan* p) { return p ? p->conv_impl : NRD_EINVAL; }
+
+// Sticky status of the plan's kernels (NRD_STATUS_* bits): synchronises `stream`, reads the word, optionally clears it.
+extern "C" int nrd_plan_status(nrd_plan* p, unsigned int* flags_out, int clear, void* stream) {
+  NRD_REQUIRE(p && flags_out, "nrd_plan_status: null pointer");
+  NRD_CHECK_CUDA(cudaSetDevice(p->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned int* w = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS);
+  NRD_CHECK_CUDA(cudaMemcpyAsync(flags_out, w, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+  if (clear) NRD_CHECK_CUDA(cudaMemsetAsync(w, 0, sizeof(unsigned int), st));
+  NRD_CHECK_CUDA(cudaStreamSynchronize(st));
+  if (*flags_out & NRD_STATUS_BN_NONFINITE) { nrd_set_error("BatchNorm statistics: a per-CTA sum was NaN/Inf (the activations or gradients diverged)"); return NRD_ERANGE; }
+  if (*flags_out & NRD_STATUS_BN_SATURATED) { nrd_set_error("BatchNorm statistics: a per-CTA sum left the fixed-point range of the persistent kernels (forward |sum| >= 2^22, backward >= 2^10): statistics of that step were clamped"); return NRD_ERANGE; }
+  return NRD_OK;
+}
 
 extern "C" int nrd_plan_tensor(nrd_plan* p, int what, int k, void** ptr, size_t* bytes) {
   NRD_REQUIRE(p && ptr && bytes, "null pointer");
@@ -1973,11 +2005,11 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
     // the backward's first kernel rides along: d(pooled) is ready when nrd_backward_body(dlogits) is called
     NRD_CHECK_CUDA(nrd_launch_pdl(k_head_tail<bf16>, dim3(((B + 7) / 8) * (K / 256)), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B),
                                   PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B, labels, grad_scale, loss_rows, dlogits, loss_out,
-                                  reinterpret_cast<unsigned int*>(p->gbar + 16), p->w1p, (bf16*)p->dxa, C));
+                                  reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_HEAD_COUNTER), p->w1p, (bf16*)p->dxa, C));
     p->dp_for = dlogits;
   } else if (labels)
     NRD_CHECK_CUDA(nrd_launch_pdl(k_fc2_ce, dim3((B + 7) / 8), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B),
-                                  p->h1, logits, B, labels, grad_scale, loss_rows, dlogits, loss_out, reinterpret_cast<unsigned int*>(p->gbar + 16)));
+                                  p->h1, logits, B, labels, grad_scale, loss_rows, dlogits, loss_out, reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_HEAD_COUNTER)));
   else
     NRD_CHECK_CUDA(nrd_launch_pdl(k_fc2_fwd, dim3((B + 7) / 8), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B),
                                   p->h1, logits, B));

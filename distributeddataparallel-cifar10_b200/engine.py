@@ -156,6 +156,15 @@ class Engine:
             self.plans[B] = pl
         return pl
 
+    def check_status(self, clear: bool = True):
+        """Raise if a kernel of any cached plan clamped or saw non-finite BatchNorm sums since the last check
+        (nrd_plan_status).  Synchronises the current stream: call it where the loop reads the loss on the host."""
+        for pl in self.plans.values():
+            flags = C.c_uint32(0)
+            rc = lib.nrd_plan_status(pl.handle, C.byref(flags), 1 if clear else 0, _stream_ptr())
+            if rc != 0:
+                raise _lib.NrdError(f"training step status {flags.value:#x} (batch {pl.B}): {_lib.last_error()}")
+
     def set_conv_impl(self, impl: int):
         self.conv_impl = impl
         for pl in self.plans.values():

@@ -7,8 +7,9 @@ from typing import Optional
 import torch
 import torch.distributed as dist
 
+from . import _lib
 from ._lib import lib, check, OPT_RESERVE_SMS
-from .engine import _stream_ptr
+from .engine import _stream_ptr, _Plan
 
 
 class TrainStep:
@@ -35,8 +36,15 @@ class TrainStep:
         self.imgs, self.labels = self.inputs[0]
         self.logits = torch.empty(batch_size, 10, dtype=torch.float32, device=dev)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
-        self.plan = self.eng.plan(batch_size, dev)
+        # a plan of its OWN (not the engine's per-batch-size cache): the exchange wiring, the BN-sync slot and the SM
+        # reservation set below must not leak into eager steps on the same model and batch size
+        if self.eng.device != dev or not self.eng._adopted():
+            self.eng.adopt(dev)
+        self.plan = _Plan(self.eng, batch_size)
+        if self.eng.conv_impl is not None:
+            check(lib.nrd_plan_set_conv_impl(self.plan.handle, self.eng.conv_impl), "nrd_plan_set_conv_impl")
         self.eng.ensure_packed(self.plan)
+        self._exchange = None
         # DDP on the graph path:
         # (1) gradients are exchanged over NVLink peer memory by our own kernels (nrd_plan_set_exchange: the producing
         #     kernels store into every rank's buffer, the optimizer kernel sums the world's slots in rank order; the head
@@ -107,6 +115,35 @@ class TrainStep:
         self._exchange = (ptr, opened)          # kept mapped for the life of the process (captured graphs point into them)
         return True
 
+    def check_status(self, clear: bool = True):
+        """Raise if a kernel of this step clamped or saw non-finite BatchNorm sums since the last check (nrd_plan_status:
+        the persistent kernels' fixed-point statistics have a finite range).  Synchronises the current stream; call it
+        where the loop reads the loss on the host anyway (main.py:41,44)."""
+        import ctypes as C
+        flags = C.c_uint32(0)
+        rc = lib.nrd_plan_status(self.plan.handle, C.byref(flags), 1 if clear else 0, _stream_ptr())
+        if rc != 0:
+            raise _lib.NrdError(f"training step status {flags.value:#x}: {_lib.last_error()}")
+
+    def close(self):
+        """Drop the captured graphs and release the peer-memory exchange buffers (ours and the mappings of the peers').
+        Every rank must call it at the same point (a peer may still be storing into our buffer until its last step is done)."""
+        self.graphs = [None, None]
+        ex, self._exchange = getattr(self, "_exchange", None), None
+        if ex is not None:
+            torch.cuda.synchronize(self.device)
+            lib.nrd_plan_set_exchange(self.plan.handle, 0, 0, None)
+            own, opened = ex
+            for q in opened:
+                lib.nrd_exchange_release(q, 1)
+            lib.nrd_exchange_release(own, 0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
     def resync_buffers(self):
         """Rank 0's BN running stats to every rank, and into the slot the next forward starts from.  Called at construction;
         call it again after changing the buffers outside the step (load_state_dict)."""
@@ -173,6 +210,9 @@ class TrainStep:
         """Replay on the static inputs already in `self.inputs[slot]` (slot 0 = `self.imgs` / `self.labels`)."""
         if self.use_graph and self.graphs[slot] is None and self.graphs[0] is not None:
             self._capture(slot)
+        # load_state_dict / in-place edits since the last step: re-derive the packed weight copies first (host-side version
+        # compare; a no-op in the steady state because the step's own update re-packs them)
+        self.eng.ensure_packed(self.plan)
         if self.graphs[slot] is not None:
             self.graphs[slot].replay()
         else:

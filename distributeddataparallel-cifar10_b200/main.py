@@ -56,6 +56,10 @@ def train_loop(model, train_loader, rank, epochs=99, lr=1e-2, save=True, log=pri
             loss_train += loss.detach()                    # main.py:41 (.item() deferred to the epoch end)
         mean_loss = loss_train.item() / len(train_loader)
         history.append(mean_loss)
+        # the one host sync of the epoch has just happened: also read the kernels' sticky status (clamped / non-finite BN sums)
+        getattr(model, "module", model).engine.check_status()
+        if step is not None:
+            step.check_status()
         if epoch == 1 or epoch % 10 == 0:                  # main.py:43
             log('Epoch {}, Training loss {}'.format(epoch, mean_loss))
             if save and rank == 0:

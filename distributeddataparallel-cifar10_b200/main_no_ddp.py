@@ -32,6 +32,7 @@ def training_loop(model, train_loader, epochs=99, lr=1e-2, log=print):
             optimizer.step()                               # :50
             loss_train += loss.detach()
         history.append(loss_train.item() / len(train_loader))
+        model.engine.check_status()
         if epoch == 1 or epoch % 10 == 0:
             log('Epoch {}, Training loss {}'.format(epoch, history[-1]))
     log(f"training time: {time.time() - start_time:.3f} seconds")

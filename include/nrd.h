@@ -38,6 +38,7 @@ extern "C" {
 #define NRD_EINVAL (-1)   /* bad argument (shape, dtype, null pointer, workspace too small) */
 #define NRD_ECUDA (-2)    /* a CUDA runtime/driver call failed */
 #define NRD_EUNSUPPORTED (-3)
+#define NRD_ERANGE (-4)    /* nrd_plan_status: a kernel of the plan clamped or saw non-finite BatchNorm sums */
 
 /* conv implementation selector for NRD_BF16 plans (nrd_plan_set_conv_impl) */
 #define NRD_CONV_CUDA_CORE 0  /* direct conv on CUDA cores (also the only NRD_F32 path) */
@@ -106,6 +107,13 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
  * Measured: forward -1 us; backward +2 us (its weight-gradient MMAs read N groups one pixel apart), hence off there. */
 #define NRD_OPT_ONE_COPY 10
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
+/* Sticky status of the plan's kernels.  The persistent kernels add their per-CTA BatchNorm sums (model/resnet.py:35 and its
+ * backward) as 64-bit fixed point; a contribution outside the representable range (forward |sum| >= 2^22, backward >= 2^10)
+ * or a NaN/Inf is clamped so that the grid keeps running, and marked here: NRD_STATUS bit 0 = clamped, bit 1 = non-finite.
+ * nrd_plan_status synchronises `stream`, copies the word to *flags_out (HOST pointer), clears it when clear != 0 and returns
+ * NRD_ERANGE (message in nrd_last_error) if any bit was set.  The reference has no counterpart (PyTorch would propagate
+ * Inf/NaN into the loss); call it where the reference reads the loss on the host (main.py:41,44). */
+int nrd_plan_status(nrd_plan* plan, unsigned int* flags_out, int clear, void* stream);
 /* DDP's per-forward buffer broadcast (torch DDP `broadcast_buffers`, reached from main.py:63 and run in front of every
  * forward, main.py:33) folded into the gradient exchange: `slot` = the 2C floats directly in front of `grads` (so slot +
  * body bucket are ONE contiguous all-reduce), `contrib` = world_size on rank 0 and 0 elsewhere, `inv_world` = 1/world_size.
@@ -122,7 +130,8 @@ int nrd_plan_set_bn_sync(nrd_plan* plan, float* slot, float contrib, float inv_w
  * the table (own pointer at index `rank`) to nrd_plan_set_exchange.  From then on nrd_backward_body() stores the body
  * gradients (and the BN slot of nrd_plan_set_bn_sync, which it then needs contrib = 1 on rank 0 and inv_world = 1 for) into
  * every rank's buffer and nrd_sgd_update_pack() sums the world's contributions in rank order before the update, so the
- * caller all-reduces only the head bucket.  Every rank must run the same sequence of steps.  world = 0 turns it off. */
+ * caller all-reduces nothing (the head bucket leaves the same way from nrd_backward_head).  The optimizer kernel waits for a
+ * peer's flag for NRD_XCHG_TIMEOUT_S seconds (environment, read here; default 600 like NCCL's watchdog) before it traps.  Every rank must run the same sequence of steps.  world = 0 turns it off. */
 size_t nrd_exchange_bytes(int C, int world);
 int nrd_exchange_alloc(int device, size_t bytes, void** ptr, void* ipc_handle_64);
 int nrd_exchange_open(int device, const void* ipc_handle_64, void** ptr);
@@ -166,7 +175,9 @@ int nrd_cross_entropy(const float* logits, const int64_t* labels, int B, float g
  * NRD_EINVAL; nothing is allocated or freed.  The first call on each device looks up the array's
  * device address (one-time set-up): make that first call before starting any stream capture.  All
  * calls on a device share the one array: calls that may overlap on the GPU (different streams) race,
- * so keep them on one stream or order them with events.  No state carries from call to call. */
+ * so keep them on one stream or order them with events.  No state carries from call to call.
+ * Precondition: the CURRENT device of the calling thread must be the device that holds `logits` (this entry has no plan and
+ * therefore cannot cudaSetDevice itself; every plan-based entry does): the scratch address is looked up per current device. */
 int nrd_cross_entropy_static(const float* logits, const int64_t* labels, int B, float grad_scale,
                              float* loss_out, float* dlogits, void* stream);
 int nrd_backward(nrd_plan* plan, const float* dlogits, void* stream);

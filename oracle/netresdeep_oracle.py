@@ -229,6 +229,141 @@ def ddp_train_step(p, bufs_per_rank: List[dict], xs, labels, n_blocks: int = 10,
     return sgd_step(p, gavg, lr), logits_all, losses, gavg
 
 
+# --------------------------------------------------------------------------- rounding-matched (bf16) oracle
+# SURVEY 8(c) tier 3(ii): the same explicit forward/backward with a quantiser `q` applied at exactly the
+# points where the bf16 CUDA path rounds: conv operands (images, conv1 weight, block
+# conv weight), every stored activation (x_k, y_k), dL/d(pooled), dy_k, dL/dx_k; BN statistics, gamma/beta,
+# the head (fc1/fc2 weights, h1, logits, loss), weight-gradient accumulators and master weights stay in the
+# arithmetic dtype.  With `q = identity` it IS `forward`/`backward` above (tests/test_oracle.py pins that),
+# which in turn is pinned to the reference's own outputs.
+def q_bf16(t: torch.Tensor) -> torch.Tensor:
+    """round-to-nearest-even to bf16, back in the arithmetic dtype"""
+    return t.to(torch.bfloat16).to(t.dtype)
+
+
+def q_none(t: torch.Tensor) -> torch.Tensor:
+    return t
+
+
+def forward_rm(p, bufs, x, n_blocks: int = 10, train: bool = True, q=q_bf16):
+    """`NetResDeep.forward` (model/resnet.py:15-22) with bf16 rounding where the kernels round.
+
+    Differences to `forward` that are NOT rounding and do not change values: the stem pools the
+    pre-bias convolution and adds bias + ReLU afterwards (max commutes with the monotone bias+ReLU;
+    the arg-max can differ only where the output is 0 and the gradient is masked anyway); BN is
+    applied as y*scale + shift with scale = gamma*invstd, shift = beta - mean*scale."""
+    C = p["conv1.weight"].shape[0]
+    c = {"x": x, "xq": q(x)}
+    a = F.conv2d(c["xq"], q(p["conv1.weight"]), None, padding=1)                 # resnet.py:16, operands rounded
+    amax, idx0 = maxpool2_fwd(a)
+    x0 = q(torch.relu(amax + p["conv1.bias"][None, :, None, None]))
+    c["idx0"] = idx0
+    wq = q(p["rb.conv.weight"])
+    gamma, beta = p["rb.bn.weight"], p["rb.bn.bias"]
+    xs, ybs, scs, shs, means, invstds = [x0], [], [], [], [], []
+    out = x0
+    for _ in range(n_blocks):                                                    # resnet.py:17
+        y = F.conv2d(out, wq, None, padding=1)                                   # resnet.py:34 (fp32 accumulate)
+        if train:
+            n = y.shape[0] * y.shape[2] * y.shape[3]
+            mean = y.mean(dim=(0, 2, 3))                                         # statistics of the UNROUNDED accumulators
+            var = (y * y).mean(dim=(0, 2, 3)) - mean * mean
+            var = torch.clamp(var, min=0.0)
+            invstd = 1.0 / torch.sqrt(var + BN_EPS)
+            bufs["running_mean"] = (1 - BN_MOMENTUM) * bufs["running_mean"] + BN_MOMENTUM * mean
+            bufs["running_var"] = (1 - BN_MOMENTUM) * bufs["running_var"] + BN_MOMENTUM * var * (n / (n - 1))
+            bufs["num_batches_tracked"] = bufs["num_batches_tracked"] + 1
+        else:
+            mean, invstd = bufs["running_mean"], 1.0 / torch.sqrt(bufs["running_var"] + BN_EPS)
+        sc = gamma * invstd
+        sh = beta - mean * sc
+        yb = q(y)                                                                # y_k as stored; BN sees the stored value
+        z = yb * sc[None, :, None, None] + sh[None, :, None, None]               # resnet.py:35
+        out = q(torch.relu(z) + out)                                             # resnet.py:36-37
+        ybs.append(yb); scs.append(sc); shs.append(sh); means.append(mean); invstds.append(invstd); xs.append(out)
+    pooled, idx2 = maxpool2_fwd(out)                                             # resnet.py:18 (exact on bf16 values)
+    flat = pooled.reshape(-1, 8 * 8 * C)                                         # resnet.py:19
+    h1 = torch.relu(flat @ p["fc1.weight"].t() + p["fc1.bias"])                  # resnet.py:20 (fp32 weights)
+    logits = h1 @ p["fc2.weight"].t() + p["fc2.bias"]                            # resnet.py:21
+    c.update(xs=xs, ybs=ybs, scs=scs, shs=shs, means=means, invstds=invstds, idx2=idx2, flat=flat, h1=h1,
+             logits=logits, n_blocks=n_blocks)
+    return logits, c
+
+
+def backward_rm(p, c, dlogits, q=q_bf16, keep_masks: bool = False):
+    """`loss.backward()` (main.py:38) with bf16 rounding where the kernels round: d(pooled), dy_k and
+    dL/dx_k are stored/kept as bf16; the BN-backward sums, dgamma/dbeta and all weight gradients
+    accumulate in the arithmetic dtype."""
+    C = p["conv1.weight"].shape[0]
+    g: Dict[str, torch.Tensor] = {}
+    g["fc2.weight"] = dlogits.t() @ c["h1"]
+    g["fc2.bias"] = dlogits.sum(0)
+    dh1 = (dlogits @ p["fc2.weight"]) * (c["h1"] > 0).to(dlogits.dtype)
+    g["fc1.weight"] = dh1.t() @ c["flat"]
+    g["fc1.bias"] = dh1.sum(0)
+    dflat = q(dh1 @ p["fc1.weight"])                                             # dL/d(pooled), stored bf16
+    dout = maxpool2_bwd(dflat.reshape(-1, C, 8, 8), c["idx2"])
+    wq = q(p["rb.conv.weight"])
+    gamma = p["rb.bn.weight"]
+    dW = torch.zeros_like(p["rb.conv.weight"]); dgam = torch.zeros_like(gamma); dbet = torch.zeros_like(gamma)
+    masks = []
+    for k in reversed(range(c["n_blocks"])):
+        yb, sc, sh, mean, invstd, xk = c["ybs"][k], c["scs"][k], c["shs"][k], c["means"][k], c["invstds"][k], c["xs"][k]
+        n = yb.shape[0] * yb.shape[2] * yb.shape[3]
+        mask = (yb * sc[None, :, None, None] + sh[None, :, None, None]) > 0
+        if keep_masks:
+            masks.append(mask)
+        dz = dout * mask.to(dout.dtype)
+        db = dz.sum(dim=(0, 2, 3))
+        dgy = (dz * yb).sum(dim=(0, 2, 3))
+        dg = invstd * (dgy - mean * db)                                          # sum dz*xhat
+        dgam += dg; dbet += db
+        a_ = gamma * invstd
+        A2 = -a_ * (dg / n) * invstd
+        A3 = a_ * (dg / n) * invstd * mean - a_ * (db / n)
+        dy = q(dz * a_[None, :, None, None] + yb * A2[None, :, None, None] + A3[None, :, None, None])
+        dW += torch.nn.grad.conv2d_weight(xk, p["rb.conv.weight"].shape, dy, padding=1)
+        dout = q(torch.nn.grad.conv2d_input(xk.shape, wq, dy, padding=1) + dout)
+    g["rb.conv.weight"], g["rb.bn.weight"], g["rb.bn.bias"] = dW, dgam, dbet
+    dr = maxpool2_bwd(dout, c["idx0"])
+    x0_full = maxpool2_bwd(c["xs"][0], c["idx0"])
+    da = dr * (x0_full > 0).to(dr.dtype)
+    g["conv1.weight"] = torch.nn.grad.conv2d_weight(c["xq"], p["conv1.weight"].shape, da, padding=1)
+    g["conv1.bias"] = da.sum(dim=(0, 2, 3))
+    if keep_masks:
+        return g, masks[::-1]
+    return g
+
+
+def train_step_rm(p, bufs, x, labels, n_blocks: int = 10, lr: float = 1e-2, q=q_bf16, keep_masks: bool = False):
+    """main.py:34-39 with the bf16 path's rounding points; master weights stay in the arithmetic dtype."""
+    logits, c = forward_rm(p, bufs, x, n_blocks, q=q)
+    loss, dlogits = cross_entropy(logits, labels)
+    out = backward_rm(p, c, dlogits, q=q, keep_masks=keep_masks)
+    g, masks = out if keep_masks else (out, None)
+    res = (sgd_step(p, g, lr), logits, loss, g)
+    return res + (masks,) if keep_masks else res
+
+
+def relu_masks(p, c):
+    """per-block ReLU masks of a plain `forward` cache (for flip counts against `backward_rm(keep_masks=True)`)"""
+    return [(xh * p["rb.bn.weight"][None, :, None, None] + p["rb.bn.bias"][None, :, None, None]) > 0 for xh in c["xhats"]]
+
+
+def ddp_train_step_rm(p, bufs_per_rank: List[dict], xs, labels, n_blocks: int = 10, lr: float = 1e-2, q=q_bf16):
+    """`ddp_train_step` with the bf16 path's rounding points on every rank."""
+    W = len(xs)
+    grads, losses, logits_all = [], [], []
+    src = {k: v.clone() for k, v in bufs_per_rank[0].items()}
+    for r in range(W):
+        bufs_per_rank[r].update({k: v.clone() for k, v in src.items()})
+        logits, c = forward_rm(p, bufs_per_rank[r], xs[r], n_blocks, q=q)
+        loss, dlogits = cross_entropy(logits, labels[r])
+        grads.append(backward_rm(p, c, dlogits, q=q)); losses.append(loss); logits_all.append(logits)
+    gavg = {k: sum(g[k] for g in grads) / W for k in p}
+    return sgd_step(p, gavg, lr), logits_all, losses, gavg
+
+
 # --------------------------------------------------------------------------- timed CPU baseline
 class TorchModulePort(torch.nn.Module):
     """nn.Module port of NetResDeep used ONLY as the timed CPU baseline (`cpu_baseline.kind =
