@@ -1,7 +1,19 @@
-"""Data-parallel semantics on real GPUs (needs >= 2; skipped otherwise): our DistributedDataParallel wrapper + bucketed NCCL
-all-reduce against the oracle's sequential simulation of torch DDP (which tests/test_oracle.py pins to real torch DDP over
-gloo): rank-0 parameter broadcast at wrap time, rank-0 BN-buffer broadcast before every forward, mean of per-rank grads,
-identical weights on every rank after the step; and the whole-step CUDA graph (all-reduce captured inside) == eager."""
+"""Data-parallel semantics on real GPUs, W = 2, 4, 8 ranks (each case is skipped when the box has fewer GPUs): our
+DistributedDataParallel wrapper and the whole-step graph path against the oracle's sequential simulation of torch DDP (which
+tests/test_oracle.py pins to REAL torch DDP over gloo at W = 2 and 4):
+
+  * rank-0 parameter broadcast at wrap time (the ranks start from different seeds, as main.py:62 does),
+  * rank 0's BN buffers in front of every forward (step 2 starts from them on every rank),
+  * mean of the per-rank gradients, identical weights on every rank after every step,
+  * fp32: eager wrapper (bucketed NCCL all-reduce) vs the fp32 oracle to 1e-5; graph path == eager path (bit for bit at
+    W = 2, where a two-term sum has one order; to 1e-6 beyond), for BOTH exchanges of the graph path: our kernels over NVLink
+    peer memory ("p2p") and NCCL all-reduces captured in the graph ("nccl");
+  * bf16 (the path bench.py --gpus N times): graph path, both exchanges, against the rounding-matched oracle inside the
+    single-GPU envelopes of tests/test_gpu_parity_bench.py; p2p == nccl bit for bit at W = 2;
+  * the literal reference loop (stock torch.optim.SGD + nn.CrossEntropyLoss, main.py:27-41) around our wrapper.
+
+One process group per W runs every combination (the exchange is chosen per TrainStep by NRD_P2P), so a case costs one spawn.
+"""
 import os
 
 import pytest
@@ -9,75 +21,143 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
+B, NB, LR = 8, 10, 1e-2
+B_BF16 = 40            # bf16: enough pixels per channel for the A.7 envelopes to apply (B*256 = 10k per statistic)
+
 
 def _worker(rank, W, port, q):
     import torch.distributed as dist
     import ddp_cifar10_b200 as nrd
-    from oracle import netresdeep_oracle as O
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=W, device_id=torch.device("cuda", rank))
     dev = f"cuda:{rank}"
-    B, NB = 8, 10
-    gen = torch.Generator().manual_seed(1234 + rank)
-    x = torch.randn(B, 3, 32, 32, generator=gen); y = torch.randint(0, 10, (B,), generator=gen)
     out = {}
-    for mode in ("eager", "graph"):
+
+    def data(b):
+        gen = torch.Generator().manual_seed(1234 + rank)
+        return torch.randn(b, 3, 32, 32, generator=gen), torch.randint(0, 10, (b,), generator=gen)
+
+    def fresh(dtype):
         torch.manual_seed(rank)                                  # ranks start DIFFERENT, as main.py:62 does
-        m = nrd.NetResDeep(32, NB, dtype="fp32").to(dev)
-        ddp = nrd.DistributedDataParallel(m, device_ids=[rank], output_device=rank)
-        losses = []
+        m = nrd.NetResDeep(32, NB, dtype=dtype).to(dev)
+        return m, nrd.DistributedDataParallel(m, device_ids=[rank], output_device=rank)
+
+    def snap(m):
+        return (m.engine.flat_params.detach().cpu().numpy().copy(), m.engine.bn_running.detach().cpu().numpy().copy())
+
+    # ---- fp32 eager: our SGD/CE, then the literal reference loop with stock torch SGD/CE ----
+    x, y = data(B)
+    for mode in ("eager", "stock"):
+        m, ddp = fresh("fp32")
         if mode == "eager":
-            opt = nrd.SGD(ddp.parameters(), lr=1e-2); loss_fn = nrd.CrossEntropyLoss()
-            for s in range(2):
-                o = ddp(x.to(dev)); loss = loss_fn(o, y.to(dev)); opt.zero_grad(); loss.backward()
-                if s == 0:
-                    out["grads"] = m.engine.flat_grads.detach().cpu().numpy().copy()
-                    out["logits"] = o.detach().cpu().numpy().copy()
-                opt.step(); losses.append(float(loss))
+            opt = nrd.SGD(ddp.parameters(), lr=LR); loss_fn = nrd.CrossEntropyLoss()
         else:
-            step = nrd.TrainStep(ddp, B, lr=1e-2)
+            opt = torch.optim.SGD(ddp.parameters(), lr=LR); loss_fn = torch.nn.CrossEntropyLoss()       # main.py:27-28
+        losses = []
+        for s in range(2):
+            o = ddp(x.to(dev)); loss = loss_fn(o, y.to(dev)); opt.zero_grad(); loss.backward()
+            if s == 0 and mode == "eager":
+                out["grads"] = m.engine.flat_grads.detach().cpu().numpy().copy()
+                out["logits"] = o.detach().cpu().numpy().copy()
+            opt.step(); losses.append(float(loss))
+        out[mode] = (losses,) + snap(m)
+    # ---- graph path, both exchanges, fp32 and bf16 ----
+    for dtype, b in (("fp32", B), ("bf16", B_BF16)):
+        xb, yb = data(b)
+        for xchg in ("p2p", "nccl"):
+            os.environ["NRD_P2P"] = "1" if xchg == "p2p" else "0"
+            m, ddp = fresh(dtype)
+            step = nrd.TrainStep(ddp, b, lr=LR)
+            losses, first = [], None
             for s in range(2):
-                losses.append(float(step(x.to(dev), y.to(dev))))
-            step.graph = None; del step          # the graph holds captured NCCL kernels: drop it before the communicator
-        out[mode] = (losses, m.engine.flat_params.detach().cpu().numpy().copy(), m.engine.bn_running.detach().cpu().numpy().copy())
+                losses.append(float(step(xb.to(dev), yb.to(dev))))
+                if s == 0:
+                    first = (step.logits.detach().cpu().numpy().copy(), m.engine.flat_grads.detach().cpu().numpy().copy() / W)   # .grad = world SUM
+            step.check_status()
+            out[f"graph/{dtype}/{xchg}"] = (losses,) + snap(m) + first + (bool(step.p2p),)
+            step.close(); del step          # graphs hold captured NCCL kernels / peer mappings: drop them before the communicator
+    os.environ.pop("NRD_P2P", None)
     torch.cuda.synchronize()
-    q.put((rank, out, x.numpy(), y.numpy()))     # numpy pickles inline: nothing refers back to this process after the put
+    xb, yb = data(B_BF16)
+    q.put((rank, out, x.numpy(), y.numpy(), xb.numpy(), yb.numpy()))     # numpy pickles inline: nothing refers back to this process
     dist.barrier()
     os._exit(0)                                  # skip communicator teardown (can block behind captured collectives)
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_ddp_two_gpus_matches_oracle_and_graph_equals_eager():
+@pytest.mark.parametrize("W", [2, 4, 8])
+def test_ddp_matches_oracle_and_graph_equals_eager(W):
+    if torch.cuda.device_count() < W:
+        pytest.skip(f"needs {W} GPUs")
+    import numpy as np
     import torch.multiprocessing as mp
     from oracle import netresdeep_oracle as O
     from util import rell2
-    ctx = mp.get_context("spawn"); q = ctx.SimpleQueue(); W = 2
-    ps = [ctx.Process(target=_worker, args=(r, W, 29561, q)) for r in range(W)]
+    import ddp_cifar10_b200 as nrd
+    ctx = mp.get_context("spawn"); q = ctx.SimpleQueue()
+    ps = [ctx.Process(target=_worker, args=(r, W, 29561 + W, q)) for r in range(W)]
     [p.start() for p in ps]
     got = {}
     for _ in range(W):
-        r, out, x, y = q.get(); got[r] = (out, x, y)
-    [p.join(60) for p in ps]
+        r, out, x, y, xb, yb = q.get(); got[r] = (out, x, y, xb, yb)
+    [p.join(120) for p in ps]
     [p.kill() for p in ps if p.is_alive()]
-    # oracle: rank 0's init wins; sequential DDP simulation
-    p, b0 = O.init_params(32, 10, seed=0)
-    bufs = [dict((k, v.clone()) for k, v in b0.items()) for _ in range(W)]
-    xs = [torch.from_numpy(got[r][1]) for r in range(W)]; ys = [torch.from_numpy(got[r][2]) for r in range(W)]
-    p1, logits, losses, gavg = O.ddp_train_step(p, bufs, xs, ys, 10, 1e-2)
-    import ddp_cifar10_b200 as nrd
     off = nrd._lib.param_offsets(32)
-    order = ["conv1.weight", "conv1.bias", "rb.conv.weight", "rb.bn.weight", "rb.bn.bias", "fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias"]
+    T = torch.from_numpy
+
+    def simulate(fn, xs, ys, steps=2):
+        p, b0 = O.init_params(32, NB, seed=0)       # rank 0's init wins (wrapper ctor broadcast); torch.manual_seed(0) == rank 0's seed
+        bufs = [dict((k, v.clone()) for k, v in b0.items()) for _ in range(W)]
+        res = []
+        for _ in range(steps):
+            p, logits, losses, gavg = fn(p, bufs, xs, ys, NB, LR)
+            res.append((p, logits, losses, gavg, [torch.cat([b["running_mean"], b["running_var"]]) for b in bufs]))
+        return res
+
+    def flat(p):
+        return torch.cat([p[k].flatten() for k in O.PARAM_ORDER])
+
+    # ---------------- fp32 ----------------
+    sim = simulate(O.ddp_train_step, [T(got[r][1]) for r in range(W)], [T(got[r][2]) for r in range(W)])
     for r in range(W):
         out = got[r][0]
-        out = {k: (torch.from_numpy(v) if not isinstance(v, tuple) else (v[0], torch.from_numpy(v[1]), torch.from_numpy(v[2]))) for k, v in out.items()}
-        got[r] = (out, got[r][1], got[r][2])
-        assert rell2(out["logits"], logits[r]) < 1e-5
-        assert abs(out["eager"][0][0] - float(losses[r])) < 1e-5 * float(losses[r])
-        for i, k in enumerate(order):
+        assert rell2(T(out["logits"]), sim[0][1][r]) < 1e-5
+        for mode in ("eager", "stock"):
+            losses, w, bn = out[mode]
+            for s in range(2):
+                assert abs(losses[s] - float(sim[s][2][r])) < 1e-5 * float(sim[s][2][r]) * (1 if s == 0 else 20), (mode, r, s)
+            assert rell2(T(w), flat(sim[1][0])) < 1e-5, (mode, r)
+            assert rell2(T(bn), sim[1][4][r]) < 1e-5, (mode, r)            # each rank's own statistics on top of rank 0's buffers
+            assert np.array_equal(w, got[0][0][mode][1]), (mode, r)        # every rank ends with the same weights
+        for i, k in enumerate(O.PARAM_ORDER):
             tol = 2e-5 if k.startswith("fc") else 5e-3
-            assert rell2(out["grads"][off[i]:off[i + 1]], gavg[k].flatten()) < tol, (r, k)
-        # graph path == eager path, bit for bit; every rank ends with the same weights
-        assert out["graph"][0] == out["eager"][0]
-        assert torch.equal(out["graph"][1], out["eager"][1]) and torch.equal(out["graph"][2], out["eager"][2])
-        assert torch.equal(out["eager"][1], torch.as_tensor(got[0][0]["eager"][1]))
+            assert rell2(T(out["grads"][off[i]:off[i + 1]]), sim[0][3][k].flatten()) < tol, (r, k)
+        # torch's foreach SGD and NCCL-mean + our fused update are the same arithmetic up to one rounding of lr * g
+        assert np.allclose(out["stock"][0], out["eager"][0], rtol=1e-6) and rell2(T(out["stock"][1]), T(out["eager"][1])) < 1e-6
+        for xchg in ("p2p", "nccl"):
+            losses, w, bn, logits, gavg, used_p2p = out[f"graph/fp32/{xchg}"]
+            assert used_p2p == (xchg == "p2p"), "peer access between the GPUs of one box is expected"
+            if W == 2:                                                     # one summation order: bit for bit
+                assert losses == out["eager"][0] and np.array_equal(w, out["eager"][1]) and np.array_equal(bn, out["eager"][2]), xchg
+            else:
+                assert np.allclose(losses, out["eager"][0], rtol=1e-6) and rell2(T(w), T(out["eager"][1])) < 1e-6 and rell2(T(bn), T(out["eager"][2])) < 1e-6
+            assert np.array_equal(w, got[0][0][f"graph/fp32/{xchg}"][1]), (xchg, r)
+    # ---------------- bf16: the benchmarked path ----------------
+    simb = simulate(O.ddp_train_step_rm, [T(got[r][3]) for r in range(W)], [T(got[r][4]) for r in range(W)])
+    HEAD, BNK = ("fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias"), ("rb.bn.weight", "rb.bn.bias")
+    for r in range(W):
+        out = got[r][0]
+        for xchg in ("p2p", "nccl"):
+            losses, w, bn, logits, gavg, used_p2p = out[f"graph/bf16/{xchg}"]
+            assert rell2(T(logits), simb[0][1][r]) < 2e-3, (xchg, r, rell2(T(logits), simb[0][1][r]))
+            assert abs(losses[0] - float(simb[0][2][r])) < 2e-3 * float(simb[0][2][r])
+            for i, k in enumerate(O.PARAM_ORDER):
+                tol = 4e-3 if k in HEAD else (1e-2 if k in BNK else 3e-2)          # small per-rank batch: conv grads carry more flip noise
+                e = rell2(T(gavg[off[i]:off[i + 1]]), simb[0][3][k].flatten())
+                assert e < tol, (xchg, r, k, e)
+            assert rell2(T(w), flat(simb[1][0])) < 1e-4, (xchg, r)
+            assert rell2(T(bn), simb[1][4][r]) < 2e-3, (xchg, r)
+            assert np.array_equal(w, got[0][0][f"graph/bf16/{xchg}"][1]), (xchg, r)
+        if W == 2:
+            a, b_ = out["graph/bf16/p2p"], out["graph/bf16/nccl"]
+            assert a[0] == b_[0] and np.array_equal(a[1], b_[1]) and np.array_equal(a[2], b_[2])
