@@ -1914,6 +1914,7 @@ extern "C" int nrd_plan_tensor(nrd_plan* p, int what, int k, void** ptr, size_t*
     case 6: *ptr = p->dxb; *bytes = act; break;
     case 7: *ptr = p->wgrad_partial; *bytes = nrd_wgrad_partial_bytes(p->B, p->C); break;
     case 9: *ptr = p->stem_partial; *bytes = nrd_stem_bwd_partial_bytes(p->B, p->C); break;
+    case 10: *ptr = p->h1; *bytes = (size_t)p->B * NRD_FC1_OUT * 4; break;
     case 8: *ptr = p->stats_partial; *bytes = (size_t)(p->B * 2 > 1024 ? p->B * 2 : 1024) * 2 * p->C * 4; break;
     default: nrd_set_error("nrd_plan_tensor: unknown selector %d", what); return NRD_EINVAL;
   }

@@ -71,6 +71,8 @@ class TrainStep:
             # the head bucket's kernel (NCCL all-reduce or our push kernel) has to fit beside the persistent kernels
             check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8"))),
                   "nrd_plan_set_option")
+        elif "NRD_RESERVE_SMS" in os.environ:       # single rank: only when asked for (tests of the reduced grid)
+            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ["NRD_RESERVE_SMS"])), "nrd_plan_set_option")
         self.graphs = [None, None]              # one captured step per input slot (slot 1 on first use)
         self.use_graph = use_graph
         self.kernel_launches = None

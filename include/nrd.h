@@ -140,7 +140,7 @@ int nrd_plan_set_exchange(nrd_plan* plan, int rank, int world, void* const* bufs
 /* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
  * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch (ping),
  * 6 = dx scratch (pong), 7 = wgrad per-CTA partials [ctas][9][C][C], 8 = BN-stat per-CTA partials [ctas][2][C],
- * 9 = stem weight-gradient per-CTA partials [ctas][28][C] (27 taps + bias) */
+ * 9 = stem weight-gradient per-CTA partials [ctas][28][C] (27 taps + bias), 10 = h1 = relu(fc1) [B,32] fp32 */
 int nrd_plan_tensor(nrd_plan* plan, int what, int k, void** ptr, size_t* bytes);
 
 /* Re-derive the packed weight copies (tap-major / transposed / bf16 / NHWC-ordered fc1) from the

@@ -342,7 +342,8 @@ def train_step_rm(p, bufs, x, labels, n_blocks: int = 10, lr: float = 1e-2, q=q_
     out = backward_rm(p, c, dlogits, q=q, keep_masks=keep_masks)
     g, masks = out if keep_masks else (out, None)
     res = (sgd_step(p, g, lr), logits, loss, g)
-    return res + (masks,) if keep_masks else res
+    # keep_masks: the ReLU masks of the NB blocks (list) and of fc1's output, for flip-aware comparisons
+    return res + ({"blocks": masks, "h1": c["h1"] > 0},) if keep_masks else res
 
 
 def relu_masks(p, c):

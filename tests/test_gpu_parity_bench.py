@@ -17,7 +17,8 @@ BN grads <= 4.4e-3, block conv weight 0.8-1.5e-2, conv1 weight 1.2-2.3e-2, mask 
   vs fp32 oracle:      logits <= 1e-2; every gradient's cosine >= 0.985 AND no more than 0.003 below the cosine the
                        rounding-matched oracle itself reaches (conv1.weight: 0.991-0.993 -- what bf16 operands cost, for any
                        implementation with these rounding points; SURVEY A.7 measured 0.9918-0.9942).
-ReLU-mask flips per block against the rounding-matched oracle are printed (pytest -s) and bounded at 1e-3 of the elements.
+ReLU-mask flips per block against the rounding-matched oracle are printed (pytest -s) and bounded at 1e-3 of the elements;
+the fc1 gradients' bar is flip-aware (a flipped ReLU of fc1's 32 x B outputs moves them by ~6e-3; 0-1 such flips per run).
 """
 import pytest
 import torch
@@ -80,13 +81,18 @@ def test_benchmarked_bf16_graph_step_vs_rounding_matched_and_fp32_oracle(B):
         st_ = step.plan.tensor_view(4, k).view(torch.float32)
         sc = gamma * st_[C:]; sh = beta - st_[:C] * sc
         ours = (yk * sc + sh > 0).permute(0, 3, 1, 2).cpu()
-        flips.append(int((ours != masks_rm[k]).sum()))
+        flips.append(int((ours != masks_rm["blocks"][k]).sum()))
     rep["relu_flips_per_block"] = flips
+    h1 = step.plan.tensor_view(10).view(torch.float32).view(B, 32).cpu()
+    h1_flips = int(((h1 > 0) != masks_rm["h1"]).sum())
+    rep["h1_relu_flips"] = h1_flips
     print(f"\nparity B={B}: {rep}")
     assert rep["logits_rm"] <= TOL["logits_rm"] and rep["loss_rm"] <= TOL["loss_rm"] and rep["logits_fp32"] <= TOL["logits_fp32"], rep
     for k in O.PARAM_ORDER:
         e_rm, cos32 = rep[k]
-        assert e_rm <= _tol(k), (k, rep)
+        # flip-aware head bar (SURVEY 8(c) tier 2): ONE flipped ReLU of the 32 x B fc1 outputs adds or removes one of the B terms
+        # of a column of the fc1 gradients, ~1/sqrt(32 B) ~ 1e-2 relL2 (measured 5-7e-3 per flip at B = 256)
+        assert e_rm <= _tol(k) + (1e-2 * h1_flips if k.startswith("fc1") else 0.0), (k, rep)
         assert cos32 >= TOL["cos_fp32"] and cos32 >= cos_rm[k] - 3e-3, (k, rep)
     assert rep["running_mean"] <= 1e-4 and rep["running_var"] <= 1e-4, rep
     assert int(bn.num_batches_tracked) == NB
@@ -94,5 +100,6 @@ def test_benchmarked_bf16_graph_step_vs_rounding_matched_and_fp32_oracle(B):
     eng = m.engine
     for i, k in enumerate(O.PARAM_ORDER):
         ours_upd = (eng.flat_params[eng.offsets[i]:eng.offsets[i + 1]] - w0[eng.offsets[i]:eng.offsets[i + 1]]).cpu()
-        assert rell2(ours_upd, (p_rm[k] - pm[k]).flatten()) <= _tol(k) + 1e-4, k       # (+ fp32 cancellation in w - w0)
+        assert rell2(ours_upd, (p_rm[k] - pm[k]).flatten()) <= _tol(k) + 1e-4 + (1e-2 * h1_flips if k.startswith("fc1") else 0.0), k   # (+ fp32 cancellation in w - w0)
+    assert h1_flips <= 4, rep
     assert max(flips) <= 1e-3 * B * 256 * C, rep
