@@ -444,9 +444,16 @@ def main():
         persist = lib.nrd_plan_run_op(step.plan.handle, 8, 0, torch.cuda.current_stream().cuda_stream) == 0
         torch.cuda.synchronize(dev)
         # algorithmic HBM bytes per launch = SURVEY 8(d) per-image figures x the images (and blocks) one launch covers
+        grid = min(B, 148)
+        head_bytes = T + T // 4 + T // (4 * s_act) + T // 4 + 64 * C * 32 * 4       # x_NB in; pooled, arg-max, dL/d(pooled) out; fc1 weight
+        reduce_bytes = grid * (9 * C * C + 28 * C) * 4 + (9 * C * C + 28 * C) * 4   # per-CTA partials in, gradients out
         if persist:
-            ops = {"stem_fwd": (5, 1, B * 3072 * 4 + T + T // s_act), "fwd_blocks(persistent)": (8, 1, NB * 4 * T),
-                   "bwd_blocks(persistent)": (9, 1, NB * 6 * T), "stem_bwd": (6, 1, B * 3072 * 4 + 2 * T + T // s_act)}
+            # every kernel on the step's critical path, in launch order (the head weight-gradient kernels run beside the backward)
+            ops = {"stem_fwd": (5, 1, B * 3072 * 4 + T + T // s_act), "fwd_blocks(persistent)": (8, 1, NB * 4 * T), "head": (10, 1, head_bytes),
+                   "bwd_blocks(persistent)": (9, 1, NB * 6 * T), "stem_bwd": (6, 1, B * 3072 * 4 + 2 * T + T // s_act),
+                   "body_reduce(+sgd)": (11, 1, reduce_bytes)}
+            if world == 1 and not getattr(step, "fused_update", False):
+                ops["sgd_pack"] = (12, 1, 3 * 4 * (64 * C * 32 + 9 * C * C + 27 * C))
         else:
             ops = {"conv_fwd": (0, NB, 2 * T), "bn_apply": (1, NB, 3 * T), "bn_bwd": (2, NB, 5 * T), "wgrad": (3, NB, 2 * T),
                    "dgrad": (4, NB, 3 * T), "stem_fwd": (5, 1, B * 3072 * 4 + T + T // s_act), "stem_bwd": (6, 1, B * 3072 * 4 + 2 * T + T // s_act)}

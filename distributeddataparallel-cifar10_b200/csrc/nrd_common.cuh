@@ -114,6 +114,24 @@ static __device__ __forceinline__ unsigned long long nrd_xchg_wait(const nrd_xch
   return epoch;
 }
 
+// the same wait when the caller knows the epoch itself (a kernel that is both producer and consumer of the bucket)
+static __device__ __forceinline__ void nrd_xchg_wait_epoch(const nrd_xchg_args& x, int bucket, int t, unsigned long long epoch) {
+  if (t >= 0 && t < x.world) {
+    const unsigned long long* f = nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, bucket) + (epoch & 1) * NRD_XCHG_MAX_WORLD + t;
+    unsigned long long v;
+    long long t0 = 0;
+    int spins = 0;
+    while (true) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+      if (v >= epoch) break;
+      if (++spins > 4096) {
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > x.timeout_cycles) __trap();
+      }
+    }
+  }
+}
+
 struct nrd_plan {
   int device, B, C, NB, dtype, conv_impl;
   size_t esz;       // activation element size
@@ -168,6 +186,16 @@ struct nrd_plan {
   int poll_ns;            // experiment knob (env NRD_POLL_NS at plan creation): back-off between polls of the BN exchange
   int pdl;                // option: programmatic dependent launch between the small kernels of the step
   int reserve_sms;        // option: SMs the cooperative kernels leave free (a concurrent NCCL kernel needs somewhere to run)
+  // NRD_OPT_TIMELINE: an event after every kernel of the step's main stream (event-record NODES when the step is captured), so
+  // that the replayed step can be read kernel by kernel in its real context (warm L2, neighbours running)
+  int tl_on, tl_n;
+  cudaEvent_t tl_ev[40];
+  const char* tl_name[40];
+  float upd_lr, upd_inv_world; // nrd_plan_set_fused_update: the optimizer step rides nrd_backward_head / _body (upd_lr > 0)
+  unsigned long long* head_ctr; // per-row-group arrival counters of the fused head kernel
+  const int64_t* labels_last;   // labels of the last nrd_forward_loss (nrd_plan_run_op replays the head with them)
+  float *logits_last, *loss_last, *dlogits_last, *loss_rows_last;
+  int head_ctas;          // how many CTAs of the head kernel fit on the device at once (cooperative launch)
   float* bn_sync;         // optional [2C] slot in front of the gradient vector: BN running stats ride the body bucket's all-reduce
   float bn_sync_contrib;  // what this rank adds to the slot: world_size on rank 0, 0 elsewhere
   float bn_sync_inv_world;
@@ -183,6 +211,8 @@ struct nrd_plan {
   unsigned long long* gbar; // grid-barrier counters (one per cooperative kernel type)
   void* trace;            // optional device buffer for in-kernel clock64 stamps (profiling aid; NULL = off)
   int dbg_skip_stores;    // profiling experiment (NRD_OPT_TRACE value 2)
+  long long* dbg_buf;     // [64 rows][16 stamps][clock64, globaltimer]
+  long long* dbg;         // in-kernel stamps of the small kernels (nrd_dbg_stamp; NULL = off; what = 11 in nrd_plan_tensor)
   void* trace_bwd;        // same for the persistent backward (lives in the pooled-gradient-free part of the dy scratch)
 };
 
@@ -321,6 +351,26 @@ static __device__ __forceinline__ void nrd_acc_wait2(const unsigned long long* w
 #define NRD_GBAR_PERSIST_BWD 3
 #define NRD_GBAR_HEAD_COUNTER 16       // word of the gbar block used as the head kernels' arrival counter
 #define NRD_GBAR_STATUS 24             // word of the gbar block that holds the sticky status flags
+
+// in-kernel stamps (profiling aid, NRD_OPT_TRACE): dbg = NULL turns them off.  Row `row` of the buffer = 16 x {clock64, globaltimer}.
+static __device__ __forceinline__ void nrd_dbg_stamp(long long* dbg, int row, int slot) {
+  if (dbg) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    dbg[(row * 16 + slot) * 2] = clock64(); dbg[(row * 16 + slot) * 2 + 1] = (long long)gt;
+  }
+}
+
+// timeline mark: record the next event of the plan's timeline on `st` behind the kernel that was just launched
+static inline void nrd_tl_mark(nrd_plan* p, cudaStream_t st, const char* name, bool restart = false) {
+  if (!p->tl_on) return;
+  if (restart) p->tl_n = 0;
+  if (p->tl_n >= 40) return;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cs);
+  cudaEventRecordWithFlags(p->tl_ev[p->tl_n], st, cs == cudaStreamCaptureStatusActive ? cudaEventRecordExternal : cudaEventRecordDefault);
+  p->tl_name[p->tl_n++] = name;
+}
 
 // tcgen05 path (conv_tc.cu)
 int nrd_tc_plan_init(nrd_plan* p);

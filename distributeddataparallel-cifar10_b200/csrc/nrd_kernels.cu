@@ -216,58 +216,127 @@ __global__ void __launch_bounds__(256) k_stem_bwd(const float* __restrict__ img,
   }
 }
 
-// conv-weight and stem partials in ONE launch: CTAs [0, 9C*C/32) reduce the conv partials, the rest the stem partials.
-// With the peer-memory exchange on (x.world > 0) every finished gradient is also stored into this rank's slot of EVERY rank's
-// exchange buffer, the last CTA adds the BN gradients (written by the persistent backward) and the BN running-stat slot, and
-// whichever CTA finishes last publishes the epoch in every rank's flag (nrd_common.cuh).
+// Where a finished gradient element goes when the optimizer step rides the kernel that produces it (nrd_plan_set_fused_update):
+// the master parameter and, for the three tensors that have them, the packed copies the kernels read (k_pack_weights' layouts).
+struct nrd_upd_args {
+  float* params;            // flat master parameters, or NULL: no update here (a separate nrd_sgd_update_pack follows)
+  float step_scale;         // lr * inv_world
+  float *w_fwd, *w_dgrad; bf16 *wtc_fwd, *wtc_dgrad; float* conv1_wp;
+};
+// flat index pi (conv weight [co][ci][tap] at off_rbw, conv1 weight [co][27] at off_c1w): master + packed copies
+static __device__ __forceinline__ void nrd_apply_update(const nrd_upd_args& u, long long pi, float g, float p_old, int C, long long off_rbw, long long off_c1w) {
+  const float w = fmaf(-u.step_scale, g, p_old);
+  u.params[pi] = w;
+  const long long n_rb = (long long)C * C * 9, n_c1 = (long long)C * 27;
+  if (pi >= off_rbw && pi < off_rbw + n_rb) {
+    const int q = (int)(pi - off_rbw), co = q / (C * 9), r9 = q % (C * 9), ci = r9 / 9, t = r9 % 9;
+    u.w_fwd[(t * C + ci) * C + co] = w;
+    u.w_dgrad[((8 - t) * C + co) * C + ci] = w;
+    u.wtc_fwd[(size_t)co * 9 * C + t * C + ci] = __float2bfloat16_rn(w);
+    u.wtc_dgrad[(size_t)ci * 9 * C + (8 - t) * C + co] = __float2bfloat16_rn(w);
+  } else if (pi >= off_c1w && pi < off_c1w + n_c1) {
+    const int q = (int)(pi - off_c1w), co = q / 27, k = q % 27;
+    u.conv1_wp[k * C + co] = w;
+  }
+}
+
+// Body gradients, last kernel of the step's critical path: the per-CTA partials of the block-conv weight gradient ([ctas][9][C][C])
+// and of the stem's ([ctas][28][C]) are summed in a fixed order -- CTA = 16 float4 columns x 16 row classes, every thread's
+// <= 10 loads independent and issued together (one L2 round trip), row classes combined in order -- and each finished element
+//   * goes to the flat gradient vector (PyTorch layouts),
+//   * peer-memory exchange on (x.world > 0): is stored into this rank's slot of EVERY rank's exchange buffer (the kernel's own
+//     order: a thread's 4 values are 16 contiguous bytes per peer); the last CTA adds the BN gradients (written by the
+//     persistent backward) and the BN running-stat slot, and whichever CTA finishes last publishes the epoch in every rank's
+//     flag (nrd_common.cuh),
+//   * fused update on (u.params != NULL): takes the optimizer step right here -- alone (world 1), or after waiting for the
+//     world's flags and summing the world's slots in rank order (the same order on every rank => identical weights) --
+//     so no optimizer launch follows the backward.
 __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ wpartial, int wblk, const float* __restrict__ spartial, int sblk,
-                                                     int C, float* __restrict__ dw, float* __restrict__ dw1, float* __restrict__ db1,
-                                                     float* __restrict__ bn_sync, const float* __restrict__ running, float contrib,
-                                                     nrd_xchg_args x, const float* grads_base, int off_bng, int off_rbw, int off_c1w) {
-  __shared__ float red[8][33];
+                                                     int C, float* __restrict__ grads_base, float* __restrict__ bn_sync,
+                                                     const float* __restrict__ running, float contrib, nrd_xchg_args x,
+                                                     int off_bng, int off_rbw, int off_c1w, int off_c1b, nrd_upd_args u, long long* __restrict__ dbg) {
+  __shared__ float4 red[16][16];
+  long long* dbgt = (dbg && threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? dbg : nullptr;
+  const int drow = blockIdx.x == 0 ? 8 : 9;
+  nrd_dbg_stamp(dbgt, drow, 0);
   nrd_pdl_launch();
   nrd_pdl_wait();
-  const bool px = x.world > 0;
+  nrd_dbg_stamp(dbgt, drow, 1);
+  const bool px = x.world > 0, upd = u.params != nullptr;
   // bumped by the last CTA, after every CTA has read it
   const unsigned long long epoch = px ? nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, 0)[NRD_XCHG_EPOCH] + 1 : 0;
   const size_t slot = px ? ((size_t)(epoch & 1) * x.world + x.rank) * x.nx : 0;
-  auto push = [&](size_t idx, float v) {
-    for (int p = 0; p < x.world; ++p) x.peer[p][slot + idx] = v;
-  };
-  // DDP buffer sync riding the body bucket: rank 0 contributes world_size * running, the others exact zeros
-  if (blockIdx.x == gridDim.x - 1) {
+  const bool last_cta = blockIdx.x == gridDim.x - 1;
+  // DDP buffer sync riding the body bucket: rank 0 contributes world_size * running, the others exact zeros; + dgamma | dbeta
+  if (last_cta && (bn_sync || px)) {
     for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
-      if (bn_sync || px) {
-        const float v = contrib != 0.f ? running[j] * contrib : 0.f;
-        if (bn_sync) bn_sync[j] = v;
-        if (px) { push(j, v); push(2 * C + off_bng + j, grads_base[off_bng + j]); }   // ... and dgamma | dbeta
-      }
+      const float v = contrib != 0.f ? running[j] * contrib : 0.f;
+      if (bn_sync && !px) bn_sync[j] = v;
+      if (px) { const float gj = grads_base[off_bng + j]; for (int p = 0; p < x.world; ++p) { x.peer[p][slot + j] = v; x.peer[p][slot + 2 * C + off_bng + j] = gj; } }
     }
   }
-  const int o = threadIdx.x & 31, r = threadIdx.x >> 5, nconv = 9 * C * C / 32;
-  const bool conv = (int)blockIdx.x < nconv;
-  const int i = (conv ? blockIdx.x : blockIdx.x - nconv) * 32 + o, n = conv ? 9 * C * C : 28 * C, nblk = conv ? wblk : sblk;
-  const float* part = conv ? wpartial : spartial;
-  // fp32, fixed order (8 row classes, each its partials in order): deterministic, and the partials are fp32 sums already --
-  // the fp64 pipe made this kernel twice as long
-  float s = 0.f;
-#pragma unroll 8
-  for (int b = r; b < nblk; b += 8) s += __ldcg(part + (size_t)b * n + i);
-  red[r][o] = s;
-  __syncthreads();
-  if (r == 0) {
-    float tot = 0.f;
+  const int c4 = threadIdx.x & 15, rc = threadIdx.x >> 4, nconv4 = 9 * C * C / 4;
+  const bool conv = (int)blockIdx.x * 16 < nconv4;     // CTA-uniform: both column ranges are multiples of 16 float4
+  const int n = conv ? 9 * C * C : 28 * C, nblk = conv ? wblk : sblk;
+  const int ibase = (conv ? (int)blockIdx.x * 16 : (int)blockIdx.x * 16 - nconv4) * 4;       // first element of this CTA's 64
+  // output role: thread t < 64 finishes element ibase + t; its destination (and, fused update, its old parameter) is known now
+  const int t = threadIdx.x;
+  long long pi = 0; size_t sidx = 0; float p_old = 0.f;
+  if (t < 64) {
+    const int i = ibase + t;
+    if (conv) { const int tap = i / (C * C), co = (i / C) % C, ci = i % C; pi = off_rbw + ((long long)co * C + ci) * 9 + tap; }
+    else { const int k = i / C, co = i % C; pi = k < 27 ? off_c1w + co * 27 + k : off_c1b + co; }
+    // the exchange slot keeps THIS kernel's order (conv [tap][co][ci], conv1 [tap][co], then the bias row): a warp's 32 values are
+    // 128 contiguous bytes per peer; the consumer un-permutes locally
+    sidx = 2 * C + (conv ? off_rbw + i : (i < 27 * C ? off_c1w + i : off_c1b + (i - 27 * C)));
+    if (upd) p_old = u.params[pi];
+  }
+  const float* part = (conv ? wpartial : spartial) + ibase + c4 * 4;
+  float4 v[10];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) tot += red[k][o];
-    float* q;
-    if (conv) { const int t = i / (C * C), co = (i / C) % C, ci = i % C; q = dw + ((size_t)co * C + ci) * 9 + t; }
-    else { const int k = i / C, co = i % C; q = k < 27 ? dw1 + co * 27 + k : db1 + co; }
-    *q = tot;
-    // the slot keeps THIS kernel's order (conv [tap][co][ci], conv1 [tap][co]): a warp's 32 values are 128 contiguous bytes per
-    // peer instead of 32 scattered 4-byte NVLink writes; k_sgd_pack applies the permutation when it reads (locally)
-    if (px) push(2 * C + (conv ? off_rbw + i : (i < 27 * C ? off_c1w + i : (size_t)(q - grads_base))), tot);
+  for (int q = 0; q < 10; ++q) {                       // nblk <= 160: rows rc, rc + 16, ...; all loads in flight together
+    const int b = rc + 16 * q;
+    v[q] = b < nblk ? __ldcg(reinterpret_cast<const float4*>(part + (size_t)b * n)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  float4 s = v[0];
+#pragma unroll
+  for (int q = 1; q < 10; ++q) { s.x += v[q].x; s.y += v[q].y; s.z += v[q].z; s.w += v[q].w; }
+  red[rc][c4] = s;
+  __syncthreads();
+  nrd_dbg_stamp(dbgt, drow, 2);
+  float tot = 0.f;
+  if (t < 64) {
+    const float* rf = reinterpret_cast<const float*>(&red[0][0]) + t;      // element t of row class k: red[k][t / 4].{x,y,z,w}
+#pragma unroll
+    for (int k = 0; k < 16; ++k) tot += rf[k * 64];                        // row classes in order
+    grads_base[pi] = tot;
+    if (px) for (int p = 0; p < x.world; ++p) x.peer[p][slot + sidx] = tot;
   }
   if (px) nrd_xchg_publish(x, 0, epoch);
+  if (!upd) return;
+  if (px) {
+    // ---- wait for the world's body buckets in OUR buffer, then every element is the rank-ordered sum of the world's slots ----
+    nrd_xchg_wait_epoch(x, 0, (int)threadIdx.x, epoch);
+    __syncthreads();
+    const float* slots = x.peer[x.rank] + (size_t)(epoch & 1) * x.world * x.nx;
+    if (t < 64) {
+      float g = 0.f;
+      for (int r = 0; r < x.world; ++r) g += __ldcg(slots + (size_t)r * x.nx + sidx);
+      tot = g;
+      grads_base[pi] = tot;                            // .grad keeps holding the world's sum, as after an all-reduce
+    }
+    if (last_cta)
+      for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
+        float sres = 0.f, gj = 0.f;
+        for (int r = 0; r < x.world; ++r) { sres += __ldcg(slots + (size_t)r * x.nx + j); gj += __ldcg(slots + (size_t)r * x.nx + 2 * C + off_bng + j); }
+        if (bn_sync) bn_sync[j] = sres;
+        grads_base[off_bng + j] = gj;
+      }
+  }
+  if (t < 64) nrd_apply_update(u, pi, tot, p_old, C, off_rbw, off_c1w);
+  if (last_cta)
+    for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) u.params[off_bng + j] = fmaf(-u.step_scale, grads_base[off_bng + j], u.params[off_bng + j]);
+  nrd_dbg_stamp(dbgt, drow, 3);
 }
 
 // head bucket of the peer-memory exchange: this rank's fc1 / fc2 gradients (flat range [lo, hi)) into its slot of every
@@ -776,179 +845,6 @@ __global__ void k_maxpool_bwd(const T* __restrict__ gp, const uint8_t* __restric
 // ------------------------------------------------------------------------------------------
 // head: fc1 + relu, fc2, softmax cross-entropy                     (model/resnet.py:19-21, main.py:28)
 // ------------------------------------------------------------------------------------------
-// max_pool2d(x_NB, 2) fused into fc1 as a split-K product (model/resnet.py:18-20): CTA (bx, ks) = 32 batch rows x 32 outputs
-// over the K slice [ks*128, ks*128+128) of the pooled NHWC vector.  Every pooled element belongs to exactly one CTA, which
-// computes it from its 2x2 window of x_NB (first max wins), writes it and its arg-max for backward, and uses it:
-// part[ks][b][j] = sum_{k in slice} pooled[b][k] * w1t[k][j].  The slices are summed in order by k_fc2_fwd.
-template <typename T>
-__global__ void __launch_bounds__(256) k_pool_fc1_fwd_part(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restrict__ idx2,
-                                                           const float* __restrict__ w1t, float* __restrict__ part, int B, int C) {
-  __shared__ __align__(16) float ws[128 * 32];
-  __shared__ float ps[32 * 129];
-  const int tid = threadIdx.x, b0 = blockIdx.x * 32, k0 = blockIdx.y * 128, K = 64 * C;
-  nrd_pdl_launch();
-  for (int i = tid; i < 128 * 32 / 4; i += 256)        // weights: untouched since the last optimizer step, safe before the wait
-    reinterpret_cast<float4*>(ws)[i] = reinterpret_cast<const float4*>(w1t + (size_t)k0 * 32)[i];
-  nrd_pdl_wait();
-  for (int i = tid; i < 32 * 16; i += 256) {          // 32 rows x 16 eight-channel chunks of the slice
-    const int r = i >> 4, c8 = i & 15, b = b0 + r;
-    const int kk = k0 + c8 * 8, hw = kk / C, c = kk % C, ph = hw >> 3, pw = hw & 7;
-    float m[8]; int mi[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { m[j] = 0.f; mi[j] = 0; }
-    if (b < B) {
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        float v[8];
-        ld8(x + (((size_t)b * 16 + 2 * ph + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + c, v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) if (q == 0 || v[j] > m[j]) { m[j] = v[j]; mi[j] = q; }
-      }
-      st8(pooled + (size_t)b * K + kk, m);
-      uint2 pk; uint8_t* pb = reinterpret_cast<uint8_t*>(&pk);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) pb[j] = (uint8_t)mi[j];
-      *reinterpret_cast<uint2*>(idx2 + (size_t)b * K + kk) = pk;
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) ps[r * 129 + c8 * 8 + j] = m[j];
-  }
-  __syncthreads();
-  const int r = tid >> 3, jq = tid & 7;
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll 8
-  for (int k = 0; k < 128; ++k) {
-    const float pv = ps[r * 129 + k];
-    const float4 w = *reinterpret_cast<const float4*>(ws + k * 32 + jq * 4);
-    a0 = fmaf(pv, w.x, a0); a1 = fmaf(pv, w.y, a1); a2 = fmaf(pv, w.z, a2); a3 = fmaf(pv, w.w, a3);
-  }
-  if (b0 + r < B)
-    *reinterpret_cast<float4*>(part + ((size_t)blockIdx.y * B + b0 + r) * NRD_FC1_OUT + jq * 4) = make_float4(a0, a1, a2, a3);
-}
-
-// the same split-K fc1 when the pooling has already been done (persistent forward): reads pooled [B,8,8,C]
-template <typename T>
-__global__ void __launch_bounds__(256) k_fc1_fwd_part(const T* __restrict__ pooled, const float* __restrict__ w1t, float* __restrict__ part,
-                                                      int B, int C) {
-  __shared__ __align__(16) float ws[128 * 32];
-  __shared__ float ps[32 * 129];
-  const int tid = threadIdx.x, b0 = blockIdx.x * 32, k0 = blockIdx.y * 128, K = 64 * C;
-  nrd_pdl_launch();
-  for (int i = tid; i < 128 * 32 / 4; i += 256)
-    reinterpret_cast<float4*>(ws)[i] = reinterpret_cast<const float4*>(w1t + (size_t)k0 * 32)[i];
-  nrd_pdl_wait();
-  for (int i = tid; i < 32 * 16; i += 256) {
-    const int r = i >> 4, c8 = i & 15, b = b0 + r;
-    float m[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) m[j] = 0.f;
-    if (b < B) ld8(pooled + (size_t)b * K + k0 + c8 * 8, m);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) ps[r * 129 + c8 * 8 + j] = m[j];
-  }
-  __syncthreads();
-  const int r = tid >> 3, jq = tid & 7;
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll 8
-  for (int k = 0; k < 128; ++k) {
-    const float pv = ps[r * 129 + k];
-    const float4 w = *reinterpret_cast<const float4*>(ws + k * 32 + jq * 4);
-    a0 = fmaf(pv, w.x, a0); a1 = fmaf(pv, w.y, a1); a2 = fmaf(pv, w.z, a2); a3 = fmaf(pv, w.w, a3);
-  }
-  if (b0 + r < B)
-    *reinterpret_cast<float4*>(part + ((size_t)blockIdx.y * B + b0 + r) * NRD_FC1_OUT + jq * 4) = make_float4(a0, a1, a2, a3);
-}
-
-// h1 = relu(sum_ks part + b1) (stored for backward), logits = h1 @ w2^T + b2.  CTA = 8 batch rows.
-__global__ void __launch_bounds__(256) k_fc2_fwd(const float* __restrict__ part, int nsplit, const float* __restrict__ b1,
-                                                 const float* __restrict__ w2, const float* __restrict__ b2,
-                                                 float* __restrict__ h1, float* __restrict__ logits, int B) {
-  __shared__ float hs[8][33];
-  const int tid = threadIdx.x, r = tid >> 5, j = tid & 31, b = blockIdx.x * 8 + r;
-  nrd_pdl_launch();
-  nrd_pdl_wait();
-  float h = 0.f;
-  if (b < B) {
-    for (int s = 0; s < nsplit; ++s) h += part[((size_t)s * B + b) * NRD_FC1_OUT + j];
-    h = fmaxf(h + b1[j], 0.f);
-    h1[(size_t)b * NRD_FC1_OUT + j] = h;
-  }
-  hs[r][j] = h;
-  __syncthreads();
-  if (tid < 8 * NRD_NCLS) {
-    const int rr = tid / NRD_NCLS, c = tid % NRD_NCLS, bb = blockIdx.x * 8 + rr;
-    if (bb < B) {
-      float sacc = b2[c];
-#pragma unroll
-      for (int jj = 0; jj < NRD_FC1_OUT; ++jj) sacc = fmaf(hs[rr][jj], w2[c * NRD_FC1_OUT + jj], sacc);
-      logits[(size_t)bb * NRD_NCLS + c] = sacc;
-    }
-  }
-}
-
-// k_fc2_fwd + softmax cross-entropy (forward and gradient) in one launch: each CTA finishes its 8 rows (loss row, dlogits);
-// the CTA that arrives last at a counter sums the B loss rows in k_ce's fixed order, so the mean is bit-identical to k_ce's.
-__global__ void __launch_bounds__(256) k_fc2_ce(const float* __restrict__ part, int nsplit, const float* __restrict__ b1,
-                                                const float* __restrict__ w2, const float* __restrict__ b2,
-                                                float* __restrict__ h1, float* __restrict__ logits, int B,
-                                                const int64_t* __restrict__ labels, float gscale, float* __restrict__ loss_rows,
-                                                float* __restrict__ dlogits, float* __restrict__ loss, unsigned int* __restrict__ counter) {
-  __shared__ float hs[8][33];
-  __shared__ float ls[8][NRD_NCLS];
-  __shared__ double red[256];
-  __shared__ int last;
-  const int tid = threadIdx.x, r = tid >> 5, j = tid & 31, b = blockIdx.x * 8 + r;
-  nrd_pdl_launch();
-  nrd_pdl_wait();
-  float h = 0.f;
-  if (b < B) {
-    for (int s = 0; s < nsplit; ++s) h += part[((size_t)s * B + b) * NRD_FC1_OUT + j];
-    h = fmaxf(h + b1[j], 0.f);
-    h1[(size_t)b * NRD_FC1_OUT + j] = h;
-  }
-  hs[r][j] = h;
-  __syncthreads();
-  if (tid < 8 * NRD_NCLS) {
-    const int rr = tid / NRD_NCLS, c = tid % NRD_NCLS, bb = blockIdx.x * 8 + rr;
-    float sacc = b2[c];
-#pragma unroll
-    for (int jj = 0; jj < NRD_FC1_OUT; ++jj) sacc = fmaf(hs[rr][jj], w2[c * NRD_FC1_OUT + jj], sacc);
-    ls[rr][c] = sacc;
-    if (bb < B) logits[(size_t)bb * NRD_NCLS + c] = sacc;
-  }
-  __syncthreads();
-  if (tid < 8) {
-    const int bb = blockIdx.x * 8 + tid;
-    if (bb < B) {
-      float v[NRD_NCLS], m = -INFINITY;
-#pragma unroll
-      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = ls[tid][c]; m = fmaxf(m, v[c]); }
-      float s = 0.f;
-#pragma unroll
-      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
-      const long long lab64 = labels[bb];
-      const bool lab_ok = lab64 >= 0 && lab64 < NRD_NCLS;          // an out-of-range label poisons the loss, never the address
-      const int lab = lab_ok ? (int)lab64 : 0;
-      const float inv = 1.f / s, sc = gscale / (float)B;
-      loss_rows[bb] = lab_ok ? logf(s) + m - ls[tid][lab] : NAN;
-#pragma unroll
-      for (int c = 0; c < NRD_NCLS; ++c) dlogits[bb * NRD_NCLS + c] = lab_ok ? (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc : NAN;
-    }
-    __threadfence();
-  }
-  __syncthreads();
-  if (tid == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1 : 0;
-  __syncthreads();
-  if (!last) return;
-  __threadfence();
-  double acc = 0.0;
-  for (int bb = tid; bb < B; bb += 256) acc += (double)__ldcg(loss_rows + bb);
-  red[tid] = acc;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
-  if (tid == 0) { *loss = (float)(red[0] / B); *counter = 0u; }
-}
-
 // softmax cross-entropy, forward and gradient, one CTA: per-row loss (kept in loss_rows) and dlogits =
 // (softmax - onehot) * grad_scale / B, then the mean loss by a fixed-shape tree over the CTA (deterministic).
 __global__ void __launch_bounds__(256) k_ce(const float* __restrict__ logits, const int64_t* __restrict__ labels, int B, float gscale,
@@ -1151,114 +1047,254 @@ __global__ void __launch_bounds__(256) k_fc1_dgrad_pooled(const float* __restric
   for (int j4 = 0; j4 < 8; ++j4) {
     const float4 w = wrow[j4];
 #pragma unroll
-    for (int r = 0; r < 8; ++r)
-      s[r] += d[r][j4 * 4] * w.x + d[r][j4 * 4 + 1] * w.y + d[r][j4 * 4 + 2] * w.z + d[r][j4 * 4 + 3] * w.w;
+    for (int r = 0; r < 8; ++r) {      // one fma chain per output, j ascending: the order of k_head_fused's backward slice (bit-identical)
+      s[r] = fmaf(d[r][j4 * 4], w.x, s[r]); s[r] = fmaf(d[r][j4 * 4 + 1], w.y, s[r]);
+      s[r] = fmaf(d[r][j4 * 4 + 2], w.z, s[r]); s[r] = fmaf(d[r][j4 * 4 + 3], w.w, s[r]);
+    }
   }
 #pragma unroll
   for (int r = 0; r < 8; ++r)
     if (b0 + r < B) dp[(size_t)(b0 + r) * K + i] = from_f<T>(s[r]);
 }
 
-// k_fc2_ce and k_fc1_dgrad_pooled as ONE launch: every CTA of the dgrad grid (8 batch rows x 256 columns of d(pooled)) first
-// redoes the tiny fc2 + cross-entropy of its 8 rows (320 + 80 MACs per row) instead of waiting for a kernel that does it
-// once; the CTAs of column group 0 also publish h1, logits, loss rows and dlogits, and the last of them to finish sums the
-// loss.  Same arithmetic, same order as the two kernels it replaces: results are bit-identical.
+// ------------------------------------------------------------------------------------------
+// The whole head in ONE cooperative launch (model/resnet.py:18-21, main.py:35 and the first products of main.py:38):
+//   max-pool 2x2 -> fc1 (split-K over the CTAs of a row group) -> +bias, ReLU -> fc2 -> softmax cross-entropy, dlogits
+//   -> dh1 -> dL/d(pooled) (each CTA its own K slice)
+// CTA (x, ks) serves row groups rg = x, x + gridDim.x, ... (32 batch rows each) for the K slice [ks*128, ks*128+128) of the
+// pooled NHWC vector; its 16 KB slice of the fc1 weight is fetched ONCE and serves both the forward partial product and
+// the backward slice.  The only cross-CTA dependency -- fc1's split-K sum -- is a counter per row group: its KS CTAs arrive
+// after storing their partials, wait for one another (cooperative launch: all CTAs are co-resident), and then EACH redoes the
+// tiny tail of its 32 rows (sum of the KS partials in slice order, fc2, softmax: ~1.4 k MACs per row) instead of waiting for
+// a second launch or for one CTA to publish it.  The ks == 0 CTAs publish h1 / logits / loss rows / dlogits, and the last of
+// them sums the loss rows in k_ce's fixed order.  Everything is fixed-order: bit-reproducible.
+// ------------------------------------------------------------------------------------------
+#define NRD_HEAD_THREADS 512
+#define NRD_HEAD_SMEM_FLOATS (128 * 32 + 32 * 132 + 32 * 129 + 32 * 32 + 320)
+static constexpr size_t head_smem_bytes() { return (size_t)NRD_HEAD_SMEM_FLOATS * 4 + 256 * 8 + 16; }
+
+// 512 threads = 2 K halves (kh) x 32 rows (r) x 8 output quads (jq); a warp = 4 rows x 8 quads, so everything a row needs from its
+// 8 threads travels by shuffles inside one warp: the tail (fc2, softmax, dh1) runs in registers without a CTA barrier.
 template <typename T>
-__global__ void __launch_bounds__(256) k_head_tail(const float* __restrict__ part, int nsplit, const float* __restrict__ b1,
-                                                   const float* __restrict__ w2, const float* __restrict__ b2,
-                                                   float* __restrict__ h1, float* __restrict__ logits, int B,
-                                                   const int64_t* __restrict__ labels, float gscale, float* __restrict__ loss_rows,
-                                                   float* __restrict__ dlogits, float* __restrict__ loss, unsigned int* __restrict__ counter,
-                                                   const float* __restrict__ w1t, T* __restrict__ dp, int C) {
-  __shared__ float hs[8][33];
-  __shared__ float ls[8][NRD_NCLS];
-  __shared__ float d[8][NRD_FC1_OUT];
-  __shared__ float dl[8 * NRD_NCLS], w2s[NRD_NCLS * NRD_FC1_OUT];
-  __shared__ double red[256];
+__global__ void __launch_bounds__(NRD_HEAD_THREADS, 1)
+k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restrict__ idx2, int pooled_in,
+             const float* __restrict__ w1t, const float* __restrict__ b1, const float* __restrict__ w2, const float* __restrict__ b2,
+             float* __restrict__ part, float* __restrict__ h1, float* __restrict__ logits, int B, int C,
+             const int64_t* __restrict__ labels, float gscale, float* __restrict__ loss_rows, float* __restrict__ dlogits,
+             float* __restrict__ loss, unsigned long long* __restrict__ rg_ctr, unsigned int* __restrict__ counter,
+             T* __restrict__ dp, long long* __restrict__ dbg) {
+  extern __shared__ __align__(16) float hsm[];
+  float* ws = hsm;                    // [128 k][32 j]      fc1 weight slice, k-major (forward partial product)
+  float* wsT = ws + 128 * 32;         // [32 j][132]        the same slice transposed (backward slice), rows padded
+  float* ps = wsT + 32 * 132;         // [32 rows][129]     pooled slice of the current row group
+  float* ph = ps + 32 * 129;          // [32 rows][32 j]    partial product of the upper K half
+  float* w2s = ph + 32 * 32;          // [10][32]
+  double* red = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(w2s + 320) + 15) & ~(uintptr_t)15);   // [256]
   __shared__ int last;
-  const int tid = threadIdx.x, K = 64 * C, per_b = K / 256, b0 = (blockIdx.x / per_b) * 8, cg = blockIdx.x % per_b, i = cg * 256 + tid;
-  const int r = tid >> 5, j = tid & 31, b = b0 + r;
-  nrd_pdl_launch();
-  for (int q = tid; q < NRD_NCLS * NRD_FC1_OUT; q += 256) w2s[q] = w2[q];
-  // this thread's fc1 weight row (column i of d(pooled)): weights are untouched since the last optimizer step, so the 128 bytes
-  // are fetched before the wait, under the predecessor's tail, instead of in front of the dgrad loop
-  float4 wreg[8];
-  {
-    const float4* wrow = reinterpret_cast<const float4*>(w1t + (size_t)i * NRD_FC1_OUT);
+  const int tid = threadIdx.x, lane = tid & 31, K = 64 * C, KS = gridDim.y, ks = blockIdx.y, k0 = ks * 128, nrg = (B + 31) / 32;
+  const int kh = tid >> 8, r = (tid >> 3) & 31, jq = tid & 7;
+  // stamps: rows 0..3 = CTAs (0,0), (0,KS-1), (last,0), (last,KS-1)
+  const int drow = (blockIdx.x == 0 ? 0 : (blockIdx.x == gridDim.x - 1 ? 2 : -1)) + (blockIdx.y == 0 ? 0 : (blockIdx.y == gridDim.y - 1 ? 1 : -100));
+  long long* dbgt = (dbg && tid == 0 && drow >= 0) ? dbg : nullptr;
+  nrd_dbg_stamp(dbgt, drow, 0);
+  // ---- this CTA's weight slice (weights are untouched since the last optimizer step): loads issued now, stored below ----
+  float4 wreg[2];
 #pragma unroll
-    for (int j4 = 0; j4 < 8; ++j4) wreg[j4] = wrow[j4];
-  }
-  nrd_pdl_wait();
-  float h = 0.f;
-  if (b < B) {
-    for (int s = 0; s < nsplit; ++s) h += part[((size_t)s * B + b) * NRD_FC1_OUT + j];
-    h = fmaxf(h + b1[j], 0.f);
-    if (cg == 0) h1[(size_t)b * NRD_FC1_OUT + j] = h;
-  }
-  hs[r][j] = h;
-  __syncthreads();
-  if (tid < 8 * NRD_NCLS) {
-    const int rr = tid / NRD_NCLS, c = tid % NRD_NCLS, bb = b0 + rr;
-    float sacc = b2[c];
+  for (int it = 0; it < 2; ++it) wreg[it] = reinterpret_cast<const float4*>(w1t + (size_t)k0 * 32)[tid + it * NRD_HEAD_THREADS];
+  for (int q = tid; q < NRD_NCLS * NRD_FC1_OUT; q += NRD_HEAD_THREADS) w2s[q] = w2[q];
+  bool w_stored = false;
+  for (int rg = blockIdx.x; rg < nrg; rg += gridDim.x) {
+    const int b0 = rg * 32, b = b0 + r;
+    nrd_dbg_stamp(dbgt, drow, 1);
+    // ---- pool: 32 rows x 16 eight-channel chunks of the slice, one per thread; all four window loads in flight together ----
+    {
+      const int rr = tid >> 4, c8 = tid & 15, bb = b0 + rr, kk = k0 + c8 * 8;
+      float v[4][8];
+      if (bb < B) {
+        if (pooled_in) ld8(pooled + (size_t)bb * K + kk, v[0]);
+        else {
+          const int hw = kk / C, c = kk % C, ph_ = hw >> 3, pw = hw & 7;
 #pragma unroll
-    for (int jj = 0; jj < NRD_FC1_OUT; ++jj) sacc = fmaf(hs[rr][jj], w2s[c * NRD_FC1_OUT + jj], sacc);
-    ls[rr][c] = sacc;
-    if (cg == 0 && bb < B) logits[(size_t)bb * NRD_NCLS + c] = sacc;
-  }
-  __syncthreads();
-  if (tid < 8) {
-    const int bb = b0 + tid;
+          for (int q = 0; q < 4; ++q) ld8(x + (((size_t)bb * 16 + 2 * ph_ + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + c, v[q]);
+        }
+      }
+      __syncthreads();                                 // previous row group's readers of ps / ph are done
+      if (!w_stored) {
 #pragma unroll
-    for (int c = 0; c < NRD_NCLS; ++c) dl[tid * NRD_NCLS + c] = 0.f;
-    if (bb < B) {
-      float v[NRD_NCLS], m = -INFINITY;
+        for (int it = 0; it < 2; ++it) {
+          const int i = tid + it * NRD_HEAD_THREADS, k = i >> 3, j = (i & 7) * 4;
+          const float4 w = wreg[it];
+          reinterpret_cast<float4*>(ws)[i] = w;
+          wsT[(j + 0) * 132 + k] = w.x; wsT[(j + 1) * 132 + k] = w.y; wsT[(j + 2) * 132 + k] = w.z; wsT[(j + 3) * 132 + k] = w.w;
+        }
+        w_stored = true;
+      }
+      float m[8]; int mi[8];
 #pragma unroll
-      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = ls[tid][c]; m = fmaxf(m, v[c]); }
-      float s = 0.f;
+      for (int j = 0; j < 8; ++j) { m[j] = 0.f; mi[j] = 0; }
+      if (bb < B) {
+        if (pooled_in) {
 #pragma unroll
-      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s += v[c]; }
-      const long long lab64 = labels[bb];
-      const bool lab_ok = lab64 >= 0 && lab64 < NRD_NCLS;          // an out-of-range label poisons the loss, never the address
-      const int lab = lab_ok ? (int)lab64 : 0;
-      const float inv = 1.f / s, sc = gscale / (float)B;
-      if (cg == 0) loss_rows[bb] = lab_ok ? logf(s) + m - ls[tid][lab] : NAN;
+          for (int j = 0; j < 8; ++j) m[j] = v[0][j];
+        } else {
 #pragma unroll
-      for (int c = 0; c < NRD_NCLS; ++c) {
-        const float g = lab_ok ? (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc : NAN;
-        dl[tid * NRD_NCLS + c] = g;
-        if (cg == 0) dlogits[bb * NRD_NCLS + c] = g;
+          for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (q == 0 || v[q][j] > m[j]) { m[j] = v[q][j]; mi[j] = q; }     // first max wins
+          st8(pooled + (size_t)bb * K + kk, m);
+          uint2 pk; uint8_t* pb = reinterpret_cast<uint8_t*>(&pk);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) pb[j] = (uint8_t)mi[j];
+          *reinterpret_cast<uint2*>(idx2 + (size_t)bb * K + kk) = pk;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ps[rr * 129 + c8 * 8 + j] = m[j];
+    }
+    __syncthreads();
+    nrd_dbg_stamp(dbgt, drow, 2);
+    // ---- fc1 partial product: thread = (K half kh, row r, outputs jq*4 .. +3); operands fetched 16 k ahead of their use ----
+    {
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      const float* prow = ps + r * 129 + kh * 64;
+      const float* wcol = ws + (kh * 64) * 32 + jq * 4;
+#pragma unroll 1                                        // executed once per CTA: unrolled copies would only be cold instruction fetches
+      for (int kb = 0; kb < 64; kb += 16) {
+        float pv[16]; float4 w[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) { pv[u] = prow[kb + u]; w[u] = *reinterpret_cast<const float4*>(wcol + (kb + u) * 32); }
+#pragma unroll
+        for (int u = 0; u < 16; ++u) { a0 = fmaf(pv[u], w[u].x, a0); a1 = fmaf(pv[u], w[u].y, a1); a2 = fmaf(pv[u], w[u].z, a2); a3 = fmaf(pv[u], w[u].w, a3); }
+      }
+      if (kh == 1) *reinterpret_cast<float4*>(ph + r * 32 + jq * 4) = make_float4(a0, a1, a2, a3);
+      __syncthreads();
+      if (kh == 0 && b < B) {                          // lower half + upper half, in that order
+        const float4 u = *reinterpret_cast<const float4*>(ph + r * 32 + jq * 4);
+        *reinterpret_cast<float4*>(part + ((size_t)ks * B + b) * NRD_FC1_OUT + jq * 4) = make_float4(a0 + u.x, a1 + u.y, a2 + u.z, a3 + u.w);
       }
     }
-    if (cg == 0) __threadfence();
+    // ---- the KS CTAs of this row group wait for one another (monotonic counter per row group, nrd_common.cuh).  The CTA barrier
+    // ---- orders every thread's partial store before thread 0's release-add (cumulative at gpu scope): the grid-sync pattern, one
+    // ---- fence per CTA instead of one per thread ----
+    __syncthreads();
+    nrd_dbg_stamp(dbgt, drow, 3);
+    if (tid == 0) {
+      const unsigned long long base = nrd_grid_barrier_base(rg_ctr + rg, (unsigned)KS);
+      __threadfence();
+      nrd_grid_barrier(rg_ctr + rg, base + (unsigned)KS);
+    }
+    __syncthreads();
+    nrd_dbg_stamp(dbgt, drow, 4);
+    // ---- tail of the 32 rows, in registers, redone by every CTA of the group (and by both K halves): thread (r, jq) holds
+    // ---- h1[r][jq*4 .. +3]; the row's 8 threads are 8 consecutive lanes ----
+    float h[4] = {0.f, 0.f, 0.f, 0.f};
+    if (b < B) {
+      float4 hv[16];
+#pragma unroll 1
+      for (int s0 = 0; s0 < KS; s0 += 16) {            // KS = 16 (C = 32) or 32 (C = 64): all loads of a batch in flight together
+#pragma unroll
+        for (int s2 = 0; s2 < 16; ++s2) hv[s2] = __ldcg(reinterpret_cast<const float4*>(part + ((size_t)(s0 + s2) * B + b) * NRD_FC1_OUT) + jq);
+#pragma unroll
+        for (int s2 = 0; s2 < 16; ++s2) { h[0] += hv[s2].x; h[1] += hv[s2].y; h[2] += hv[s2].z; h[3] += hv[s2].w; }     // slice order: fixed
+      }
+      const float4 bb4 = *reinterpret_cast<const float4*>(b1 + jq * 4);
+      h[0] = fmaxf(h[0] + bb4.x, 0.f); h[1] = fmaxf(h[1] + bb4.y, 0.f); h[2] = fmaxf(h[2] + bb4.z, 0.f); h[3] = fmaxf(h[3] + bb4.w, 0.f);
+      if (ks == 0 && kh == 0) *reinterpret_cast<float4*>(h1 + (size_t)b * NRD_FC1_OUT + jq * 4) = make_float4(h[0], h[1], h[2], h[3]);
+    }
+    // logits: each thread's 4-term partial of the 32-term products, butterfly over the row's 8 lanes (xor 1, 2, 4: a fixed tree)
+    float lg[NRD_NCLS];
+#pragma unroll
+    for (int c = 0; c < NRD_NCLS; ++c) {
+      const float4 w = *reinterpret_cast<const float4*>(w2s + c * NRD_FC1_OUT + jq * 4);
+      float t = fmaf(h[3], w.w, fmaf(h[2], w.z, fmaf(h[1], w.y, h[0] * w.x)));
+      t += __shfl_xor_sync(0xffffffffu, t, 1); t += __shfl_xor_sync(0xffffffffu, t, 2); t += __shfl_xor_sync(0xffffffffu, t, 4);
+      lg[c] = t + b2[c];
+    }
+    const bool pub = ks == 0 && kh == 0 && jq == 0 && b < B;      // one thread per row publishes
+    if (pub) {
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) logits[(size_t)b * NRD_NCLS + c] = lg[c];
+    }
+    if (labels == nullptr) continue;                   // forward only (uniform over the grid)
+    nrd_dbg_stamp(dbgt, drow, 5);
+    // softmax cross-entropy of the row, by each of its threads (same arithmetic, same order as k_ce)
+    float dlr[NRD_NCLS];
+#pragma unroll
+    for (int c = 0; c < NRD_NCLS; ++c) dlr[c] = 0.f;
+    if (b < B) {
+      float v[NRD_NCLS], m = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = lg[c]; m = fmaxf(m, v[c]); }
+      float s2 = 0.f;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s2 += v[c]; }
+      const long long lab64 = labels[b];
+      const bool lab_ok = lab64 >= 0 && lab64 < NRD_NCLS;          // an out-of-range label poisons the loss, never the address
+      const int lab = lab_ok ? (int)lab64 : 0;
+      const float inv = 1.f / s2, sc = gscale / (float)B;
+      float llab = lg[0];
+#pragma unroll
+      for (int c = 1; c < NRD_NCLS; ++c) llab = (c == lab) ? lg[c] : llab;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) dlr[c] = lab_ok ? (v[c] * inv - (c == lab ? 1.f : 0.f)) * sc : NAN;
+      if (pub) {
+        loss_rows[b] = lab_ok ? logf(s2) + m - llab : NAN;
+#pragma unroll
+        for (int c = 0; c < NRD_NCLS; ++c) dlogits[(size_t)b * NRD_NCLS + c] = dlr[c];
+      }
+    }
+    // dL/dh1 of this thread's 4 outputs (c ascending, one fma chain: dh1_elem's order)
+    float dreg[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float sacc = 0.f;
+#pragma unroll
+      for (int c = 0; c < NRD_NCLS; ++c) sacc = fmaf(dlr[c], w2s[c * NRD_FC1_OUT + jq * 4 + e], sacc);
+      dreg[e] = (b < B && h[e] > 0.f) ? sacc : 0.f;
+    }
+    nrd_dbg_stamp(dbgt, drow, 6);
+    if (dp != nullptr) {
+      // ---- dL/d(pooled) for this slice: thread = (row r, columns m*32 + jq*4 .. +3 for m = 2kh, 2kh+1); dh1[r][j] comes from
+      // ---- the row's lane j/4 by shuffle; j ascending, one fma chain per output ----
+      float acc[2][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[m][e] = 0.f;
+      const int lbase = lane & 24;
+#pragma unroll 1
+      for (int j4 = 0; j4 < NRD_FC1_OUT / 4; ++j4) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float d = __shfl_sync(0xffffffffu, dreg[e], lbase + j4);
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            const float4 w = *reinterpret_cast<const float4*>(wsT + (j4 * 4 + e) * 132 + (2 * kh + m) * 32 + jq * 4);
+            acc[m][0] = fmaf(d, w.x, acc[m][0]); acc[m][1] = fmaf(d, w.y, acc[m][1]); acc[m][2] = fmaf(d, w.z, acc[m][2]); acc[m][3] = fmaf(d, w.w, acc[m][3]);
+          }
+        }
+      }
+      if (b < B) {
+#pragma unroll
+        for (int m = 0; m < 2; ++m) st4(dp + (size_t)b * K + k0 + (2 * kh + m) * 32 + jq * 4, acc[m]);
+      }
+    }
+    nrd_dbg_stamp(dbgt, drow, 7);
+    // mean loss: the last row group to get here sums the B loss rows in k_ce's fixed order
+    if (ks == 0) {
+      __syncthreads();                                 // every publishing thread of this CTA has stored its rows
+      if (tid == 0) { __threadfence(); last = (atomicAdd(counter, 1u) == (unsigned)nrg - 1) ? 1 : 0; }
+      __syncthreads();
+      if (last) {
+        __threadfence();
+        double acc = 0.0;
+        if (tid < 256) { for (int bb = tid; bb < B; bb += 256) acc += (double)__ldcg(loss_rows + bb); red[tid] = acc; }
+        __syncthreads();
+        for (int o = 128; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
+        if (tid == 0) { *loss = (float)(red[0] / B); *counter = 0u; }
+      }
+    }
   }
-  __syncthreads();
-  d[r][j] = (b < B) ? dh1_elem(dl + r * NRD_NCLS, w2s, j, hs[r][j]) : 0.f;
-  __syncthreads();
-  float s8[8];
-#pragma unroll
-  for (int rr = 0; rr < 8; ++rr) s8[rr] = 0.f;
-#pragma unroll
-  for (int j4 = 0; j4 < 8; ++j4) {
-    const float4 w = wreg[j4];
-#pragma unroll
-    for (int rr = 0; rr < 8; ++rr)
-      s8[rr] += d[rr][j4 * 4] * w.x + d[rr][j4 * 4 + 1] * w.y + d[rr][j4 * 4 + 2] * w.z + d[rr][j4 * 4 + 3] * w.w;
-  }
-#pragma unroll
-  for (int rr = 0; rr < 8; ++rr)
-    if (b0 + rr < B) dp[(size_t)(b0 + rr) * K + i] = from_f<T>(s8[rr]);
-  if (cg != 0) return;
-  // mean loss: the last row group to get here sums the B loss rows in k_ce's fixed order
-  if (tid == 0) last = (atomicAdd(counter, 1u) == (unsigned)((B + 7) / 8) - 1) ? 1 : 0;
-  __syncthreads();
-  if (!last) return;
-  __threadfence();
-  double acc = 0.0;
-  for (int bb = tid; bb < B; bb += 256) acc += (double)__ldcg(loss_rows + bb);
-  red[tid] = acc;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
-  if (tid == 0) { *loss = (float)(red[0] / B); *counter = 0u; }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1271,11 +1307,13 @@ __global__ void k_sgd(float* __restrict__ p, const float* __restrict__ g, size_t
 
 // p <- p - step_scale * g over the whole flat vector AND the packed copies of the three tensors that have them, one launch
 // (off[] = flat offsets of the 9 tensors; index order as k_pack_weights)
-__global__ void k_sgd_pack(float* __restrict__ p, float* g, float step_scale, int C, const long long* __restrict__ offp,
+// [lo, hi): the part of the flat vector this launch updates (whole vector, or one bucket when the update rides the backward);
+// wait_mask: which exchange buckets it needs (bit 0 body, bit 1 head)
+__global__ void k_sgd_pack(float* __restrict__ p, float* g, float step_scale, int C, long long lo, long long hi, int wait_mask,
                            long long o_c1w, long long o_rbw, long long o_fc1w, long long n,
                            float* __restrict__ w_fwd, float* __restrict__ w_dgrad, bf16* __restrict__ wtc_fwd, bf16* __restrict__ wtc_dgrad,
                            float* __restrict__ w1p, float* __restrict__ conv1_wp, nrd_xchg_args x, float* bn_sync) {
-  (void)offp;
+  (void)n;
   nrd_pdl_wait();
   // peer-memory exchange: every gradient is the rank-ordered sum of the world's slots in OUR buffer (body bucket [0, o_fc1w)
   // and head bucket [o_fc1w, n) arrive separately)
@@ -1284,12 +1322,12 @@ __global__ void k_sgd_pack(float* __restrict__ p, float* g, float step_scale, in
   const float* slots_head = nullptr;
   if (px) {
     float* own = x.peer[x.rank];
-    const unsigned long long e_body = nrd_xchg_wait(x, 0, (int)threadIdx.x);
-    const unsigned long long e_head = nrd_xchg_wait(x, 1, (int)threadIdx.x - 32);
+    const unsigned long long e_body = (wait_mask & 1) ? nrd_xchg_wait(x, 0, (int)threadIdx.x) : 0ull;
+    const unsigned long long e_head = (wait_mask & 2) ? nrd_xchg_wait(x, 1, (int)threadIdx.x - 32) : 0ull;
     __syncthreads();
     slots = own + (size_t)(e_body & 1) * x.world * x.nx;
     slots_head = own + (size_t)(e_head & 1) * x.world * x.nx;
-    if (blockIdx.x == 0 && bn_sync)
+    if (blockIdx.x == 0 && bn_sync && (wait_mask & 1))
       for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
         float sres = 0.f;
         for (int r = 0; r < x.world; ++r) sres += __ldcg(slots + (size_t)r * x.nx + j);
@@ -1297,7 +1335,7 @@ __global__ void k_sgd_pack(float* __restrict__ p, float* g, float step_scale, in
       }
   }
   const long long n_rb = (long long)C * C * 9, n_fc1 = (long long)NRD_FC1_OUT * 64 * C, n_c1 = (long long)C * 27;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x) {
     float gi;
     if (px) {
       const float* sl = i < o_fc1w ? slots : slots_head;
@@ -1678,6 +1716,40 @@ extern "C" int nrd_gen_batch(float* images, int64_t* labels, int B, uint64_t see
   return NRD_OK;
 }
 
+// ---- head (one cooperative launch) -----------------------------------------------------------
+static int head_init(nrd_plan* p) {
+  int occ = 0, sms = 0;
+  NRD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p->device));
+  if (p->dtype == NRD_F32) {
+    NRD_CHECK_CUDA(cudaFuncSetAttribute(k_head_fused<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)head_smem_bytes()));
+    NRD_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_head_fused<float>, NRD_HEAD_THREADS, head_smem_bytes()));
+  } else {
+    NRD_CHECK_CUDA(cudaFuncSetAttribute(k_head_fused<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)head_smem_bytes()));
+    NRD_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_head_fused<bf16>, NRD_HEAD_THREADS, head_smem_bytes()));
+  }
+  p->head_ctas = occ * sms;
+  NRD_REQUIRE(p->head_ctas >= 64 * p->C / 128, "the head kernel does not fit this device (%d co-resident CTAs)", p->head_ctas);
+  return NRD_OK;
+}
+
+// pool + fc1 + fc2 (+ loss, dlogits when labels != NULL) (+ dL/d(pooled) into dp when dp != NULL), one launch
+static int launch_head(nrd_plan* p, const void* x_last, int pooled_in, float* logits, const int64_t* labels, float gscale, float* loss_rows,
+                       float* dlogits, float* loss, void* dp, cudaStream_t st) {
+  const int B = p->B, C = p->C, KS = 64 * C / 128, nrg = (B + 31) / 32;
+  int gx = p->head_ctas / KS; if (gx > nrg) gx = nrg;
+  const float* w1t = p->w1p; const float* b1 = p->params + p->off[6]; const float* w2 = p->params + p->off[7]; const float* b2 = p->params + p->off[8];
+  unsigned int* counter = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_HEAD_COUNTER);
+  void* pooled = p->pooled; uint8_t* idx2 = p->idx2; float* part = p->fc1_part; float* h1 = p->h1; unsigned long long* ctr = p->head_ctr;
+  int Bv = B, Cv = C;
+  void* args[] = {(void*)&x_last, (void*)&pooled, (void*)&idx2, (void*)&pooled_in, (void*)&w1t, (void*)&b1, (void*)&w2, (void*)&b2, (void*)&part, (void*)&h1,
+                  (void*)&logits, (void*)&Bv, (void*)&Cv, (void*)&labels, (void*)&gscale, (void*)&loss_rows, (void*)&dlogits, (void*)&loss, (void*)&ctr,
+                  (void*)&counter, (void*)&dp, (void*)&p->dbg};
+  const void* fn = p->dtype == NRD_F32 ? (const void*)k_head_fused<float> : (const void*)k_head_fused<bf16>;
+  NRD_CHECK_CUDA(cudaLaunchCooperativeKernel(fn, dim3(gx, KS), dim3(NRD_HEAD_THREADS), args, head_smem_bytes(), st));
+  nrd_count_launch();
+  return NRD_OK;
+}
+
 // ---- plan ---------------------------------------------------------------------------------
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
@@ -1717,6 +1789,8 @@ static void carve(nrd_plan* p, char* base, size_t* total) {
   p->wtc_fwd = cv.take<bf16>((size_t)9 * C * C * 2);
   p->wtc_dgrad = cv.take<bf16>((size_t)9 * C * C * 2);
   p->gbar = cv.take<unsigned long long>(256);
+  p->head_ctr = cv.take<unsigned long long>((size_t)((B + 31) / 32) * sizeof(unsigned long long));
+  p->dbg_buf = cv.take<long long>(64 * 16 * 2 * sizeof(long long));
   p->bn_acc = cv.take<unsigned long long>((size_t)2 * 32 * NRD_ACC_ROW * sizeof(unsigned long long));
   *total = cv.off;
 }
@@ -1766,6 +1840,10 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaMemset(grid barrier): %s", cudaGetErrorString(e)); return NRD_ECUDA; }
   e = cudaMemset(p->bn_acc, 0, (size_t)2 * 32 * NRD_ACC_ROW * sizeof(unsigned long long));   // the persistent kernels keep it zero
   if (e != cudaSuccess) { delete p; nrd_set_error("cudaMemset(BN accumulators): %s", cudaGetErrorString(e)); return NRD_ECUDA; }
+  e = cudaMemset(p->head_ctr, 0, (size_t)((B + 31) / 32) * sizeof(unsigned long long));
+  if (e != cudaSuccess) { delete p; nrd_set_error("cudaMemset(head counters): %s", cudaGetErrorString(e)); return NRD_ECUDA; }
+  r = head_init(p);
+  if (r != NRD_OK) { delete p; return r; }
   if (dtype == NRD_BF16) {
     r = nrd_tc_plan_init(p);
     if (r != NRD_OK) { delete p; return r; }   // no silent fallback: the bf16 product path IS the tcgen05 path
@@ -1812,8 +1890,15 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
       p->reserve_sms = value;
       if (p->tc_ready) nrd_tc_refresh_limits(p);
       return NRD_OK;
+    case NRD_OPT_TIMELINE:
+      if (value && !p->tl_ev[0]) {
+        NRD_CHECK_CUDA(cudaSetDevice(p->device));
+        for (int i = 0; i < 40; ++i) NRD_CHECK_CUDA(cudaEventCreate(&p->tl_ev[i]));
+      }
+      p->tl_on = value ? 1 : 0; p->tl_n = 0;
+      return NRD_OK;
     case NRD_OPT_TRACE: p->dbg_skip_stores = (value == 2);
-      p->trace = value ? (void*)p->dxb : nullptr; p->trace_bwd = value ? (void*)p->dy : nullptr; return NRD_OK;   // stamps land in the dx pong / dy scratch
+      p->trace = value ? (void*)p->dxb : nullptr; p->trace_bwd = value ? (void*)p->dy : nullptr; p->dbg = value ? p->dbg_buf : nullptr; return NRD_OK;   // stamps land in the dx pong / dy scratch
     default: nrd_set_error("nrd_plan_set_option: unknown option %d", option); return NRD_EINVAL;
   }
 }
@@ -1914,6 +1999,7 @@ extern "C" int nrd_plan_tensor(nrd_plan* p, int what, int k, void** ptr, size_t*
     case 6: *ptr = p->dxb; *bytes = act; break;
     case 7: *ptr = p->wgrad_partial; *bytes = nrd_wgrad_partial_bytes(p->B, p->C); break;
     case 9: *ptr = p->stem_partial; *bytes = nrd_stem_bwd_partial_bytes(p->B, p->C); break;
+    case 11: *ptr = p->dbg_buf; *bytes = 64 * 16 * 2 * sizeof(long long); break;
     case 10: *ptr = p->h1; *bytes = (size_t)p->B * NRD_FC1_OUT * 4; break;
     case 8: *ptr = p->stats_partial; *bytes = (size_t)(p->B * 2 > 1024 ? p->B * 2 : 1024) * 2 * p->C * 4; break;
     default: nrd_set_error("nrd_plan_tensor: unknown selector %d", what); return NRD_EINVAL;
@@ -1936,15 +2022,44 @@ extern "C" int nrd_pack_weights(nrd_plan* p, void* stream) {
   return NRD_OK;
 }
 
+// optimizer step over [lo, hi) of the flat vector (+ the packed copies of what it touches); wait_mask: exchange buckets it needs
+static int sgd_pack_range(nrd_plan* p, float step_scale, long long lo, long long hi, int wait_mask, int pdl, cudaStream_t st) {
+  NRD_CHECK_CUDA(nrd_launch_pdl(k_sgd_pack, dim3(grid_for((size_t)(hi - lo), 256, NRD_NUM_SMS * 2)), dim3(256), 0, st, pdl,
+                                p->params, p->grads, step_scale, p->C, lo, hi, wait_mask, p->off[P_C1W], p->off[P_RBW], p->off[P_FC1W], (long long)p->off[9], p->w_fwd,
+                                p->w_dgrad, p->wtc_fwd, p->wtc_dgrad, p->w1p, p->conv1_wp, p->xchg, p->bn_sync));
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
 // optimizer.step() (+ DDP mean) and the weight re-pack in ONE launch over the flat vector
 extern "C" int nrd_sgd_update_pack(nrd_plan* p, float lr, float inv_world, void* stream) {
   NRD_REQUIRE(p, "null plan");
   NRD_CHECK_CUDA(cudaSetDevice(p->device));
-  const long long n = p->off[9];
-  NRD_CHECK_CUDA(nrd_launch_pdl(k_sgd_pack, dim3(grid_for((size_t)n, 256, NRD_NUM_SMS * 2)), dim3(256), 0, (cudaStream_t)stream, (p->pdl >> 2) & 1,
-                                p->params, p->grads, lr * inv_world, p->C, nullptr, p->off[P_C1W], p->off[P_RBW], p->off[P_FC1W], n, p->w_fwd,
-                                p->w_dgrad, p->wtc_fwd, p->wtc_dgrad, p->w1p, p->conv1_wp, p->xchg, p->bn_sync));
-  LAUNCH_CHECK();
+  const int r = sgd_pack_range(p, lr * inv_world, 0, p->off[9], 3, (p->pdl >> 2) & 1, (cudaStream_t)stream);
+  nrd_tl_mark(p, (cudaStream_t)stream, "join+sgd_pack");
+  return r;
+}
+
+// Read the timeline of the last step run with NRD_OPT_TIMELINE on (synchronise first): us[i] = microseconds between mark i and
+// mark i+1, names[i] = what ran in between (the kernel launched before mark i+1).  Returns the number of intervals, < 0 on error.
+extern "C" int nrd_plan_timeline(nrd_plan* p, int max_n, float* us, const char** names) {
+  NRD_REQUIRE(p && us && names, "nrd_plan_timeline: null pointer");
+  NRD_REQUIRE(p->tl_on, "nrd_plan_timeline: NRD_OPT_TIMELINE is off");
+  NRD_CHECK_CUDA(cudaSetDevice(p->device));
+  int n = 0;
+  for (int i = 0; i + 1 < p->tl_n && n < max_n; ++i, ++n) {
+    float ms = 0.f;
+    NRD_CHECK_CUDA(cudaEventElapsedTime(&ms, p->tl_ev[i], p->tl_ev[i + 1]));
+    us[n] = ms * 1e3f; names[n] = p->tl_name[i + 1];
+  }
+  return n;
+}
+
+extern "C" int nrd_plan_set_fused_update(nrd_plan* p, float lr, float inv_world) {
+  NRD_REQUIRE(p, "null plan");
+  NRD_REQUIRE(!(lr > 0.f) || inv_world > 0.f, "nrd_plan_set_fused_update: inv_world must be positive (got %g)", (double)inv_world);
+  p->upd_lr = lr > 0.f ? lr : 0.f;
+  p->upd_inv_world = inv_world;
   return NRD_OK;
 }
 
@@ -1970,14 +2085,17 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
   const int B = p->B, C = p->C, NB = p->NB, dt = p->dtype;
   const size_t act = p->act_elems * p->esz;
   p->images_last = images;
+  nrd_tl_mark(p, st, "start", true);
   const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_fwd;
   const bool stem_in_blocks = persist && p->fuse_stem && p->tc_stem && p->use_tc_stem;
   if (stem_in_blocks) {}                                         // x_0 is produced inside the persistent kernel
   else if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_fwd(p, images, training, st));
   else NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st, nrd_bn_sync_of(p, training)));
+  nrd_tl_mark(p, st, "stem_fwd");
   if (!training) { k_bn_eval_coeffs<<<1, 64, 0, st>>>(p->bn_running, PRM(P_BNG), PRM(P_BNB), C, p->scale_shift); LAUNCH_CHECK(); }
   const bool pool_in_blocks = persist && p->fuse_pool;
   if (persist) NRD_TRY(nrd_tc_forward_blocks(p, pool_in_blocks ? 1 : 0, stem_in_blocks ? images : nullptr, training, st));       // ... and the max-pool behind the last block
+  if (persist) nrd_tl_mark(p, st, "fwd_blocks");
   for (int k = 0; k < (persist ? 0 : NB); ++k) {
     char* xk = p->xs + act * k; char* yk = p->ys + act * k; char* xn = p->xs + act * (k + 1);
     float* ss = training ? p->scale_shift + (size_t)k * 2 * C : p->scale_shift;
@@ -1995,26 +2113,13 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
     }
     NRD_TRY(bn_relu_add_any(yk, xk, ss, xn, B, C, dt, st));
   }
-  const int K = 64 * C;
-  const dim3 g1((B + 31) / 32, K / 128);
-  if (pool_in_blocks) NRD_CHECK_CUDA(nrd_launch_pdl(k_fc1_fwd_part<bf16>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const bf16*)p->pooled, p->w1p, p->fc1_part, B, C));
-  else if (dt == NRD_F32) NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<float>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const float*)(p->xs + act * NB), (float*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
-  else NRD_CHECK_CUDA(nrd_launch_pdl(k_pool_fc1_fwd_part<bf16>, g1, dim3(256), 0, st, (p->pdl >> 1) & 1, (const bf16*)(p->xs + act * NB), (bf16*)p->pooled, p->idx2, p->w1p, p->fc1_part, B, C));
-  LAUNCH_CHECK();
+  // head: pool + fc1 + fc2 (+ loss and dlogits, + the backward's first product dL/d(pooled)) in ONE cooperative launch
   p->dp_for = nullptr;
-  if (labels && dt == NRD_BF16 && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd && p->fuse_head_tail) {
-    // the backward's first kernel rides along: d(pooled) is ready when nrd_backward_body(dlogits) is called
-    NRD_CHECK_CUDA(nrd_launch_pdl(k_head_tail<bf16>, dim3(((B + 7) / 8) * (K / 256)), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B),
-                                  PRM(P_FC2W), PRM(P_FC2B), p->h1, logits, B, labels, grad_scale, loss_rows, dlogits, loss_out,
-                                  reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_HEAD_COUNTER), p->w1p, (bf16*)p->dxa, C));
-    p->dp_for = dlogits;
-  } else if (labels)
-    NRD_CHECK_CUDA(nrd_launch_pdl(k_fc2_ce, dim3((B + 7) / 8), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B),
-                                  p->h1, logits, B, labels, grad_scale, loss_rows, dlogits, loss_out, reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_HEAD_COUNTER)));
-  else
-    NRD_CHECK_CUDA(nrd_launch_pdl(k_fc2_fwd, dim3((B + 7) / 8), dim3(256), 0, st, p->pdl & 1, p->fc1_part, K / 128, PRM(P_FC1B), PRM(P_FC2W), PRM(P_FC2B),
-                                  p->h1, logits, B));
-  LAUNCH_CHECK();
+  const bool tail = labels && dt == NRD_BF16 && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd && p->fuse_head_tail;
+  NRD_TRY(launch_head(p, p->xs + act * NB, pool_in_blocks ? 1 : 0, logits, labels, grad_scale, loss_rows, dlogits, loss_out, tail ? (void*)p->dxa : nullptr, st));
+  nrd_tl_mark(p, st, "head");
+  if (tail) p->dp_for = dlogits;       // d(pooled) is ready when nrd_backward_body(dlogits) is called
+  if (labels) { p->labels_last = labels; p->logits_last = logits; p->loss_last = loss_out; p->dlogits_last = dlogits; p->loss_rows_last = loss_rows; }
   return NRD_OK;
 }
 
@@ -2036,12 +2141,31 @@ extern "C" int nrd_backward_head(nrd_plan* p, const float* dlogits, void* stream
     k_xchg_push_head<<<32, 256, 0, st>>>(p->xchg, p->grads, (int)p->off[P_FC1W], (int)p->off[9], C);
     LAUNCH_CHECK();
   }
+  // fused update: the head bucket (fc1 / fc2, 87 % of the parameters) takes its optimizer step here, on the caller's side stream,
+  // under the body backward -- nothing after this point reads these weights or their packed copy before the next forward
+  if (p->upd_lr > 0.f) NRD_TRY(sgd_pack_range(p, p->upd_lr * p->upd_inv_world, p->off[P_FC1W], p->off[9], 2, 0, st));
   return NRD_OK;
 }
 
 extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
   NRD_TRY(nrd_backward_head(p, dlogits, stream));
   return nrd_backward_body(p, dlogits, stream);
+}
+
+// fixed-order reduce of the conv / stem partials into the flat gradient vector (+ exchange push, + fused optimizer step)
+static int launch_body_reduce(nrd_plan* p, cudaStream_t st) {
+  const int B = p->B, C = p->C;
+  nrd_upd_args u = {};
+  if (p->upd_lr > 0.f) {
+    u.params = p->params; u.step_scale = p->upd_lr * p->upd_inv_world;
+    u.w_fwd = p->w_fwd; u.w_dgrad = p->w_dgrad; u.wtc_fwd = p->wtc_fwd; u.wtc_dgrad = p->wtc_dgrad; u.conv1_wp = p->conv1_wp;
+  }
+  NRD_CHECK_CUDA(nrd_launch_pdl(k_body_reduce, dim3((9 * C * C + 28 * C) / 64), dim3(256), 0, st, (p->pdl >> 2) & 1, (const float*)p->wgrad_partial,
+                                p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B), (const float*)p->stem_partial, stem_bwd_blocks(B), C,
+                                p->grads, p->bn_sync, (const float*)p->bn_running, p->bn_sync_contrib, p->xchg,
+                                (int)p->off[P_BNG], (int)p->off[P_RBW], (int)p->off[P_C1W], (int)p->off[P_C1B], u, p->dbg));
+  LAUNCH_CHECK();
+  return NRD_OK;
 }
 
 // everything below the head: d(pooled) -> residual blocks -> stem; fills the body gradients (conv1, block conv, gamma, beta)
@@ -2061,9 +2185,11 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   else k_fc1_dgrad_unpool<bf16><<<((B + 7) / 8) * (K / 256), 256, 0, st>>>(dlogits, p->h1, PRM(P_FC2W), p->w1p, p->idx2, (bf16*)g, B, C);
   LAUNCH_CHECK();
   // residual blocks, last to first; the shared block's grads accumulate over the NB applications
+  nrd_tl_mark(p, st, "fork/dgrad_fc1");
   if (persist) {
     NRD_TRY(nrd_tc_backward_blocks(p, g, gn, st));
     char* t = g; g = gn; gn = t;
+    nrd_tl_mark(p, st, "bwd_blocks");
   }
   for (int k = NB - 1; k >= (persist ? NB : 0); --k) {
     const int first = (k == NB - 1);
@@ -2083,11 +2209,9 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   p->dx0_last = g;
   if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_bwd(p, p->images_last, g, st));
   else NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
-  NRD_CHECK_CUDA(nrd_launch_pdl(k_body_reduce, dim3(9 * C * C / 32 + 28 * C / 32), dim3(256), 0, st, (p->pdl >> 2) & 1, p->wgrad_partial,
-                                p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B), p->stem_partial, stem_bwd_blocks(B), C,
-                                GRD(P_RBW), GRD(P_C1W), GRD(P_C1B), p->bn_sync, p->bn_running, p->bn_sync_contrib, p->xchg, (const float*)p->grads,
-                                (int)p->off[P_BNG], (int)p->off[P_RBW], (int)p->off[P_C1W]));
-  LAUNCH_CHECK();
+  nrd_tl_mark(p, st, "stem_bwd");
+  NRD_TRY(launch_body_reduce(p, st));
+  nrd_tl_mark(p, st, "body_reduce(+sgd)");
   return NRD_OK;
 }
 
@@ -2144,6 +2268,24 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
     case NRD_OP_BLOCK_FWD:
       NRD_REQUIRE(p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_fused_fwd, "fused block forward not available for this plan");
       return nrd_tc_block_fwd(p, k, st);
+    case NRD_OP_HEAD: {
+      NRD_REQUIRE(p->labels_last, "run nrd_forward_loss first");
+      const bool tail = dt == NRD_BF16 && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd && p->fuse_head_tail;
+      return launch_head(p, p->xs + act * p->NB, 0, p->logits_last, p->labels_last, 1.0f, p->loss_rows_last, p->dlogits_last, p->loss_last,
+                         tail ? (void*)p->dxa : nullptr, st);     // rewrites the same values
+    }
+    case NRD_OP_BODY_REDUCE: {
+      // timing only: no exchange (the peers are not running this) and no optimizer step
+      const float lr = p->upd_lr; const int world = p->xchg.world;
+      p->upd_lr = 0.f; p->xchg.world = 0;
+      const int r = launch_body_reduce(p, st);
+      p->upd_lr = lr; p->xchg.world = world;
+      return r;
+    }
+    case NRD_OP_SGD: {
+      NRD_REQUIRE(p->xchg.world == 0, "NRD_OP_SGD would wait for peers that are not running it");
+      return sgd_pack_range(p, 0.f, 0, p->off[9], 0, 0, st);      // step 0: same memory traffic, weights unchanged
+    }
     default: nrd_set_error("nrd_plan_run_op: unknown op %d", op); return NRD_EINVAL;
   }
 }

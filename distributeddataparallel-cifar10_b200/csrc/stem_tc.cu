@@ -12,6 +12,7 @@
 //             window position w (and x0 > 0): the same A tiles as MN-major operand, G_w tiles built beside them, 4 x 8
 //             tcgen05.mma per item into ONE accumulator that lives in TMEM for the whole kernel; tap 27 of every A row is 1.0,
 //             so row 27 of the accumulator is the bias gradient.
+#include <stdlib.h>
 #include "tc_common.cuh"
 
 namespace {
@@ -67,16 +68,30 @@ __device__ __forceinline__ void build_a_tiles(const float* __restrict__ im, uint
   }
 }
 
+// zero the halo of the two padded image slots (rows 0 and 33, columns 0..3 and 36..39 of rows 1..32): 2016 floats, disjoint
+// from the bytes cp.async fills
+__device__ __forceinline__ void zero_image_halos(float* im_gen, int tid, int nthreads) {
+  for (int i = tid; i < 2016; i += nthreads) {
+    int off;
+    if (i < 480) { const int s_ = i / 240, rem = i % 240, ci = rem / 80, rr = (rem % 80) / 40, c = rem % 40; off = s_ * IMG_FLOATS + (ci * 34 + rr * 33) * IMG_ROW + c; }
+    else { const int j = i - 480, s_ = j / 768, rem = j % 768, ci = rem / 256, r = 1 + (rem % 256) / 8, cc = rem % 8; off = s_ * IMG_FLOATS + (ci * 34 + r) * IMG_ROW + (cc < 4 ? cc : 32 + cc); }
+    im_gen[off] = 0.f;
+  }
+}
+
 constexpr int STAGE_F = 4 * TILE_BYTES;                 // forward stage: 4 A tiles
 constexpr int STAGE_B = 8 * TILE_BYTES;                 // backward stage: 4 A tiles + 4 gradient tiles
 
 // ============================================================================================
 // forward.  288 threads: warp 0 MMA, warps 1..4 image loader + im2col builders, warps 5..8 epilogue
 // ============================================================================================
-__global__ void __launch_bounds__(288, 1)
+__global__ void __launch_bounds__(288, 2)
 k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27][32] fp32*/, const float* __restrict__ bias,
-              bf16* __restrict__ x0, uint8_t* __restrict__ idx0, int B, nrd_bn_sync_args bs) {
+              bf16* __restrict__ x0, uint8_t* __restrict__ idx0, int B, nrd_bn_sync_args bs, long long* __restrict__ dbg) {
   extern __shared__ uint8_t smem_raw[];
+  long long* dbgt = (dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? dbg : nullptr;     // stamp rows 16 / 17
+  const int drow = blockIdx.x == 0 ? 16 : 17;
+  if (threadIdx.x == 0) nrd_dbg_stamp(dbgt, drow, 0);
   nrd_bn_sync_apply(bs);
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
@@ -94,7 +109,11 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr uint32_t TMEM_COLS = 256;                              // 2 buffers x 4 window positions x 32 columns
 
-  for (int i = threadIdx.x; i < 2 * IMG_FLOATS; i += blockDim.x) im_gen[i] = 0.f;       // halos stay zero for good
+  // image 0 first (the longest latency of the prologue: DRAM): its interior goes in by cp.async, the halo is zeroed below by
+  // plain stores -- disjoint bytes, so the two need no ordering
+  const int nimg = (B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // images of this CTA
+  if (warp >= 1 && warp <= 4 && nimg > 0) load_image_async(img + (size_t)blockIdx.x * 3072, smem_u32(im_gen), threadIdx.x - 32);
+  zero_image_halos(im_gen, threadIdx.x, blockDim.x);                                    // halos stay zero for good
   if (threadIdx.x < 128) {                                         // W1 -> bf16 K-major rows; row co, chunk ch = taps ch*8..+7
     const int co = threadIdx.x >> 2, ch = threadIdx.x & 3;
     float k[8];
@@ -114,7 +133,7 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_gen;
-  const int nimg = (B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // images of this CTA
+  if (threadIdx.x == 0) nrd_dbg_stamp(dbgt, drow, 1);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -140,10 +159,10 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
     // ===== image loader + im2col builders =====
     const int t = threadIdx.x - 32;
     const uint32_t im_s = smem_u32(im_gen);
-    if (nimg > 0) load_image_async(img + (size_t)blockIdx.x * 3072, im_s, t);
     for (int i = 0; i < nimg; ++i) {
       asm volatile("cp.async.wait_group 0;" ::: "memory");
       asm volatile("bar.sync 2, 128;" ::: "memory");               // image i complete and visible; image i-1's buffer is free
+      if (t == 0 && i == 0) nrd_dbg_stamp(dbgt, drow, 2);
       if (i + 1 < nimg) load_image_async(img + (size_t)(blockIdx.x + (i + 1) * gridDim.x) * 3072, im_s + ((i + 1) & 1) * IMG_FLOATS * 4, t);
       const float* im = im_gen + (i & 1) * IMG_FLOATS;
 #pragma unroll 1
@@ -153,6 +172,7 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
         build_a_tiles(im, a_gen + st * STAGE_F, h, t, 1.0f);
         fence_proxy_async();
         mbar_arrive(afull(st));
+        if (t == 0 && it < 2) nrd_dbg_stamp(dbgt, drow, 3 + it);
       }
     }
   } else {
@@ -163,6 +183,7 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
       const int b = blockIdx.x + i * gridDim.x;
       mbar_wait(tfull(st), (it >> 1) & 1);
       tc_fence_after();
+      if (threadIdx.x == 160 && it < 2) nrd_dbg_stamp(dbgt, drow, 5 + 2 * it);
       float m[32]; uint32_t mi[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) mi[j] = 0;
@@ -189,11 +210,13 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
       }
       reinterpret_cast<uint4*>(idx0 + o)[0] = make_uint4(mi[0], mi[1], mi[2], mi[3]);
       reinterpret_cast<uint4*>(idx0 + o)[1] = make_uint4(mi[4], mi[5], mi[6], mi[7]);
+      if (threadIdx.x == 160 && it < 2) nrd_dbg_stamp(dbgt, drow, 6 + 2 * it);
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+  if (threadIdx.x == 0) nrd_dbg_stamp(dbgt, drow, 9);
 }
 
 // ============================================================================================
@@ -201,8 +224,11 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
 // ============================================================================================
 __global__ void __launch_bounds__(288, 1)
 k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const bf16* __restrict__ x0, const uint8_t* __restrict__ idx0,
-              float* __restrict__ partial /*[grid][28][32]*/, int B) {
+              float* __restrict__ partial /*[grid][28][32]*/, int B, long long* __restrict__ dbg) {
   extern __shared__ uint8_t smem_raw[];
+  long long* dbgt = (dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? dbg : nullptr;     // stamp rows 24 / 25
+  const int drow = blockIdx.x == 0 ? 24 : 25;
+  if (threadIdx.x == 0) nrd_dbg_stamp(dbgt, drow, 0);
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
   uint8_t* a_gen = gen;                                            // 2 stages x (4 A tiles + 4 G tiles)
@@ -216,7 +242,10 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr uint32_t TMEM_COLS = 32;
 
-  for (int i = threadIdx.x; i < 2 * IMG_FLOATS; i += blockDim.x) im_gen[i] = 0.f;
+  // image 0 first (it does not depend on the predecessor kernel): interior by cp.async, halo zeroed by plain stores (disjoint bytes)
+  const int nimg = (B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  if (warp >= 1 && warp <= 4 && nimg > 0) load_image_async(img + (size_t)blockIdx.x * 3072, smem_u32(im_gen), threadIdx.x - 32);
+  zero_image_halos(im_gen, threadIdx.x, blockDim.x);
   for (int i = threadIdx.x; i < 4 * TILE_BYTES / 16; i += blockDim.x)                 // the slack the junk M-groups read: finite
     reinterpret_cast<uint4*>(gen + 2 * STAGE_B)[i] = make_uint4(0, 0, 0, 0);
   fence_proxy_async();
@@ -229,10 +258,11 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (threadIdx.x == 0) nrd_dbg_stamp(dbgt, drow, 1);
   nrd_pdl_launch();
   nrd_pdl_wait();          // set-up above overlaps the predecessor's tail; dL/dx_0 is read below
+  if (threadIdx.x == 0) nrd_dbg_stamp(dbgt, drow, 2);
   const uint32_t tmem_base = *tmem_slot_gen;
-  const int nimg = (B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -258,10 +288,10 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
   } else if (warp <= 4) {
     const int t = threadIdx.x - 32;
     const uint32_t im_s = smem_u32(im_gen);
-    if (nimg > 0) load_image_async(img + (size_t)blockIdx.x * 3072, im_s, t);
     for (int i = 0; i < nimg; ++i) {
       asm volatile("cp.async.wait_group 0;" ::: "memory");
       asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (t == 0 && i == 0) nrd_dbg_stamp(dbgt, drow, 3);
       if (i + 1 < nimg) load_image_async(img + (size_t)(blockIdx.x + (i + 1) * gridDim.x) * 3072, im_s + ((i + 1) & 1) * IMG_FLOATS * 4, t);
       const float* im = im_gen + (i & 1) * IMG_FLOATS;
 #pragma unroll 1
@@ -271,6 +301,7 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
         build_a_tiles(im, a_gen + st * STAGE_B, h, t, 1.0f);       // tap 27 = 1 -> accumulator row 27 = bias gradient
         fence_proxy_async();
         mbar_arrive(afull(st));
+        if (t == 0 && it < 4) nrd_dbg_stamp(dbgt, drow, 4 + it);
       }
     }
   } else {
@@ -307,10 +338,12 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
       }
       fence_proxy_async();
       mbar_arrive(afull(st));
+      if (t == 0 && it < 4) nrd_dbg_stamp(dbgt, drow, 8 + it);
     }
     if (q == 0) {                                                  // TMEM lanes 0..31 = taps
       mbar_wait(done, 0);
       tc_fence_after();
+      if (t == 0) nrd_dbg_stamp(dbgt, drow, 12);
       float v[32];
       tmem_ld32(tmem_base, v);
       if (nimg == 0) {
@@ -327,6 +360,7 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
   tc_fence_before();
   __syncthreads();
   if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+  if (threadIdx.x == 0) nrd_dbg_stamp(dbgt, drow, 13);
 }
 
 constexpr size_t stem_fwd_smem() { return 1024 + 2 * STAGE_F + 2048 + 2 * IMG_FLOATS * 4 + 128 + 128 + 64; }
@@ -340,16 +374,26 @@ int nrd_tc_stem_init(nrd_plan* p) {
   p->tc_stem = 0;
   if (p->dtype != NRD_BF16 || p->C != 32 || !p->tc_ready) return NRD_OK;
   NRD_CHECK_CUDA(cudaFuncSetAttribute(k_stem_tc_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stem_fwd_smem()));
+  // two CTAs per SM (2 x 101 KB of shared memory, 2 x 256 TMEM columns): ask for the full shared-memory carve-out
+  NRD_CHECK_CUDA(cudaFuncSetAttribute(k_stem_tc_fwd, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   NRD_CHECK_CUDA(cudaFuncSetAttribute(k_stem_tc_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stem_bwd_smem()));
   p->tc_stem = 1;
   return NRD_OK;
 }
 
 static int stem_grid(const nrd_plan* p) { return p->B < NRD_NUM_SMS ? p->B : NRD_NUM_SMS; }
+// forward: the kernel is a latency chain per image (load, im2col build, 8 small MMAs, pooled epilogue), so two CTAs share an SM
+// and at B = 256 every CTA has ONE image instead of 108 CTAs having two in a row (NRD_STEM_CTAS_PER_SM=1 restores one per SM)
+static int stem_fwd_grid(const nrd_plan* p) {
+  static int per_sm = 0;
+  if (!per_sm) { const char* e = getenv("NRD_STEM_CTAS_PER_SM"); per_sm = (e && atoi(e) == 1) ? 1 : 2; }
+  const int cap = per_sm * NRD_NUM_SMS;
+  return p->B < cap ? p->B : cap;
+}
 
 int nrd_tc_stem_fwd(nrd_plan* p, const float* images, int training, cudaStream_t st) {
   NRD_REQUIRE(p->tc_stem, "tensor-core stem not available for this plan");
-  k_stem_tc_fwd<<<stem_grid(p), 288, stem_fwd_smem(), st>>>(images, p->conv1_wp, p->params + p->off[1], (bf16*)p->xs, p->idx0, p->B, nrd_bn_sync_of(p, training));
+  k_stem_tc_fwd<<<stem_fwd_grid(p), 288, stem_fwd_smem(), st>>>(images, p->conv1_wp, p->params + p->off[1], (bf16*)p->xs, p->idx0, p->B, nrd_bn_sync_of(p, training), p->dbg);
   nrd_count_launch();
   NRD_CHECK_CUDA(cudaGetLastError());
   return NRD_OK;
@@ -359,7 +403,7 @@ int nrd_tc_stem_fwd(nrd_plan* p, const float* images, int training, cudaStream_t
 int nrd_tc_stem_bwd(nrd_plan* p, const float* images, const void* g0, cudaStream_t st) {
   NRD_REQUIRE(p->tc_stem, "tensor-core stem not available for this plan");
   NRD_CHECK_CUDA(nrd_launch_pdl(k_stem_tc_bwd, dim3(stem_grid(p)), dim3(288), stem_bwd_smem(), st, (p->pdl >> 1) & 1, images, (const bf16*)g0, (const bf16*)p->xs,
-                                (const uint8_t*)p->idx0, p->stem_partial, p->B));
+                                (const uint8_t*)p->idx0, p->stem_partial, p->B, p->dbg));
   nrd_count_launch();
   NRD_CHECK_CUDA(cudaGetLastError());
   return NRD_OK;

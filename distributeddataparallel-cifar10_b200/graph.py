@@ -73,6 +73,13 @@ class TrainStep:
                   "nrd_plan_set_option")
         elif "NRD_RESERVE_SMS" in os.environ:       # single rank: only when asked for (tests of the reduced grid)
             check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ["NRD_RESERVE_SMS"])), "nrd_plan_set_option")
+        # optimizer.step() rides the backward (nrd_plan_set_fused_update): the head bucket is updated on the side stream under
+        # the body backward, the body bucket by the kernel that finishes its gradients -- no optimizer launch at the end
+        self.fused_update = os.environ.get("NRD_FUSED_UPDATE", "1") != "0" and os.environ.get("NRD_DIAG_NO_EXCHANGE") != "1" and (self.world == 1 or self.p2p)
+        if self.fused_update:
+            check(lib.nrd_plan_set_fused_update(self.plan.handle, self.lr, 1.0 / self.world), "nrd_plan_set_fused_update")
+        if os.environ.get("NRD_TIMELINE") == "1":   # measurement aid: event marks behind every main-stream kernel (see timeline())
+            check(lib.nrd_plan_set_option(self.plan.handle, _lib.OPT_TIMELINE, 1), "nrd_plan_set_option")
         self.graphs = [None, None]              # one captured step per input slot (slot 1 on first use)
         self.use_graph = use_graph
         self.kernel_launches = None
@@ -116,6 +123,17 @@ class TrainStep:
         check(lib.nrd_plan_set_exchange(self.plan.handle, rank, W, ptrs), "nrd_plan_set_exchange")
         self._exchange = (ptr, opened)          # kept mapped for the life of the process (captured graphs point into them)
         return True
+
+    def timeline(self):
+        """[(kernel name, microseconds)] of the main stream in the last step, when the step was built with NRD_TIMELINE=1
+        (nrd_plan_timeline: event-record nodes inside the captured graph)."""
+        import ctypes as C
+        torch.cuda.synchronize(self.device)
+        us = (C.c_float * 40)(); names = (C.c_char_p * 40)()
+        n = lib.nrd_plan_timeline(self.plan.handle, 40, us, names)
+        if n < 0:
+            raise _lib.NrdError("nrd_plan_timeline: " + _lib.last_error())
+        return [(names[i].decode(), float(us[i])) for i in range(n)]
 
     def check_status(self, clear: bool = True):
         """Raise if a kernel of this step clamped or saw non-finite BatchNorm sums since the last check (nrd_plan_status:
@@ -180,8 +198,9 @@ class TrainStep:
         if os.environ.get("NRD_DIAG_NO_EXCHANGE") == "1":          # timing diagnosis only: every rank trains alone
             sum_head = sum_body = None
         eng.backward(pl, pl.dlogits, sum_head, sum_body)
-        # fused mean + SGD (K16), then re-derive the packed weight copies
-        check(lib.nrd_sgd_update_pack(pl.handle, self.lr, 1.0 / self.world, st), "nrd_sgd_update_pack")
+        # fused mean + SGD (K16) and the re-derived packed weight copies: inside the backward's own kernels, or one launch here
+        if not self.fused_update:
+            check(lib.nrd_sgd_update_pack(pl.handle, self.lr, 1.0 / self.world, st), "nrd_sgd_update_pack")
 
     def _capture(self, slot: int = 0):
         s = torch.cuda.Stream(device=self.device)

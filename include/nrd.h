@@ -106,6 +106,11 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
  * column-haloed operand copy per image (a tap is a pixel-granular descriptor start) instead of three kx-shifted copies.
  * Measured: forward -1 us; backward +2 us (its weight-gradient MMAs read N groups one pixel apart), hence off there. */
 #define NRD_OPT_ONE_COPY 10
+/* NRD_OPT_TIMELINE (default 0): measurement aid.  An event is recorded behind every kernel of the step's main stream -- an
+ * event-record NODE when the step is being captured -- and nrd_plan_timeline() reads the intervals after a (replayed) step:
+ * the step kernel by kernel in its real context (warm L2, side stream running).  The marks serialise neighbouring kernels
+ * (no programmatic overlap across a mark), so the marked step is a little slower than the unmarked one. */
+#define NRD_OPT_TIMELINE 11
 int nrd_plan_set_option(nrd_plan* plan, int option, int value);
 /* Sticky status of the plan's kernels.  The persistent kernels add their per-CTA BatchNorm sums (model/resnet.py:35 and its
  * backward) as 64-bit fixed point; a contribution outside the representable range (forward |sum| >= 2^22, backward >= 2^10)
@@ -140,7 +145,8 @@ int nrd_plan_set_exchange(nrd_plan* plan, int rank, int world, void* const* bufs
 /* debugging/tests: device pointer to a saved tensor.  what: 0 = x_k (k in 0..NB), 1 = y_k,
  * 2 = dy scratch, 3 = pooled, 4 = saved BN mean|invstd of block k ([2C] fp32), 5 = dx scratch (ping),
  * 6 = dx scratch (pong), 7 = wgrad per-CTA partials [ctas][9][C][C], 8 = BN-stat per-CTA partials [ctas][2][C],
- * 9 = stem weight-gradient per-CTA partials [ctas][28][C] (27 taps + bias), 10 = h1 = relu(fc1) [B,32] fp32 */
+ * 9 = stem weight-gradient per-CTA partials [ctas][28][C] (27 taps + bias), 10 = h1 = relu(fc1) [B,32] fp32,
+ * 11 = in-kernel stamps of the small kernels (NRD_OPT_TRACE): [64 rows][16][clock64, globaltimer] int64 */
 int nrd_plan_tensor(nrd_plan* plan, int what, int k, void** ptr, size_t* bytes);
 
 /* Re-derive the packed weight copies (tap-major / transposed / bf16 / NHWC-ordered fc1) from the
@@ -189,6 +195,13 @@ int nrd_backward_body(nrd_plan* plan, const float* dlogits, void* stream);
 int nrd_sgd_update(float* params, const float* grads, size_t n, float lr, float inv_world, void* stream);
 /* nrd_sgd_update_pack = nrd_sgd_update over the plan's whole flat vector + nrd_pack_weights, one launch. */
 int nrd_sgd_update_pack(nrd_plan* plan, float lr, float inv_world, void* stream);
+/* optimizer.step() (main.py:39) riding the backward: after nrd_plan_set_fused_update(plan, lr, inv_world) with lr > 0,
+ * nrd_backward_head() ends with the update of the head bucket (fc1/fc2: on the caller's side stream, under the body backward)
+ * and nrd_backward_body()'s last kernel -- the one that finishes the body gradients -- applies p <- p - lr * inv_world * g to the
+ * body bucket (after summing the world's slots when the peer-memory exchange is on) and re-derives the packed weight copies, so
+ * NO nrd_sgd_update_pack() follows (calling it as well would step twice).  The flat gradient vector still holds the step's
+ * gradients (the world's sum under the exchange).  lr <= 0 turns it off (default). */
+int nrd_plan_set_fused_update(nrd_plan* plan, float lr, float inv_world);
 int nrd_train_step(nrd_plan* plan, const float* images, const int64_t* labels, float lr,
                    float* logits, float* loss_out, void* stream);
 
@@ -254,7 +267,14 @@ int nrd_maxpool_bwd(const void* gpooled, const uint8_t* idx, void* gx, int B, in
                               NOTE: applies the running-stat EMA and nbt += 1 like a real forward */
 #define NRD_OP_FWD_BLOCKS 8 /* all residual blocks' forward in the persistent kernel (same side effects as a real forward) */
 #define NRD_OP_BWD_BLOCKS 9 /* all residual blocks' backward in the persistent kernel (overwrites the block gradients) */
+#define NRD_OP_HEAD 10       /* pool + fc1 + fc2 + loss + dlogits + dL/d(pooled), the one head launch (model/resnet.py:18-21, main.py:35);
+                                needs a preceding nrd_forward_loss (its labels and outputs are reused) */
+#define NRD_OP_BODY_REDUCE 11 /* fixed-order reduce of the body-gradient partials (no exchange, no optimizer step) */
+#define NRD_OP_SGD 12        /* the optimizer kernel over the whole flat vector with step 0 (same traffic, weights unchanged) */
 unsigned long long nrd_launch_count(void);
+/* us[i] = microseconds the i-th kernel of the main stream took in the last step run with NRD_OPT_TIMELINE on (synchronise the
+ * device first), names[i] = a static string naming it; returns the number of entries (< 0: error).  HOST pointers. */
+int nrd_plan_timeline(nrd_plan* plan, int max_n, float* us, const char** names);
 int nrd_plan_run_op(nrd_plan* plan, int op, int k, void* stream);
 
 #ifdef __cplusplus
