@@ -6,6 +6,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libnrd.so")
 
 NRD_F32, NRD_BF16 = 0, 1
+LOSS_RING = 8          # NRD_LOSS_RING (include/nrd.h)
 CONV_CUDA_CORE, CONV_TCGEN05, CONV_TCGEN05_UNFUSED = 0, 1, 2
 OPT_FUSE_BN_BWD, OPT_PERSIST_FWD, OPT_TRACE, OPT_PERSIST_BWD, OPT_TC_STEM, OPT_RESERVE_SMS, OPT_PDL, OPT_HEAD_TAIL, OPT_FUSE_POOL, OPT_FUSE_STEM, OPT_ONE_COPY, OPT_TIMELINE = range(12)
 
@@ -54,6 +55,7 @@ _PROTOS = {
     "nrd_sgd_update": (i32, [vp, vp, sz, f32, f32, vp]),
     "nrd_sgd_update_pack": (i32, [vp, f32, f32, vp]),
     "nrd_plan_set_fused_update": (i32, [vp, f32, f32]),
+    "nrd_plan_set_loss_mirror": (i32, [vp, vp, vp]),
     "nrd_train_step": (i32, [vp, vp, vp, f32, vp, vp, vp]),
     "nrd_gen_batch": (i32, [vp, vp, i32, u64, u32, u64, vp]),
     "nrd_pack_conv_weight": (i32, [vp, i32, vp, vp, vp]),

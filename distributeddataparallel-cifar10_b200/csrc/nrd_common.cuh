@@ -193,6 +193,7 @@ struct nrd_plan {
   const char* tl_name[40];
   float upd_lr, upd_inv_world; // nrd_plan_set_fused_update: the optimizer step rides nrd_backward_head / _body (upd_lr > 0)
   unsigned long long* head_ctr; // per-row-group arrival counters of the fused head kernel
+  float* loss_mirror; unsigned int* seq_mirror;   // pinned host words the head kernel also writes the loss / its sequence number to
   const int64_t* labels_last;   // labels of the last nrd_forward_loss (nrd_plan_run_op replays the head with them)
   float *logits_last, *loss_last, *dlogits_last, *loss_rows_last;
   int head_ctas;          // how many CTAs of the head kernel fit on the device at once (cooperative launch)
@@ -351,6 +352,7 @@ static __device__ __forceinline__ void nrd_acc_wait2(const unsigned long long* w
 #define NRD_GBAR_PERSIST_BWD 3
 #define NRD_GBAR_HEAD_COUNTER 16       // word of the gbar block used as the head kernels' arrival counter
 #define NRD_GBAR_STATUS 24             // word of the gbar block that holds the sticky status flags
+#define NRD_GBAR_LOSS_SEQ 25           // ... the number of losses written to the host mirror so far (nrd_plan_set_loss_mirror)
 
 // in-kernel stamps (profiling aid, NRD_OPT_TRACE): dbg = NULL turns them off.  Row `row` of the buffer = 16 x {clock64, globaltimer}.
 static __device__ __forceinline__ void nrd_dbg_stamp(long long* dbg, int row, int slot) {

@@ -1082,7 +1082,8 @@ k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restric
              float* __restrict__ part, float* __restrict__ h1, float* __restrict__ logits, int B, int C,
              const int64_t* __restrict__ labels, float gscale, float* __restrict__ loss_rows, float* __restrict__ dlogits,
              float* __restrict__ loss, unsigned long long* __restrict__ rg_ctr, unsigned int* __restrict__ counter,
-             T* __restrict__ dp, long long* __restrict__ dbg) {
+             T* __restrict__ dp, long long* __restrict__ dbg, volatile float* loss_mirror, volatile unsigned int* seq_mirror,
+             unsigned int* __restrict__ seq_dev) {
   extern __shared__ __align__(16) float hsm[];
   float* ws = hsm;                    // [128 k][32 j]      fc1 weight slice, k-major (forward partial product)
   float* wsT = ws + 128 * 32;         // [32 j][132]        the same slice transposed (backward slice), rows padded
@@ -1291,7 +1292,19 @@ k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restric
         if (tid < 256) { for (int bb = tid; bb < B; bb += 256) acc += (double)__ldcg(loss_rows + bb); red[tid] = acc; }
         __syncthreads();
         for (int o = 128; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
-        if (tid == 0) { *loss = (float)(red[0] / B); *counter = 0u; }
+        if (tid == 0) {
+          const float lv = (float)(red[0] / B);
+          *loss = lv; *counter = 0u;
+          if (loss_mirror) {
+            // main.py:41 `loss.item()` without a copy or a sync in the stream: the loss lands in (mapped, pinned) HOST memory by
+            // itself, then the step's sequence number; the host reads the value once it sees the number (nrd_plan_set_loss_mirror)
+            const unsigned int sq = *seq_dev + 1u;
+            *seq_dev = sq;
+            loss_mirror[(sq - 1u) % NRD_LOSS_RING] = lv;
+            __threadfence_system();
+            *seq_mirror = sq;
+          }
+        }
       }
     }
   }
@@ -1739,11 +1752,12 @@ static int launch_head(nrd_plan* p, const void* x_last, int pooled_in, float* lo
   int gx = p->head_ctas / KS; if (gx > nrg) gx = nrg;
   const float* w1t = p->w1p; const float* b1 = p->params + p->off[6]; const float* w2 = p->params + p->off[7]; const float* b2 = p->params + p->off[8];
   unsigned int* counter = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_HEAD_COUNTER);
+  unsigned int* seq_dev = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_LOSS_SEQ);
   void* pooled = p->pooled; uint8_t* idx2 = p->idx2; float* part = p->fc1_part; float* h1 = p->h1; unsigned long long* ctr = p->head_ctr;
   int Bv = B, Cv = C;
   void* args[] = {(void*)&x_last, (void*)&pooled, (void*)&idx2, (void*)&pooled_in, (void*)&w1t, (void*)&b1, (void*)&w2, (void*)&b2, (void*)&part, (void*)&h1,
                   (void*)&logits, (void*)&Bv, (void*)&Cv, (void*)&labels, (void*)&gscale, (void*)&loss_rows, (void*)&dlogits, (void*)&loss, (void*)&ctr,
-                  (void*)&counter, (void*)&dp, (void*)&p->dbg};
+                  (void*)&counter, (void*)&dp, (void*)&p->dbg, (void*)&p->loss_mirror, (void*)&p->seq_mirror, (void*)&seq_dev};
   const void* fn = p->dtype == NRD_F32 ? (const void*)k_head_fused<float> : (const void*)k_head_fused<bf16>;
   NRD_CHECK_CUDA(cudaLaunchCooperativeKernel(fn, dim3(gx, KS), dim3(NRD_HEAD_THREADS), args, head_smem_bytes(), st));
   nrd_count_launch();
@@ -2053,6 +2067,23 @@ extern "C" int nrd_plan_timeline(nrd_plan* p, int max_n, float* us, const char**
     us[n] = ms * 1e3f; names[n] = p->tl_name[i + 1];
   }
   return n;
+}
+
+extern "C" int nrd_plan_set_loss_mirror(nrd_plan* p, float* host_loss, unsigned int* host_seq) {
+  NRD_REQUIRE(p, "null plan");
+  NRD_REQUIRE((host_loss == nullptr) == (host_seq == nullptr), "nrd_plan_set_loss_mirror: give both pointers or neither");
+  if (host_loss) {
+    NRD_CHECK_CUDA(cudaSetDevice(p->device));
+    // must be memory the device can write: pinned host memory is mapped at its own address under unified addressing
+    cudaPointerAttributes a;
+    NRD_CHECK_CUDA(cudaPointerGetAttributes(&a, host_loss));
+    NRD_REQUIRE(a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged || a.type == cudaMemoryTypeDevice,
+                "nrd_plan_set_loss_mirror: the mirror must be pinned (page-locked) host memory");
+    NRD_CHECK_CUDA(cudaMemset(p->gbar + NRD_GBAR_LOSS_SEQ, 0, sizeof(unsigned long long)));
+    *host_seq = 0u;
+  }
+  p->loss_mirror = host_loss; p->seq_mirror = host_seq;
+  return NRD_OK;
 }
 
 extern "C" int nrd_plan_set_fused_update(nrd_plan* p, float lr, float inv_world) {

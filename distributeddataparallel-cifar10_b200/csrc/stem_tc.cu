@@ -246,8 +246,8 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
   const int nimg = (B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   if (warp >= 1 && warp <= 4 && nimg > 0) load_image_async(img + (size_t)blockIdx.x * 3072, smem_u32(im_gen), threadIdx.x - 32);
   zero_image_halos(im_gen, threadIdx.x, blockDim.x);
-  for (int i = threadIdx.x; i < 4 * TILE_BYTES / 16; i += blockDim.x)                 // the slack the junk M-groups read: finite
-    reinterpret_cast<uint4*>(gen + 2 * STAGE_B)[i] = make_uint4(0, 0, 0, 0);
+  // (the slack behind the last stage, which the junk M-groups 1..3 of the last tiles read, stays uninitialised: a junk row of A
+  // only ever reaches the same junk row of the accumulator, which nobody reads)
   fence_proxy_async();
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < 2; ++s) { mbar_init(afull(s), 256); mbar_init(aempty(s), 1); }
@@ -306,15 +306,21 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
     }
   } else {
     // ===== gradient tiles: G_w[pixel][co] = g0 where (argmax == w and x0 > 0) else 0 =====
+    // the next half image's g0 / x0 / arg-max rows are fetched while the current one is turned into tiles (L2 latency off the
+    // per-half critical path)
     const int t = threadIdx.x - 160, q = warp & 3;
-    for (int it = 0; it < 2 * nimg; ++it) {
-      const int st = it & 1, i = it >> 1, h = it & 1;
-      const int b = blockIdx.x + i * gridDim.x;
+    uint4 gv[4], xv[4], iv[2], gn[4], xn[4], in_[2];
+    auto fetch = [&](int it, uint4 (&g)[4], uint4 (&x)[4], uint4 (&ii)[2]) {
+      const int i = it >> 1, h = it & 1, b = blockIdx.x + i * gridDim.x;
       const size_t o = ((size_t)b * 256 + h * 128 + t) * SC;
-      uint4 gv[4], xv[4], iv[2];
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) { gv[ch] = reinterpret_cast<const uint4*>(g0 + o)[ch]; xv[ch] = reinterpret_cast<const uint4*>(x0 + o)[ch]; }
-      iv[0] = reinterpret_cast<const uint4*>(idx0 + o)[0]; iv[1] = reinterpret_cast<const uint4*>(idx0 + o)[1];
+      for (int ch = 0; ch < 4; ++ch) { g[ch] = reinterpret_cast<const uint4*>(g0 + o)[ch]; x[ch] = reinterpret_cast<const uint4*>(x0 + o)[ch]; }
+      ii[0] = reinterpret_cast<const uint4*>(idx0 + o)[0]; ii[1] = reinterpret_cast<const uint4*>(idx0 + o)[1];
+    };
+    if (nimg > 0) fetch(0, gv, xv, iv);
+    for (int it = 0; it < 2 * nimg; ++it) {
+      const int st = it & 1;
+      if (it + 1 < 2 * nimg) fetch(it + 1, gn, xn, in_);
       mbar_wait(aempty(st), ((it >> 1) & 1) ^ 1);
       const uint32_t* gw = reinterpret_cast<const uint32_t*>(gv); const uint32_t* xw = reinterpret_cast<const uint32_t*>(xv);
       const uint8_t* ib = reinterpret_cast<const uint8_t*>(iv);
@@ -339,6 +345,9 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
       fence_proxy_async();
       mbar_arrive(afull(st));
       if (t == 0 && it < 4) nrd_dbg_stamp(dbgt, drow, 8 + it);
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) { gv[ch] = gn[ch]; xv[ch] = xn[ch]; }
+      iv[0] = in_[0]; iv[1] = in_[1];
     }
     if (q == 0) {                                                  // TMEM lanes 0..31 = taps
       mbar_wait(done, 0);

@@ -78,6 +78,17 @@ class TrainStep:
         self.fused_update = os.environ.get("NRD_FUSED_UPDATE", "1") != "0" and os.environ.get("NRD_DIAG_NO_EXCHANGE") != "1" and (self.world == 1 or self.p2p)
         if self.fused_update:
             check(lib.nrd_plan_set_fused_update(self.plan.handle, self.lr, 1.0 / self.world), "nrd_plan_set_fused_update")
+        # main.py:41 `loss.item()`: the head kernel also writes every step's loss into a small ring in pinned host memory and then
+        # the step count (nrd_plan_set_loss_mirror), so reading it needs no copy node and no stream synchronisation
+        self._mirror = torch.zeros(_lib.LOSS_RING + 2, dtype=torch.float32).pin_memory()      # ring | seq (as int32 view)
+        self._mirror_seq = self._mirror[_lib.LOSS_RING:].view(torch.int32)
+        self._mirror_np = self._mirror.numpy(); self._mirror_seq_np = self._mirror_seq.numpy()
+        self.steps_run = 0
+        if os.environ.get("NRD_LOSS_MIRROR", "1") != "0":
+            check(lib.nrd_plan_set_loss_mirror(self.plan.handle, self._mirror.data_ptr(), self._mirror_seq.data_ptr()), "nrd_plan_set_loss_mirror")
+            self.loss_mirror = True
+        else:
+            self.loss_mirror = False
         if os.environ.get("NRD_TIMELINE") == "1":   # measurement aid: event marks behind every main-stream kernel (see timeline())
             check(lib.nrd_plan_set_option(self.plan.handle, _lib.OPT_TIMELINE, 1), "nrd_plan_set_option")
         self.graphs = [None, None]              # one captured step per input slot (slot 1 on first use)
@@ -221,6 +232,8 @@ class TrainStep:
             torch.mul(keep[1], self.slot_scale, out=self.eng.xchg[:2 * self.eng.C])
         check(lib.nrd_pack_weights(self.plan.handle, _stream_ptr()), "nrd_pack_weights")
         torch.cuda.synchronize(self.device)
+        if self.loss_mirror:
+            self.steps_run = int(self._mirror_seq_np[0])      # the warm-up steps above were counted by the device as well
 
     def __call__(self, imgs: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         self.imgs.copy_(imgs, non_blocking=True)
@@ -240,12 +253,29 @@ class TrainStep:
             self._body(slot)
         self.eng.weights_epoch += 1
         self.plan.packed_version = self.eng._weights_version()
+        self.steps_run += 1
         return self.loss
+
+    def host_loss(self, n: int, spin_s: float = 30.0) -> float:
+        """The loss of the n-th step run since this TrainStep was (re)captured (1-based), read from the pinned-host ring the head
+        kernel writes: no copy, no stream synchronisation; spins (briefly) only if that step's head kernel has not run yet.
+        Valid while fewer than LOSS_RING further steps have been launched."""
+        import time
+        seq = self._mirror_seq_np
+        if int(seq[0]) < n:
+            t0 = time.perf_counter()
+            while int(seq[0]) < n:
+                if time.perf_counter() - t0 > spin_s:
+                    torch.cuda.synchronize(self.device)
+                    if int(seq[0]) < n:
+                        raise RuntimeError(f"loss of step {n} never reached the host mirror (count {int(seq[0])})")
+        return float(self._mirror_np[(n - 1) % _lib.LOSS_RING])
 
     def iterate(self, loader, lookahead: int = 0):
         """One pass over `loader` (HOST batches `(imgs, labels)`; pinned memory makes the copies asynchronous), one step per
-        batch: the loop of main.py:31-41.  Yields the step's loss as a pinned HOST scalar tensor, already synchronised (the
-        reference's per-step `loss.item()`, main.py:41), valid until the next iteration.  Order per step: launch the step
+        batch: the loop of main.py:31-41.  Yields the step's loss as a host value (the reference's per-step `loss.item()`,
+        main.py:41): a Python float read from the pinned-host ring the head kernel writes (no copy node, no stream
+        synchronisation), or, with NRD_LOSS_MIRROR=0, a pinned host scalar tensor filled by a D2H copy.  Order per step: launch the step
         on the slot that is ready, THEN fetch the next host batch and start its copy into the other slot on a copy stream
         -- loader work and PCIe traffic run beside the step's kernels instead of in front of them.
 
@@ -303,22 +333,28 @@ class TrainStep:
             main.wait_event(self._ready[slot])
             self.run(slot)
             self._consumed[slot].record(main)
-            self._h_loss[k].copy_(self.loss, non_blocking=True)
-            self._loss_done[k].record(main)
+            if self.loss_mirror:
+                tok = self.steps_run                                  # this step's number in the device's count
+                fetch = self.host_loss
+            else:
+                self._h_loss[k].copy_(self.loss, non_blocking=True)
+                self._loss_done[k].record(main)
+                tok = k
+
+                def fetch(j):
+                    self._loss_done[j].synchronize()
+                    return self._h_loss[j]
             nxt = next(it, None)
             if nxt is not None:
                 issue(slot ^ 1, nxt)
             if lookahead and nxt is not None:
                 if pending is not None:
-                    self._loss_done[pending].synchronize()
-                    yield self._h_loss[pending]
-                pending = k
+                    yield fetch(pending)
+                pending = tok
             else:
                 if pending is not None:
-                    self._loss_done[pending].synchronize()
-                    yield self._h_loss[pending]
+                    yield fetch(pending)
                     pending = None
-                self._loss_done[k].synchronize()
-                yield self._h_loss[k]
+                yield fetch(tok)
             slot ^= 1
             k ^= 1

@@ -202,6 +202,14 @@ int nrd_sgd_update_pack(nrd_plan* plan, float lr, float inv_world, void* stream)
  * NO nrd_sgd_update_pack() follows (calling it as well would step twice).  The flat gradient vector still holds the step's
  * gradients (the world's sum under the exchange).  lr <= 0 turns it off (default). */
 int nrd_plan_set_fused_update(nrd_plan* plan, float lr, float inv_world);
+/* `loss.item()` (main.py:41) without a copy node or a stream synchronisation: nrd_forward_loss() additionally writes the mean
+ * loss of its n-th call (n = 1, 2, ...) to host_loss[(n - 1) % NRD_LOSS_RING] and then, behind a system-scope fence, n to
+ * *host_seq.  Both must be page-locked HOST memory (device-accessible at the same address under unified addressing, e.g.
+ * cudaHostAlloc / torch pin_memory; host_loss: NRD_LOSS_RING floats); the host polls *host_seq (volatile) and reads the ring
+ * slot of the step it waits for once the count has reached it -- the ring keeps a value valid for NRD_LOSS_RING - 1 further
+ * steps.  NULL, NULL turns it off (default). */
+#define NRD_LOSS_RING 8
+int nrd_plan_set_loss_mirror(nrd_plan* plan, float* host_loss, unsigned int* host_seq);
 int nrd_train_step(nrd_plan* plan, const float* images, const int64_t* labels, float lr,
                    float* logits, float* loss_out, void* stream);
 
