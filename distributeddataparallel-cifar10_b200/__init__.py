@@ -6,6 +6,6 @@ from .model.resnet import NetResDeep, ResBlock  # noqa: F401
 from .nn import CrossEntropyLoss  # noqa: F401
 from .optim import SGD  # noqa: F401
 from .parallel import DistributedDataParallel  # noqa: F401
-from .data import SyntheticCifar10Loader, DevicePrefetcher  # noqa: F401
+from .data import SyntheticCifar10Loader, DevicePrefetcher, Cifar10DeviceLoader  # noqa: F401
 from .graph import TrainStep  # noqa: F401
 from . import main, main_no_ddp  # noqa: F401,E402

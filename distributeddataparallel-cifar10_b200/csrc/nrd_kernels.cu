@@ -1380,6 +1380,28 @@ __global__ void k_sgd_pack(float* __restrict__ p, float* g, float step_scale, in
 }
 
 // ------------------------------------------------------------------------------------------
+// Real input path (main.py:53-61): the uint8 HWC dataset stays resident in HBM; a batch is a gather by sample index fused with
+// ToTensor (u8 -> [0,1] fp32, HWC -> CHW) and Normalize((x - mean[c]) / std[c]) -- 4x fewer bytes read than an fp32 dataset,
+// one pass.  Thread = one pixel of one sample: reads its 3 bytes, writes one float into each of the 3 channel planes (the
+// warp's 32 pixels are 128 contiguous bytes per plane).  The arithmetic is torchvision's, in its order:
+// (float(u8) / 255 - mean) / std with fp32 division, so the batch equals the reference DataLoader's bit for bit.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_gather_normalize(const uint8_t* __restrict__ data /*[N,32,32,3]*/, const int64_t* __restrict__ labels_all,
+                                                          const int64_t* __restrict__ idx /*[B]*/, int B, long long N, float m0, float m1, float m2,
+                                                          float s0, float s1, float s2, float* __restrict__ out /*[B,3,32,32]*/,
+                                                          int64_t* __restrict__ labels_out) {
+  const int b = blockIdx.x >> 2, p = (blockIdx.x & 3) * 256 + threadIdx.x;       // 4 CTAs per sample, 1024 pixels
+  if (b >= B) return;
+  long long src = idx[b];
+  if (src < 0 || src >= N) src = 0;                    // never read outside the dataset; the host validates the index list
+  const uint8_t* px = data + ((size_t)src * 1024 + p) * 3;
+  const float r = (float)px[0], g = (float)px[1], bl = (float)px[2];
+  float* o = out + (size_t)b * 3072 + p;
+  o[0] = (r / 255.f - m0) / s0; o[1024] = (g / 255.f - m1) / s1; o[2048] = (bl / 255.f - m2) / s2;
+  if (p == 0 && labels_out) labels_out[b] = labels_all[src];
+}
+
+// ------------------------------------------------------------------------------------------
 // synthetic CIFAR-shaped batch: Philox-4x32-10, counter = (element/4, rank, step lo, step hi)
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
@@ -1717,6 +1739,16 @@ extern "C" int nrd_sgd_update(float* params, const float* grads, size_t n, float
   NRD_REQUIRE(params && grads, "nrd_sgd_update: null pointer");
   if (n == 0) return NRD_OK;
   k_sgd<<<grid_for(n, 256, NRD_NUM_SMS * 2), 256, 0, (cudaStream_t)stream>>>(params, grads, n, lr * inv_world);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_gather_normalize(const uint8_t* data_u8_nhwc, const int64_t* labels_all, long long n_samples, const int64_t* indices, int B,
+                                    const float mean[3], const float std[3], float* images, int64_t* labels, void* stream) {
+  NRD_REQUIRE(data_u8_nhwc && labels_all && indices && images && mean && std && B > 0 && n_samples > 0, "nrd_gather_normalize: bad arguments");
+  NRD_REQUIRE(std[0] != 0.f && std[1] != 0.f && std[2] != 0.f, "nrd_gather_normalize: zero std");
+  k_gather_normalize<<<B * 4, 256, 0, (cudaStream_t)stream>>>(data_u8_nhwc, labels_all, indices, B, n_samples, mean[0], mean[1], mean[2], std[0], std[1], std[2],
+                                                              images, labels);
   LAUNCH_CHECK();
   return NRD_OK;
 }

@@ -45,6 +45,7 @@ class TrainStep:
             check(lib.nrd_plan_set_conv_impl(self.plan.handle, self.eng.conv_impl), "nrd_plan_set_conv_impl")
         self.eng.ensure_packed(self.plan)
         self._exchange = None
+        self._tails = {}                        # TrainSteps for batches of other sizes (the ragged tail of drop_last=False)
         # DDP on the graph path:
         # (1) gradients are exchanged over NVLink peer memory by our own kernels (nrd_plan_set_exchange: the producing
         #     kernels store into every rank's buffer, the optimizer kernel sums the world's slots in rank order; the head
@@ -160,6 +161,8 @@ class TrainStep:
         """Drop the captured graphs and release the peer-memory exchange buffers (ours and the mappings of the peers').
         Every rank must call it at the same point (a peer may still be storing into our buffer until its last step is done)."""
         self.graphs = [None, None]
+        for t in getattr(self, "_tails", {}).values():
+            t.close()
         ex, self._exchange = getattr(self, "_exchange", None), None
         if ex is not None:
             torch.cuda.synchronize(self.device)
@@ -281,7 +284,12 @@ class TrainStep:
 
         `lookahead=1`: step t's loss is handed out after step t+1 has been LAUNCHED (same values, same order, one step
         later), so the GPU never waits for the host between steps; the price is that breaking out of the loop at step t
-        leaves step t+1 applied as well."""
+        leaves step t+1 applied as well.
+
+        A batch of another size -- the ragged last batch of the reference's `drop_last=False` loader (main.py:61: 10 samples at
+        8 ranks) -- runs through a second TrainStep of that size on the same model (built on first use, kept), after the
+        steps in flight have been handed out; every rank must see it at the same point of the epoch, which
+        DistributedSampler's equal-length index lists guarantee."""
         dev = self.device
         main = torch.cuda.current_stream(dev)
         if self.use_graph and self.graphs[1] is None:
@@ -297,11 +305,24 @@ class TrainStep:
                 e.record(main)
         copy = self._copy_stream
 
+        def fits(batch):
+            imgs = batch[0]
+            if imgs.dim() != 4 or tuple(imgs.shape[1:]) != (3, 32, 32) or imgs.shape[0] < 1:
+                raise ValueError(f"expected batches of shape [b,3,32,32], got {tuple(imgs.shape)}")
+            return imgs.shape[0] == self.B
+
+        def run_other_size(batch):
+            """a batch of another size (the ragged tail): its own TrainStep on the same model; returns the loss on the host"""
+            imgs, labels = batch
+            tail = self._tails.get(imgs.shape[0])
+            if tail is None:
+                tail = self._tails[imgs.shape[0]] = TrainStep(self.ddp if self.ddp is not None else self.module, imgs.shape[0], lr=self.lr,
+                                                              use_graph=self.use_graph)
+            loss = tail(imgs.to(dev, non_blocking=True), labels.to(dev, non_blocking=True))
+            return tail.host_loss(tail.steps_run) if tail.loss_mirror else float(loss)
+
         def issue(slot, batch):
             imgs, labels = batch
-            if tuple(imgs.shape) != tuple(self.inputs[slot][0].shape):
-                raise ValueError(f"TrainStep was built for batches of {tuple(self.inputs[slot][0].shape)}, got {tuple(imgs.shape)} "
-                                 "(use drop_last=True or a second TrainStep for the ragged tail)")
             if imgs.is_cuda or labels.is_cuda:
                 # device-resident batch (e.g. SyntheticCifar10Loader): its producer runs on the current stream, so the copy
                 # goes there too (nothing to overlap: there is no PCIe transfer)
@@ -327,8 +348,13 @@ class TrainStep:
         if nxt is None:
             return
         slot = 0
-        issue(slot, nxt)
         k, pending = 0, None
+        while nxt is not None and not fits(nxt):            # (a loader that starts with an odd-sized batch)
+            yield run_other_size(nxt)
+            nxt = next(it, None)
+        if nxt is None:
+            return
+        issue(slot, nxt)
         while nxt is not None:
             main.wait_event(self._ready[slot])
             self.run(slot)
@@ -345,9 +371,22 @@ class TrainStep:
                     self._loss_done[j].synchronize()
                     return self._h_loss[j]
             nxt = next(it, None)
-            if nxt is not None:
+            odd = []
+            while nxt is not None and not fits(nxt):        # ragged batch(es): after the steps in flight
+                odd.append(nxt)
+                nxt = next(it, None)
+            if nxt is not None and not odd:
                 issue(slot ^ 1, nxt)
-            if lookahead and nxt is not None:
+            if odd:
+                if pending is not None:
+                    yield fetch(pending)
+                    pending = None
+                yield fetch(tok)
+                for ob in odd:
+                    yield run_other_size(ob)
+                if nxt is not None:
+                    issue(slot ^ 1, nxt)
+            elif lookahead and nxt is not None:
                 if pending is not None:
                     yield fetch(pending)
                 pending = tok

@@ -70,13 +70,33 @@ def train_loop(model, train_loader, rank, epochs=99, lr=1e-2, save=True, log=pri
     return history
 
 
-def main(rank, world_size, epochs=99, batch_size=32, steps_per_epoch=196, dtype=None, save=True):
+def make_loader(rank, world_size, batch_size=32, steps_per_epoch=196, dataset=None):
+    """main.py:53-61.  dataset=None: the on-device synthetic generator (no files on the box).  "cifar10": the reference's own
+    input path -- torchvision's files under data_path, resident in HBM as uint8, DistributedSampler order, ToTensor+Normalize
+    fused into the batch gather (raises like the reference's download=False when the files are missing).  "synthetic-uint8[:N]":
+    the same path over a generated uint8 dataset of N images.  Or a (uint8 [N,32,32,3], labels [N]) pair."""
+    from .data import Cifar10DeviceLoader, load_cifar10_python_batches, synthetic_cifar10_uint8
+    if dataset is None:
+        return SyntheticCifar10Loader(batch_size=batch_size, steps_per_epoch=steps_per_epoch, device=f"cuda:{rank}", rank=rank)
+    if isinstance(dataset, str):
+        if dataset == "cifar10":
+            data, labels = load_cifar10_python_batches(data_path)                  # main.py:54 (download=False)
+        elif dataset.startswith("synthetic-uint8"):
+            n = int(dataset.split(":")[1]) if ":" in dataset else 50000
+            data, labels = synthetic_cifar10_uint8(n)
+        else:
+            raise ValueError(f"unknown dataset {dataset!r}")
+    else:
+        data, labels = dataset
+    return Cifar10DeviceLoader(data, labels, batch_size=batch_size, num_replicas=world_size, rank=rank, device=f"cuda:{rank}")   # main.py:60-61
+
+
+def main(rank, world_size, epochs=99, batch_size=32, steps_per_epoch=196, dtype=None, save=True, dataset=None, graph=False):
     setup(rank, world_size)
-    train_loader = SyntheticCifar10Loader(batch_size=batch_size, steps_per_epoch=steps_per_epoch,
-                                          device=f"cuda:{rank}", rank=rank)     # replaces main.py:53-61
+    train_loader = make_loader(rank, world_size, batch_size, steps_per_epoch, dataset)   # main.py:53-61
     model = NetResDeep(dtype=dtype).to(rank)               # main.py:62
     model = DDP(model, device_ids=[rank], output_device=rank)   # main.py:63
-    train_loop(model, train_loader, rank, epochs=epochs, save=save)
+    train_loop(model, train_loader, rank, epochs=epochs, save=save, graph=graph)
     destroy_process_group()                                # main.py:65
 
 

@@ -219,6 +219,16 @@ int nrd_train_step(nrd_plan* plan, const float* images, const int64_t* labels, f
 int nrd_gen_batch(float* images, int64_t* labels, int B, uint64_t seed, uint32_t rank, uint64_t step,
                   void* stream);
 
+/* ---- the reference's real input path on the device (main.py:53-61; main_no_ddp.py:22-34) ---------
+ * The CIFAR-10 training set as torchvision holds it -- uint8 [N,32,32,3] (HWC) plus int64 labels [N] -- stays resident in HBM.
+ * One call builds a batch: gather by sample index (the DistributedSampler order of main.py:60, computed on the host), ToTensor
+ * (u8 -> [0,1] fp32, HWC -> CHW) and Normalize(mean, std) (main.py:55-57) in one pass, into the fp32 NCHW batch nrd_forward
+ * takes, and the batch's labels.  (float(u8)/255 - mean)/std in fp32, torchvision's order: equal to the DataLoader's batch bit
+ * for bit.  mean/std are HOST pointers to 3 floats; everything else is on the device.  B may be any size (the reference's
+ * drop_last=False leaves a ragged last batch: 10 samples at 8 ranks). */
+int nrd_gather_normalize(const uint8_t* data_u8_nhwc, const int64_t* labels_all, long long n_samples, const int64_t* indices, int B,
+                         const float mean[3], const float std[3], float* images, int64_t* labels, void* stream);
+
 /* ---- per-op entries (unit parity tests; the Python autograd Functions of single ops) ------
  * T = plan dtype is replaced by an explicit `dtype`; tensors NHWC.  H = W = 16 for the block
  * convolution (the only resolution the ResBlock runs at, model/resnet.py:16-17). */

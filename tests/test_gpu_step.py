@@ -284,5 +284,9 @@ def test_trainstep_iterate_equals_step_by_step():
         res.append((losses, m.engine.flat_params.clone(), m.engine.bn_running.clone(), int(m.engine.nbt)))
     assert res[0][0] == res[1][0] == losses and len(res[1][0]) == 5
     assert torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2]) and res[0][3] == res[1][3] == 50
+    # a batch of another size (the ragged tail of drop_last=False) runs through a second TrainStep of that size
+    tail = [(torch.randn(8, 3, 32, 32, generator=g).pin_memory(), torch.randint(0, 10, (8,), generator=g).pin_memory())]
+    got = [float(l) for l in step.iterate(host[:2] + tail, lookahead=1)]
+    assert len(got) == 3 and all(np.isfinite(got)) and 8 in step._tails
     with pytest.raises(ValueError):
-        list(step.iterate([(torch.zeros(8, 3, 32, 32), torch.zeros(8, dtype=torch.int64))]))
+        list(step.iterate([(torch.zeros(8, 3, 16, 16), torch.zeros(8, dtype=torch.int64))]))

@@ -107,3 +107,25 @@ def test_bucketed_mean_allreduce_world_size_2_gloo():
     [p.join() for p in ps]
     for r in range(2):
         assert got[r][0] == [0.0, 10175 * 1.5, 10176 * 1.5, 76073 * 1.5] and got[r][1] == 0.0
+
+
+def test_sampler_order_equals_torch_distributed_sampler():
+    """The device loader's sample order is torch's DistributedSampler order (main.py:60), the same in every epoch (the reference
+    never calls set_epoch), with the reference's batch boundaries: 196 batches of 32 at 8 ranks, the last one of 10."""
+    from torch.utils.data import DistributedSampler
+    from ddp_cifar10_b200.data import distributed_sampler_indices
+
+    class D:
+        def __init__(self, n): self.n = n
+        def __len__(self): return self.n
+
+    for n in (50000, 1003, 7):
+        for W in (1, 2, 8):
+            for r in range(W):
+                smp = DistributedSampler(D(n), num_replicas=W, rank=r)
+                e0 = list(iter(smp)); e1 = list(iter(smp))                     # second epoch without set_epoch
+                ours = distributed_sampler_indices(n, W, r)
+                assert ours == e0 == e1, (n, W, r)
+    per_rank = len(distributed_sampler_indices(50000, 8, 3))
+    assert per_rank == 6250 and (per_rank + 31) // 32 == 196 and per_rank - 195 * 32 == 10      # SURVEY A.7
+    assert (len(distributed_sampler_indices(50000, 1, 0)) + 31) // 32 == 1563
