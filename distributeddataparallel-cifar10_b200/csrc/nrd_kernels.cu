@@ -1043,18 +1043,22 @@ __global__ void __launch_bounds__(256) k_fc1_dgrad_pooled(const float* __restric
 #pragma unroll
   for (int r = 0; r < 8; ++r) s[r] = 0.f;
   const float4* wrow = reinterpret_cast<const float4*>(w1t + (size_t)i * NRD_FC1_OUT);
+  float su[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) su[r] = 0.f;
 #pragma unroll
   for (int j4 = 0; j4 < 8; ++j4) {
     const float4 w = wrow[j4];
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {      // one fma chain per output, j ascending: the order of k_head_fused's backward slice (bit-identical)
-      s[r] = fmaf(d[r][j4 * 4], w.x, s[r]); s[r] = fmaf(d[r][j4 * 4 + 1], w.y, s[r]);
-      s[r] = fmaf(d[r][j4 * 4 + 2], w.z, s[r]); s[r] = fmaf(d[r][j4 * 4 + 3], w.w, s[r]);
+    for (int r = 0; r < 8; ++r) {      // k_head_fused's order (bit-identical): one fma chain over j = 0..15, one over 16..31, then lower + upper
+      float& a = j4 < 4 ? s[r] : su[r];
+      a = fmaf(d[r][j4 * 4], w.x, a); a = fmaf(d[r][j4 * 4 + 1], w.y, a);
+      a = fmaf(d[r][j4 * 4 + 2], w.z, a); a = fmaf(d[r][j4 * 4 + 3], w.w, a);
     }
   }
 #pragma unroll
   for (int r = 0; r < 8; ++r)
-    if (b0 + r < B) dp[(size_t)(b0 + r) * K + i] = from_f<T>(s[r]);
+    if (b0 + r < B) dp[(size_t)(b0 + r) * K + i] = from_f<T>(s[r] + su[r]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1070,11 +1074,14 @@ __global__ void __launch_bounds__(256) k_fc1_dgrad_pooled(const float* __restric
 // them sums the loss rows in k_ce's fixed order.  Everything is fixed-order: bit-reproducible.
 // ------------------------------------------------------------------------------------------
 #define NRD_HEAD_THREADS 512
-#define NRD_HEAD_SMEM_FLOATS (128 * 32 + 32 * 132 + 32 * 129 + 32 * 32 + 320)
+// shared memory (floats): weight slice k-major [128][32] | the same transposed [32][132] | pooled slice, k-major [128][33] |
+// dL/dh1, j-major [32][32] | cross-thread partial sums [8 k-groups | 2 j-halves][...] (32 KB) | fc2 weight + bias [320 + 16]
+#define NRD_HEAD_SMEM_FLOATS (128 * 32 + 32 * 132 + 128 * 33 + 32 * 32 + 8 * 64 * 16 + 336)
 static constexpr size_t head_smem_bytes() { return (size_t)NRD_HEAD_SMEM_FLOATS * 4 + 256 * 8 + 16; }
 
-// 512 threads = 2 K halves (kh) x 32 rows (r) x 8 output quads (jq); a warp = 4 rows x 8 quads, so everything a row needs from its
-// 8 threads travels by shuffles inside one warp: the tail (fc2, softmax, dh1) runs in registers without a CTA barrier.
+// 512 threads.  The two GEMM-shaped phases are register-tiled 4 x 4 (16 FMAs per 2 shared-memory reads; the first version's
+// 1 x 4 tiles were bound by shared-memory bandwidth, ~3 us per phase) with the reduction dimension split over thread groups
+// and combined in a fixed order; the tail of a row (fc2, softmax, dh1) runs in the registers of its 8 consecutive lanes.
 template <typename T>
 __global__ void __launch_bounds__(NRD_HEAD_THREADS, 1)
 k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restrict__ idx2, int pooled_in,
@@ -1087,26 +1094,32 @@ k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restric
   extern __shared__ __align__(16) float hsm[];
   float* ws = hsm;                    // [128 k][32 j]      fc1 weight slice, k-major (forward partial product)
   float* wsT = ws + 128 * 32;         // [32 j][132]        the same slice transposed (backward slice), rows padded
-  float* ps = wsT + 32 * 132;         // [32 rows][129]     pooled slice of the current row group
-  float* ph = ps + 32 * 129;          // [32 rows][32 j]    partial product of the upper K half
-  float* w2s = ph + 32 * 32;          // [10][32]
-  double* red = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(w2s + 320) + 15) & ~(uintptr_t)15);   // [256]
+  float* psT = wsT + 32 * 132;        // [128 k][33]        pooled slice of the current row group, k-major
+  float* ddT = psT + 128 * 33;        // [32 j][32 rows]    dL/dh1 of the row group
+  float* xr = ddT + 32 * 32;          // [8][64 tiles][16]  partial sums of the k-groups (forward) / [256 tiles][16] upper j half (backward)
+  float* w2s = xr + 8 * 64 * 16;      // [10][32] fc2 weight, then [10] fc2 bias
+  float* b2s = w2s + 320;
+  double* red = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(b2s + 16) + 15) & ~(uintptr_t)15);   // [256]
   __shared__ int last;
   const int tid = threadIdx.x, lane = tid & 31, K = 64 * C, KS = gridDim.y, ks = blockIdx.y, k0 = ks * 128, nrg = (B + 31) / 32;
-  const int kh = tid >> 8, r = (tid >> 3) & 31, jq = tid & 7;
+  const int kh = tid >> 8, r = (tid >> 3) & 31, jq = tid & 7;      // tail role: (copy kh of) row r, outputs jq*4 .. +3
   // stamps: rows 0..3 = CTAs (0,0), (0,KS-1), (last,0), (last,KS-1)
   const int drow = (blockIdx.x == 0 ? 0 : (blockIdx.x == gridDim.x - 1 ? 2 : -1)) + (blockIdx.y == 0 ? 0 : (blockIdx.y == gridDim.y - 1 ? 1 : -100));
   long long* dbgt = (dbg && tid == 0 && drow >= 0) ? dbg : nullptr;
   nrd_dbg_stamp(dbgt, drow, 0);
-  // ---- this CTA's weight slice (weights are untouched since the last optimizer step): loads issued now, stored below ----
+  // ---- everything that does not depend on the row group is requested first (weights are untouched since the last optimizer
+  // ---- step): this CTA's fc1 weight slice, fc1 bias, fc2 weight and bias ----
   float4 wreg[2];
 #pragma unroll
   for (int it = 0; it < 2; ++it) wreg[it] = reinterpret_cast<const float4*>(w1t + (size_t)k0 * 32)[tid + it * NRD_HEAD_THREADS];
-  for (int q = tid; q < NRD_NCLS * NRD_FC1_OUT; q += NRD_HEAD_THREADS) w2s[q] = w2[q];
+  const float4 bb4 = *reinterpret_cast<const float4*>(b1 + jq * 4);
+  for (int q = tid; q < NRD_NCLS * NRD_FC1_OUT + NRD_NCLS; q += NRD_HEAD_THREADS) w2s[q] = q < NRD_NCLS * NRD_FC1_OUT ? w2[q] : b2[q - NRD_NCLS * NRD_FC1_OUT];
   bool w_stored = false;
   for (int rg = blockIdx.x; rg < nrg; rg += gridDim.x) {
     const int b0 = rg * 32, b = b0 + r;
     nrd_dbg_stamp(dbgt, drow, 1);
+    long long lab64 = 0;
+    if (labels != nullptr && b < B) lab64 = labels[b];             // needed only after the barrier: in flight until then
     // ---- pool: 32 rows x 16 eight-channel chunks of the slice, one per thread; all four window loads in flight together ----
     {
       const int rr = tid >> 4, c8 = tid & 15, bb = b0 + rr, kk = k0 + c8 * 8;
@@ -1119,7 +1132,7 @@ k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restric
           for (int q = 0; q < 4; ++q) ld8(x + (((size_t)bb * 16 + 2 * ph_ + (q >> 1)) * 16 + 2 * pw + (q & 1)) * C + c, v[q]);
         }
       }
-      __syncthreads();                                 // previous row group's readers of ps / ph are done
+      __syncthreads();                                 // previous row group's readers of psT / ddT / xr are done
       if (!w_stored) {
 #pragma unroll
         for (int it = 0; it < 2; ++it) {
@@ -1150,46 +1163,56 @@ k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restric
         }
       }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) ps[rr * 129 + c8 * 8 + j] = m[j];
+      for (int j = 0; j < 8; ++j) psT[(c8 * 8 + j) * 33 + rr] = m[j];
     }
     __syncthreads();
     nrd_dbg_stamp(dbgt, drow, 2);
-    // ---- fc1 partial product: thread = (K half kh, row r, outputs jq*4 .. +3); operands fetched 16 k ahead of their use ----
+    // ---- fc1 partial product: thread = (k-group kg of 16 k, tile of 4 rows x 4 outputs); the 8 k-groups are combined in order ----
     {
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-      const float* prow = ps + r * 129 + kh * 64;
-      const float* wcol = ws + (kh * 64) * 32 + jq * 4;
-#pragma unroll 1                                        // executed once per CTA: unrolled copies would only be cold instruction fetches
-      for (int kb = 0; kb < 64; kb += 16) {
-        float pv[16]; float4 w[16];
+      const int kg = tid >> 6, tile = tid & 63, rt = tile >> 3, jt = tile & 7;
+      float acc[4][4];
 #pragma unroll
-        for (int u = 0; u < 16; ++u) { pv[u] = prow[kb + u]; w[u] = *reinterpret_cast<const float4*>(wcol + (kb + u) * 32); }
+      for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int u = 0; u < 16; ++u) { a0 = fmaf(pv[u], w[u].x, a0); a1 = fmaf(pv[u], w[u].y, a1); a2 = fmaf(pv[u], w[u].z, a2); a3 = fmaf(pv[u], w[u].w, a3); }
+        for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+      const float* pk_ = psT + (kg * 16) * 33 + rt * 4;
+      const float* wk_ = ws + (kg * 16) * 32 + jt * 4;
+#pragma unroll 4
+      for (int k = 0; k < 16; ++k) {
+        const float4 w = *reinterpret_cast<const float4*>(wk_ + k * 32);
+        const float p0 = pk_[k * 33], p1 = pk_[k * 33 + 1], p2 = pk_[k * 33 + 2], p3 = pk_[k * 33 + 3];
+        acc[0][0] = fmaf(p0, w.x, acc[0][0]); acc[0][1] = fmaf(p0, w.y, acc[0][1]); acc[0][2] = fmaf(p0, w.z, acc[0][2]); acc[0][3] = fmaf(p0, w.w, acc[0][3]);
+        acc[1][0] = fmaf(p1, w.x, acc[1][0]); acc[1][1] = fmaf(p1, w.y, acc[1][1]); acc[1][2] = fmaf(p1, w.z, acc[1][2]); acc[1][3] = fmaf(p1, w.w, acc[1][3]);
+        acc[2][0] = fmaf(p2, w.x, acc[2][0]); acc[2][1] = fmaf(p2, w.y, acc[2][1]); acc[2][2] = fmaf(p2, w.z, acc[2][2]); acc[2][3] = fmaf(p2, w.w, acc[2][3]);
+        acc[3][0] = fmaf(p3, w.x, acc[3][0]); acc[3][1] = fmaf(p3, w.y, acc[3][1]); acc[3][2] = fmaf(p3, w.z, acc[3][2]); acc[3][3] = fmaf(p3, w.w, acc[3][3]);
       }
-      if (kh == 1) *reinterpret_cast<float4*>(ph + r * 32 + jq * 4) = make_float4(a0, a1, a2, a3);
+      float4* dst = reinterpret_cast<float4*>(xr + (kg * 64 + tile) * 16);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dst[i] = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
       __syncthreads();
-      if (kh == 0 && b < B) {                          // lower half + upper half, in that order
-        const float4 u = *reinterpret_cast<const float4*>(ph + r * 32 + jq * 4);
-        *reinterpret_cast<float4*>(part + ((size_t)ks * B + b) * NRD_FC1_OUT + jq * 4) = make_float4(a0 + u.x, a1 + u.y, a2 + u.z, a3 + u.w);
-      }
+      // thread -> 2 outputs of one tile: (row rt*4 + i, outputs jt*4 + e, e = 2*(tid&1) .. +1), k-groups in order
+      const int tl = tid >> 3, i2 = (tid >> 1) & 3, e2 = (tid & 1) * 2;
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+      for (int g = 0; g < 8; ++g) { const float2 t2 = *reinterpret_cast<const float2*>(xr + (g * 64 + tl) * 16 + i2 * 4 + e2); s0 += t2.x; s1 += t2.y; }
+      const int orow = b0 + (tl >> 3) * 4 + i2, oj = (tl & 7) * 4 + e2;
+      if (orow < B) *reinterpret_cast<float2*>(part + ((size_t)ks * B + orow) * NRD_FC1_OUT + oj) = make_float2(s0, s1);
     }
     // ---- the KS CTAs of this row group wait for one another (monotonic counter per row group, nrd_common.cuh).  The CTA barrier
-    // ---- orders every thread's partial store before thread 0's release-add (cumulative at gpu scope): the grid-sync pattern, one
-    // ---- fence per CTA instead of one per thread ----
+    // ---- orders every thread's partial store before thread 0's release-add, which is cumulative at gpu scope: the grid-sync
+    // ---- pattern, one release per CTA ----
     __syncthreads();
     nrd_dbg_stamp(dbgt, drow, 3);
     if (tid == 0) {
       const unsigned long long base = nrd_grid_barrier_base(rg_ctr + rg, (unsigned)KS);
-      __threadfence();
       nrd_grid_barrier(rg_ctr + rg, base + (unsigned)KS);
     }
     __syncthreads();
     nrd_dbg_stamp(dbgt, drow, 4);
-    // ---- tail of the 32 rows, in registers, redone by every CTA of the group (and by both K halves): thread (r, jq) holds
-    // ---- h1[r][jq*4 .. +3]; the row's 8 threads are 8 consecutive lanes ----
+    // ---- tail of the 32 rows, in registers, redone by every CTA of the group (threads 0..255: the other half would only double
+    // ---- the L2 traffic of the partials): thread (r, jq) holds h1[r][jq*4 .. +3]; the row's 8 threads are 8 consecutive lanes ----
     float h[4] = {0.f, 0.f, 0.f, 0.f};
-    if (b < B) {
+    if (kh == 0 && b < B) {
       float4 hv[16];
 #pragma unroll 1
       for (int s0 = 0; s0 < KS; s0 += 16) {            // KS = 16 (C = 32) or 32 (C = 64): all loads of a batch in flight together
@@ -1198,18 +1221,20 @@ k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restric
 #pragma unroll
         for (int s2 = 0; s2 < 16; ++s2) { h[0] += hv[s2].x; h[1] += hv[s2].y; h[2] += hv[s2].z; h[3] += hv[s2].w; }     // slice order: fixed
       }
-      const float4 bb4 = *reinterpret_cast<const float4*>(b1 + jq * 4);
       h[0] = fmaxf(h[0] + bb4.x, 0.f); h[1] = fmaxf(h[1] + bb4.y, 0.f); h[2] = fmaxf(h[2] + bb4.z, 0.f); h[3] = fmaxf(h[3] + bb4.w, 0.f);
       if (ks == 0 && kh == 0) *reinterpret_cast<float4*>(h1 + (size_t)b * NRD_FC1_OUT + jq * 4) = make_float4(h[0], h[1], h[2], h[3]);
     }
     // logits: each thread's 4-term partial of the 32-term products, butterfly over the row's 8 lanes (xor 1, 2, 4: a fixed tree)
     float lg[NRD_NCLS];
 #pragma unroll
+    for (int c = 0; c < NRD_NCLS; ++c) lg[c] = 0.f;
+    if (kh == 0)                                       // (warp-uniform: warps 0..7)
+#pragma unroll
     for (int c = 0; c < NRD_NCLS; ++c) {
       const float4 w = *reinterpret_cast<const float4*>(w2s + c * NRD_FC1_OUT + jq * 4);
       float t = fmaf(h[3], w.w, fmaf(h[2], w.z, fmaf(h[1], w.y, h[0] * w.x)));
       t += __shfl_xor_sync(0xffffffffu, t, 1); t += __shfl_xor_sync(0xffffffffu, t, 2); t += __shfl_xor_sync(0xffffffffu, t, 4);
-      lg[c] = t + b2[c];
+      lg[c] = t + b2s[c];
     }
     const bool pub = ks == 0 && kh == 0 && jq == 0 && b < B;      // one thread per row publishes
     if (pub) {
@@ -1222,14 +1247,13 @@ k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restric
     float dlr[NRD_NCLS];
 #pragma unroll
     for (int c = 0; c < NRD_NCLS; ++c) dlr[c] = 0.f;
-    if (b < B) {
+    if (kh == 0 && b < B) {
       float v[NRD_NCLS], m = -INFINITY;
 #pragma unroll
       for (int c = 0; c < NRD_NCLS; ++c) { v[c] = lg[c]; m = fmaxf(m, v[c]); }
       float s2 = 0.f;
 #pragma unroll
       for (int c = 0; c < NRD_NCLS; ++c) { v[c] = expf(v[c] - m); s2 += v[c]; }
-      const long long lab64 = labels[b];
       const bool lab_ok = lab64 >= 0 && lab64 < NRD_NCLS;          // an out-of-range label poisons the loss, never the address
       const int lab = lab_ok ? (int)lab64 : 0;
       const float inv = 1.f / s2, sc = gscale / (float)B;
@@ -1244,40 +1268,51 @@ k_head_fused(const T* __restrict__ x, T* __restrict__ pooled, uint8_t* __restric
         for (int c = 0; c < NRD_NCLS; ++c) dlogits[(size_t)b * NRD_NCLS + c] = dlr[c];
       }
     }
-    // dL/dh1 of this thread's 4 outputs (c ascending, one fma chain: dh1_elem's order)
-    float dreg[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      float sacc = 0.f;
-#pragma unroll
-      for (int c = 0; c < NRD_NCLS; ++c) sacc = fmaf(dlr[c], w2s[c * NRD_FC1_OUT + jq * 4 + e], sacc);
-      dreg[e] = (b < B && h[e] > 0.f) ? sacc : 0.f;
-    }
-    nrd_dbg_stamp(dbgt, drow, 6);
     if (dp != nullptr) {
-      // ---- dL/d(pooled) for this slice: thread = (row r, columns m*32 + jq*4 .. +3 for m = 2kh, 2kh+1); dh1[r][j] comes from
-      // ---- the row's lane j/4 by shuffle; j ascending, one fma chain per output ----
-      float acc[2][4];
-#pragma unroll
-      for (int m = 0; m < 2; ++m)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) acc[m][e] = 0.f;
-      const int lbase = lane & 24;
-#pragma unroll 1
-      for (int j4 = 0; j4 < NRD_FC1_OUT / 4; ++j4) {
+      // dL/dh1 of this thread's 4 outputs (c ascending, one fma chain: dh1_elem's order) -> ddT[j][row]
+      if (kh == 0) {
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          const float d = __shfl_sync(0xffffffffu, dreg[e], lbase + j4);
+          float sacc = 0.f;
 #pragma unroll
-          for (int m = 0; m < 2; ++m) {
-            const float4 w = *reinterpret_cast<const float4*>(wsT + (j4 * 4 + e) * 132 + (2 * kh + m) * 32 + jq * 4);
-            acc[m][0] = fmaf(d, w.x, acc[m][0]); acc[m][1] = fmaf(d, w.y, acc[m][1]); acc[m][2] = fmaf(d, w.z, acc[m][2]); acc[m][3] = fmaf(d, w.w, acc[m][3]);
-          }
+          for (int c = 0; c < NRD_NCLS; ++c) sacc = fmaf(dlr[c], w2s[c * NRD_FC1_OUT + jq * 4 + e], sacc);
+          ddT[(jq * 4 + e) * 32 + r] = (b < B && h[e] > 0.f) ? sacc : 0.f;
         }
       }
-      if (b < B) {
+      __syncthreads();
+      nrd_dbg_stamp(dbgt, drow, 6);
+      // ---- dL/d(pooled) for this slice: thread = (j half jh, tile of 4 rows x 4 columns); per output one fma chain over its 16 j,
+      // ---- ascending; lower half + upper half, in that order ----
+      const int jh = tid >> 8, tile = tid & 255, rt = tile >> 5, kq = tile & 31;
+      float acc[4][4];
 #pragma unroll
-        for (int m = 0; m < 2; ++m) st4(dp + (size_t)b * K + k0 + (2 * kh + m) * 32 + jq * 4, acc[m]);
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+#pragma unroll 4
+      for (int jj = 0; jj < 16; ++jj) {
+        const int j = jh * 16 + jj;
+        const float4 w = *reinterpret_cast<const float4*>(wsT + j * 132 + kq * 4);
+        const float4 d = *reinterpret_cast<const float4*>(ddT + j * 32 + rt * 4);
+        acc[0][0] = fmaf(d.x, w.x, acc[0][0]); acc[0][1] = fmaf(d.x, w.y, acc[0][1]); acc[0][2] = fmaf(d.x, w.z, acc[0][2]); acc[0][3] = fmaf(d.x, w.w, acc[0][3]);
+        acc[1][0] = fmaf(d.y, w.x, acc[1][0]); acc[1][1] = fmaf(d.y, w.y, acc[1][1]); acc[1][2] = fmaf(d.y, w.z, acc[1][2]); acc[1][3] = fmaf(d.y, w.w, acc[1][3]);
+        acc[2][0] = fmaf(d.z, w.x, acc[2][0]); acc[2][1] = fmaf(d.z, w.y, acc[2][1]); acc[2][2] = fmaf(d.z, w.z, acc[2][2]); acc[2][3] = fmaf(d.z, w.w, acc[2][3]);
+        acc[3][0] = fmaf(d.w, w.x, acc[3][0]); acc[3][1] = fmaf(d.w, w.y, acc[3][1]); acc[3][2] = fmaf(d.w, w.z, acc[3][2]); acc[3][3] = fmaf(d.w, w.w, acc[3][3]);
+      }
+      float4* up = reinterpret_cast<float4*>(xr + tile * 16);
+      if (jh == 1) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) up[i] = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+      }
+      __syncthreads();
+      if (jh == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 u4 = up[i];
+          const float o4[4] = {acc[i][0] + u4.x, acc[i][1] + u4.y, acc[i][2] + u4.z, acc[i][3] + u4.w};
+          const int orow = b0 + rt * 4 + i;
+          if (orow < B) st4(dp + (size_t)orow * K + k0 + kq * 4, o4);
+        }
       }
     }
     nrd_dbg_stamp(dbgt, drow, 7);

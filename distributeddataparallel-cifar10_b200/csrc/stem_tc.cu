@@ -113,6 +113,7 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
   // plain stores -- disjoint bytes, so the two need no ordering
   const int nimg = (B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // images of this CTA
   if (warp >= 1 && warp <= 4 && nimg > 0) load_image_async(img + (size_t)blockIdx.x * 3072, smem_u32(im_gen), threadIdx.x - 32);
+  if (warp >= 1 && warp <= 4 && nimg > 1) load_image_async(img + (size_t)(blockIdx.x + gridDim.x) * 3072, smem_u32(im_gen) + IMG_FLOATS * 4, threadIdx.x - 32);
   zero_image_halos(im_gen, threadIdx.x, blockDim.x);                                    // halos stay zero for good
   if (threadIdx.x < 128) {                                         // W1 -> bf16 K-major rows; row co, chunk ch = taps ch*8..+7
     const int co = threadIdx.x >> 2, ch = threadIdx.x & 3;
@@ -163,7 +164,7 @@ k_stem_tc_fwd(const float* __restrict__ img, const float* __restrict__ wp /*[27]
       asm volatile("cp.async.wait_group 0;" ::: "memory");
       asm volatile("bar.sync 2, 128;" ::: "memory");               // image i complete and visible; image i-1's buffer is free
       if (t == 0 && i == 0) nrd_dbg_stamp(dbgt, drow, 2);
-      if (i + 1 < nimg) load_image_async(img + (size_t)(blockIdx.x + (i + 1) * gridDim.x) * 3072, im_s + ((i + 1) & 1) * IMG_FLOATS * 4, t);
+      if (i >= 1 && i + 1 < nimg) load_image_async(img + (size_t)(blockIdx.x + (i + 1) * gridDim.x) * 3072, im_s + ((i + 1) & 1) * IMG_FLOATS * 4, t);
       const float* im = im_gen + (i & 1) * IMG_FLOATS;
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
@@ -245,6 +246,7 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
   // image 0 first (it does not depend on the predecessor kernel): interior by cp.async, halo zeroed by plain stores (disjoint bytes)
   const int nimg = (B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   if (warp >= 1 && warp <= 4 && nimg > 0) load_image_async(img + (size_t)blockIdx.x * 3072, smem_u32(im_gen), threadIdx.x - 32);
+  if (warp >= 1 && warp <= 4 && nimg > 1) load_image_async(img + (size_t)(blockIdx.x + gridDim.x) * 3072, smem_u32(im_gen) + IMG_FLOATS * 4, threadIdx.x - 32);
   zero_image_halos(im_gen, threadIdx.x, blockDim.x);
   // (the slack behind the last stage, which the junk M-groups 1..3 of the last tiles read, stays uninitialised: a junk row of A
   // only ever reaches the same junk row of the accumulator, which nobody reads)
@@ -292,7 +294,8 @@ k_stem_tc_bwd(const float* __restrict__ img, const bf16* __restrict__ g0, const 
       asm volatile("cp.async.wait_group 0;" ::: "memory");
       asm volatile("bar.sync 2, 128;" ::: "memory");
       if (t == 0 && i == 0) nrd_dbg_stamp(dbgt, drow, 3);
-      if (i + 1 < nimg) load_image_async(img + (size_t)(blockIdx.x + (i + 1) * gridDim.x) * 3072, im_s + ((i + 1) & 1) * IMG_FLOATS * 4, t);
+      // images 0 and 1 were requested in the prologue; image i+1 (i >= 1) goes into the slot image i-1 has left (the barrier above)
+      if (i >= 1 && i + 1 < nimg) load_image_async(img + (size_t)(blockIdx.x + (i + 1) * gridDim.x) * 3072, im_s + ((i + 1) & 1) * IMG_FLOATS * 4, t);
       const float* im = im_gen + (i & 1) * IMG_FLOATS;
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
