@@ -63,34 +63,95 @@ void nrd_set_error(const char* fmt, ...);
 struct nrd_xchg_args {
   float* peer[NRD_XCHG_MAX_WORLD];
   int world, rank, nx;          // world == 0: exchange off
+  int nll;                      // elements of the body bucket's flag-in-data slots (BN slot + body gradients, rounded up to 4)
   long long timeout_cycles;     // how long a consumer spins for a peer's flag before it gives up (nrd_plan_set_exchange)
 };
 static __host__ __device__ __forceinline__ size_t nrd_xchg_flags_off(int world, int nx) {
   return (((size_t)2 * world * nx * sizeof(float)) + 127) & ~(size_t)127;
 }
-static __host__ __device__ __forceinline__ size_t nrd_xchg_bytes(int world, int nx) {
-  return nrd_xchg_flags_off(world, nx) + NRD_XCHG_CTRL_WORDS * sizeof(unsigned long long);
+// Body bucket with the optimizer step fused into the producing kernel: "flag in data" slots behind the control words --
+//   ll   [2 parities][world][nll] x {float value, u32 epoch}
+// every 8-byte word carries its own arrival flag, so the producer needs no fence, no arrival counter and no flag store, and
+// the consumer's wait is ONE NVLink crossing: it polls the words it sums until each shows this step's epoch.
+static __host__ __device__ __forceinline__ size_t nrd_xchg_ll_off(int world, int nx) {
+  return (nrd_xchg_flags_off(world, nx) + NRD_XCHG_CTRL_WORDS * sizeof(unsigned long long) + 127) & ~(size_t)127;
+}
+static __host__ __device__ __forceinline__ size_t nrd_xchg_bytes(int world, int nx, int nll) {
+  return nrd_xchg_ll_off(world, nx) + (size_t)2 * world * nll * sizeof(uint2);
+}
+static __device__ __forceinline__ uint2* nrd_xchg_ll(float* base, const nrd_xchg_args& x, unsigned long long epoch, int from_rank) {
+  return reinterpret_cast<uint2*>(reinterpret_cast<char*>(base) + nrd_xchg_ll_off(x.world, x.nx)) + ((size_t)(epoch & 1) * x.world + from_rank) * x.nll;
+}
+// two consecutive elements {v0, v1} of this rank's slot into every rank's buffer: one 16-byte store per peer, each 8-byte half
+// carries the epoch
+static __device__ __forceinline__ void nrd_ll_push2(const nrd_xchg_args& x, unsigned long long epoch, size_t idx, float v0, float v1) {
+  const unsigned int e = (unsigned int)epoch;
+  for (int p = 0; p < x.world; ++p) {
+    uint2* d = nrd_xchg_ll(x.peer[p], x, epoch, x.rank) + idx;
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(d), "r"(__float_as_uint(v0)), "r"(e), "r"(__float_as_uint(v1)), "r"(e) : "memory");
+  }
+}
+static __device__ __forceinline__ void nrd_ll_push1(const nrd_xchg_args& x, unsigned long long epoch, size_t idx, float v) {
+  const unsigned int e = (unsigned int)epoch;
+  for (int p = 0; p < x.world; ++p) {
+    uint2* d = nrd_xchg_ll(x.peer[p], x, epoch, x.rank) + idx;
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(d), "r"(__float_as_uint(v)), "r"(e) : "memory");
+  }
+}
+// rank-ordered sum of element idx over the world's slots in OUR buffer, waiting for each word's epoch (all loads of a round in flight)
+static __device__ __forceinline__ float nrd_ll_sum(const nrd_xchg_args& x, unsigned long long epoch, size_t idx) {
+  const unsigned int e = (unsigned int)epoch;
+  const uint2* base = nrd_xchg_ll(x.peer[x.rank], x, epoch, 0) + idx;
+  uint2 v[NRD_XCHG_MAX_WORLD];
+  long long t0 = 0;
+  int spins = 0;
+  while (true) {
+    bool ok = true;
+#pragma unroll
+    for (int r = 0; r < NRD_XCHG_MAX_WORLD; ++r)
+      if (r < x.world) {
+        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v[r].x), "=r"(v[r].y) : "l"(base + (size_t)r * x.nll) : "memory");
+      }
+#pragma unroll
+    for (int r = 0; r < NRD_XCHG_MAX_WORLD; ++r) if (r < x.world) ok = ok && (v[r].y == e);
+    if (ok) break;
+    if (++spins > 4096) {
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > x.timeout_cycles) __trap();     // a peer is gone
+    }
+  }
+  float g = 0.f;
+#pragma unroll
+  for (int r = 0; r < NRD_XCHG_MAX_WORLD; ++r) if (r < x.world) g += __uint_as_float(v[r].x);      // rank order: the same on every rank
+  return g;
 }
 static __device__ __forceinline__ unsigned long long* nrd_xchg_flags(float* base, int world, int nx, int bucket = 0) {
   return reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(base) + nrd_xchg_flags_off(world, nx)) + bucket * NRD_XCHG_BUCKET_WORDS;
 }
-// last step of a producing kernel (every thread calls it after its peer stores): the CTA that arrives last publishes `epoch`
-// in every rank's flag of this bucket and records it locally
+// last step of a producing kernel (every thread calls it after its peer stores): the CTA that arrives last publishes `epoch` in
+// every rank's flag of this bucket and records it locally.  Ordering, one fence per CTA instead of one per thread and one per
+// flag: the CTA barrier orders every thread's peer stores before thread 0's system-scope fence (fences are cumulative), which
+// precedes the CTA's arrival; the last arriver fences once more (acquire side of the arrival counter) and then writes the
+// world's flags as RELAXED stores from `world` lanes at once -- data, fence, flag is the release pattern; a release store per
+// flag would put a full system-scope fence (an NVLink round trip, ~2 us) in front of every one of them, one after the other:
+// measured 12-18 us between a rank's publish and the arrival of the last peer's flag at 8 ranks (profiles/r02_ddp_tail.md).
 static __device__ __forceinline__ void nrd_xchg_publish(const nrd_xchg_args& x, int bucket, unsigned long long epoch) {
-  __threadfence_system();                     // this thread's peer stores are performed before the CTA reports in
+  __shared__ int s_last;
   __syncthreads();
+  unsigned long long* ctrl = nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, bucket);
   if (threadIdx.x == 0) {
-    unsigned long long* ctrl = nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, bucket);
+    __threadfence_system();                   // this CTA's peer stores are performed system-wide before it reports in
     unsigned int* arrive = reinterpret_cast<unsigned int*>(ctrl + NRD_XCHG_ARRIVE);
-    if (atomicAdd(arrive, 1u) == gridDim.x * gridDim.y - 1) {
-      *arrive = 0u;
-      __threadfence_system();
-      for (int p = 0; p < x.world; ++p) {
-        unsigned long long* f = nrd_xchg_flags(x.peer[p], x.world, x.nx, bucket) + (epoch & 1) * NRD_XCHG_MAX_WORLD + x.rank;
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(epoch) : "memory");
-      }
-      ctrl[NRD_XCHG_EPOCH] = epoch;
+    s_last = (atomicAdd(arrive, 1u) == gridDim.x * gridDim.y - 1) ? 1 : 0;
+    if (s_last) { *arrive = 0u; __threadfence_system(); }
+  }
+  __syncthreads();
+  if (s_last) {
+    if ((int)threadIdx.x < x.world) {
+      unsigned long long* f = nrd_xchg_flags(x.peer[threadIdx.x], x.world, x.nx, bucket) + (epoch & 1) * NRD_XCHG_MAX_WORLD + x.rank;
+      asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(f), "l"(epoch) : "memory");
     }
+    if (threadIdx.x == 0) ctrl[NRD_XCHG_EPOCH] = epoch;
   }
 }
 // consumer: threads 0 .. world-1 of the CTA wait for the world's flags of a bucket in the own buffer; returns the epoch

@@ -263,8 +263,19 @@ __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ w
   nrd_pdl_wait();
   nrd_dbg_stamp(dbgt, drow, 1);
   const bool px = x.world > 0, upd = u.params != nullptr;
-  // bumped by the last CTA, after every CTA has read it
-  const unsigned long long epoch = px ? nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, 0)[NRD_XCHG_EPOCH] + 1 : 0;
+  const bool ll = px && upd;                           // fused update: flag-in-data slots (nrd_common.cuh); else flags published per bucket
+  // the step's epoch: read by every CTA at entry, bumped by whichever CTA arrives last at a counter (after every CTA has read it)
+  __shared__ unsigned long long s_epoch;
+  if (px && threadIdx.x == 0) {
+    unsigned long long* ctrl = nrd_xchg_flags(x.peer[x.rank], x.world, x.nx, 0);
+    s_epoch = ctrl[NRD_XCHG_EPOCH] + 1;
+    if (ll) {                                          // (the flag protocol bumps it in nrd_xchg_publish)
+      unsigned int* arrive = reinterpret_cast<unsigned int*>(ctrl + NRD_XCHG_ARRIVE);
+      if (atomicAdd(arrive, 1u) == gridDim.x - 1) { *arrive = 0u; ctrl[NRD_XCHG_EPOCH] = s_epoch; }
+    }
+  }
+  if (px) __syncthreads();
+  const unsigned long long epoch = px ? s_epoch : 0;
   const size_t slot = px ? ((size_t)(epoch & 1) * x.world + x.rank) * x.nx : 0;
   const bool last_cta = blockIdx.x == gridDim.x - 1;
   // DDP buffer sync riding the body bucket: rank 0 contributes world_size * running, the others exact zeros; + dgamma | dbeta
@@ -272,7 +283,11 @@ __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ w
     for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
       const float v = contrib != 0.f ? running[j] * contrib : 0.f;
       if (bn_sync && !px) bn_sync[j] = v;
-      if (px) { const float gj = grads_base[off_bng + j]; for (int p = 0; p < x.world; ++p) { x.peer[p][slot + j] = v; x.peer[p][slot + 2 * C + off_bng + j] = gj; } }
+      if (px) {
+        const float gj = grads_base[off_bng + j];
+        if (ll) { nrd_ll_push1(x, epoch, j, v); nrd_ll_push1(x, epoch, 2 * C + off_bng + j, gj); }
+        else for (int p = 0; p < x.world; ++p) { x.peer[p][slot + j] = v; x.peer[p][slot + 2 * C + off_bng + j] = gj; }
+      }
     }
   }
   const int c4 = threadIdx.x & 15, rc = threadIdx.x >> 4, nconv4 = 9 * C * C / 4;
@@ -310,25 +325,27 @@ __global__ void __launch_bounds__(256) k_body_reduce(const float* __restrict__ w
 #pragma unroll
     for (int k = 0; k < 16; ++k) tot += rf[k * 64];                        // row classes in order
     grads_base[pi] = tot;
-    if (px) for (int p = 0; p < x.world; ++p) x.peer[p][slot + sidx] = tot;
+    if (px) {
+      // 16-byte peer stores (warps 0 and 1 are fully inside t < 64): flag-in-data: lanes 2q, 2q+1 -> {v, epoch, v', epoch};
+      // flag protocol: lanes 4q .. 4q+3 -> 4 consecutive slot elements
+      const float v1 = __shfl_down_sync(0xffffffffu, tot, 1), v2 = __shfl_down_sync(0xffffffffu, tot, 2), v3 = __shfl_down_sync(0xffffffffu, tot, 3);
+      if (ll) { if ((t & 1) == 0) nrd_ll_push2(x, epoch, sidx, tot, v1); }
+      else if ((t & 3) == 0) for (int p = 0; p < x.world; ++p) *reinterpret_cast<float4*>(x.peer[p] + slot + sidx) = make_float4(tot, v1, v2, v3);
+    }
   }
-  if (px) nrd_xchg_publish(x, 0, epoch);
+  if (px && !ll) nrd_xchg_publish(x, 0, epoch);
+  nrd_dbg_stamp(dbgt, drow, 4);
   if (!upd) return;
   if (px) {
-    // ---- wait for the world's body buckets in OUR buffer, then every element is the rank-ordered sum of the world's slots ----
-    nrd_xchg_wait_epoch(x, 0, (int)threadIdx.x, epoch);
-    __syncthreads();
-    const float* slots = x.peer[x.rank] + (size_t)(epoch & 1) * x.world * x.nx;
+    // ---- every element is the rank-ordered sum of the world's slots in OUR buffer; each word is waited for by itself ----
     if (t < 64) {
-      float g = 0.f;
-      for (int r = 0; r < x.world; ++r) g += __ldcg(slots + (size_t)r * x.nx + sidx);
-      tot = g;
+      tot = nrd_ll_sum(x, epoch, sidx);
       grads_base[pi] = tot;                            // .grad keeps holding the world's sum, as after an all-reduce
     }
+    nrd_dbg_stamp(dbgt, drow, 5);
     if (last_cta)
       for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
-        float sres = 0.f, gj = 0.f;
-        for (int r = 0; r < x.world; ++r) { sres += __ldcg(slots + (size_t)r * x.nx + j); gj += __ldcg(slots + (size_t)r * x.nx + 2 * C + off_bng + j); }
+        const float sres = nrd_ll_sum(x, epoch, j), gj = nrd_ll_sum(x, epoch, 2 * C + off_bng + j);
         if (bn_sync) bn_sync[j] = sres;
         grads_base[off_bng + j] = gj;
       }
@@ -1997,7 +2014,7 @@ extern "C" int nrd_plan_set_bn_sync(nrd_plan* p, float* slot, float contrib, flo
 extern "C" size_t nrd_exchange_bytes(int C, int world) {
   int64_t off[10];
   if (world < 2 || world > NRD_XCHG_MAX_WORLD || nrd_param_offsets(C, off) != NRD_OK) return 0;
-  return nrd_xchg_bytes(world, (2 * C + (int)off[9] + 3) & ~3);
+  return nrd_xchg_bytes(world, (2 * C + (int)off[9] + 3) & ~3, (2 * C + (int)off[5] + 3) & ~3);
 }
 
 // The exchange buffer is the one piece of device memory the library allocates itself: it must be a whole cudaMalloc
@@ -2038,6 +2055,7 @@ extern "C" int nrd_plan_set_exchange(nrd_plan* p, int rank, int world, void* con
   NRD_REQUIRE(world >= 2 && world <= NRD_XCHG_MAX_WORLD && rank >= 0 && rank < world, "nrd_plan_set_exchange: world %d / rank %d out of range", world, rank);
   for (int r = 0; r < world; ++r) { NRD_REQUIRE(bufs[r], "nrd_plan_set_exchange: null buffer for rank %d", r); p->xchg.peer[r] = (float*)bufs[r]; }
   p->xchg.world = world; p->xchg.rank = rank; p->xchg.nx = (2 * p->C + (int)p->off[9] + 3) & ~3;
+  p->xchg.nll = (2 * p->C + (int)p->off[5] + 3) & ~3;
   {
     // how long the optimizer kernel waits for a peer's gradients before it traps the context: 10 minutes by default (the
     // default of the NCCL watchdog this exchange replaces), NRD_XCHG_TIMEOUT_S overrides; converted with the SM clock rate

@@ -66,8 +66,9 @@ def _worker(rank, W, port, q):
     # ---- graph path, both exchanges, fp32 and bf16 ----
     for dtype, b in (("fp32", B), ("bf16", B_BF16)):
         xb, yb = data(b)
-        for xchg in ("p2p", "nccl"):
-            os.environ["NRD_P2P"] = "1" if xchg == "p2p" else "0"
+        for xchg in ("p2p", "nccl", "p2p-unfused"):
+            os.environ["NRD_P2P"] = "0" if xchg == "nccl" else "1"
+            os.environ["NRD_FUSED_UPDATE"] = "0" if xchg == "p2p-unfused" else "1"       # unfused: flags per bucket + a separate optimizer kernel
             m, ddp = fresh(dtype)
             step = nrd.TrainStep(ddp, b, lr=LR if dtype == "fp32" else LR_BF16)
             losses, first = [], None
@@ -78,7 +79,7 @@ def _worker(rank, W, port, q):
             step.check_status()
             out[f"graph/{dtype}/{xchg}"] = (losses,) + snap(m) + first + (bool(step.p2p),)
             step.close(); del step          # graphs hold captured NCCL kernels / peer mappings: drop them before the communicator
-    os.environ.pop("NRD_P2P", None)
+    os.environ.pop("NRD_P2P", None); os.environ.pop("NRD_FUSED_UPDATE", None)
     torch.cuda.synchronize()
     xb, yb = data(B_BF16)
     q.put((rank, out, x.numpy(), y.numpy(), xb.numpy(), yb.numpy()))     # numpy pickles inline: nothing refers back to this process
@@ -164,3 +165,8 @@ def test_ddp_matches_oracle_and_graph_equals_eager(W):
         if W == 2:
             a, b_ = out["graph/bf16/p2p"], out["graph/bf16/nccl"]
             assert a[0] == b_[0] and np.array_equal(a[1], b_[1]) and np.array_equal(a[2], b_[2])
+        # the two peer-memory protocols (flag-in-data slots with the optimizer step fused into the reduce kernel; flags per bucket
+        # and a separate optimizer kernel) sum the world's slots in the same rank order: bit for bit, any W, both dtypes
+        for dtype in ("fp32", "bf16"):
+            a, b_ = out[f"graph/{dtype}/p2p"], out[f"graph/{dtype}/p2p-unfused"]
+            assert a[0] == b_[0] and np.array_equal(a[1], b_[1]) and np.array_equal(a[2], b_[2]) and np.array_equal(a[4], b_[4]), dtype
