@@ -3,7 +3,7 @@ BaamPark/DistributedDataParallel-Cifar10).  Importing this package loads libnrd.
 CPU fallback."""
 from . import _lib  # noqa: F401  (fails loudly when the CUDA library is missing)
 from .model.resnet import NetResDeep, ResBlock  # noqa: F401
-from .nn import CrossEntropyLoss  # noqa: F401
+from .nn import CrossEntropyLoss, BCEWithLogitsLoss, binary_cross_entropy_with_logits  # noqa: F401
 from .optim import SGD  # noqa: F401
 from .parallel import DistributedDataParallel  # noqa: F401
 from .data import SyntheticCifar10Loader, DevicePrefetcher, Cifar10DeviceLoader  # noqa: F401

@@ -58,6 +58,8 @@ _PROTOS = {
     "nrd_plan_set_loss_mirror": (i32, [vp, vp, vp]),
     "nrd_train_step": (i32, [vp, vp, vp, f32, vp, vp, vp]),
     "nrd_gen_batch": (i32, [vp, vp, i32, u64, u32, u64, vp]),
+    "nrd_sgd_momentum_update": (i32, [vp, vp, vp, sz, f32, f32, i32, vp]),
+    "nrd_bce_with_logits": (i32, [vp, vp, sz, f32, vp, vp, vp]),
     "nrd_gather_normalize": (i32, [vp, vp, C.c_longlong, vp, i32, C.POINTER(f32), C.POINTER(f32), vp, vp, vp]),
     "nrd_pack_conv_weight": (i32, [vp, i32, vp, vp, vp]),
     "nrd_conv3x3_fwd": (i32, [vp, vp, vp, i32, i32, i32, vp, C.POINTER(i32), vp, vp]),

@@ -1370,6 +1370,36 @@ __global__ void k_sgd(float* __restrict__ p, const float* __restrict__ g, size_t
     p[i] = fmaf(-step_scale, g[i], p[i]);
 }
 
+// SGD with momentum as torch.optim.SGD(lr, momentum) runs it (ppe_main_ddp.py:133; dampening 0, no nesterov, no weight decay):
+// buf <- g on the first step, buf <- mu * buf + g afterwards; p <- p - lr * buf
+__global__ void k_sgd_momentum(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, size_t n, float lr, float mu, int first) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float b = first ? gi : fmaf(mu, buf[i], gi);
+    buf[i] = b;
+    p[i] = fmaf(-lr, b, p[i]);
+  }
+}
+
+// binary_cross_entropy_with_logits, mean reduction (ppe_main_ddp.py:147), forward and gradient in one pass:
+// loss_i = max(x,0) - x*t + log1p(exp(-|x|));  dL/dx_i = (sigmoid(x) - t) * grad_scale / n.  One CTA, fixed-shape tree.
+__global__ void __launch_bounds__(256) k_bce_logits(const float* __restrict__ x, const float* __restrict__ t, size_t n, float gscale,
+                                                    float* __restrict__ dx, float* __restrict__ loss) {
+  __shared__ double red[256];
+  double acc = 0.0;
+  const float sc = gscale / (float)n;
+  for (size_t i = threadIdx.x; i < n; i += 256) {
+    const float xi = x[i], ti = t[i];
+    const float l = fmaxf(xi, 0.f) - xi * ti + log1pf(expf(-fabsf(xi)));
+    acc += (double)l;
+    if (dx) dx[i] = (1.f / (1.f + expf(-xi)) - ti) * sc;
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0 && loss) *loss = (float)(red[0] / (double)n);
+}
+
 // p <- p - step_scale * g over the whole flat vector AND the packed copies of the three tensors that have them, one launch
 // (off[] = flat offsets of the 9 tensors; index order as k_pack_weights)
 // [lo, hi): the part of the flat vector this launch updates (whole vector, or one bucket when the update rides the backward);
@@ -1791,6 +1821,21 @@ extern "C" int nrd_sgd_update(float* params, const float* grads, size_t n, float
   NRD_REQUIRE(params && grads, "nrd_sgd_update: null pointer");
   if (n == 0) return NRD_OK;
   k_sgd<<<grid_for(n, 256, NRD_NUM_SMS * 2), 256, 0, (cudaStream_t)stream>>>(params, grads, n, lr * inv_world);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_sgd_momentum_update(float* params, const float* grads, float* momentum_buf, size_t n, float lr, float momentum, int first_step,
+                                       void* stream) {
+  NRD_REQUIRE(params && grads && momentum_buf && n > 0, "nrd_sgd_momentum_update: bad arguments");
+  k_sgd_momentum<<<grid_for(n, 256, NRD_NUM_SMS * 2), 256, 0, (cudaStream_t)stream>>>(params, grads, momentum_buf, n, lr, momentum, first_step ? 1 : 0);
+  LAUNCH_CHECK();
+  return NRD_OK;
+}
+
+extern "C" int nrd_bce_with_logits(const float* logits, const float* targets, size_t n, float grad_scale, float* loss_out, float* dlogits, void* stream) {
+  NRD_REQUIRE(logits && targets && n > 0 && (loss_out || dlogits), "nrd_bce_with_logits: bad arguments");
+  k_bce_logits<<<1, 256, 0, (cudaStream_t)stream>>>(logits, targets, n, grad_scale, dlogits, loss_out);
   LAUNCH_CHECK();
   return NRD_OK;
 }

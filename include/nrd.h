@@ -219,6 +219,16 @@ int nrd_train_step(nrd_plan* plan, const float* images, const int64_t* labels, f
 int nrd_gen_batch(float* images, int64_t* labels, int B, uint64_t seed, uint32_t rank, uint64_t step,
                   void* stream);
 
+/* ---- optimizer / loss variants of the reference's second script (ppe_main_ddp.py:133,147) -------------------
+ * nrd_sgd_momentum_update = optim.SGD(lr, momentum).step() with torch's defaults (dampening 0, nesterov off, weight decay 0):
+ *   buf <- g (first_step != 0) or momentum * buf + g; p <- p - lr * buf, over n floats of the flat vectors; the caller re-packs
+ *   the weight copies afterwards (nrd_pack_weights).
+ * nrd_bce_with_logits = F.binary_cross_entropy_with_logits(logits, targets) (mean over all n elements) AND its gradient
+ *   dlogits = (sigmoid(x) - t) * grad_scale / n, one pass; either output may be NULL. */
+int nrd_sgd_momentum_update(float* params, const float* grads, float* momentum_buf, size_t n, float lr, float momentum, int first_step,
+                            void* stream);
+int nrd_bce_with_logits(const float* logits, const float* targets, size_t n, float grad_scale, float* loss_out, float* dlogits, void* stream);
+
 /* ---- the reference's real input path on the device (main.py:53-61; main_no_ddp.py:22-34) ---------
  * The CIFAR-10 training set as torchvision holds it -- uint8 [N,32,32,3] (HWC) plus int64 labels [N] -- stays resident in HBM.
  * One call builds a batch: gather by sample index (the DistributedSampler order of main.py:60, computed on the host), ToTensor

@@ -306,3 +306,34 @@ def test_eager_step_after_graph_steps_on_the_same_model():
         finals.append((losses, m.engine.flat_params.clone(), m.engine.bn_running.clone(), int(m.engine.nbt)))
     assert finals[0][0] == finals[1][0]
     assert torch.equal(finals[0][1], finals[1][1]) and torch.equal(finals[0][2], finals[1][2]) and finals[0][3] == finals[1][3] == 40
+
+
+def test_sgd_momentum_and_bce_with_logits_variants():
+    """the optimizer / loss of the reference's second script (ppe_main_ddp.py:133,147) around the same model:
+    SGD(lr=0.001, momentum=0.9) against torch.optim.SGD on the same gradients over 3 steps, binary_cross_entropy_with_logits
+    (value and gradient) against torch's."""
+    import torch.nn.functional as F
+    x, y = _data(16, 41)
+    pm, bm = O.init_params(32, 10, seed=9)
+    m = model_from_oracle(pm, bm, 10, "fp32")
+    opt = nrd.SGD(m.parameters(), lr=1e-3, momentum=0.9)
+    m.engine.adopt(next(m.parameters()).device)             # (normally done by the first forward)
+    ref_p = m.engine.flat_params.detach().clone().requires_grad_(True)
+    ref_opt = torch.optim.SGD([ref_p], lr=1e-3, momentum=0.9)
+    for s in range(3):
+        out = m(x.to(DEV))
+        onehot = F.one_hot(y, 10).float().to(DEV)
+        loss = nrd.binary_cross_entropy_with_logits(out, onehot)
+        want = F.binary_cross_entropy_with_logits(out.detach(), onehot)
+        assert abs(float(loss) - float(want)) < 1e-6 * abs(float(want))
+        o2 = out.detach().clone().requires_grad_(True)
+        F.binary_cross_entropy_with_logits(o2, onehot).backward()
+        opt.zero_grad(); loss.backward()
+        ref_p.grad = m.engine.flat_grads.detach().clone()
+        opt.step(); ref_opt.step()
+        assert rell2(m.engine.flat_params, ref_p.detach()) < 1e-7, s
+    # dlogits of the fused kernel vs autograd through torch's own loss
+    lg = torch.randn(64, 10, device=DEV, requires_grad=True); tg = torch.rand(64, 10, device=DEV)
+    nrd.binary_cross_entropy_with_logits(lg, tg).backward()
+    l2 = lg.detach().clone().requires_grad_(True); F.binary_cross_entropy_with_logits(l2, tg).backward()
+    assert rell2(lg.grad, l2.grad) < 1e-6

@@ -57,7 +57,9 @@ def test_cpu_has_no_fallback_and_arguments_are_validated():
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         m(torch.zeros(2, 3, 32, 32))
     with pytest.raises(NotImplementedError):
-        nrd.SGD(m.parameters(), lr=0.1, momentum=0.9)
+        nrd.SGD(m.parameters(), lr=0.1, momentum=0.9, nesterov=True)
+    with pytest.raises(NotImplementedError):
+        nrd.SGD(m.parameters(), lr=0.1, weight_decay=1e-4)
     with pytest.raises(NotImplementedError):
         nrd.CrossEntropyLoss(label_smoothing=0.1)
     with pytest.raises(ValueError):
