@@ -468,6 +468,8 @@ def main():
             ops = {"stem_fwd": (5, 1, B * 3072 * 4 + T + T // s_act), "fwd_blocks(persistent)": (8, 1, NB * 4 * T), "head": (10, 1, head_bytes),
                    "bwd_blocks(persistent)": (9, 1, NB * 6 * T), "stem_bwd": (6, 1, B * 3072 * 4 + 2 * T + T // s_act),
                    "body_reduce(+sgd)": (11, 1, reduce_bytes)}
+            if os.environ.get("NRD_FUSE_STEM_BWD", "0") == "1":
+                ops.pop("stem_bwd")                       # conv1's gradient is computed in the persistent backward's tail: no such launch
             if world == 1 and not getattr(step, "fused_update", False):
                 ops["sgd_pack"] = (12, 1, 3 * 4 * (64 * C * 32 + 9 * C * C + 27 * C))
         else:

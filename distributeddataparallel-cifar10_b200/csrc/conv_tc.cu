@@ -15,6 +15,7 @@
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM alloc + MMA issuer (one lane), warps 2..5 = epilogue
 // (TMEM -> registers -> bf16 -> global), double-buffered TMEM accumulators so the epilogue of tile i overlaps the MMAs
 // of tile i+1.  Every mbarrier wait has a clock64() timeout that traps instead of hanging the GPU.
+#include <type_traits>
 #include "tc_common.cuh"
 
 namespace {
@@ -846,6 +847,11 @@ struct PersistBwdArgs {
   long long* trace;           // optional clock64 stamps (profiling aid), or NULL
   int poll_ns;
   unsigned int* status;       // the plan's sticky status word (nrd_acc_add)
+  // fused stem backward (NRD_OPT_FUSE_STEM_BWD, ONE = 0 only): conv1's weight / bias gradient of this CTA's images right here, from
+  // dL/dx_0 in the epilogue registers and x_0 still in shared memory; NULL images = off (the stand-alone stem kernel follows)
+  const float* images;        // [B,3,32,32] fp32
+  const uint8_t* idx0;        // [B,16,16,C] stem pool arg-max
+  float* stem_partial;        // [gridDim.x][28][C]
 };
 
 // ONE = 1: dy lives in ONE row- and column-haloed copy per image (see k_tc_fwd_persist): dgrad taps are pixel-granular
@@ -870,8 +876,9 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   auto wfree = [&](int s) { return bar0 + 8u * (5 + s); };
   auto dxfull = [&](int s, int m) { return bar0 + 8u * (7 + s * 2 + m); };
   const uint32_t wdone = bar0 + 8u * 11;
+  const uint32_t stfull = bar0 + 8u * 12, stdone = bar0 + 8u * 14;      // fused stem backward: tiles of an image built / its MMAs done
   const uint32_t tmem_slot = bar0 + 8u * 13;
-  constexpr int BAR_BYTES = 8 * 14;
+  constexpr int BAR_BYTES = 8 * 16;
   constexpr int MISC_OFF = 2 * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
   float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][2][C] = 1024 floats
   float* coef = red + 1024;                                               // [3C] = gamma*invstd | mean(dz) | mean(dz*xhat)
@@ -897,7 +904,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
   fence_proxy_async();
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmXall); tma_prefetch_desc(&tmWd);
-    mbar_init(wfull, 1); mbar_init(wdone, 1);
+    mbar_init(wfull, 1); mbar_init(wdone, 1); mbar_init(stfull, 512); mbar_init(stdone, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(xready(s), 1); mbar_init(dyready(s), 512); mbar_init(wfree(s), 1);
       mbar_init(dxfull(s, 0), 1); mbar_init(dxfull(s, 1), 1);
@@ -972,6 +979,24 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       wgrad(a.NB - 1);
       umma_commit(wdone);
       dgrad(a.NB - 1);
+      if (!ONE && a.images) {
+        // fused stem backward: D[tap (M rows 0..31; 32..127 junk M-groups)][co] += A_w[pixel][tap]^T * G_w[pixel][co], both MN-major,
+        // per image 2 halves x 4 window positions x 8 k-steps of 16 pooled pixels (the order of k_stem_tc_bwd: bit-identical partials)
+        constexpr uint32_t idesc_s = make_idesc(128, C, 1, 1);
+        for (int s = 0; s < nslots; ++s) {
+          mbar_wait(stfull, (uint32_t)(s & 1));
+          tc_fence_after();
+#pragma unroll 1
+          for (int hw = 0; hw < 8; ++hw) {              // hw = half * 4 + window
+            const uint32_t at = a_smem + ((hw >> 2) * 8 + (hw & 3)) * 8192, gt = at + 4 * 8192;
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks)
+              umma_bf16(tmem_base + ACCW + 3 * C, make_sdesc(at + ks * 1024, 8192, 512, 4), make_sdesc(gt + ks * 1024, 8192, 512, 4), idesc_s,
+                        (s | hw | ks) != 0);
+          }
+          umma_commit(stdone);
+        }
+      }
     }
   } else {
     // ===== epilogue: 16 warps; warp = (channel half h, tile m, TMEM lane quarter q); thread = one pixel x 16 channels, of =====
@@ -1003,6 +1028,7 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
     auto y_chunk = [&](int s, int j) -> uint4 { return ybuf[(s * 2 + j) * 512 + et]; };
     load_y(a.NB - 1);                                 // the longest latency of the prologue (DRAM) goes first
     uint32_t gpk[2][8];                               // dL/d(out) of this thread's pixel and channels, per image slot, bf16 pairs
+    uint4 st_idx[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};   // fused stem backward: this thread's 16 arg-max bytes per slot
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
 #pragma unroll
@@ -1148,6 +1174,28 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       }
       if (tr) tr[5] = clock64();
       if (k > 0 && !a.dbg_skip) load_y(k - 1);          // y_k is dead: fetch the next block's rows while the dgrad MMAs run
+      if (!ONE && k == 0 && a.images) {
+        // fused stem backward: the y prefetch buffers are dead from here on -- this CTA's (zero-padded, fp32) images go there while
+        // the last dgrad runs, and this thread's arg-max bytes into registers
+        asm volatile("bar.sync 1, 512;" ::: "memory");                           // every thread is past its last read of ybuf
+        float* im_gen = reinterpret_cast<float*>(ybuf);
+        const uint32_t im_s = smem_u32(im_gen);
+        for (int c = et; c < nslots * 768; c += 512) {                           // 768 16-byte chunks per image
+          const int s_ = c / 768, qq = c % 768, ci = qq >> 8, r = (qq >> 3) & 31, c4 = qq & 7;
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(im_s + (uint32_t)((s_ * 4080 + (ci * 34 + r + 1) * 40 + 4 + c4 * 4) * 4)),
+                       "l"(a.images + (size_t)(s_ == 0 ? img0 : img1) * 3072 + ci * 1024 + r * 32 + c4 * 4) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        for (int i = et; i < 2016; i += 512) {                                    // halo of both slots: rows 0 / 33, columns 0..3 / 36..39
+          int off;
+          if (i < 480) { const int s_ = i / 240, rem = i % 240, ci = rem / 80, rr = (rem % 80) / 40, c = rem % 40; off = s_ * 4080 + (ci * 34 + rr * 33) * 40 + c; }
+          else { const int j = i - 480, s_ = j / 768, rem = j % 768, ci = rem / 256, r = 1 + (rem % 256) / 8, cc = rem % 8; off = s_ * 4080 + (ci * 34 + r) * 40 + (cc < 4 ? cc : 32 + cc); }
+          im_gen[off] = 0.f;
+        }
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+          if (s < nslots) st_idx[s] = *reinterpret_cast<const uint4*>(a.idx0 + (size_t)(s == 0 ? img0 : img1) * NRD_PIX * C + pix_off);
+      }
       // ---- weight-gradient partial of this CTA: accumulator lanes (j, ci), columns (kxb, co) ----
       if (it == a.NB - 1 && h == 0 && m == 0) {
         mbar_wait(wdone, 0);
@@ -1193,6 +1241,105 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
       if (tr) tr[6] = clock64();
     }
     if (blockIdx.x == 0 && ew == 0) { a.dgamma[lane] = dg_acc; a.dbeta[lane] = db_acc; }
+    if (!ONE && a.images) {
+      // ===== fused stem backward: conv1's weight / bias gradient of this CTA's images (model/resnet.py:16 under main.py:38) =====
+      // dL/dx_0 is in gpk (this thread's pixel x 16 channels), x_0 still in the x tile of the last block (k = 0), the images
+      // in the y buffers.  Per image: 4 im2col tiles A_w [128 pooled pixels][27 taps + 1] and 4 masked-gradient tiles G_w
+      // [128 pooled pixels][C] per half image, as in k_stem_tc_bwd; the tiles take over the (dead) dy / x slots.
+      uint32_t x0r[2][8];
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+        if (s < nslots) {
+          const uint8_t* xt = gen_base + s * SLOT_BYTES + DY_BYTES;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int ch = h * 2 + j;
+            const uint4 v = *reinterpret_cast<const uint4*>(xt + P1 * 64 + ((ch ^ ((P1 >> 1) & 3)) << 4));
+            x0r[s][j * 4] = v.x; x0r[s][j * 4 + 1] = v.y; x0r[s][j * 4 + 2] = v.z; x0r[s][j * 4 + 3] = v.w;
+          }
+        }
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      asm volatile("bar.sync 1, 512;" ::: "memory");     // x_0 read, images landed, every dgrad MMA consumed (each thread waited for its tile)
+      const float* im_gen = reinterpret_cast<const float*>(ybuf);
+      const int hh = pi >> 3, pl = (pi & 7) * 16 + pj, sw = (pl >> 1) & 3;        // half image, row inside its tiles, its swizzle
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {                      // (unrolled: gpk / x0r / st_idx stay in registers)
+        if (s >= nslots) break;
+        if (s > 0) mbar_wait(stdone, 0u);                // the previous image's MMAs have read the tiles
+        const float* im = im_gen + s * 4080;
+        // A rows of window positions w = 2h, 2h + 1 (the other channel-half thread of this pixel builds the other two)
+        {
+          float patch[3][4][4];
+#pragma unroll
+          for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+              for (int cc = 0; cc < 4; ++cc) patch[ci][rr][cc] = im[(ci * 34 + 2 * pi + rr) * 40 + 3 + 2 * pj + cc];
+          auto rows = [&](auto HC) {                     // windows 2H, 2H + 1: static indices into the patch (h is warp-uniform)
+            constexpr int H = decltype(HC)::value;
+#pragma unroll
+          for (int wi = 0; wi < 2; ++wi) {
+            constexpr int dy_ = H;
+            const int w = H * 2 + wi, dx_ = wi;
+            float kv[32];
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+              for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+                for (int kx = 0; kx < 3; ++kx) kv[ci * 9 + ky * 3 + kx] = patch[ci][dy_ + ky][dx_ + kx];
+            kv[27] = 1.0f; kv[28] = kv[29] = kv[30] = kv[31] = 0.f;             // tap 27 = 1: accumulator row 27 is the bias gradient
+            uint8_t* row = gen_base + (hh * 8 + w) * 8192 + pl * 64;
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) {
+              uint32_t pk[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const __nv_bfloat162 hv = __floats2bfloat162_rn(kv[ch * 8 + 2 * e], kv[ch * 8 + 2 * e + 1]);
+                pk[e] = *reinterpret_cast<const uint32_t*>(&hv);
+              }
+              *reinterpret_cast<uint4*>(row + ((ch ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+          }
+          };
+          if (h == 0) rows(std::integral_constant<int, 0>{}); else rows(std::integral_constant<int, 1>{});
+        }
+        // G rows: this thread's 16 channels of its pixel, for each window position: dL/dx_0 where that position was the arg-max and x_0 > 0
+        {
+          const uint8_t* ib = reinterpret_cast<const uint8_t*>(&st_idx[s]);
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            uint8_t* row = gen_base + (hh * 8 + 4 + w) * 8192 + pl * 64;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              uint32_t o4[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const int c = j * 8 + 2 * e;
+                const uint32_t g2 = gpk[s][j * 4 + e], x2 = x0r[s][j * 4 + e];
+                const bool k0 = ib[c] == w && (x2 & 0x7FFFu) != 0, k1 = ib[c + 1] == w && (x2 & 0x7FFF0000u) != 0;
+                o4[e] = (k0 ? (g2 & 0xFFFFu) : 0u) | (k1 ? (g2 & 0xFFFF0000u) : 0u);
+              }
+              *reinterpret_cast<uint4*>(row + (((h * 2 + j) ^ sw) << 4)) = make_uint4(o4[0], o4[1], o4[2], o4[3]);
+            }
+          }
+        }
+        fence_proxy_async();
+        mbar_arrive(stfull);
+      }
+      if (ew == 2) {                                     // warp 4: the TMEM lane quarter 0 (warp % 4 == 0) = lanes 0..31 = taps (27 + bias row)
+        mbar_wait(stdone, (uint32_t)((nslots - 1) & 1));
+        tc_fence_after();
+        float v[32];
+        tmem_ld32(tmem_base + ACCW + 3 * C, v);
+        if (lane < 28) {
+          float4* dst = reinterpret_cast<float4*>(a.stem_partial + ((size_t)blockIdx.x * 28 + lane) * C);
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) dst[c4] = make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
+        }
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -1373,7 +1520,7 @@ constexpr size_t persist_smem(int one) {
 }
 
 constexpr size_t persist_bwd_smem(int one) {
-  return 1024 + 2 * ((one ? 21 * 1024 : 3 * Cfg<32>::BUF_BYTES) + Cfg<32>::BUF_BYTES) + 9 * Cfg<32>::WTAP_BYTES + 112 + (1024 + 96 + 256) * sizeof(float) + (2048 + 256) * sizeof(double) + 4 * 512 * 16 + 64;
+  return 1024 + 2 * ((one ? 21 * 1024 : 3 * Cfg<32>::BUF_BYTES) + Cfg<32>::BUF_BYTES) + 9 * Cfg<32>::WTAP_BYTES + 128 + (1024 + 96 + 256) * sizeof(float) + (2048 + 256) * sizeof(double) + 4 * 512 * 16 + 64;
 }
 
 static int items(const nrd_plan* p) { return p->B * (p->C == 32 ? 1 : 2); }
@@ -1515,7 +1662,7 @@ int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int t
 
 // all NB residual blocks of the backward in ONE cooperative launch: g_in = dL/dx_NB -> dx0_out = dL/dx_0, dgamma, dbeta,
 // per-CTA weight-gradient partials (reduced by k_wgrad_reduce)
-int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cudaStream_t st) {
+int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, const float* stem_images, cudaStream_t st) {
   NRD_REQUIRE(p->tc_ready && p->tc_persist_fwd, "persistent block-stack backward not available for this plan");
   PersistBwdArgs a;
   a.gamma = p->params + p->off[3]; a.scale_shift = p->scale_shift; a.saved = p->saved_stats;
@@ -1524,6 +1671,8 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cud
   a.acc = p->bn_acc + (size_t)32 * NRD_ACC_ROW; a.wpartial = p->wgrad_partial; a.gbar = p->gbar + NRD_GBAR_PERSIST_BWD;
   a.B = p->B; a.NB = p->NB; a.act_elems = p->act_elems; a.trace = (long long*)p->trace_bwd; a.dbg_skip = p->dbg_skip_stores; a.inv_count = 1.0 / ((double)p->B * NRD_PIX);
   a.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS);
+  const bool stem_here = stem_images != nullptr && !(p->one_copy & 2);
+  a.images = stem_here ? stem_images : nullptr; a.idx0 = p->idx0; a.stem_partial = p->stem_partial;
   void* args[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&a};
   if (p->one_copy & 2) NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist<1>, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(1), st));
   else NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_persist<0>, dim3(conv_grid(p)), dim3(576), args, persist_bwd_smem(0), st));

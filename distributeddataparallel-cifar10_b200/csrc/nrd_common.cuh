@@ -202,6 +202,7 @@ struct nrd_plan {
   int64_t off[10];
   const float* images_last;  // images of the last nrd_forward (stem backward reads them)
   const float* dp_for;       // dlogits pointer whose d(pooled) nrd_forward_loss already computed (consumed by nrd_backward_body)
+  int fuse_stem_bwd;         // option: the persistent backward also computes conv1's weight / bias gradient partials (no stem backward kernel)
   int fuse_stem;             // option: the persistent forward computes x_0 itself (no stem kernel, no x_0 round trip)
   int fuse_pool;             // option: the persistent forward's last block also does the max-pool in front of fc1
   int fuse_head_tail;        // option: fc2 + loss + fc1 dgrad in one launch inside nrd_forward_loss
@@ -449,6 +450,7 @@ int nrd_tc_wgrad_blocks(const nrd_plan* p);
 int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int training, cudaStream_t st);   // x_0 -> all y_k, x_{k+1}
                                                                                 // (stem_images: compute x_0 from the images first)
                                                                                 // (pool: also maxpool2(x_NB) -> pooled, idx2)
-int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, cudaStream_t st);   // all blocks' backward, one launch;
+int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, const float* stem_images, cudaStream_t st);   // all blocks' backward, one launch
+                                                                            // (stem_images: also conv1's weight-gradient partials, no stem kernel);
                                                                             // g_pooled = dL/d(pooled) [B,8,8,C]
 int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st);                      // y_k, x_{k+1}, BN stats + EMA, one launch

@@ -1973,6 +1973,8 @@ extern "C" int nrd_plan_create(nrd_plan** out, int device, int B, int C, int NB,
   p->use_tc_stem = 1;
   p->fuse_head_tail = 1;
   p->one_copy = 1;           // forward only: in the backward the one-pixel-apart N groups of the weight gradient measured 2 us slower
+  p->fuse_stem_bwd = 0;      // conv1's weight-gradient partials in the persistent backward's tail: bit-identical, measured +-0 (the tail
+                             // costs the 2-image CTAs ~8 us, what the stand-alone kernel costs behind its programmatic launch)
   p->fuse_stem = 0;          // measured: as long as the stem kernel it replaces (its four half images run one after the other)
   p->fuse_pool = 0;          // measured 1 us slower per step than pooling in the fc1 kernel (it sits on the blocks' critical path)
   { const char* e = getenv("NRD_POLL_NS"); p->poll_ns = e ? atoi(e) : 0; }
@@ -2019,6 +2021,7 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_HEAD_TAIL: p->fuse_head_tail = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_FUSE_POOL: p->fuse_pool = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_FUSE_STEM: p->fuse_stem = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_FUSE_STEM_BWD: p->fuse_stem_bwd = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_ONE_COPY: p->one_copy = value & 3; return NRD_OK;
     case NRD_OPT_RESERVE_SMS:
       NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
@@ -2314,15 +2317,16 @@ extern "C" int nrd_backward(nrd_plan* p, const float* dlogits, void* stream) {
 }
 
 // fixed-order reduce of the conv / stem partials into the flat gradient vector (+ exchange push, + fused optimizer step)
-static int launch_body_reduce(nrd_plan* p, cudaStream_t st) {
+static int launch_body_reduce(nrd_plan* p, int stem_rows, int after_persistent, cudaStream_t st) {
   const int B = p->B, C = p->C;
   nrd_upd_args u = {};
   if (p->upd_lr > 0.f) {
     u.params = p->params; u.step_scale = p->upd_lr * p->upd_inv_world;
     u.w_fwd = p->w_fwd; u.w_dgrad = p->w_dgrad; u.wtc_fwd = p->wtc_fwd; u.wtc_dgrad = p->wtc_dgrad; u.conv1_wp = p->conv1_wp;
   }
-  NRD_CHECK_CUDA(nrd_launch_pdl(k_body_reduce, dim3((9 * C * C + 28 * C) / 64), dim3(256), 0, st, (p->pdl >> 2) & 1, (const float*)p->wgrad_partial,
-                                p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B), (const float*)p->stem_partial, stem_bwd_blocks(B), C,
+  // directly behind a persistent kernel a programmatic dependent would only sit on the SMs and wait (measured: slower), see NRD_OPT_PDL
+  NRD_CHECK_CUDA(nrd_launch_pdl(k_body_reduce, dim3((9 * C * C + 28 * C) / 64), dim3(256), 0, st, after_persistent ? (p->pdl >> 1) & 1 : (p->pdl >> 2) & 1, (const float*)p->wgrad_partial,
+                                p->conv_impl != NRD_CONV_CUDA_CORE ? nrd_tc_wgrad_blocks(p) : wgrad_blocks(B), (const float*)p->stem_partial, stem_rows, C,
                                 p->grads, p->bn_sync, (const float*)p->bn_running, p->bn_sync_contrib, p->xchg,
                                 (int)p->off[P_BNG], (int)p->off[P_RBW], (int)p->off[P_C1W], (int)p->off[P_C1B], u, p->dbg));
   LAUNCH_CHECK();
@@ -2339,6 +2343,7 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   char* g = p->dxa; char* gn = p->dxb;
   const int K = 64 * C;
   const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd;
+  const bool stem_in_blocks = persist && p->fuse_stem_bwd && p->tc_stem && p->use_tc_stem && !(p->one_copy & 2) && p->images_last != nullptr;
   if (persist && p->dp_for == dlogits) p->dp_for = nullptr;      // nrd_forward_loss already left d(pooled) in the dx scratch
   else if (persist) NRD_CHECK_CUDA(nrd_launch_pdl(k_fc1_dgrad_pooled<bf16>, dim3(((B + 7) / 8) * (K / 256)), dim3(256), 0, st, p->pdl & 1, dlogits, p->h1,
                                              PRM(P_FC2W), p->w1p, (bf16*)g, B, C));
@@ -2348,7 +2353,7 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   // residual blocks, last to first; the shared block's grads accumulate over the NB applications
   nrd_tl_mark(p, st, "fork/dgrad_fc1");
   if (persist) {
-    NRD_TRY(nrd_tc_backward_blocks(p, g, gn, st));
+    NRD_TRY(nrd_tc_backward_blocks(p, g, gn, stem_in_blocks ? p->images_last : nullptr, st));
     char* t = g; g = gn; gn = t;
     nrd_tl_mark(p, st, "bwd_blocks");
   }
@@ -2368,10 +2373,11 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
     char* t = g; g = gn; gn = t;
   }
   p->dx0_last = g;
-  if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_bwd(p, p->images_last, g, st));
+  if (stem_in_blocks) {}                                         // conv1's partials came out of the persistent backward
+  else if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_bwd(p, p->images_last, g, st));
   else NRD_TRY(stem_bwd_any(p->images_last, g, p->xs, p->idx0, GRD(P_C1W), GRD(P_C1B), B, C, dt, p->stem_partial, st, false));
   nrd_tl_mark(p, st, "stem_bwd");
-  NRD_TRY(launch_body_reduce(p, st));
+  NRD_TRY(launch_body_reduce(p, stem_in_blocks ? nrd_tc_wgrad_blocks(p) : stem_bwd_blocks(p->B), stem_in_blocks ? 1 : 0, st));
   nrd_tl_mark(p, st, "body_reduce(+sgd)");
   return NRD_OK;
 }
@@ -2425,7 +2431,7 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       return nrd_tc_forward_blocks(p, 0, nullptr, 0, st);
     case NRD_OP_BWD_BLOCKS:
       NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent backward not available for this plan");
-      return nrd_tc_backward_blocks(p, p->dxa, p->dxb, st);
+      return nrd_tc_backward_blocks(p, p->dxa, p->dxb, nullptr, st);
     case NRD_OP_BLOCK_FWD:
       NRD_REQUIRE(p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_fused_fwd, "fused block forward not available for this plan");
       return nrd_tc_block_fwd(p, k, st);
@@ -2439,7 +2445,7 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       // timing only: no exchange (the peers are not running this) and no optimizer step
       const float lr = p->upd_lr; const int world = p->xchg.world;
       p->upd_lr = 0.f; p->xchg.world = 0;
-      const int r = launch_body_reduce(p, st);
+      const int r = launch_body_reduce(p, stem_bwd_blocks(p->B), 0, st);
       p->upd_lr = lr; p->xchg.world = world;
       return r;
     }

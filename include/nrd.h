@@ -106,6 +106,11 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
  * column-haloed operand copy per image (a tap is a pixel-granular descriptor start) instead of three kx-shifted copies.
  * Measured: forward -1 us; backward +2 us (its weight-gradient MMAs read N groups one pixel apart), hence off there. */
 #define NRD_OPT_ONE_COPY 10
+/* NRD_OPT_FUSE_STEM_BWD (default 0: bit-identical, measured no faster -- 195.1 vs 194.4 us per step): the persistent backward also computes conv1's weight / bias gradient (model/resnet.py:16 under
+ * main.py:38) of its images in its tail -- dL/dx_0 is in its registers, x_0 in its shared memory -- as the same tcgen05 GEMM
+ * over the same tiles, in the same order as the stem backward kernel it replaces (bit-identical partials at equal grids);
+ * 0 = the stand-alone stem backward kernel. */
+#define NRD_OPT_FUSE_STEM_BWD 12
 /* NRD_OPT_TIMELINE (default 0): measurement aid.  An event is recorded behind every kernel of the step's main stream -- an
  * event-record NODE when the step is being captured -- and nrd_plan_timeline() reads the intervals after a (replayed) step:
  * the step kernel by kernel in its real context (warm L2, side stream running).  The marks serialise neighbouring kernels

@@ -245,3 +245,24 @@ def test_one_copy_operand_layouts_match_three_copy_layouts(B):
     # forward layout fixed: the backward layouts see identical inputs and must agree closely
     for k in res[1][1]:
         assert rell2(res[2][1][k], res[1][1][k]) < 1e-2 and cosine(res[2][1][k], res[1][1][k]) > 0.9999, k
+
+
+@pytest.mark.parametrize("B", [256, 149, 40])
+def test_fused_stem_backward_equals_stem_kernel_bitwise(B, monkeypatch):
+    """NRD_OPT_FUSE_STEM_BWD (an option kept with its numbers: measured no faster): conv1's weight / bias gradient computed in the persistent backward's tail (from dL/dx_0 in registers
+    and x_0 in shared memory) against the stand-alone stem backward kernel: same tiles, same MMA order, same CTA -> image map,
+    hence bit-identical partials and gradients (and an identical step)."""
+    import ddp_cifar10_b200 as nrd
+    g = torch.Generator().manual_seed(17)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for fused in ("0", "1"):
+        monkeypatch.setenv("NRD_FUSE_STEM_BWD", fused)
+        torch.manual_seed(4)
+        m = nrd.NetResDeep(32, 10, dtype="bf16").to(DEV)
+        step = nrd.TrainStep(m, B, lr=1e-2)
+        losses = [float(step(x, y)) for _ in range(2)]
+        res.append((losses, m.engine.flat_grads.clone(), m.engine.flat_params.clone()))
+    off = m.engine.offsets
+    assert float(res[0][1][off[0]:off[2]].abs().sum()) > 0
+    assert res[0][0] == res[1][0] and torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2])

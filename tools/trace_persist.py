@@ -34,7 +34,10 @@ if int(st[0, 0]) != 0:
 
 # ---- backward ----
 y = torch.randint(0, 10, (B,), device=dev)
-out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+step = nrd.TrainStep(m, B, lr=1e-3, use_graph=False)          # the graph path's backward (fused stem backward when on)
+check(lib.nrd_plan_set_option(step.plan.handle, 2, 1))
+pl = step.plan
+step(x, y)
 torch.cuda.synchronize()
 trb = pl.tensor_view(2, 0).view(torch.int64)[: grid * 10 * 16].view(grid, 10, 16).cpu()
 namesb = ["start", "phaseA", "pre-barrier", "post-barrier", "combined", "phaseB(dy ready)", "phaseC(dx)"]
