@@ -8,7 +8,7 @@ LIB_PATH = os.path.join(HERE, "libnrd.so")
 NRD_F32, NRD_BF16 = 0, 1
 LOSS_RING = 8          # NRD_LOSS_RING (include/nrd.h)
 CONV_CUDA_CORE, CONV_TCGEN05, CONV_TCGEN05_UNFUSED = 0, 1, 2
-OPT_FUSE_BN_BWD, OPT_PERSIST_FWD, OPT_TRACE, OPT_PERSIST_BWD, OPT_TC_STEM, OPT_RESERVE_SMS, OPT_PDL, OPT_HEAD_TAIL, OPT_FUSE_POOL, OPT_FUSE_STEM, OPT_ONE_COPY, OPT_TIMELINE, OPT_FUSE_STEM_BWD = range(13)
+OPT_FUSE_BN_BWD, OPT_PERSIST_FWD, OPT_TRACE, OPT_PERSIST_BWD, OPT_TC_STEM, OPT_RESERVE_SMS, OPT_PDL, OPT_HEAD_TAIL, OPT_FUSE_POOL, OPT_FUSE_STEM, OPT_ONE_COPY, OPT_TIMELINE, OPT_FUSE_STEM_BWD, OPT_STREAM = range(14)
 
 
 class NrdError(RuntimeError):

@@ -812,6 +812,290 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
 }
 
 // ============================================================================================
+// Streaming persistent forward: ALL residual blocks, ANY batch size (C = 32, cooperative launch) -- the kernel for batches
+// beyond the two images per CTA that k_tc_fwd_persist keeps on chip.  A CTA owns images j = 0 .. n-1 (blockIdx.x + j * grid) and
+// streams them through two haloed operand slots per block:
+//   phase 1, per image   DMA thread: x_k[img] by ONE TMA load (18 x 18 box, halo zero-filled) into operand slot j & 1;
+//                        MMA warp: 36 tcgen05.mma into TMEM slot j & 3;  epilogue: BN sums straight from TMEM (accumulated over
+//                        the CTA's images), y_k staged and bulk-stored
+//   exchange             the count-carrying fixed-point words of k_tc_fwd_persist
+//   phase 2, per image   epilogue: x_{k+1} = relu(bn(y_k)) + x_k from the STORED y_k and x_k (this thread's own 32 B of each, L2
+//                        hits: written / loaded a few microseconds earlier), staged and bulk-stored: the next block's TMA source
+// so every tensor crosses L2 once per use and HBM at most once, with ONE launch for the whole stack and no per-block kernel
+// boundary (the per-block path it replaces: one fused launch per block, accumulators of <= 8 images per CTA).
+// 576 threads: warp 0 lane 0 = DMA (TMA loads and bulk stores), warp 1 lane 0 = MMA issue, 16 epilogue warps as in
+// k_tc_fwd_persist<1> (thread = one pixel x 16 channels; pixel tile m = columns 8m .. 8m+7 of all 16 rows).
+// ============================================================================================
+constexpr int STREAM_NSLOT = 4;          // haloed operand slots of the streaming kernels (21 KB each)
+struct StreamFwdArgs {
+  const float* gamma; const float* beta;
+  float* saved; float* scale_shift; float* running; long long* nbt;
+  const bf16* xs; const bf16* ys;             // the x_k / y_k stacks (phase 2 reads this thread's own pixels back)
+  unsigned long long* acc;
+  int B, NB;
+  size_t act_elems;
+  double inv_count, unbias;
+  int poll_ns;
+  unsigned int* status;
+};
+
+__global__ void __launch_bounds__(576, 1)
+k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmXst,
+                const __grid_constant__ CUtensorMap tmYst, StreamFwdArgs a) {
+  constexpr int C = 32;
+  using K = Cfg<C>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+  constexpr int PITCH = 18, SLOT_BYTES = 21 * 1024, YST_BYTES = NRD_PIX * C * 2, NSLOT = STREAM_NSLOT;
+  const uint32_t a_smem = base;                                    // NSLOT operand slots
+  const uint32_t w_smem = a_smem + NSLOT * SLOT_BYTES;             // 9 taps
+  const uint32_t y_smem = w_smem + 9 * K::WTAP_BYTES;              // 2 y staging tiles
+  const uint32_t xst_smem = y_smem + 2 * YST_BYTES;                // 2 x staging tiles
+  const uint32_t bar0 = xst_smem + 2 * YST_BYTES;
+  const uint32_t wfull = bar0;
+  auto xfull = [&](int s) { return bar0 + 8u * (1 + s); };         // operand slot loaded (TMA bytes)
+  auto opfree = [&](int s) { return bar0 + 8u * (5 + s); };        // the MMAs that read operand slot s are done
+  auto tfull = [&](int t, int m) { return bar0 + 8u * (9 + t * 2 + m); };   // accumulator (TMEM slot t, tile m) ready
+  auto tfree = [&](int t) { return bar0 + 8u * (17 + t); };        // pass 1 has read TMEM slot t (512 arrivals)
+  auto yready = [&](int s) { return bar0 + 8u * (21 + s); };       // y staged (512)
+  auto xready = [&](int s) { return bar0 + 8u * (23 + s); };       // x staged (512)
+  auto yfree = [&](int s) { return bar0 + 8u * (25 + s); };        // the bulk store has read y staging tile s
+  auto xfree = [&](int s) { return bar0 + 8u * (27 + s); };
+  const uint32_t p1done = bar0 + 8u * 29;                          // every y store of this block's phase 1 is complete
+  const uint32_t tmem_slot = bar0 + 8u * 30;
+  constexpr int BAR_BYTES = 8 * 32;
+  constexpr int MISC_OFF = NSLOT * SLOT_BYTES + 9 * K::WTAP_BYTES + 4 * YST_BYTES + BAR_BYTES;
+  float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][sum | sum of squares][16 channels]
+  float* ss_sm = red + 1024;                                             // [2C] scale | shift of the current block
+  volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nimg = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;      // images of this CTA (>= 1)
+  auto img_of = [&](int j) { return (int)blockIdx.x + j * (int)gridDim.x; };
+  constexpr uint32_t TMEM_COLS = 256;                              // 4 image slots x 2 tiles x 32 columns
+  // Slots rotate over the GLOBAL image counter g = k * nimg + j (operand slot g % NSLOT, TMEM slot g & 3, staging tile g & 1), so
+  // the n-th use of a slot is g / slots and every mbarrier parity follows from g alone.
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX18); tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmXst); tma_prefetch_desc(&tmYst);
+    mbar_init(wfull, 1); mbar_init(p1done, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(yready(s), 512); mbar_init(xready(s), 512); mbar_init(yfree(s), 1); mbar_init(xfree(s), 1); }
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(xfull(s), 1); mbar_init(opfree(s), 1); }
+    for (int t = 0; t < 4; ++t) { mbar_init(tfull(t, 0), 1); mbar_init(tfull(t, 1), 1); mbar_init(tfree(t), 512); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_gen;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== DMA thread =====
+      mbar_expect_tx(wfull, 9 * K::WTAP_BYTES);
+      for (int t = 0; t < 9; ++t) tma_load_2d(w_smem + t * K::WTAP_BYTES, &tmW, wfull, t * C, 0);
+      auto load = [&](int k, int j) {
+        const int g = k * nimg + j, s = g % NSLOT, u = g / NSLOT;
+        if (u > 0) mbar_wait(opfree(s), (u - 1) & 1);              // the previous occupant's MMAs are done
+        mbar_expect_tx(xfull(s), PITCH * PITCH * 64);
+        tma_load_5d(a_smem + s * SLOT_BYTES, &tmX18, xfull(s), 0, -1, -1, img_of(j), k);   // box 18 x 18: halo zero-filled
+      };
+      const int npre = nimg < NSLOT ? nimg : NSLOT;                // loads issued ahead of a block's first MMA
+      for (int j = 0; j < npre; ++j) load(0, j);
+      for (int k = 0; k < a.NB; ++k) {
+        // phase 1: NSLOT loads ahead, y stores behind
+        for (int j = 0; j < nimg; ++j) {
+          const int g = k * nimg + j, s = g & 1;
+          if (j + NSLOT < nimg) load(k, j + NSLOT);                // as soon as image j's MMAs have read the slot
+          mbar_wait(yready(s), (g >> 1) & 1);
+          tma_store_5d(&tmYst, y_smem + s * YST_BYTES, 0, 0, 0, img_of(j), k);
+          bulk_commit(); bulk_wait_read0();
+          mbar_arrive(yfree(s));
+        }
+        bulk_wait0();                                              // y_k is in memory: phase 2 reads it back
+        fence_proxy_async();
+        mbar_arrive(p1done);
+        // phase 2: x_{k+1} stores; the next block's first operands are requested as soon as their stores are complete
+        const bool more = k + 1 < a.NB;
+        for (int j = 0; j < nimg; ++j) {
+          const int g = k * nimg + j, s = g & 1;
+          mbar_wait(xready(s), (g >> 1) & 1);
+          tma_store_5d(&tmXst, xst_smem + s * YST_BYTES, 0, 0, 0, img_of(j), k + 1);
+          bulk_commit(); bulk_wait_read0();
+          mbar_arrive(xfree(s));
+          if (more && j >= 1 && j - 1 < npre) { bulk_wait1(); load(k + 1, j - 1); }
+        }
+        bulk_wait0();                                              // x_{k+1} is in memory
+        fence_proxy_async();
+        if (more && nimg - 1 < npre) load(k + 1, nimg - 1);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===== MMA issuer =====
+      constexpr uint32_t idesc = make_idesc(128, C, 0, 0);
+      mbar_wait(wfull, 0);
+      const int total = a.NB * nimg;
+      for (int g = 0; g < total; ++g) {
+        const int s = g % NSLOT, t = g & 3;
+        mbar_wait(xfull(s), (g / NSLOT) & 1);
+        if (g >= 4) mbar_wait(tfree(t), ((g >> 2) - 1) & 1);       // pass 1 has read this TMEM slot's previous accumulators
+        tc_fence_after();
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const uint32_t d_tmem = tmem_base + (t * 2 + m) * C;
+#pragma unroll
+          for (int tp = 0; tp < 9; ++tp) {
+            const uint32_t a_addr = a_smem + s * SLOT_BYTES + ((tp / 3) * PITCH + m * 8 + (tp % 3)) * 64;
+            const uint64_t ad = make_sdesc(a_addr, 16, PITCH * 64, K::LAYOUT);
+            const uint64_t bd = make_sdesc(w_smem + tp * K::WTAP_BYTES, 16, K::SBO, K::LAYOUT);
+#pragma unroll
+            for (int kk = 0; kk < K::KSTEPS; ++kk) umma_bf16(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (tp | kk) != 0);
+          }
+          umma_commit(tfull(t, m));
+        }
+        umma_commit(opfree(s));
+      }
+    }
+  } else {
+    // ===== epilogue: 16 warps; warp = (channel half h, tile m, TMEM lane quarter q); thread = one pixel x 16 channels =====
+    const int ew = warp - 2, h = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
+    const int pi = q * 4 + (lane >> 3), pj = m * 8 + (lane & 7);
+    const int P0y = pi * 16 + pj;                                                    // pixel index inside a staging tile
+    const size_t pix_off = (size_t)P0y * C + h * 16;                                 // this thread's 16 channels inside an image
+    const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + t * 2C
+    const uint32_t st_off = P0y * 64;                                                // this pixel's 64-byte row of a staging tile
+    const uint32_t st_c0 = ((h * 2 + 0) ^ ((P0y >> 1) & 3)) << 4, st_c1 = ((h * 2 + 1) ^ ((P0y >> 1) & 3)) << 4;
+    const float* ss_w = ss_sm + h * 16;
+    const float gamma_r = a.gamma[lane], beta_r = a.beta[lane];
+    if (blockIdx.x == 0 && ew == 0) {            // the last row of the previous launch (see k_tc_fwd_persist)
+      unsigned long long* last = a.acc + (size_t)(a.NB - 1) * NRD_ACC_ROW;
+#pragma unroll
+      for (int r = 0; r < NRD_ACC_REPL; ++r) { last[NRD_ACC_IDX(r, lane)] = 0ull; last[NRD_ACC_IDX(r, C + lane)] = 0ull; }
+      __threadfence();
+    }
+    for (int k = 0; k < a.NB; ++k) {
+      // ---- phase 1: statistics of every image's accumulators, y_k staged for its bulk store ----
+      float ssum = 0.f, qsum = 0.f;
+      for (int j = 0; j < nimg; ++j) {
+        const int g = k * nimg + j, s = g & 1, t = g & 3;
+        mbar_wait(tfull(t, m), (g >> 2) & 1);
+        tc_fence_after();
+        float v[16];
+        tmem_ld16(my_tmem + t * 2 * C, v);
+        tc_fence_before();
+        mbar_arrive(tfree(t));                                     // the accumulators are in registers
+        uint4 ypk[2];
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&ypk[jj]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[jj * 8 + 2 * e], v[jj * 8 + 2 * e + 1]);
+        }
+        if (g >= 2) mbar_wait(yfree(s), ((g >> 1) - 1) & 1);       // the previous store has read this staging tile
+        uint8_t* yst = gen_base + (y_smem - base) + s * YST_BYTES + st_off;
+        *reinterpret_cast<uint4*>(yst + st_c0) = ypk[0]; *reinterpret_cast<uint4*>(yst + st_c1) = ypk[1];
+        fence_proxy_async();
+        mbar_arrive(yready(s));
+        {
+          float sq[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) sq[i] = v[i] * v[i];
+          qsum += warp_col_sum16(sq, lane);
+        }
+        ssum += warp_col_sum16(v, lane);
+      }
+      red[ew * 32 + (lane & 1) * 16 + (lane >> 1)] = (lane & 1) ? qsum : ssum;
+      asm volatile("bar.sync 1, 512;" ::: "memory");
+      unsigned long long* acc = a.acc + (size_t)k * NRD_ACC_ROW;
+      if (et < 2 * C) {
+        const int which = et >> 5, ch = et & 31;
+        float tsum = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) tsum += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
+        nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), tsum, 16777216.0, a.status), gridDim.x);
+      }
+      // phase 2's first operands travel during the exchange: x_k is final since the previous block; y_k needs p1done
+      const bf16* yk = a.ys + (size_t)k * a.act_elems + pix_off;
+      const bf16* xk = a.xs + (size_t)k * a.act_elems + pix_off;
+      uint4 yA[2], xA[2], yB[2], xB[2];
+      auto fetch_x = [&](uint4 (&xv)[2], int j) {
+        const uint4* px = reinterpret_cast<const uint4*>(xk + (size_t)img_of(j) * NRD_PIX * C);
+        xv[0] = __ldcg(px); xv[1] = __ldcg(px + 1);
+      };
+      auto fetch_y = [&](uint4 (&yv)[2], int j) {
+        const uint4* py = reinterpret_cast<const uint4*>(yk + (size_t)img_of(j) * NRD_PIX * C);
+        yv[0] = __ldcg(py); yv[1] = __ldcg(py + 1);
+      };
+      fetch_x(xA, 0);
+      if (nimg > 1) fetch_x(xB, 1);
+      if (ew == 0) {
+        unsigned long long ws, wq;
+        nrd_acc_wait2(acc + NRD_ACC_IDX(0, lane), acc + NRD_ACC_IDX(0, C + lane), gridDim.x, ws, wq, a.poll_ns);
+        if (blockIdx.x == 0 && k > 0) {
+#pragma unroll
+          for (int r = 0; r < NRD_ACC_REPL; ++r) { (acc - NRD_ACC_ROW)[NRD_ACC_IDX(r, lane)] = 0ull; (acc - NRD_ACC_ROW)[NRD_ACC_IDX(r, C + lane)] = 0ull; }
+        }
+        const double S = nrd_acc_value(ws, gridDim.x, 1.0 / 16777216.0), Q = nrd_acc_value(wq, gridDim.x, 1.0 / 16777216.0);
+        const double mean = S * a.inv_count;
+        double var = Q * a.inv_count - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float invstd = fast_invstd(var + (double)NRD_BN_EPS);
+        const float sc = gamma_r * invstd, sh = beta_r - (float)mean * sc;
+        ss_sm[lane] = sc; ss_sm[C + lane] = sh;
+        if (blockIdx.x == gridDim.x - 1) {
+          a.saved[(size_t)k * 2 * C + lane] = (float)mean; a.saved[(size_t)k * 2 * C + C + lane] = invstd;
+          a.scale_shift[(size_t)k * 2 * C + lane] = sc; a.scale_shift[(size_t)k * 2 * C + C + lane] = sh;
+          const double unbiased = var * a.unbias;
+          a.running[lane] = (1.f - NRD_BN_MOMENTUM) * a.running[lane] + NRD_BN_MOMENTUM * (float)mean;
+          a.running[C + lane] = (1.f - NRD_BN_MOMENTUM) * a.running[C + lane] + NRD_BN_MOMENTUM * (float)unbiased;
+          if (lane == 0) *a.nbt += 1;
+        }
+      }
+      mbar_wait(p1done, (uint32_t)(k & 1));                        // this block's y_k stores are complete
+      fetch_y(yA, 0);
+      if (nimg > 1) fetch_y(yB, 1);
+      asm volatile("bar.sync 1, 512;" ::: "memory");               // scale | shift of this block are in shared memory
+      // ---- phase 2: x_{k+1} = relu(bn(y_k)) + x_k from the stored tensors (this thread's own 32 B of each, two images in flight) ----
+      auto emit = [&](uint4 (&yv)[2], uint4 (&xv)[2], int j) {
+        const int g = k * nimg + j, s = g & 1;
+        uint4 ok[2];
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&yv[jj]);
+          const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xv[jj]);
+          __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok[jj]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int c = jj * 8 + 2 * e;
+            const float2 yr = __bfloat1622float2(yh[e]), xr = __bfloat1622float2(xh[e]);
+            const float2 sc2 = *reinterpret_cast<const float2*>(ss_w + c), sh2 = *reinterpret_cast<const float2*>(ss_w + C + c);
+            oh[e] = __floats2bfloat162_rn(fmaxf(fmaf(yr.x, sc2.x, sh2.x), 0.f) + xr.x, fmaxf(fmaf(yr.y, sc2.y, sh2.y), 0.f) + xr.y);
+          }
+        }
+        if (j + 2 < nimg) { fetch_y(yv, j + 2); fetch_x(xv, j + 2); }     // two images ahead, while this one is staged
+        if (g >= 2) mbar_wait(xfree(s), ((g >> 1) - 1) & 1);
+        uint8_t* xst = gen_base + (xst_smem - base) + s * YST_BYTES + st_off;
+        *reinterpret_cast<uint4*>(xst + st_c0) = ok[0]; *reinterpret_cast<uint4*>(xst + st_c1) = ok[1];
+        fence_proxy_async();
+        mbar_arrive(xready(s));
+      };
+      for (int j = 0; j < nimg; j += 2) {
+        emit(yA, xA, j);
+        if (j + 1 < nimg) emit(yB, xB, j + 1);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+}
+
+constexpr size_t stream_fwd_smem() { return 1024 + STREAM_NSLOT * 21 * 1024 + 9 * Cfg<32>::WTAP_BYTES + 4 * NRD_PIX * 32 * 2 + 8 * 32 + (1024 + 64) * sizeof(float) + 64; }
+
+// ============================================================================================
 // Persistent backward over ALL residual blocks (C = 32, at most 2 images per CTA, cooperative launch).
 // dL/dx of an image never leaves the SM: it lives in the epilogue threads' registers (bf16 pairs, the same rounding the
 // per-block kernels apply when they store it).  Per block k = NB-1 .. 0 and image:
@@ -1348,6 +1632,367 @@ k_tc_bwd_persist(const __grid_constant__ CUtensorMap tmXall, const __grid_consta
 }
 
 // ============================================================================================
+// Streaming persistent backward: ALL residual blocks, ANY batch size (C = 32, cooperative launch) -- k_tc_bwd_persist for batches
+// beyond two images per CTA.  dL/dx lives in ONE global buffer G [B,16,16,C] (bf16, the rounding k_tc_bwd_persist applies to its
+// registers), updated in place: a thread only ever reads and writes its own pixel's 16 channels of it, and an image's new value is
+// written after the dgrad MMAs that needed the old one.  A CTA owns images j = 0 .. n-1 (blockIdx.x + j * grid).  Per block
+// k = NB-1 .. 0:
+//   exchange   per-channel sums of dz and dz*y over the whole batch (count-carrying fixed-point words) -> dy coefficients
+//   B(j)       dy of image j from G and y_k (both prefetched one image ahead: G into registers, y_k by cp.async into a 3-deep ring
+//              of per-thread shared-memory slots) into the haloed dy copy of operand slot gi % 3
+//   MMA        dgrad (36 tcgen05.mma, TMEM slot gi & 1) and wgrad (16 tcgen05.mma against the x_k tile the DMA thread loaded into
+//              the same operand slot; ONE accumulator set over all blocks and images, one partial store per CTA)
+//   C(j)       dx = dgrad + g -> G, and phase A of block k-1 for the same image (y_{k-1} prefetched into the ring slot y_k left)
+// in the order B(0) B(1) C(0) B(2) C(1) ..., so image j's MMAs run under B(j+1).  Only block NB-1 has a stand-alone phase A: it
+// also builds dL/dx_NB from dL/d(pooled) through pool-2's arg-max and stores it to G.
+// L2 / HBM traffic per image and block: G read + written, y_k read twice (phase A one block earlier, then B), x_k read once.
+// ============================================================================================
+struct StreamBwdArgs {
+  const float* gamma;
+  const float* scale_shift;   // [NB][2C]
+  const float* saved;         // [NB][2C] mean | invstd
+  float* dgamma; float* dbeta;
+  const bf16* ys;             // y_0 .. y_NB-1
+  const bf16* g_pool;         // dL/d(pooled) [B,8,8,C]
+  const uint8_t* idx2;        // pool-2 argmax [B,8,8,C]
+  bf16* G;                    // dL/dx of the current block, in place; dL/dx_0 at exit
+  unsigned long long* acc;    // [NB] rows of count-carrying words
+  float* wpartial;            // [gridDim.x][9][C][C]
+  int B, NB;
+  size_t act_elems;
+  double inv_count;
+  int poll_ns;
+  unsigned int* status;
+};
+
+constexpr int STREAM_BWD_NS = 3;          // operand slots (dy copy + x_k tile)
+constexpr int STREAM_BWD_NY = 3;          // y ring depth (per-thread slots)
+
+__global__ void __launch_bounds__(576, 1)
+k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constant__ CUtensorMap tmWd, StreamBwdArgs a) {
+  constexpr int C = 32;
+  using K = Cfg<C>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+  constexpr int PITCH = 18, NS = STREAM_BWD_NS, NY = STREAM_BWD_NY;
+  constexpr int DY_BYTES = 21 * 1024;                             // one haloed copy (18*18*64 B rounded up)
+  constexpr int SLOT_BYTES = DY_BYTES + K::BUF_BYTES;             // + row-haloed x_k tile
+  const uint32_t a_smem = base;
+  const uint32_t w_smem = a_smem + NS * SLOT_BYTES;
+  const uint32_t bar0 = w_smem + 9 * K::WTAP_BYTES;
+  const uint32_t wfull = bar0, wdone = bar0 + 8u;
+  auto xready = [&](int s) { return bar0 + 8u * (2 + s); };       // x_k tile landed (TMA bytes)
+  auto dyready = [&](int s) { return bar0 + 8u * (6 + s); };      // dy written (512 arrivals)
+  auto wfree = [&](int s) { return bar0 + 8u * (10 + s); };       // the MMAs that read operand slot s are done
+  auto dxfull = [&](int t, int m) { return bar0 + 8u * (14 + t * 2 + m); };
+  const uint32_t tmem_slot = bar0 + 8u * 18;
+  constexpr int BAR_BYTES = 8 * 20;
+  constexpr int MISC_OFF = NS * SLOT_BYTES + 9 * K::WTAP_BYTES + BAR_BYTES;
+  float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][2][16] = 512 floats (1024 reserved)
+  float* bnp2 = red + 1024;                                              // 2 x 64 floats (scale/shift pairs, double-buffered) + 128 floats (dy coefficients)
+  uint4* ybuf = reinterpret_cast<uint4*>(bnp2 + 256);                    // [NY][2 chunks][512 threads]
+  volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nimg = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;      // images of this CTA (>= 1)
+  auto img_of = [&](int j) { return (int)blockIdx.x + j * (int)gridDim.x; };
+  const int total = a.NB * nimg;                                   // gi = it * nimg + j: operand slot gi % NS, TMEM slot gi & 1, y ring gi % NY
+  constexpr uint32_t TMEM_COLS = 256;                              // dgrad 2 x 2 x 32 columns + wgrad 3 x 32 columns
+  constexpr uint32_t ACCW = 128;
+  nrd_pdl_launch();
+
+  // the halo rows / columns of the dy copies are the convolution padding: zero everything once, never write them again
+  for (int i = threadIdx.x; i < NS * DY_BYTES / 16; i += blockDim.x) {
+    const int s = i / (DY_BYTES / 16), o = i % (DY_BYTES / 16);
+    reinterpret_cast<uint4*>(gen_base + s * SLOT_BYTES)[o] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async();
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmXall); tma_prefetch_desc(&tmWd);
+    mbar_init(wfull, 1); mbar_init(wdone, 1);
+    for (int s = 0; s < NS; ++s) { mbar_init(xready(s), 1); mbar_init(dyready(s), 512); mbar_init(wfree(s), 1); }
+    for (int t = 0; t < 2; ++t) { mbar_init(dxfull(t, 0), 1); mbar_init(dxfull(t, 1), 1); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_gen;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer: flipped weights once; the x_k tile of every (block, image), NS ahead of the MMAs =====
+      mbar_expect_tx(wfull, 9 * K::WTAP_BYTES);
+      for (int t = 0; t < 9; ++t) tma_load_2d(w_smem + t * K::WTAP_BYTES, &tmWd, wfull, t * C, 0);
+      int it = 0, j = 0;
+      for (int gi = 0; gi < total; ++gi) {
+        const int s = gi % NS, u = gi / NS;
+        if (u > 0) mbar_wait(wfree(s), (uint32_t)((u - 1) & 1));  // the wgrad MMAs that read the old tile are done
+        mbar_expect_tx(xready(s), K::BUF_BYTES);
+        tma_load_5d(a_smem + s * SLOT_BYTES + DY_BYTES, &tmXall, xready(s), 0, 0, -1, img_of(j), a.NB - 1 - it);
+        if (++j == nimg) { j = 0; ++it; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===== MMA issuer =====
+      constexpr uint32_t idesc_d = make_idesc(128, C, 0, 0);      // dgrad: both K-major
+      constexpr uint32_t idesc_w = make_idesc(128, 3 * C, 1, 1);  // wgrad: both MN-major, N = three kx taps x C
+      mbar_wait(wfull, 0);
+      for (int gi = 0; gi < total; ++gi) {
+        const int s = gi % NS, t = gi & 1;
+        const uint32_t par = (uint32_t)((gi / NS) & 1);
+        const uint32_t sb = a_smem + s * SLOT_BYTES;
+        mbar_wait(dyready(s), par);          // (also: every thread has read TMEM slot t's previous accumulators, see C below)
+        tc_fence_after();
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const uint32_t d_tmem = tmem_base + (t * 2 + m) * C;
+#pragma unroll
+          for (int tp = 0; tp < 9; ++tp) {
+            const uint64_t ad = make_sdesc(sb + ((tp / 3) * PITCH + m * 8 + (tp % 3)) * 64, 16, PITCH * 64, K::LAYOUT);
+            const uint64_t bd = make_sdesc(w_smem + tp * K::WTAP_BYTES, 16, K::SBO, K::LAYOUT);
+#pragma unroll
+            for (int kk = 0; kk < K::KSTEPS; ++kk) umma_bf16(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc_d, (tp | kk) != 0);
+          }
+          umma_commit(dxfull(t, m));
+        }
+        mbar_wait(xready(s), par);
+        tc_fence_after();
+        for (int yy = 0; yy < 16; ++yy) {              // K step = image row yy = 16 pixels; ONE MMA per row (see k_tc_bwd_persist<1>)
+          const uint64_t ad = make_sdesc(sb + DY_BYTES + yy * K::IMGROW_BYTES, K::IMGROW_BYTES, K::SBO, K::LAYOUT);
+          const uint64_t bd = make_sdesc(sb + (yy + 1) * PITCH * 64, 64, K::SBO, K::LAYOUT);          // N groups one pixel apart
+          umma_bf16(tmem_base + ACCW, ad, bd, idesc_w, (gi > 0 || yy > 0) ? 1u : 0u);
+        }
+        umma_commit(wfree(s));
+      }
+      umma_commit(wdone);
+    }
+  } else {
+    // ===== epilogue: 16 warps; warp = (channel half h, tile m, TMEM lane quarter q); thread = one pixel x 16 channels =====
+    const int ew = warp - 2, h = ew >> 3, m = (ew >> 2) & 1, q = warp & 3, et = threadIdx.x - 64;    // et: 0..511
+    const int pi = q * 4 + (lane >> 3), pj = m * 8 + (lane & 7);
+    const size_t pix_off = (size_t)(pi * 16 + pj) * C + h * 16;               // this thread's 16 channels inside an image
+    const int P1 = (pi + 1) * PITCH + pj + 1;                                 // its index inside the haloed dy copy
+    const uint32_t dy_c0 = P1 * 64 + (((h * 2 + 0) ^ ((P1 >> 1) & 3)) << 4), dy_c1 = P1 * 64 + (((h * 2 + 1) ^ ((P1 >> 1) & 3)) << 4);
+    const uint32_t my_tmem = tmem_base + ((uint32_t)(q * 32) << 16) + m * C + h * 16;   // + t * 2C
+    float dg_acc = 0.f, db_acc = 0.f;                 // CTA 0, warp ew == 0 (lane = channel): running dgamma / dbeta over the blocks
+    const uint32_t ybuf_s = smem_u32(ybuf);
+    // y of block k, image j -> ring slot r of this thread (2 x 16 B), one cp.async group
+    auto load_y = [&](int k, int j, int r) {
+      const bf16* yk = a.ys + (size_t)k * a.act_elems + (size_t)img_of(j) * NRD_PIX * C + pix_off;
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ybuf_s + (uint32_t)(((r * 2 + c) * 512 + et) * 16)),
+                     "l"(reinterpret_cast<const uint4*>(yk) + c) : "memory");
+    };
+    auto commit = [&]() { asm volatile("cp.async.commit_group;" ::: "memory"); };
+    auto y_chunk = [&](int r, int c) -> uint4 { return ybuf[(r * 2 + c) * 512 + et]; };
+    auto g_ptr = [&](int j) { return reinterpret_cast<uint4*>(a.G + (size_t)img_of(j) * NRD_PIX * C + pix_off); };
+    auto write_ssp = [&](int it2) {                  // scale/shift pairs of block NB-1-it2 -> buffer it2 & 1 (warp ew == 0, lane = channel)
+      const int k2 = a.NB - 1 - it2;
+      float* d = bnp2 + (it2 & 1) * 64 + (lane >> 1) * 4 + (lane & 1) * 2;
+      d[0] = a.scale_shift[(size_t)k2 * 2 * C + lane]; d[1] = a.scale_shift[(size_t)k2 * 2 * C + C + lane];
+    };
+    if (ew == 0) write_ssp(0);
+    const float gamma_r = a.gamma[lane];
+    if (blockIdx.x == 0 && ew == 0) {                // the last row of the previous launch (see k_tc_bwd_persist)
+      unsigned long long* last = a.acc + (size_t)(a.NB - 1) * NRD_ACC_ROW;
+#pragma unroll
+      for (int r = 0; r < NRD_ACC_REPL; ++r) { last[NRD_ACC_IDX(r, lane)] = 0ull; last[NRD_ACC_IDX(r, C + lane)] = 0ull; }
+      __threadfence();
+    }
+    asm volatile("bar.sync 1, 512;" ::: "memory");
+    float4* cfp = reinterpret_cast<float4*>(bnp2 + 128);   // per channel pair: {A1, A2, A3, -, A1', A2', A3', -}, dy = dz*A1 + y*A2 + A3
+    float s1 = 0.f, s2 = 0.f;                              // lanes 2c, 2c+1: sums of dz / dz*y over this warp's pixels, channel 16h + c
+    // ---- phase A of block it for one image: per-channel sums of dz and dz*y over this warp's 32 pixels ----
+    auto phase_a = [&](const uint32_t (&g)[8], int r, int it) {
+      const float4* ssp = reinterpret_cast<const float4*>(bnp2 + (it & 1) * 64);
+      float t1[16], t2[16];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const uint4 yv = y_chunk(r, c);
+        const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = c * 8 + 2 * e;
+          const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&yw[e]));
+          const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&g[c * 4 + e]));
+          const float4 ss = ssp[h * 8 + c * 4 + e];
+          const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
+          t1[i] = d0; t1[i + 1] = d1; t2[i] = d0 * y2.x; t2[i + 1] = d1 * y2.y;
+        }
+      }
+      s1 += warp_col_sum16(t1, lane);
+      s2 += warp_col_sum16(t2, lane);
+    };
+    // ---- block NB-1: dL/dx_NB from dL/d(pooled) through pool-2's arg-max -> G, and its phase A ----
+    {
+      load_y(a.NB - 1, 0, 0); commit();
+      for (int j = 0; j < nimg; ++j) {
+        if (j + 1 < nimg) load_y(a.NB - 1, j + 1, (j + 1) & 1);
+        commit();
+        uint32_t g[8];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const size_t po = ((size_t)img_of(j) * 64 + (pi >> 1) * 8 + (pj >> 1)) * C + h * 16 + c * 8;
+          const uint4 gp4 = *reinterpret_cast<const uint4*>(a.g_pool + po);
+          const uint2 id = *reinterpret_cast<const uint2*>(a.idx2 + po);
+          const uint32_t sel = (uint32_t)((pi & 1) * 2 + (pj & 1));
+          const uint32_t gw[4] = {gp4.x, gp4.y, gp4.z, gp4.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t ib = (e < 2 ? id.x : id.y) >> ((e & 1) * 16);
+            const uint32_t lo = ((ib & 0xffu) == sel) ? 0x0000ffffu : 0u, hi = (((ib >> 8) & 0xffu) == sel) ? 0xffff0000u : 0u;
+            g[c * 4 + e] = gw[e] & (lo | hi);
+          }
+        }
+        uint4* dst = g_ptr(j);
+        dst[0] = make_uint4(g[0], g[1], g[2], g[3]); dst[1] = make_uint4(g[4], g[5], g[6], g[7]);
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        phase_a(g, j & 1, 0);
+      }
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    uint32_t gA[8], gB[8], pg[8];                    // dL/dx of the even / odd image in flight; the next image's (prefetched)
+    for (int it = 0; it < a.NB; ++it) {
+      const int k = a.NB - 1 - it;
+      const float mean_r = (ew == 0) ? a.saved[(size_t)k * 2 * C + lane] : 0.f, is_r = (ew == 0) ? a.saved[(size_t)k * 2 * C + C + lane] : 0.f;
+      red[ew * 32 + (lane & 1) * 16 + (lane >> 1)] = (lane & 1) ? s2 : s1;
+      s1 = 0.f; s2 = 0.f;
+      asm volatile("bar.sync 1, 512;" ::: "memory");
+      unsigned long long* acc = a.acc + (size_t)it * NRD_ACC_ROW;
+      if (et < 2 * C) {
+        const int which = et >> 5, ch = et & 31;
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
+        nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0, a.status), gridDim.x);
+      }
+      {   // the first image's operands travel during the exchange
+        const uint4* gp = g_ptr(0);
+        const uint4 v0 = __ldcg(gp), v1 = __ldcg(gp + 1);
+        pg[0] = v0.x; pg[1] = v0.y; pg[2] = v0.z; pg[3] = v0.w; pg[4] = v1.x; pg[5] = v1.y; pg[6] = v1.z; pg[7] = v1.w;
+        load_y(k, 0, (it * nimg) % NY); commit();
+      }
+      if (ew == 0) {
+        unsigned long long wb, wg;
+        nrd_acc_wait2(acc + NRD_ACC_IDX(0, lane), acc + NRD_ACC_IDX(0, C + lane), gridDim.x, wb, wg, a.poll_ns);
+        if (blockIdx.x == 0 && it > 0) {
+#pragma unroll
+          for (int r = 0; r < NRD_ACC_REPL; ++r) { (acc - NRD_ACC_ROW)[NRD_ACC_IDX(r, lane)] = 0ull; (acc - NRD_ACC_ROW)[NRD_ACC_IDX(r, C + lane)] = 0ull; }
+        }
+        const double db = nrd_acc_value(wb, gridDim.x, 1.0 / 68719476736.0), dgy = nrd_acc_value(wg, gridDim.x, 1.0 / 68719476736.0);
+        if (it + 1 < a.NB) write_ssp(it + 1);
+        const double mean = (double)mean_r, is = (double)is_r;
+        const double dg = is * (dgy - mean * db);       // sum dz*xhat = invstd * (sum dz*y - mean * sum dz)
+        db_acc += (float)db; dg_acc += (float)dg;
+        const double a_ = (double)gamma_r * is, b_ = db * a.inv_count, c_ = dg * a.inv_count;
+        float* d = reinterpret_cast<float*>(cfp) + (lane >> 1) * 8 + (lane & 1) * 4;
+        d[0] = (float)a_; d[1] = (float)(-a_ * c_ * is); d[2] = (float)(a_ * c_ * is * mean - a_ * b_); d[3] = 0.f;
+      }
+      asm volatile("bar.sync 1, 512;" ::: "memory");
+      const float4* ssp = reinterpret_cast<const float4*>(bnp2 + (it & 1) * 64);
+      // ---- B(i): dy of image i -> operand slot; then y_{k-1}[i] into the ring slot y_k[i] leaves, and image i+1's operands ----
+      auto phase_b = [&](uint32_t (&g)[8], int i) {
+        const int gi = it * nimg + i, s = gi % NS, u = gi / NS, r = gi % NY;
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] = pg[e];
+        if (u > 0) mbar_wait(wfree(s), (uint32_t)((u - 1) & 1));
+        uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int ch = h * 2 + c;
+          uint4 ok;
+          __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&ok);
+          const uint4 yv = y_chunk(r, c);
+          const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int pe = ch * 4 + e;
+            const float2 y2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&yw[e]));
+            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&g[c * 4 + e]));
+            const float4 ss = ssp[pe], c0 = cfp[pe * 2], c1 = cfp[pe * 2 + 1];
+            const float d0 = fmaf(y2.x, ss.x, ss.y) > 0.f ? g2.x : 0.f, d1 = fmaf(y2.y, ss.z, ss.w) > 0.f ? g2.y : 0.f;
+            oh[e] = __floats2bfloat162_rn(fmaf(d0, c0.x, fmaf(y2.x, c0.y, c0.z)), fmaf(d1, c1.x, fmaf(y2.y, c1.y, c1.z)));
+          }
+          *reinterpret_cast<uint4*>(slot_gen + (c == 0 ? dy_c0 : dy_c1)) = ok;
+        }
+        fence_proxy_async();
+        mbar_arrive(dyready(s));
+        if (k > 0) load_y(k - 1, i, r);
+        commit();
+        if (i + 1 < nimg) {
+          const uint4* gp = g_ptr(i + 1);
+          const uint4 v0 = __ldcg(gp), v1 = __ldcg(gp + 1);
+          pg[0] = v0.x; pg[1] = v0.y; pg[2] = v0.z; pg[3] = v0.w; pg[4] = v1.x; pg[5] = v1.y; pg[6] = v1.z; pg[7] = v1.w;
+          load_y(k, i + 1, (gi + 1) % NY);
+        }
+        commit();
+      };
+      // ---- C(i): dx_k = dgrad + g -> G, then phase A of block k-1 for the same image ----
+      auto phase_c = [&](uint32_t (&g)[8], int i) {
+        const int gi = it * nimg + i, t = gi & 1, r = gi % NY;
+        mbar_wait(dxfull(t, m), (uint32_t)((gi >> 1) & 1));
+        tc_fence_after();
+        float v[16];
+        tmem_ld16(my_tmem + t * 2 * C, v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&g[e]));
+          const __nv_bfloat162 o = __floats2bfloat162_rn(v[2 * e] + g2.x, v[2 * e + 1] + g2.y);
+          g[e] = *reinterpret_cast<const uint32_t*>(&o);
+        }
+        tc_fence_before();      // the accumulator is in registers: image i+2's dgrad may overwrite it (ordered by its dyready)
+        uint4* dst = g_ptr(i);
+        dst[0] = make_uint4(g[0], g[1], g[2], g[3]); dst[1] = make_uint4(g[4], g[5], g[6], g[7]);
+        if (k > 0) {
+          // y_{k-1}[i] was committed in B(i); behind it at most the two groups of B(i+1)
+          if (i + 1 < nimg) asm volatile("cp.async.wait_group 2;" ::: "memory");
+          else asm volatile("cp.async.wait_group 0;" ::: "memory");
+          phase_a(g, r, it + 1);
+        }
+      };
+      for (int i0 = 0; i0 <= nimg; i0 += 2) {
+        if (i0 < nimg) phase_b(gA, i0);
+        if (i0 >= 1) phase_c(gB, i0 - 1);
+        if (i0 + 1 < nimg) phase_b(gB, i0 + 1);
+        if (i0 + 1 <= nimg) phase_c(gA, i0);
+      }
+    }
+    if (blockIdx.x == 0 && ew == 0) { a.dgamma[lane] = dg_acc; a.dbeta[lane] = db_acc; }
+    // ---- weight-gradient partial of this CTA: accumulator lanes (j, ci), columns (kxb, co) ----
+    if (h == 0 && m == 0) {
+      mbar_wait(wdone, 0);
+      tc_fence_after();
+      float* outp = a.wpartial + (size_t)blockIdx.x * 9 * C * C;
+      const int j = q, ci = lane;
+#pragma unroll
+      for (int kxb = 0; kxb < 3; ++kxb) {
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ACCW + kxb * C, v);
+        if (j < 3) {
+          float* dst = outp + (size_t)(j * 3 + (2 - kxb)) * C * C + ci;                     // [tap = (ky, kx)][co][ci]
+#pragma unroll
+          for (int co = 0; co < 32; ++co) dst[co * C] = v[co];
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+}
+
+constexpr size_t stream_bwd_smem() {
+  return 1024 + STREAM_BWD_NS * (21 * 1024 + Cfg<32>::BUF_BYTES) + 9 * Cfg<32>::WTAP_BYTES + 8 * 20 + (1024 + 256) * sizeof(float) +
+         (size_t)STREAM_BWD_NY * 2 * 512 * 16 + 64;
+}
+
+// ============================================================================================
 // wgrad: both operands MN-major (channels contiguous, pixels = K).  Per work item: the 3 kx-shifted row-haloed copies of x
 // and the dy rows.  One MMA stacks 128/C vertical taps along M: tap ky+1 is one image row further = LBO.
 // ============================================================================================
@@ -1561,6 +2206,8 @@ int nrd_tc_plan_init(nrd_plan* p) {
   if (p->C == 32) {
     NRD_TRY(set_attr(k_tc_fwd_persist<0>, persist_smem(0)));
     NRD_TRY(set_attr(k_tc_fwd_persist<1>, persist_smem(1)));
+    NRD_TRY(set_attr(k_tc_fwd_stream, stream_fwd_smem()));
+    NRD_TRY(set_attr(k_tc_bwd_stream, stream_bwd_smem()));
     NRD_TRY(set_attr(k_tc_bwd_persist<0>, persist_bwd_smem(0)));
     NRD_TRY(set_attr(k_tc_bwd_persist<1>, persist_bwd_smem(1)));
     // all saved x_k as ONE 5-D tensor {C, W, H, N, k}: the block index is just the last TMA coordinate
@@ -1577,6 +2224,12 @@ int nrd_tc_plan_init(nrd_plan* p) {
     r = enc(&p->tm_xst, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, p->xs, dims, strides, sbox, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { nrd_set_error("cuTensorMapEncodeTiled(x store) failed: %d", (int)r); return NRD_ECUDA; }
+    {   // streaming forward: any x_k WITH its halo
+      cuuint32_t b5[5] = {32, 18, 18, 1, 1};
+      r = enc(&p->tm_x18all, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, p->xs, dims, strides, b5, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) { nrd_set_error("cuTensorMapEncodeTiled(x stack, haloed) failed: %d", (int)r); return NRD_ECUDA; }
+    }
     {   // one-copy layout: x_0 WITH its halo, 18 x 18 pixels (zero-filled by the load)
       cuuint64_t d4[4] = {32, 16, 16, (cuuint64_t)p->B};
       cuuint64_t s4[3] = {64, 1024, 16384};
@@ -1599,7 +2252,10 @@ void nrd_tc_refresh_limits(nrd_plan* p) {
   const int rows = p->C == 32 ? 16 : 8;
   const int grid = conv_grid(p), per_cta = (items(p) + grid - 1) / grid * (rows / 8);
   p->tc_fused_fwd = (per_cta * p->C <= 512) ? 1 : 0;
-  p->tc_persist_fwd = (p->C == 32 && p->B <= 2 * grid && p->NB >= 2) ? 1 : 0;   // NB = 1: the row cleaned at kernel start would be the live row 0
+  const bool fits2 = p->B <= 2 * grid;
+  // NB = 1: the row cleaned at kernel start would be the live row 0
+  p->tc_persist_fwd = (p->C == 32 && p->NB >= 2 && (fits2 || p->stream_opt != 2)) ? 1 : 0;
+  p->tc_stream = (p->tc_persist_fwd && (!fits2 || p->stream_opt == 1)) ? 1 : 0;
 }
 
 int nrd_tc_stats_blocks(const nrd_plan* p) { return conv_grid(p); }
@@ -1644,6 +2300,19 @@ int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st) {
 // all NB residual blocks in ONE cooperative launch (C = 32, <= 2 images per CTA)
 int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int training, cudaStream_t st) {
   NRD_REQUIRE(p->tc_ready && p->tc_persist_fwd, "persistent block-stack forward not available for this plan");
+  if (p->tc_stream) {
+    NRD_REQUIRE(!pool && !stem_images, "the streaming forward neither pools nor runs the stem");
+    StreamFwdArgs sa;
+    sa.gamma = p->params + p->off[3]; sa.beta = p->params + p->off[4];
+    sa.saved = p->saved_stats; sa.scale_shift = p->scale_shift; sa.running = p->bn_running; sa.nbt = (long long*)p->nbt;
+    sa.xs = (const bf16*)p->xs; sa.ys = (const bf16*)p->ys; sa.acc = p->bn_acc; sa.B = p->B; sa.NB = p->NB; sa.act_elems = p->act_elems;
+    sa.inv_count = 1.0 / ((double)p->B * NRD_PIX); sa.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
+    sa.poll_ns = p->poll_ns; sa.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS);
+    void* sargs[] = {(void*)&p->tm_x18all, (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&sa};
+    NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_stream, dim3(conv_grid(p)), dim3(576), sargs, stream_fwd_smem(), st));
+    nrd_count_launch();
+    return NRD_OK;
+  }
   PersistFwdArgs a;
   a.gamma = p->params + p->off[3]; a.beta = p->params + p->off[4];
   a.saved = p->saved_stats; a.scale_shift = p->scale_shift; a.running = p->bn_running; a.nbt = (long long*)p->nbt;
@@ -1663,7 +2332,21 @@ int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int t
 // all NB residual blocks of the backward in ONE cooperative launch: g_in = dL/dx_NB -> dx0_out = dL/dx_0, dgamma, dbeta,
 // per-CTA weight-gradient partials (reduced by k_wgrad_reduce)
 int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, const float* stem_images, cudaStream_t st) {
-  NRD_REQUIRE(p->tc_ready && p->tc_persist_fwd, "persistent block-stack backward not available for this plan");
+  NRD_REQUIRE(p->tc_ready && nrd_persist_bwd_ok(p), "persistent block-stack backward not available for this plan");
+  if (p->tc_stream) {
+    NRD_REQUIRE(!stem_images, "the streaming backward does not run the stem");
+    StreamBwdArgs sa;
+    sa.gamma = p->params + p->off[3]; sa.scale_shift = p->scale_shift; sa.saved = p->saved_stats;
+    sa.dgamma = p->grads + p->off[3]; sa.dbeta = p->grads + p->off[4];
+    sa.ys = (const bf16*)p->ys; sa.g_pool = (const bf16*)g_pooled; sa.idx2 = p->idx2; sa.G = (bf16*)dx0_out;
+    sa.acc = p->bn_acc + (size_t)32 * NRD_ACC_ROW; sa.wpartial = p->wgrad_partial;
+    sa.B = p->B; sa.NB = p->NB; sa.act_elems = p->act_elems; sa.inv_count = 1.0 / ((double)p->B * NRD_PIX); sa.poll_ns = p->poll_ns;
+    sa.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS);
+    void* sargs[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&sa};
+    NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_stream, dim3(conv_grid(p)), dim3(576), sargs, stream_bwd_smem(), st));
+    nrd_count_launch();
+    return NRD_OK;
+  }
   PersistBwdArgs a;
   a.gamma = p->params + p->off[3]; a.scale_shift = p->scale_shift; a.saved = p->saved_stats;
   a.dgamma = p->grads + p->off[3]; a.dbeta = p->grads + p->off[4];

@@ -267,7 +267,10 @@ struct nrd_plan {
   int persist_fwd;        // option: use the persistent block-stack forward when available
   int persist_bwd;        // option: use the persistent block-stack backward when available
   int fuse_bn_bwd;        // BN+ReLU backward as one cooperative kernel when it fits shared memory
-  int tc_persist_fwd;     // all NB blocks of the forward in ONE cooperative kernel (C=32, <= 2 images per CTA)
+  int tc_persist_fwd;     // all NB blocks of the forward / backward in ONE cooperative kernel each (C = 32, NB >= 2)
+  int tc_stream;          // ... as the STREAMING kernels (any batch size) instead of the resident ones (<= 2 images per CTA)
+  int stream_opt;         // NRD_OPT_STREAM: 0 = streaming kernels only beyond 2 images per CTA, 1 = always, 2 = never (per-block kernels there)
+  CUtensorMap tm_x18all;  // all x_k, 18 x 18 (haloed) boxes: the streaming forward's operand loads
   int tc_fused_fwd;       // whole ResBlock forward in one cooperative kernel (accumulators fit TMEM)
   unsigned long long* bn_acc; // BN-sum words of the persistent kernels: fwd [32 blocks][NRD_ACC_REPL][64] then bwd, same shape;
                               // zero between launches (the kernels clean up behind themselves)
@@ -454,3 +457,7 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, con
                                                                             // (stem_images: also conv1's weight-gradient partials, no stem kernel);
                                                                             // g_pooled = dL/d(pooled) [B,8,8,C]
 int nrd_tc_block_fwd(nrd_plan* p, int k, cudaStream_t st);                      // y_k, x_{k+1}, BN stats + EMA, one launch
+// persistent stacks usable for this plan?  (the streaming backward exists from NRD_HAVE_BWD_STREAM on)
+#define NRD_HAVE_BWD_STREAM 1
+static inline bool nrd_persist_fwd_ok(const nrd_plan* p) { return p->tc_persist_fwd != 0; }
+static inline bool nrd_persist_bwd_ok(const nrd_plan* p) { return p->tc_persist_fwd != 0 && (!p->tc_stream || NRD_HAVE_BWD_STREAM); }

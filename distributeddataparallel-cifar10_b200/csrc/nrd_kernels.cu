@@ -2022,6 +2022,11 @@ extern "C" int nrd_plan_set_option(nrd_plan* p, int option, int value) {
     case NRD_OPT_FUSE_POOL: p->fuse_pool = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_FUSE_STEM: p->fuse_stem = value ? 1 : 0; return NRD_OK;
     case NRD_OPT_FUSE_STEM_BWD: p->fuse_stem_bwd = value ? 1 : 0; return NRD_OK;
+    case NRD_OPT_STREAM:
+      NRD_REQUIRE(value >= 0 && value <= 2, "NRD_OPT_STREAM: 0 (auto), 1 (always) or 2 (never), got %d", value);
+      p->stream_opt = value;
+      if (p->tc_ready) nrd_tc_refresh_limits(p);
+      return NRD_OK;
     case NRD_OPT_ONE_COPY: p->one_copy = value & 3; return NRD_OK;
     case NRD_OPT_RESERVE_SMS:
       NRD_REQUIRE(value >= 0 && value <= NRD_NUM_SMS / 2, "NRD_OPT_RESERVE_SMS: %d out of range [0, %d]", value, NRD_NUM_SMS / 2);
@@ -2250,14 +2255,14 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
   const size_t act = p->act_elems * p->esz;
   p->images_last = images;
   nrd_tl_mark(p, st, "start", true);
-  const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_fwd;
-  const bool stem_in_blocks = persist && p->fuse_stem && p->tc_stem && p->use_tc_stem;
+  const bool persist = training && p->conv_impl == NRD_CONV_TCGEN05 && nrd_persist_fwd_ok(p) && p->persist_fwd;
+  const bool stem_in_blocks = persist && !p->tc_stream && p->fuse_stem && p->tc_stem && p->use_tc_stem;
   if (stem_in_blocks) {}                                         // x_0 is produced inside the persistent kernel
   else if (p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_stem && p->use_tc_stem) NRD_TRY(nrd_tc_stem_fwd(p, images, training, st));
   else NRD_TRY(stem_fwd_any(images, p->conv1_wp, PRM(P_C1B), p->xs, p->idx0, B, C, dt, st, nrd_bn_sync_of(p, training)));
   nrd_tl_mark(p, st, "stem_fwd");
   if (!training) { k_bn_eval_coeffs<<<1, 64, 0, st>>>(p->bn_running, PRM(P_BNG), PRM(P_BNB), C, p->scale_shift); LAUNCH_CHECK(); }
-  const bool pool_in_blocks = persist && p->fuse_pool;
+  const bool pool_in_blocks = persist && !p->tc_stream && p->fuse_pool;
   if (persist) NRD_TRY(nrd_tc_forward_blocks(p, pool_in_blocks ? 1 : 0, stem_in_blocks ? images : nullptr, training, st));       // ... and the max-pool behind the last block
   if (persist) nrd_tl_mark(p, st, "fwd_blocks");
   for (int k = 0; k < (persist ? 0 : NB); ++k) {
@@ -2279,7 +2284,7 @@ static int forward_impl(nrd_plan* p, const float* images, float* logits, int tra
   }
   // head: pool + fc1 + fc2 (+ loss and dlogits, + the backward's first product dL/d(pooled)) in ONE cooperative launch
   p->dp_for = nullptr;
-  const bool tail = labels && dt == NRD_BF16 && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd && p->fuse_head_tail;
+  const bool tail = labels && dt == NRD_BF16 && p->conv_impl == NRD_CONV_TCGEN05 && nrd_persist_bwd_ok(p) && p->persist_bwd && p->fuse_head_tail;
   NRD_TRY(launch_head(p, p->xs + act * NB, pool_in_blocks ? 1 : 0, logits, labels, grad_scale, loss_rows, dlogits, loss_out, tail ? (void*)p->dxa : nullptr, st));
   nrd_tl_mark(p, st, "head");
   if (tail) p->dp_for = dlogits;       // d(pooled) is ready when nrd_backward_body(dlogits) is called
@@ -2342,8 +2347,8 @@ extern "C" int nrd_backward_body(nrd_plan* p, const float* dlogits, void* stream
   const size_t act = p->act_elems * p->esz;
   char* g = p->dxa; char* gn = p->dxb;
   const int K = 64 * C;
-  const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd;
-  const bool stem_in_blocks = persist && p->fuse_stem_bwd && p->tc_stem && p->use_tc_stem && !(p->one_copy & 2) && p->images_last != nullptr;
+  const bool persist = p->conv_impl == NRD_CONV_TCGEN05 && nrd_persist_bwd_ok(p) && p->persist_bwd;
+  const bool stem_in_blocks = persist && !p->tc_stream && p->fuse_stem_bwd && p->tc_stem && p->use_tc_stem && !(p->one_copy & 2) && p->images_last != nullptr;
   if (persist && p->dp_for == dlogits) p->dp_for = nullptr;      // nrd_forward_loss already left d(pooled) in the dx scratch
   else if (persist) NRD_CHECK_CUDA(nrd_launch_pdl(k_fc1_dgrad_pooled<bf16>, dim3(((B + 7) / 8) * (K / 256)), dim3(256), 0, st, p->pdl & 1, dlogits, p->h1,
                                              PRM(P_FC2W), p->w1p, (bf16*)g, B, C));
@@ -2430,14 +2435,14 @@ extern "C" int nrd_plan_run_op(nrd_plan* p, int op, int k, void* stream) {
       NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent forward not available for this plan");
       return nrd_tc_forward_blocks(p, 0, nullptr, 0, st);
     case NRD_OP_BWD_BLOCKS:
-      NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd, "persistent backward not available for this plan");
+      NRD_REQUIRE(p->conv_impl == NRD_CONV_TCGEN05 && nrd_persist_bwd_ok(p), "persistent backward not available for this plan");
       return nrd_tc_backward_blocks(p, p->dxa, p->dxb, nullptr, st);
     case NRD_OP_BLOCK_FWD:
       NRD_REQUIRE(p->conv_impl != NRD_CONV_CUDA_CORE && p->tc_fused_fwd, "fused block forward not available for this plan");
       return nrd_tc_block_fwd(p, k, st);
     case NRD_OP_HEAD: {
       NRD_REQUIRE(p->labels_last, "run nrd_forward_loss first");
-      const bool tail = dt == NRD_BF16 && p->conv_impl == NRD_CONV_TCGEN05 && p->tc_persist_fwd && p->persist_bwd && p->fuse_head_tail;
+      const bool tail = dt == NRD_BF16 && p->conv_impl == NRD_CONV_TCGEN05 && nrd_persist_bwd_ok(p) && p->persist_bwd && p->fuse_head_tail;
       return launch_head(p, p->xs + act * p->NB, 0, p->logits_last, p->labels_last, 1.0f, p->loss_rows_last, p->dlogits_last, p->loss_last,
                          tail ? (void*)p->dxa : nullptr, st);     // rewrites the same values
     }

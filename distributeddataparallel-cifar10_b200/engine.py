@@ -42,7 +42,7 @@ class _Plan:
                                   eng.nbt.data_ptr()), "nrd_plan_create")
         self.handle = h
         for env, opt in (("NRD_HEAD_TAIL", _lib.OPT_HEAD_TAIL), ("NRD_FUSE_POOL", _lib.OPT_FUSE_POOL), ("NRD_FUSE_STEM", _lib.OPT_FUSE_STEM), ("NRD_ONE_COPY", _lib.OPT_ONE_COPY),
-                         ("NRD_FUSE_STEM_BWD", _lib.OPT_FUSE_STEM_BWD)):   # A/B switches
+                         ("NRD_FUSE_STEM_BWD", _lib.OPT_FUSE_STEM_BWD), ("NRD_STREAM", _lib.OPT_STREAM)):   # A/B switches
             if env in os.environ:
                 check(lib.nrd_plan_set_option(h, opt, int(os.environ[env])), "nrd_plan_set_option")
         if "NRD_PDL" in os.environ:                        # A/B switch for measurements (bit mask, see nrd.h)

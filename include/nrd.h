@@ -111,6 +111,11 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
  * over the same tiles, in the same order as the stem backward kernel it replaces (bit-identical partials at equal grids);
  * 0 = the stand-alone stem backward kernel. */
 #define NRD_OPT_FUSE_STEM_BWD 12
+/* NRD_OPT_STREAM (default 0): which kernels run the residual blocks of a bf16, C = 32 plan.  0: the resident persistent kernels up to
+ * 2 images per CTA (B <= 296 on 148 SMs), the STREAMING persistent kernels beyond (any batch size: every image passes through two
+ * operand slots per block, one launch for the whole stack); 1: the streaming kernels always (cross-check: bit-identical to the
+ * resident ones); 2: never (per-block kernels beyond 2 images per CTA, as in round 1). */
+#define NRD_OPT_STREAM 13
 /* NRD_OPT_TIMELINE (default 0): measurement aid.  An event is recorded behind every kernel of the step's main stream -- an
  * event-record NODE when the step is being captured -- and nrd_plan_timeline() reads the intervals after a (replayed) step:
  * the step kernel by kernel in its real context (warm L2, side stream running).  The marks serialise neighbouring kernels

@@ -266,3 +266,58 @@ def test_fused_stem_backward_equals_stem_kernel_bitwise(B, monkeypatch):
     off = m.engine.offsets
     assert float(res[0][1][off[0]:off[2]].abs().sum()) > 0
     assert res[0][0] == res[1][0] and torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2])
+
+
+@pytest.mark.parametrize("B", [1, 2, 149, 256, 296])
+def test_streaming_kernels_are_bitwise_the_resident_persistent_kernels(B):
+    """NRD_OPT_STREAM = 1: the streaming persistent forward (every image through two operand slots per block, y_k / x_k read back
+    from L2 for the second pass) against the resident one (<= 2 images per CTA kept on chip): same MMAs, same image-to-CTA
+    assignment, same order of the BN partial sums, same rounding points -- bit for bit."""
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for stream in (0, 1):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(32, 10, dtype="bf16").to(DEV)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 13, stream))
+        check(lib.nrd_plan_set_option(pl.handle, 10, 3))     # resident kernels in the streaming kernels' operand layout (one haloed copy:
+        #                                                      the same pixels per warp, so the same grouping of the fp32 partial sums)
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        bn = m.resblocks[0].batch_norm
+        res.append(dict(out=out.detach().clone(), rm=bn.running_mean.clone(), rv=bn.running_var.clone(), nbt=int(bn.num_batches_tracked),
+                        xs=[pl.tensor_view(0, k).clone() for k in range(11)], ys=[pl.tensor_view(1, k).clone() for k in range(10)],
+                        st=[pl.tensor_view(4, k).clone() for k in range(10)], grads=m.engine.flat_grads.clone()))
+    a, b = res
+    assert a["nbt"] == b["nbt"] == 10
+    for k in range(10):
+        assert torch.equal(a["ys"][k], b["ys"][k]), k
+        assert torch.equal(a["st"][k], b["st"][k]), k
+        assert torch.equal(a["xs"][k + 1], b["xs"][k + 1]), k
+    assert torch.equal(a["out"], b["out"]) and torch.equal(a["rm"], b["rm"]) and torch.equal(a["rv"], b["rv"])
+    # ... and the streaming backward (dL/dx in one global buffer updated in place, y_k through a shared-memory ring) against the
+    # resident one (dL/dx in registers): same per-element arithmetic, same order of every partial sum
+    assert torch.equal(a["grads"], b["grads"]), (B, (a["grads"] - b["grads"]).abs().max().item(), rell2(b["grads"], a["grads"]))
+
+
+@pytest.mark.parametrize("B", [297, 512, 1000])
+def test_streaming_kernels_beyond_two_images_per_cta_match_per_block_kernels(B):
+    """Default dispatch beyond 2 images per CTA = the streaming kernels; against the per-block kernels (NRD_OPT_STREAM = 2)."""
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
+    res = []
+    for stream in (2, 0):
+        torch.manual_seed(0)
+        m = nrd.NetResDeep(32, 10, dtype="bf16").to(DEV)
+        pl = m.engine.plan(B, torch.device(DEV))
+        check(lib.nrd_plan_set_option(pl.handle, 13, stream))
+        out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
+        bn = m.resblocks[0].batch_norm
+        res.append(dict(out=out.detach().clone(), grads=m.engine.flat_grads.clone(), rm=bn.running_mean.clone(), rv=bn.running_var.clone(),
+                        nbt=int(bn.num_batches_tracked), x10=pl.tensor_view(0, 10).view(torch.bfloat16).float().clone(),
+                        y9=pl.tensor_view(1, 9).view(torch.bfloat16).float().clone(), st9=pl.tensor_view(4, 9).view(torch.float32).clone()))
+    a, b = res
+    assert a["nbt"] == b["nbt"] == 10
+    assert relmax(b["rm"], a["rm"]) < 1e-5 and relmax(b["rv"], a["rv"]) < 1e-5 and relmax(b["st9"], a["st9"]) < 1e-4
+    assert rell2(b["y9"], a["y9"]) < 2e-3 and rell2(b["x10"], a["x10"]) < 2e-3 and rell2(b["out"], a["out"]) < 2e-3
+    assert rell2(b["grads"], a["grads"]) < 4e-2
