@@ -826,7 +826,10 @@ k_tc_fwd_persist(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
 // 576 threads: warp 0 lane 0 = DMA (TMA loads and bulk stores), warp 1 lane 0 = MMA issue, 16 epilogue warps as in
 // k_tc_fwd_persist<1> (thread = one pixel x 16 channels; pixel tile m = columns 8m .. 8m+7 of all 16 rows).
 // ============================================================================================
-constexpr int STREAM_NSLOT = 4;          // haloed operand slots of the streaming kernels (21 KB each)
+constexpr int STREAM_NSLOT = 4;          // haloed operand slots of the streaming forward (21 KB each)
+constexpr int STREAM_NT = 4;             // its TMEM image slots (64 columns each).  Measured: 6 operand / 8 TMEM slots (more of the next block's
+//                                          MMAs under pass 2) shorten pass 1 by 4k cycles per block and lengthen pass 2 by 8k (B = 2048): rejected
+constexpr int STREAM_BAR_BYTES = 8 * 48;
 struct StreamFwdArgs {
   const float* gamma; const float* beta;
   float* saved; float* scale_shift; float* running; long long* nbt;
@@ -837,6 +840,7 @@ struct StreamFwdArgs {
   double inv_count, unbias;
   int poll_ns;
   unsigned int* status;
+  long long* trace;           // optional clock64 stamps [CTA][block][8] (profiling aid), or NULL
 };
 
 __global__ void __launch_bounds__(576, 1)
@@ -847,7 +851,7 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
-  constexpr int PITCH = 18, SLOT_BYTES = 21 * 1024, YST_BYTES = NRD_PIX * C * 2, NSLOT = STREAM_NSLOT;
+  constexpr int PITCH = 18, SLOT_BYTES = 21 * 1024, YST_BYTES = NRD_PIX * C * 2, NSLOT = STREAM_NSLOT, NT = STREAM_NT;
   const uint32_t a_smem = base;                                    // NSLOT operand slots
   const uint32_t w_smem = a_smem + NSLOT * SLOT_BYTES;             // 9 taps
   const uint32_t y_smem = w_smem + 9 * K::WTAP_BYTES;              // 2 y staging tiles
@@ -855,16 +859,18 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
   const uint32_t bar0 = xst_smem + 2 * YST_BYTES;
   const uint32_t wfull = bar0;
   auto xfull = [&](int s) { return bar0 + 8u * (1 + s); };         // operand slot loaded (TMA bytes)
-  auto opfree = [&](int s) { return bar0 + 8u * (5 + s); };        // the MMAs that read operand slot s are done
-  auto tfull = [&](int t, int m) { return bar0 + 8u * (9 + t * 2 + m); };   // accumulator (TMEM slot t, tile m) ready
-  auto tfree = [&](int t) { return bar0 + 8u * (17 + t); };        // pass 1 has read TMEM slot t (512 arrivals)
-  auto yready = [&](int s) { return bar0 + 8u * (21 + s); };       // y staged (512)
-  auto xready = [&](int s) { return bar0 + 8u * (23 + s); };       // x staged (512)
-  auto yfree = [&](int s) { return bar0 + 8u * (25 + s); };        // the bulk store has read y staging tile s
-  auto xfree = [&](int s) { return bar0 + 8u * (27 + s); };
-  const uint32_t p1done = bar0 + 8u * 29;                          // every y store of this block's phase 1 is complete
-  const uint32_t tmem_slot = bar0 + 8u * 30;
-  constexpr int BAR_BYTES = 8 * 32;
+  auto opfree = [&](int s) { return bar0 + 8u * (1 + NSLOT + s); };        // the MMAs that read operand slot s are done
+  auto tfull = [&](int t, int m) { return bar0 + 8u * (1 + 2 * NSLOT + t * 2 + m); };   // accumulator (TMEM slot t, tile m) ready
+  auto tfree = [&](int t) { return bar0 + 8u * (1 + 2 * NSLOT + 2 * NT + t); };          // pass 1 has read TMEM slot t (512 arrivals)
+  constexpr int BX = 1 + 2 * NSLOT + 3 * NT;
+  auto yready = [&](int s) { return bar0 + 8u * (BX + s); };       // y staged (512)
+  auto xready = [&](int s) { return bar0 + 8u * (BX + 2 + s); };   // x staged (512)
+  auto yfree = [&](int s) { return bar0 + 8u * (BX + 4 + s); };    // the bulk store has read y staging tile s
+  auto xfree = [&](int s) { return bar0 + 8u * (BX + 6 + s); };
+  const uint32_t p1done = bar0 + 8u * (BX + 8);                    // every y store of this block's phase 1 is complete
+  const uint32_t tmem_slot = bar0 + 8u * (BX + 9);
+  constexpr int BAR_BYTES = STREAM_BAR_BYTES;
+  static_assert(8 * (BX + 10) <= BAR_BYTES, "barrier area");
   constexpr int MISC_OFF = NSLOT * SLOT_BYTES + 9 * K::WTAP_BYTES + 4 * YST_BYTES + BAR_BYTES;
   float* red = reinterpret_cast<float*>(gen_base + MISC_OFF);            // [16 warps][sum | sum of squares][16 channels]
   float* ss_sm = red + 1024;                                             // [2C] scale | shift of the current block
@@ -873,16 +879,16 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nimg = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;      // images of this CTA (>= 1)
   auto img_of = [&](int j) { return (int)blockIdx.x + j * (int)gridDim.x; };
-  constexpr uint32_t TMEM_COLS = 256;                              // 4 image slots x 2 tiles x 32 columns
-  // Slots rotate over the GLOBAL image counter g = k * nimg + j (operand slot g % NSLOT, TMEM slot g & 3, staging tile g & 1), so
-  // the n-th use of a slot is g / slots and every mbarrier parity follows from g alone.
+  constexpr uint32_t TMEM_COLS = NT * 2 * C;                       // NT image slots x 2 tiles x 32 columns
+  // Slots rotate over the GLOBAL image counter g = k * nimg + j (operand slot g % NSLOT, TMEM slot g % NT, staging tile g & 1), so
+  // the n-th use of a slot is g / slots (operand slot g % NSLOT, TMEM slot g % NT) and every mbarrier parity follows from g alone.
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX18); tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmXst); tma_prefetch_desc(&tmYst);
     mbar_init(wfull, 1); mbar_init(p1done, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(yready(s), 512); mbar_init(xready(s), 512); mbar_init(yfree(s), 1); mbar_init(xfree(s), 1); }
     for (int s = 0; s < NSLOT; ++s) { mbar_init(xfull(s), 1); mbar_init(opfree(s), 1); }
-    for (int t = 0; t < 4; ++t) { mbar_init(tfull(t, 0), 1); mbar_init(tfull(t, 1), 1); mbar_init(tfree(t), 512); }
+    for (int t = 0; t < NT; ++t) { mbar_init(tfull(t, 0), 1); mbar_init(tfull(t, 1), 1); mbar_init(tfree(t), 512); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -939,9 +945,9 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
       mbar_wait(wfull, 0);
       const int total = a.NB * nimg;
       for (int g = 0; g < total; ++g) {
-        const int s = g % NSLOT, t = g & 3;
+        const int s = g % NSLOT, t = g % NT;
         mbar_wait(xfull(s), (g / NSLOT) & 1);
-        if (g >= 4) mbar_wait(tfree(t), ((g >> 2) - 1) & 1);       // pass 1 has read this TMEM slot's previous accumulators
+        if (g >= NT) mbar_wait(tfree(t), ((g / NT) - 1) & 1);      // pass 1 has read this TMEM slot's previous accumulators
         tc_fence_after();
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
@@ -977,11 +983,17 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
       __threadfence();
     }
     for (int k = 0; k < a.NB; ++k) {
+      long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + k) * 8 : nullptr;
+      long long w_mma = 0, w_st = 0;
+      if (tr) tr[0] = clock64();
       // ---- phase 1: statistics of every image's accumulators, y_k staged for its bulk store ----
-      float ssum = 0.f, qsum = 0.f;
+      float ssum = 0.f, qsum = 0.f;           // (summing the images per thread first and reducing once per block: 3 % faster at
+      //                                         B = 2048, but no longer the resident kernel's order of additions: not taken)
       for (int j = 0; j < nimg; ++j) {
-        const int g = k * nimg + j, s = g & 1, t = g & 3;
-        mbar_wait(tfull(t, m), (g >> 2) & 1);
+        const int g = k * nimg + j, s = g & 1, t = g % NT;
+        const long long c0 = tr ? clock64() : 0;
+        mbar_wait(tfull(t, m), (g / NT) & 1);
+        if (tr) w_mma += clock64() - c0;
         tc_fence_after();
         float v[16];
         tmem_ld16(my_tmem + t * 2 * C, v);
@@ -994,7 +1006,9 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
 #pragma unroll
           for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(v[jj * 8 + 2 * e], v[jj * 8 + 2 * e + 1]);
         }
+        const long long c1 = tr ? clock64() : 0;
         if (g >= 2) mbar_wait(yfree(s), ((g >> 1) - 1) & 1);       // the previous store has read this staging tile
+        if (tr) w_st += clock64() - c1;
         uint8_t* yst = gen_base + (y_smem - base) + s * YST_BYTES + st_off;
         *reinterpret_cast<uint4*>(yst + st_c0) = ypk[0]; *reinterpret_cast<uint4*>(yst + st_c1) = ypk[1];
         fence_proxy_async();
@@ -1007,6 +1021,7 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
         }
         ssum += warp_col_sum16(v, lane);
       }
+      if (tr) tr[1] = clock64();
       red[ew * 32 + (lane & 1) * 16 + (lane >> 1)] = (lane & 1) ? qsum : ssum;
       asm volatile("bar.sync 1, 512;" ::: "memory");
       unsigned long long* acc = a.acc + (size_t)k * NRD_ACC_ROW;
@@ -1017,6 +1032,7 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
         for (int w = 0; w < 8; ++w) tsum += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
         nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), tsum, 16777216.0, a.status), gridDim.x);
       }
+      if (tr) tr[2] = clock64();
       // phase 2's first operands travel during the exchange: x_k is final since the previous block; y_k needs p1done
       const bf16* yk = a.ys + (size_t)k * a.act_elems + pix_off;
       const bf16* xk = a.xs + (size_t)k * a.act_elems + pix_off;
@@ -1054,10 +1070,12 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
           if (lane == 0) *a.nbt += 1;
         }
       }
+      if (tr) tr[3] = clock64();
       mbar_wait(p1done, (uint32_t)(k & 1));                        // this block's y_k stores are complete
       fetch_y(yA, 0);
       if (nimg > 1) fetch_y(yB, 1);
       asm volatile("bar.sync 1, 512;" ::: "memory");               // scale | shift of this block are in shared memory
+      if (tr) tr[4] = clock64();
       // ---- phase 2: x_{k+1} = relu(bn(y_k)) + x_k from the stored tensors (this thread's own 32 B of each, two images in flight) ----
       auto emit = [&](uint4 (&yv)[2], uint4 (&xv)[2], int j) {
         const int g = k * nimg + j, s = g & 1;
@@ -1076,7 +1094,9 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
           }
         }
         if (j + 2 < nimg) { fetch_y(yv, j + 2); fetch_x(xv, j + 2); }     // two images ahead, while this one is staged
+        const long long c1 = tr ? clock64() : 0;
         if (g >= 2) mbar_wait(xfree(s), ((g >> 1) - 1) & 1);
+        if (tr) w_st += clock64() - c1;
         uint8_t* xst = gen_base + (xst_smem - base) + s * YST_BYTES + st_off;
         *reinterpret_cast<uint4*>(xst + st_c0) = ok[0]; *reinterpret_cast<uint4*>(xst + st_c1) = ok[1];
         fence_proxy_async();
@@ -1086,6 +1106,7 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
         emit(yA, xA, j);
         if (j + 1 < nimg) emit(yB, xB, j + 1);
       }
+      if (tr) { tr[5] = clock64(); tr[6] = w_mma; tr[7] = w_st; }
     }
   }
   tc_fence_before();
@@ -1093,7 +1114,7 @@ k_tc_fwd_stream(const __grid_constant__ CUtensorMap tmX18, const __grid_constant
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
 }
 
-constexpr size_t stream_fwd_smem() { return 1024 + STREAM_NSLOT * 21 * 1024 + 9 * Cfg<32>::WTAP_BYTES + 4 * NRD_PIX * 32 * 2 + 8 * 32 + (1024 + 64) * sizeof(float) + 64; }
+constexpr size_t stream_fwd_smem() { return 1024 + STREAM_NSLOT * 21 * 1024 + 9 * Cfg<32>::WTAP_BYTES + 4 * NRD_PIX * 32 * 2 + STREAM_BAR_BYTES + (1024 + 64) * sizeof(float) + 64; }
 
 // ============================================================================================
 // Persistent backward over ALL residual blocks (C = 32, at most 2 images per CTA, cooperative launch).
@@ -1663,6 +1684,7 @@ struct StreamBwdArgs {
   double inv_count;
   int poll_ns;
   unsigned int* status;
+  long long* trace;           // optional clock64 stamps [CTA][block][16] (profiling aid), or NULL
 };
 
 constexpr int STREAM_BWD_NS = 3;          // operand slots (dy copy + x_k tile)
@@ -1859,6 +1881,9 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
     uint32_t gA[8], gB[8], pg[8];                    // dL/dx of the even / odd image in flight; the next image's (prefetched)
     for (int it = 0; it < a.NB; ++it) {
       const int k = a.NB - 1 - it;
+      long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + it) * 16 : nullptr;
+      long long w_ld = 0, w_slot = 0, w_mma = 0, t_b = 0, t_c = 0;
+      if (tr) tr[0] = clock64();
       const float mean_r = (ew == 0) ? a.saved[(size_t)k * 2 * C + lane] : 0.f, is_r = (ew == 0) ? a.saved[(size_t)k * 2 * C + C + lane] : 0.f;
       red[ew * 32 + (lane & 1) * 16 + (lane >> 1)] = (lane & 1) ? s2 : s1;
       s1 = 0.f; s2 = 0.f;
@@ -1871,6 +1896,7 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
         for (int w = 0; w < 8; ++w) t += red[((ch >> 4) * 8 + w) * 32 + which * 16 + (ch & 15)];
         nrd_acc_check(nrd_acc_add(acc + NRD_ACC_IDX(blockIdx.x % NRD_ACC_REPL, et), t, 68719476736.0, a.status), gridDim.x);
       }
+      if (tr) tr[1] = clock64();
       {   // the first image's operands travel during the exchange
         const uint4* gp = g_ptr(0);
         const uint4 v0 = __ldcg(gp), v1 = __ldcg(gp + 1);
@@ -1894,14 +1920,18 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
         d[0] = (float)a_; d[1] = (float)(-a_ * c_ * is); d[2] = (float)(a_ * c_ * is * mean - a_ * b_); d[3] = 0.f;
       }
       asm volatile("bar.sync 1, 512;" ::: "memory");
+      if (tr) tr[2] = clock64();
       const float4* ssp = reinterpret_cast<const float4*>(bnp2 + (it & 1) * 64);
       // ---- B(i): dy of image i -> operand slot; then y_{k-1}[i] into the ring slot y_k[i] leaves, and image i+1's operands ----
       auto phase_b = [&](uint32_t (&g)[8], int i) {
         const int gi = it * nimg + i, s = gi % NS, u = gi / NS, r = gi % NY;
+        const long long c0 = tr ? clock64() : 0;
         asm volatile("cp.async.wait_group 0;" ::: "memory");
 #pragma unroll
         for (int e = 0; e < 8; ++e) g[e] = pg[e];
+        const long long c1 = tr ? clock64() : 0;
         if (u > 0) mbar_wait(wfree(s), (uint32_t)((u - 1) & 1));
+        if (tr) { const long long c2 = clock64(); w_ld += c1 - c0; w_slot += c2 - c1; }
         uint8_t* slot_gen = gen_base + s * SLOT_BYTES;
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -1932,11 +1962,14 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
           load_y(k, i + 1, (gi + 1) % NY);
         }
         commit();
+        if (tr) t_b += clock64() - c0;
       };
       // ---- C(i): dx_k = dgrad + g -> G, then phase A of block k-1 for the same image ----
       auto phase_c = [&](uint32_t (&g)[8], int i) {
         const int gi = it * nimg + i, t = gi & 1, r = gi % NY;
+        const long long c0 = tr ? clock64() : 0;
         mbar_wait(dxfull(t, m), (uint32_t)((gi >> 1) & 1));
+        if (tr) w_mma += clock64() - c0;
         tc_fence_after();
         float v[16];
         tmem_ld16(my_tmem + t * 2 * C, v);
@@ -1955,6 +1988,7 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
           else asm volatile("cp.async.wait_group 0;" ::: "memory");
           phase_a(g, r, it + 1);
         }
+        if (tr) t_c += clock64() - c0;
       };
       for (int i0 = 0; i0 <= nimg; i0 += 2) {
         if (i0 < nimg) phase_b(gA, i0);
@@ -1962,6 +1996,7 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
         if (i0 + 1 < nimg) phase_b(gB, i0 + 1);
         if (i0 + 1 <= nimg) phase_c(gA, i0);
       }
+      if (tr) { tr[3] = clock64(); tr[4] = w_ld; tr[5] = w_slot; tr[6] = w_mma; tr[7] = t_b; tr[8] = t_c; }
     }
     if (blockIdx.x == 0 && ew == 0) { a.dgamma[lane] = dg_acc; a.dbeta[lane] = db_acc; }
     // ---- weight-gradient partial of this CTA: accumulator lanes (j, ci), columns (kxb, co) ----
@@ -2307,7 +2342,7 @@ int nrd_tc_forward_blocks(nrd_plan* p, int pool, const float* stem_images, int t
     sa.saved = p->saved_stats; sa.scale_shift = p->scale_shift; sa.running = p->bn_running; sa.nbt = (long long*)p->nbt;
     sa.xs = (const bf16*)p->xs; sa.ys = (const bf16*)p->ys; sa.acc = p->bn_acc; sa.B = p->B; sa.NB = p->NB; sa.act_elems = p->act_elems;
     sa.inv_count = 1.0 / ((double)p->B * NRD_PIX); sa.unbias = ((double)p->B * NRD_PIX) / ((double)p->B * NRD_PIX - 1.0);
-    sa.poll_ns = p->poll_ns; sa.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS);
+    sa.poll_ns = p->poll_ns; sa.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS); sa.trace = (long long*)p->trace;
     void* sargs[] = {(void*)&p->tm_x18all, (void*)&p->tm_wf, (void*)&p->tm_xst, (void*)&p->tm_yst, (void*)&sa};
     NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_fwd_stream, dim3(conv_grid(p)), dim3(576), sargs, stream_fwd_smem(), st));
     nrd_count_launch();
@@ -2341,7 +2376,7 @@ int nrd_tc_backward_blocks(nrd_plan* p, const void* g_pooled, void* dx0_out, con
     sa.ys = (const bf16*)p->ys; sa.g_pool = (const bf16*)g_pooled; sa.idx2 = p->idx2; sa.G = (bf16*)dx0_out;
     sa.acc = p->bn_acc + (size_t)32 * NRD_ACC_ROW; sa.wpartial = p->wgrad_partial;
     sa.B = p->B; sa.NB = p->NB; sa.act_elems = p->act_elems; sa.inv_count = 1.0 / ((double)p->B * NRD_PIX); sa.poll_ns = p->poll_ns;
-    sa.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS);
+    sa.status = reinterpret_cast<unsigned int*>(p->gbar + NRD_GBAR_STATUS); sa.trace = (long long*)p->trace_bwd;
     void* sargs[] = {(void*)&p->tm_xall, (void*)&p->tm_wd, (void*)&sa};
     NRD_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)k_tc_bwd_stream, dim3(conv_grid(p)), dim3(576), sargs, stream_bwd_smem(), st));
     nrd_count_launch();

@@ -9,7 +9,8 @@ tests/test_oracle.py pins to REAL torch DDP over gloo at W = 2 and 4):
     W = 2, where a two-term sum has one order; to 1e-6 beyond), for BOTH exchanges of the graph path: our kernels over NVLink
     peer memory ("p2p") and NCCL all-reduces captured in the graph ("nccl");
   * bf16 (the path bench.py --gpus N times): graph path, both exchanges, against the rounding-matched oracle inside the
-    single-GPU envelopes of tests/test_gpu_parity_bench.py; p2p == nccl bit for bit at W = 2;
+    single-GPU envelopes of tests/test_gpu_parity_bench.py; p2p == nccl bit for bit at W = 2; the same with the streaming
+    persistent kernels forced (NRD_STREAM=1: what per-rank batches beyond two images per CTA run);
   * the literal reference loop (stock torch.optim.SGD + nn.CrossEntropyLoss, main.py:27-41) around our wrapper.
 
 One process group per W runs every combination (the exchange is chosen per TrainStep by NRD_P2P), so a case costs one spawn.
@@ -66,9 +67,10 @@ def _worker(rank, W, port, q):
     # ---- graph path, both exchanges, fp32 and bf16 ----
     for dtype, b in (("fp32", B), ("bf16", B_BF16)):
         xb, yb = data(b)
-        for xchg in ("p2p", "nccl", "p2p-unfused"):
+        for xchg in ("p2p", "nccl", "p2p-unfused") + (("p2p-stream",) if dtype == "bf16" else ()):
             os.environ["NRD_P2P"] = "0" if xchg == "nccl" else "1"
             os.environ["NRD_FUSED_UPDATE"] = "0" if xchg == "p2p-unfused" else "1"       # unfused: flags per bucket + a separate optimizer kernel
+            os.environ["NRD_STREAM"] = "1" if xchg == "p2p-stream" else "0"              # the streaming persistent kernels (large per-rank batches)
             m, ddp = fresh(dtype)
             step = nrd.TrainStep(ddp, b, lr=LR if dtype == "fp32" else LR_BF16)
             losses, first = [], None
@@ -79,7 +81,7 @@ def _worker(rank, W, port, q):
             step.check_status()
             out[f"graph/{dtype}/{xchg}"] = (losses,) + snap(m) + first + (bool(step.p2p),)
             step.close(); del step          # graphs hold captured NCCL kernels / peer mappings: drop them before the communicator
-    os.environ.pop("NRD_P2P", None); os.environ.pop("NRD_FUSED_UPDATE", None)
+    os.environ.pop("NRD_P2P", None); os.environ.pop("NRD_FUSED_UPDATE", None); os.environ.pop("NRD_STREAM", None)
     torch.cuda.synchronize()
     xb, yb = data(B_BF16)
     q.put((rank, out, x.numpy(), y.numpy(), xb.numpy(), yb.numpy()))     # numpy pickles inline: nothing refers back to this process
@@ -149,7 +151,7 @@ def test_ddp_matches_oracle_and_graph_equals_eager(W):
     HEAD, BNK = ("fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias"), ("rb.bn.weight", "rb.bn.bias")
     for r in range(W):
         out = got[r][0]
-        for xchg in ("p2p", "nccl"):
+        for xchg in ("p2p", "nccl", "p2p-stream"):
             losses, w, bn, logits, gavg, used_p2p = out[f"graph/bf16/{xchg}"]
             assert rell2(T(logits), simb[0][1][r]) < 2e-3, (xchg, r, rell2(T(logits), simb[0][1][r]))
             assert abs(losses[0] - float(simb[0][2][r])) < 2e-3 * float(simb[0][2][r])
