@@ -721,21 +721,22 @@ __global__ void k_bn_bwd_apply(const T* __restrict__ g, const T* __restrict__ y,
   }
 }
 
-// Fused BN + ReLU backward (cooperative launch, grid <= #SMs, every CTA owns <= IPC whole images which it keeps in shared
-// memory between the two phases): phase 1 stages g and y and takes the per-CTA sums, a grid barrier publishes them, every
-// CTA combines all partial rows in the same fixed order, phase 2 produces dy from shared memory.  One launch and 3T of HBM
-// traffic instead of three launches and 5T.
+// Fused BN + ReLU backward (cooperative launch, grid <= #SMs, every CTA owns <= IPC whole images, the first IPC_S of which it
+// keeps in shared memory between the two phases): phase 1 stages g and y and takes the per-CTA sums, a grid barrier publishes
+// them, every CTA combines all partial rows in the same fixed order, phase 2 produces dy from shared memory -- and, for the
+// images beyond IPC_S, from g and y read again (they were read microseconds earlier: L2 hits while 2T fits there).  One launch
+// and 3T of HBM traffic instead of three launches and 5T.
 template <typename T>
 __global__ void __launch_bounds__(256, 1) k_bn_bwd_fused(const T* __restrict__ g, const T* __restrict__ y,
                                                          const float* __restrict__ scale_shift, const float* __restrict__ saved,
                                                          const float* __restrict__ gamma, T* __restrict__ dy,
                                                          float* __restrict__ dgamma, float* __restrict__ dbeta, int accumulate,
-                                                         float* __restrict__ partial, unsigned long long* gbar, int B, int C, int ipc) {
+                                                         float* __restrict__ partial, unsigned long long* gbar, int B, int C, int ipc, int ipc_s) {
   extern __shared__ __align__(16) uint8_t smraw[];
   const int img_elems = NRD_PIX * C;
   T* gs = reinterpret_cast<T*>(smraw);
-  T* ys = gs + (size_t)ipc * img_elems;
-  double* dsum = reinterpret_cast<double*>(ys + (size_t)ipc * img_elems);   // [1024]
+  T* ys = gs + (size_t)ipc_s * img_elems;
+  double* dsum = reinterpret_cast<double*>(ys + (size_t)ipc_s * img_elems);   // [1024]
   float* red = reinterpret_cast<float*>(dsum + 1024);                       // [4096]
   float* coef = red + 4096;                                                 // [3C]
   const int tid = threadIdx.x, ncg = C / 8, cg = tid % ncg, pr = tid / ncg, nrow = 256 / ncg;
@@ -759,7 +760,7 @@ __global__ void __launch_bounds__(256, 1) k_bn_bwd_fused(const T* __restrict__ g
     for (int ch = tid; ch < chunks; ch += 256) {
       float gv[8], yv[8];
       ld8(g + base + (size_t)ch * 8, gv); ld8(y + base + (size_t)ch * 8, yv);
-      st8(gs + (size_t)i * img_elems + (size_t)ch * 8, gv); st8(ys + (size_t)i * img_elems + (size_t)ch * 8, yv);
+      if (i < ipc_s) { st8(gs + (size_t)i * img_elems + (size_t)ch * 8, gv); st8(ys + (size_t)i * img_elems + (size_t)ch * 8, yv); }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float z = fmaf(yv[j], sc[j], sh[j]);
@@ -802,7 +803,8 @@ __global__ void __launch_bounds__(256, 1) k_bn_bwd_fused(const T* __restrict__ g
 #pragma unroll 4
     for (int ch = tid; ch < chunks; ch += 256) {
       float gv[8], yv[8], o[8];
-      ld8(gs + (size_t)i * img_elems + (size_t)ch * 8, gv); ld8(ys + (size_t)i * img_elems + (size_t)ch * 8, yv);
+      if (i < ipc_s) { ld8(gs + (size_t)i * img_elems + (size_t)ch * 8, gv); ld8(ys + (size_t)i * img_elems + (size_t)ch * 8, yv); }
+      else { ld8(g + base + (size_t)ch * 8, gv); ld8(y + base + (size_t)ch * 8, yv); }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float z = fmaf(yv[j], sc[j], sh[j]);
@@ -1625,11 +1627,15 @@ static int bn_relu_add_any(const void* y, const void* x, const float* ss, void* 
   return NRD_OK;
 }
 
-static size_t bn_bwd_fused_smem(int B, int C, int dt, int* grid_out, int* ipc_out) {
+// grid, images per CTA, and how many of those stay in shared memory (200 KB budget); returns the dynamic shared-memory size
+static size_t bn_bwd_fused_smem(int B, int C, int dt, int* grid_out, int* ipc_out, int* ipcs_out = nullptr) {
   const int grid = B < NRD_NUM_SMS ? B : NRD_NUM_SMS, ipc = (B + grid - 1) / grid;
+  const size_t fixed = 1024 * sizeof(double) + (4096 + 3 * 64) * sizeof(float), per_img = (size_t)2 * NRD_PIX * C * (dt == NRD_F32 ? 4 : 2);
+  const int fit = (int)((200 * 1024 - fixed) / per_img), ipc_s = ipc < fit ? ipc : fit;
   if (grid_out) *grid_out = grid;
   if (ipc_out) *ipc_out = ipc;
-  return (size_t)ipc * 2 * NRD_PIX * C * (dt == NRD_F32 ? 4 : 2) + 1024 * sizeof(double) + (4096 + 3 * 64) * sizeof(float);
+  if (ipcs_out) *ipcs_out = ipc_s;
+  return (size_t)ipc_s * per_img + fixed;
 }
 
 // scratch layout: [B][2C] partials | coef [3C].  gbar != NULL selects the one-launch cooperative kernel when it fits.
@@ -1637,11 +1643,11 @@ static int bn_relu_bwd_any(const void* g, const void* y, const float* ss, const 
                            float* dgamma, float* dbeta, int accumulate, int B, int C, int dt, float* scratch, cudaStream_t st,
                            unsigned long long* gbar = nullptr) {
   float* partial = scratch; float* coef = scratch + (size_t)B * 2 * C;
-  int grid = 0, ipc = 0;
-  const size_t fsmem = bn_bwd_fused_smem(B, C, dt, &grid, &ipc);
-  if (gbar && fsmem <= 200 * 1024) {
+  int grid = 0, ipc = 0, ipc_s = 0;
+  const size_t fsmem = bn_bwd_fused_smem(B, C, dt, &grid, &ipc, &ipc_s);
+  if (gbar) {
     void* args[] = {(void*)&g, (void*)&y, (void*)&ss, (void*)&saved, (void*)&gamma, (void*)&dy, (void*)&dgamma, (void*)&dbeta,
-                    (void*)&accumulate, (void*)&partial, (void*)&gbar, (void*)&B, (void*)&C, (void*)&ipc};
+                    (void*)&accumulate, (void*)&partial, (void*)&gbar, (void*)&B, (void*)&C, (void*)&ipc, (void*)&ipc_s};
     static bool done32[64], done16[64];
     if (dt == NRD_F32) {
       NRD_TRY(set_smem_once(k_bn_bwd_fused<float>, 200 * 1024, done32));

@@ -87,11 +87,11 @@ def test_fused_block_forward_bitwise_equals_unfused(B, Cc, NB):
         assert torch.equal(a[i], b[i]), i
 
 
-@pytest.mark.parametrize("dtype,B,Cc", [("bf16", 7, 32), ("bf16", 256, 32), ("fp32", 40, 32), ("bf16", 20, 64), ("bf16", 800, 32)])
+@pytest.mark.parametrize("dtype,B,Cc", [("bf16", 7, 32), ("bf16", 256, 32), ("fp32", 40, 32), ("bf16", 20, 64), ("bf16", 600, 64), ("fp32", 500, 32)])
 def test_fused_bn_backward_matches_three_kernel_path(dtype, B, Cc):
     """One cooperative BN+ReLU-backward kernel (sums -> grid barrier -> dy from shared memory) against the reduce /
-    finalize / apply kernels: same math, different partial-sum grouping => fp32 round-off only (B=800 does not fit
-    shared memory and must silently be the three-kernel path in both runs: bit-equal)."""
+    finalize / apply kernels: same math, different partial-sum grouping => fp32 round-off only.  B = 600 at C = 64 and
+    B = 500 in fp32 are 5 / 4 images per CTA of which 3 fit in shared memory: the rest is read again (L2) in phase 2."""
     g = torch.Generator().manual_seed(B)
     x = torch.randn(B, 3, 32, 32, generator=g).to(DEV); y = torch.randint(0, 10, (B,), generator=g).to(DEV)
     res = []
@@ -102,8 +102,6 @@ def test_fused_bn_backward_matches_three_kernel_path(dtype, B, Cc):
         check(lib.nrd_plan_set_option(pl.handle, 0, fuse))
         out = m(x); loss = nrd.CrossEntropyLoss()(out, y); loss.backward()
         res.append(m.engine.flat_grads.clone())
-    if B == 800:
-        assert torch.equal(res[0], res[1])
     assert rell2(res[1], res[0]) < (1e-5 if dtype == "fp32" else 2e-3), rell2(res[1], res[0])
 
 
