@@ -1879,6 +1879,15 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
       asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     uint32_t gA[8], gB[8], pg[8];                    // dL/dx of the even / odd image in flight; the next image's (prefetched)
+    // The prefetch loads write pg DIRECTLY (inline asm outputs): written as uint4 temporaries copied into pg, the compiler put
+    // the copies right behind the loads and every thread waited out the L2 latency there (ncu: 14 % of all stall samples).
+    // (Prefetching two images ahead -- a second register set, a 4-deep y ring -- measured 4 % SLOWER: the kernel is bound by
+    // shared-memory bandwidth and issue slots, not by this latency.)
+    auto prefetch_g = [&](int j) {
+      const uint4* gp = g_ptr(j);
+      asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(pg[0]), "=r"(pg[1]), "=r"(pg[2]), "=r"(pg[3]) : "l"(gp));
+      asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(pg[4]), "=r"(pg[5]), "=r"(pg[6]), "=r"(pg[7]) : "l"(gp + 1));
+    };
     for (int it = 0; it < a.NB; ++it) {
       const int k = a.NB - 1 - it;
       long long* tr = (a.trace && et == 0) ? a.trace + ((size_t)blockIdx.x * a.NB + it) * 16 : nullptr;
@@ -1898,9 +1907,7 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
       }
       if (tr) tr[1] = clock64();
       {   // the first image's operands travel during the exchange
-        const uint4* gp = g_ptr(0);
-        const uint4 v0 = __ldcg(gp), v1 = __ldcg(gp + 1);
-        pg[0] = v0.x; pg[1] = v0.y; pg[2] = v0.z; pg[3] = v0.w; pg[4] = v1.x; pg[5] = v1.y; pg[6] = v1.z; pg[7] = v1.w;
+        prefetch_g(0);
         load_y(k, 0, (it * nimg) % NY); commit();
       }
       if (ew == 0) {
@@ -1956,9 +1963,7 @@ k_tc_bwd_stream(const __grid_constant__ CUtensorMap tmXall, const __grid_constan
         if (k > 0) load_y(k - 1, i, r);
         commit();
         if (i + 1 < nimg) {
-          const uint4* gp = g_ptr(i + 1);
-          const uint4 v0 = __ldcg(gp), v1 = __ldcg(gp + 1);
-          pg[0] = v0.x; pg[1] = v0.y; pg[2] = v0.z; pg[3] = v0.w; pg[4] = v1.x; pg[5] = v1.y; pg[6] = v1.z; pg[7] = v1.w;
+          prefetch_g(i + 1);
           load_y(k, i + 1, (gi + 1) % NY);
         }
         commit();
