@@ -72,8 +72,11 @@ class TrainStep:
             # the head bucket's kernel (NCCL all-reduce or our push kernel) has to fit beside the persistent kernels
             check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8"))),
                   "nrd_plan_set_option")
-        elif "NRD_RESERVE_SMS" in os.environ:       # single rank: only when asked for (tests of the reduced grid)
-            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ["NRD_RESERVE_SMS"])), "nrd_plan_set_option")
+        else:
+            # single rank: the side stream (head weight gradients, head optimizer step) and the programmatically launched successors
+            # of the persistent kernels need SMs to run UNDER them -- with all 148 SMs holding a persistent CTA they queue behind
+            # the backward stack.  Measured at B = 256: 195.0 us with 0 reserved SMs, 188.5 with 2, 184.3-184.7 with 4-16.
+            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8"))), "nrd_plan_set_option")
         # optimizer.step() rides the backward (nrd_plan_set_fused_update): the head bucket is updated on the side stream under
         # the body backward, the body bucket by the kernel that finishes its gradients -- no optimizer launch at the end
         self.fused_update = os.environ.get("NRD_FUSED_UPDATE", "1") != "0" and os.environ.get("NRD_DIAG_NO_EXCHANGE") != "1" and (self.world == 1 or self.p2p)

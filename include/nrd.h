@@ -85,8 +85,10 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
 /* NRD_OPT_TC_STEM (default 1): stem forward / weight gradient as tcgen05 implicit GEMMs with the im2col operand built in
  * shared memory (bf16 plans, C = 32); 0 = the CUDA-core stem kernels. */
 #define NRD_OPT_TC_STEM 4
-/* NRD_OPT_RESERVE_SMS (default 0): the cooperative kernels use 148 - value SMs.  They fill an SM's shared memory, so a
- * collective launched beside them (the head bucket's all-reduce, parallel.py) can only run on SMs they leave free. */
+/* NRD_OPT_RESERVE_SMS (default 0): the cooperative kernels use 148 - value SMs.  They fill an SM's shared memory, so anything
+ * launched beside them (side-stream kernels: head weight gradients, the head bucket's all-reduce or push; programmatically
+ * launched successors) can only run on SMs they leave free.  A caller that overlaps such work sets 8 (graph.py does, on one GPU
+ * and on DDP ranks: 195 -> 184 us per step at B = 256); a caller that runs nrd_train_step on ONE stream gains nothing from it. */
 #define NRD_OPT_RESERVE_SMS 5
 /* NRD_OPT_PDL (bit mask, default 5): kernels launched with programmatic stream serialization, i.e. already resident with
  * their prologue done when the predecessor's last CTA retires.  bit 0: loss and fc1-dgrad kernels, bit 2: body gradient

@@ -1,7 +1,7 @@
 """Parity of the BENCHMARKED code path with the oracle, directly: `TrainStep` (whole-step CUDA graph, bf16, persistent
-tcgen05 kernels, default options) at the BASELINE batch B = 256 (two images per CTA, both slots busy), B = 149 (one CTA
-with two images, 147 with one), B = 296 (the largest batch of the two-image persistent kernels) and B = 500 (the STREAMING
-persistent kernels that take over beyond two images per CTA: 56 CTAs with 4 images, 92 with 3), against
+tcgen05 kernels, default options: 140 CTAs, 8 SMs left to the side stream) at the BASELINE batch B = 256 (116 CTAs with two
+images, 24 with one), B = 149 (9 CTAs with two images, 131 with one), B = 280 (the largest batch of the two-image persistent
+kernels) and B = 296, 500 (the STREAMING persistent kernels that take over beyond two images per CTA), against
 
   (i)  the rounding-matched oracle (`oracle.train_step_rm`: the reference's layers with bf16 rounding at exactly the points
        where the kernels round, fp32 between them), and
@@ -46,7 +46,7 @@ def _flat_grads(m):
     return out
 
 
-@pytest.mark.parametrize("B", [256, 149, 296, 500])
+@pytest.mark.parametrize("B", [256, 149, 280, 296, 500])
 def test_benchmarked_bf16_graph_step_vs_rounding_matched_and_fp32_oracle(B):
     C, NB, lr = 32, 10, 1e-2
     torch.set_num_threads(max(1, min(16, (torch.get_num_threads() or 1))))
