@@ -18,8 +18,13 @@ BN grads <= 4.4e-3, block conv weight 0.8-1.5e-2, conv1 weight 1.2-2.3e-2, mask 
   vs fp32 oracle:      logits <= 1e-2; every gradient's cosine >= 0.985 AND no more than 0.003 below the cosine the
                        rounding-matched oracle itself reaches (conv1.weight: 0.991-0.993 -- what bf16 operands cost, for any
                        implementation with these rounding points; SURVEY A.7 measured 0.9918-0.9942).
-ReLU-mask flips per block against the rounding-matched oracle are printed (pytest -s) and bounded at 1e-3 of the elements;
-the fc1 gradients' bar is flip-aware (a flipped ReLU of fc1's 32 x B outputs moves them by ~6e-3; 0-1 such flips per run).
+ReLU-mask flips per block against the rounding-matched oracle are printed (pytest -s) and bounded at 1e-3 of the elements.
+The bars of fc1 and of everything below it are flip-aware: a flipped ReLU of fc1's 32 x B outputs (0-1 per run: a pre-activation
+within rounding noise of zero) switches one unit of ONE sample's dL/dh1, which moves the fc1 gradients by ~6e-3 and, through that
+sample's dL/d(pooled), every body gradient (measured on B200, tools/parity_reserve.py, same batch, the flip present or not
+depending on the number of CTAs, i.e. on the order of the fp32 partial sums: BN gradients 4.2e-3 -> 8.3e-3, block conv weight
+1.45e-2 -> 1.95e-2, conv1 weight 2.3e-2 -> 2.9e-2; another batch with one flip: 9.4e-3 / 2.1e-2 / 3.7e-2 whatever the grid).  The
+flips are counted (h1 of the kernels against the oracle's mask) and each adds 1e-2 to those bars; at most 4 are accepted.
 """
 import pytest
 import torch
@@ -91,9 +96,10 @@ def test_benchmarked_bf16_graph_step_vs_rounding_matched_and_fp32_oracle(B):
     assert rep["logits_rm"] <= TOL["logits_rm"] and rep["loss_rm"] <= TOL["loss_rm"] and rep["logits_fp32"] <= TOL["logits_fp32"], rep
     for k in O.PARAM_ORDER:
         e_rm, cos32 = rep[k]
-        # flip-aware head bar (SURVEY 8(c) tier 2): ONE flipped ReLU of the 32 x B fc1 outputs adds or removes one of the B terms
-        # of a column of the fc1 gradients, ~1/sqrt(32 B) ~ 1e-2 relL2 (measured 5-7e-3 per flip at B = 256)
-        assert e_rm <= _tol(k) + (1e-2 * h1_flips if k.startswith("fc1") else 0.0), (k, rep)
+        # flip-aware bars (SURVEY 8(c) tier 2): ONE flipped ReLU of the 32 x B fc1 outputs adds or removes one of the B terms
+        # of a column of the fc1 gradients, ~1/sqrt(32 B) ~ 1e-2 relL2 (measured 5-7e-3 per flip at B = 256), and changes that
+        # sample's dL/d(pooled), hence every gradient below the head (module docstring)
+        assert e_rm <= _tol(k) + (0.0 if k.startswith("fc2") else 1e-2 * h1_flips), (k, rep)
         assert cos32 >= TOL["cos_fp32"] and cos32 >= cos_rm[k] - 3e-3, (k, rep)
     assert rep["running_mean"] <= 1e-4 and rep["running_var"] <= 1e-4, rep
     assert int(bn.num_batches_tracked) == NB
@@ -101,6 +107,6 @@ def test_benchmarked_bf16_graph_step_vs_rounding_matched_and_fp32_oracle(B):
     eng = m.engine
     for i, k in enumerate(O.PARAM_ORDER):
         ours_upd = (eng.flat_params[eng.offsets[i]:eng.offsets[i + 1]] - w0[eng.offsets[i]:eng.offsets[i + 1]]).cpu()
-        assert rell2(ours_upd, (p_rm[k] - pm[k]).flatten()) <= _tol(k) + 1e-4 + (1e-2 * h1_flips if k.startswith("fc1") else 0.0), k   # (+ fp32 cancellation in w - w0)
+        assert rell2(ours_upd, (p_rm[k] - pm[k]).flatten()) <= _tol(k) + 1e-4 + (0.0 if k.startswith("fc2") else 1e-2 * h1_flips), k   # (+ fp32 cancellation in w - w0)
     assert h1_flips <= 4, rep
     assert max(flips) <= 1e-3 * B * 256 * C, rep
