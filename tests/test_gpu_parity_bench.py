@@ -24,7 +24,7 @@ within rounding noise of zero) switches one unit of ONE sample's dL/dh1, which m
 sample's dL/d(pooled), every body gradient (measured on B200, tools/parity_reserve.py, same batch, the flip present or not
 depending on the number of CTAs, i.e. on the order of the fp32 partial sums: BN gradients 4.2e-3 -> 8.3e-3, block conv weight
 1.45e-2 -> 1.95e-2, conv1 weight 2.3e-2 -> 2.9e-2; another batch with one flip: 9.4e-3 / 2.1e-2 / 3.7e-2 whatever the grid).  The
-flips are counted (h1 of the kernels against the oracle's mask) and each adds 1e-2 to those bars; at most 4 are accepted.
+flips are counted (h1 of the kernels against the oracle's mask) and each adds 1e-2 to those bars; at most max(4, B/64) are accepted.
 """
 import pytest
 import torch
@@ -108,5 +108,5 @@ def test_benchmarked_bf16_graph_step_vs_rounding_matched_and_fp32_oracle(B):
     for i, k in enumerate(O.PARAM_ORDER):
         ours_upd = (eng.flat_params[eng.offsets[i]:eng.offsets[i + 1]] - w0[eng.offsets[i]:eng.offsets[i + 1]]).cpu()
         assert rell2(ours_upd, (p_rm[k] - pm[k]).flatten()) <= _tol(k) + 1e-4 + (0.0 if k.startswith("fc2") else 1e-2 * h1_flips), k   # (+ fp32 cancellation in w - w0)
-    assert h1_flips <= 4, rep
+    assert h1_flips <= max(4, B // 64), rep          # of 32 x B units (measured 0-3 for B = 149 .. 500)
     assert max(flips) <= 1e-3 * B * 256 * C, rep
