@@ -73,7 +73,7 @@ int nrd_plan_conv_impl(const nrd_plan* plan); /* current selector */
  * CTA's images fit shared memory; 0 = the three-kernel path (any batch size; cross-check). */
 #define NRD_OPT_FUSE_BN_BWD 0
 /* NRD_OPT_PERSIST_FWD (default 1): run ALL residual blocks of the forward in one persistent cooperative kernel that keeps
- * each image's activations in shared memory / TMEM between blocks (C = 32, B <= 296); 0 = one fused kernel per block. */
+ * each image's activations in shared memory / TMEM between blocks (C = 32, B <= 2 x (148 - NRD_OPT_RESERVE_SMS)); 0 = one fused kernel per block. */
 #define NRD_OPT_PERSIST_FWD 1
 /* NRD_OPT_TRACE (default 0): profiling aid -- the persistent kernels write clock64 stamps of their phases into the dx pong
  * scratch (forward; nrd_plan_tensor what=6) and the dy scratch (backward; what=2): [cta][block][8] int64.  Never enable in
