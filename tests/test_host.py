@@ -24,6 +24,15 @@ def test_library_exports_every_declared_symbol():
     assert lib.nrd_version() >= 100
 
 
+def test_option_numbers_match_the_header():
+    """`_lib.OPT_*` (what engine.py / graph.py pass to nrd_plan_set_option) against the `#define NRD_OPT_*` values of include/nrd.h."""
+    hdr = open(os.path.join(ROOT, "include", "nrd.h")).read()
+    defs = {k: int(v) for k, v in re.findall(r"#define\s+NRD_OPT_([A-Z_0-9]+)\s+(\d+)", hdr)}
+    assert len(defs) >= 14 and sorted(defs.values()) == list(range(len(defs))), defs
+    for name, val in defs.items():
+        assert getattr(_lib, "OPT_" + name) == val, name
+
+
 def test_param_layout_and_workspace_sizes():
     off = _lib.param_offsets(32)
     assert off[-1] == 76074 and off[5] == 10176            # SURVEY fact 2; body bucket = 40,704 B
