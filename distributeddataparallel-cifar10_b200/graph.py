@@ -76,7 +76,11 @@ class TrainStep:
             # single rank: the side stream (head weight gradients, head optimizer step) and the programmatically launched successors
             # of the persistent kernels need SMs to run UNDER them -- with all 148 SMs holding a persistent CTA they queue behind
             # the backward stack.  Measured at B = 256: 195.0 us with 0 reserved SMs, 188.5 with 2, 184.3-184.7 with 4-16.
-            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8"))), "nrd_plan_set_option")
+            # Only where the persistent kernels run (bf16, C = 32): the per-block kernels of the other configurations are
+            # throughput-bound and leave the side stream its turn between launches (C = 64, B = 512: 2313 us with 0, 2446 with 8).
+            persistent = self.eng.C == 32 and self.eng.dtype_code == _lib.NRD_BF16
+            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8" if persistent else "0"))),
+                  "nrd_plan_set_option")
         # optimizer.step() rides the backward (nrd_plan_set_fused_update): the head bucket is updated on the side stream under
         # the body backward, the body bucket by the kernel that finishes its gradients -- no optimizer launch at the end
         self.fused_update = os.environ.get("NRD_FUSED_UPDATE", "1") != "0" and os.environ.get("NRD_DIAG_NO_EXCHANGE") != "1" and (self.world == 1 or self.p2p)
