@@ -70,7 +70,8 @@ class TrainStep:
                                                1.0 / self.slot_scale), "nrd_plan_set_bn_sync")
                 self.resync_buffers()
             # the head bucket's kernel (NCCL all-reduce or our push kernel) has to fit beside the persistent kernels
-            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8"))),
+            reserve = self._default_reserve(batch_size) if self.p2p else 8
+            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", str(max(reserve, 1))))),
                   "nrd_plan_set_option")
         else:
             # single rank: the side stream (head weight gradients, head optimizer step) and the programmatically launched successors
@@ -79,7 +80,8 @@ class TrainStep:
             # Only where the persistent kernels run (bf16, C = 32): the per-block kernels of the other configurations are
             # throughput-bound and leave the side stream its turn between launches (C = 64, B = 512: 2313 us with 0, 2446 with 8).
             persistent = self.eng.C == 32 and self.eng.dtype_code == _lib.NRD_BF16
-            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", "8" if persistent else "0"))),
+            reserve = self._default_reserve(batch_size) if persistent else 0
+            check(lib.nrd_plan_set_option(self.plan.handle, OPT_RESERVE_SMS, int(os.environ.get("NRD_RESERVE_SMS", str(reserve)))),
                   "nrd_plan_set_option")
         # optimizer.step() rides the backward (nrd_plan_set_fused_update): the head bucket is updated on the side stream under
         # the body backward, the body bucket by the kernel that finishes its gradients -- no optimizer launch at the end
@@ -104,6 +106,15 @@ class TrainStep:
         self.kernel_launches = None
         if use_graph:
             self._capture(0)
+
+    def _default_reserve(self, batch_size: int) -> int:
+        """SMs the persistent kernels leave to the side stream: 8, or fewer when 8 would put one more image on some CTA (the
+        kernels' time goes with the LARGEST number of images per CTA).  Measured on one B200 (us/step with 0 / 1 / 8 reserved SMs):
+        B = 256: 195.0 / 190.0 / 184.3; 512: 362.9 / 355.1 / 349.2; 768: 502.6 / 488.3 / 474.1 (same images per CTA either way);
+        B = 1024: 571.8 / 566.9 / 589.2 (7 images per CTA on 147-148 CTAs, 8 on 140)."""
+        sms = torch.cuda.get_device_properties(self.eng.device).multi_processor_count
+        per_cta = -(-batch_size // sms)                       # images on the busiest CTA with every SM in use
+        return max(0, min(8, sms - -(-batch_size // per_cta)))
 
     def _setup_exchange(self, rank: int) -> bool:
         """Exchange buffers for the body bucket: allocate ours, swap CUDA IPC handles over the process group, map the peers'.

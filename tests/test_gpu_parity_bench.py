@@ -1,7 +1,8 @@
 """Parity of the BENCHMARKED code path with the oracle, directly: `TrainStep` (whole-step CUDA graph, bf16, persistent
-tcgen05 kernels, default options: 140 CTAs, 8 SMs left to the side stream) at the BASELINE batch B = 256 (116 CTAs with two
-images, 24 with one), B = 149 (9 CTAs with two images, 131 with one), B = 280 (the largest batch of the two-image persistent
-kernels) and B = 296, 500 (the STREAMING persistent kernels that take over beyond two images per CTA), against
+tcgen05 kernels, default options: 8 SMs left to the side stream unless that would add an image to a CTA) at the BASELINE batch
+B = 256 (140 CTAs: 116 with two images, 24 with one), B = 149 (9 CTAs with two images, 131 with one), B = 280 and 296 (the
+largest batches of the two-image persistent kernels on 140 and on all 148 SMs) and B = 500 (the STREAMING persistent kernels
+that take over beyond two images per CTA), against
 
   (i)  the rounding-matched oracle (`oracle.train_step_rm`: the reference's layers with bf16 rounding at exactly the points
        where the kernels round, fp32 between them), and
